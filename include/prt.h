@@ -1,0 +1,153 @@
+/* prt.h -- C ABI of the B200-native RtReference path tracer (libprt_b200.so).
+ *
+ * Drop-in boundary for prosper's render::RtReference pass (src/render/RtReference.hpp:19-107)
+ * and the acceleration-structure half of scene::World it depends on (src/scene/World.hpp:49,
+ * 64-65). Plain pointers and sizes only. All `const void *` inputs are HOST pointers unless the
+ * name says `_device`; the library copies them to HBM on the context's stream. One context per
+ * GPU; calls on a context are single-threaded and stream-ordered. Every function returns
+ * PRT_OK or a negative prt_status; prt_last_error() gives the message (the C++ wrapper
+ * host/RtReference.hpp re-throws it as std::runtime_error like the reference does,
+ * RtRef.cpp:112-113). There is no CPU fallback: without a CUDA device prt_create fails.
+ */
+#ifndef PRT_H
+#define PRT_H
+
+#include "prt_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct prt_ctx prt_ctx;
+
+typedef enum prt_status {
+    PRT_OK = 0,
+    PRT_ERR_INVALID = -1,   /* programmer error: the reference would WHEELS_ASSERT */
+    PRT_ERR_CUDA = -2,      /* CUDA runtime failure */
+    PRT_ERR_NO_DEVICE = -3, /* no usable sm_100 device */
+    PRT_ERR_CAPACITY = -4   /* a fixed capacity from prt_config was exceeded */
+} prt_status;
+
+typedef struct prt_config {
+    int32_t device;            /* CUDA ordinal */
+    uint32_t maxWidth;         /* largest render area (RtRef.cpp:178-189 image extent) */
+    uint32_t maxHeight;
+    uint32_t samplesPerLaunch; /* path-state capacity = maxWidth*maxHeight*samplesPerLaunch */
+    uint32_t maxInstances;     /* TLAS capacity (World.cpp:838-876 reserveTlasInstances) */
+    uint32_t flags;            /* PRT_CFG_* */
+} prt_config;
+enum { PRT_CFG_COUNTERS = 1u << 0 /* run the instrumented traversal kernels (untimed runs) */ };
+
+/* ---- lifetime: RtReference::init / ~RtReference (RtRef.cpp:90-120) ------------------------ */
+prt_status prt_create(const prt_config *cfg, prt_ctx **out);
+void prt_destroy(prt_ctx *ctx);
+const char *prt_last_error(void);
+/* The CUDA stream every call of this context is ordered on (a cudaStream_t). */
+void *prt_stream(prt_ctx *ctx);
+prt_status prt_synchronize(prt_ctx *ctx);
+
+/* ---- scene data: WorldData buffers bound through WorldDSLayouts (WorldData.hpp:100-111) --- */
+/* geometry buffer `index` (WorldData.cpp:1271-1320; bytes multiple of 4) */
+prt_status prt_set_geometry_buffer(prt_ctx *ctx, uint32_t index, const void *data, uint64_t bytes);
+/* GeometryMetadata[] + MeshInfo[] (WorldData.cpp:481-530 uploadMeshDatas) */
+prt_status prt_set_meshes(prt_ctx *ctx, const prt_geometry_metadata *metadatas,
+                          const prt_mesh_info *infos, uint32_t count);
+/* MaterialData[] (WorldData.cpp:532-586 uploadMaterialDatas) */
+prt_status prt_set_materials(prt_ctx *ctx, const prt_material_data *materials, uint32_t count);
+/* sampler table (WorldData.cpp:686-720) */
+prt_status prt_set_samplers(prt_ctx *ctx, const prt_sampler_desc *samplers, uint32_t count);
+/* texture `index` >= 1 of the bindless table (Texture.cpp:369-489); index 0 is the reserved
+ * "no texture" slot (WorldData.cpp:727-741) */
+prt_status prt_set_texture(prt_ctx *ctx, uint32_t index, const prt_texture_desc *desc);
+/* skybox cubemap, RGBA16F, faces +X,-X,+Y,-Y,+Z,-Z (Texture.cpp:595-601; skybox.glsl:4) */
+prt_status prt_set_sky_cubemap(prt_ctx *ctx, uint32_t faceSize, const void *rgba16f);
+/* models: sub-models of model m are subModels[offsets[m] .. offsets[m+1]) */
+prt_status prt_set_models(prt_ctx *ctx, const uint32_t *offsets, const prt_sub_model *subModels,
+                          uint32_t modelCount);
+
+/* ---- acceleration structures: World::buildAccelerationStructures (World.cpp:538-575) ------ */
+/* buildNextBlas (World.cpp:585-747). *outReference goes into prt_tlas_instance.blasReference */
+prt_status prt_build_blas(prt_ctx *ctx, uint32_t modelIndex, uint64_t *outReference);
+/* updateTlasInstances + buildCurrentTlas (World.cpp:878-928, 749-802): full rebuild */
+prt_status prt_build_tlas(prt_ctx *ctx, const prt_tlas_instance *instances, uint32_t count);
+
+/* ---- per-frame rings: World::updateBuffers (World.cpp:468-536), Camera::updateBuffer ------- */
+prt_status prt_set_draw_instances(prt_ctx *ctx, const prt_draw_instance *instances, uint32_t count);
+prt_status prt_set_instance_transforms(prt_ctx *ctx, const prt_model_instance_transforms *t,
+                                       uint32_t count);
+prt_status prt_set_lights(prt_ctx *ctx, const prt_directional_light *directional,
+                          const prt_point_light *points, uint32_t pointCount,
+                          const prt_spot_light *spots, uint32_t spotCount);
+prt_status prt_set_camera(prt_ctx *ctx, const prt_camera_uniforms *camera);
+
+/* ---- the pass: RtReference::record (RtRef.cpp:161-383) -------------------------------------- */
+/* Renders `sampleCount` consecutive frames (frameIndex = pc->frameIndex + k, wrapping at
+ * PRT_FRAME_PERIOD like RtRef.cpp:170) into the preserved fp32 accumulation image with the
+ * running mean of main.rgen:285-298; PRT_FLAG_SKIP_HISTORY applies to the first of them only.
+ * width*height must fit prt_config (renderArea.offset must be 0, RtRef.cpp:327). */
+prt_status prt_record(prt_ctx *ctx, const prt_reference_pc *pc, uint32_t width, uint32_t height,
+                      uint32_t sampleCount);
+/* m_previousIllumination: RGBA fp32, sample count in .a (DEVICE pointer, width*height*16 B) */
+prt_status prt_output_f32_device(prt_ctx *ctx, const float **out);
+/* Output::illumination: RGBA fp16 blit of the above (RtRef.cpp:336-377), into HOST memory */
+prt_status prt_read_illumination_f16(prt_ctx *ctx, void *dstHost, uint64_t dstBytes);
+prt_status prt_read_output_f32(prt_ctx *ctx, float *dstHost, uint64_t dstBytes);
+/* RtReference::releasePreserved (RtRef.cpp:385-391): drops the accumulation history */
+prt_status prt_release_preserved(prt_ctx *ctx);
+
+/* Primary-ray hit records (traceClosest payload, main.rgen:62-81) for frame pc->frameIndex:
+ * what the reference can only show through its DrawType debug views (main.rgen:181-193). */
+prt_status prt_trace_primary(prt_ctx *ctx, const prt_reference_pc *pc, uint32_t width,
+                             uint32_t height, prt_hit *dstHost);
+/* Traverse caller-supplied rays (origin xyz + tMin, direction xyz + tMax per ray; HOST) with the
+ * closest-hit or the shadow (terminate-on-first-hit, main.rgen:49-60) kernel. */
+prt_status prt_trace_rays(prt_ctx *ctx, const float *originTmin, const float *dirTmax,
+                          const uint32_t *seeds, uint32_t count, int shadow, prt_hit *dstHost);
+
+/* ---- multi-GPU: one ctx per rank, accumulation kept as sum + count ------------- */
+/* Device pointer to the fp32 RGBA *sum* image (rgb = sum of samples, a = count) suitable for
+ * ncclReduce(sum); prt_resolve_sum turns a reduced sum back into the running-mean image. */
+prt_status prt_export_sum_device(prt_ctx *ctx, float **outSum);
+prt_status prt_import_sum_device(prt_ctx *ctx, const float *sumDevice);
+
+/* ---- metrics (the reference's "RtReference"/"BuildTLAS" profiler scopes, App.cpp:575) ------ */
+typedef struct prt_counters {
+    uint64_t closestRays;   /* traceRayEXT equivalents, main.rgen:73 */
+    uint64_t shadowRays;    /* main.rgen:57 */
+    uint64_t nodesVisited;  /* 80-byte wide nodes fetched (TLAS + BLAS) */
+    uint64_t trisTested;    /* 48-byte triangle records fetched */
+    uint64_t instancesEntered; /* 64-byte instance records fetched */
+    uint64_t anyHitCalls;   /* scene.rahit invocations */
+    uint64_t shadedHits;    /* evaluateSurface calls */
+    uint64_t textureTaps;   /* bilinear material/alpha fetches */
+    uint64_t pixelSamples;  /* rgen invocations */
+    uint64_t kernelLaunches;
+} prt_counters;
+prt_status prt_get_counters(prt_ctx *ctx, prt_counters *out);
+prt_status prt_reset_counters(prt_ctx *ctx);
+typedef struct prt_timings {
+    float lastRecordMs;   /* CUDA-event time of the last prt_record ("RtReference" scope) */
+    float lastTlasMs;     /* ... of the last prt_build_tlas ("BuildTLAS" scope) */
+    float lastBlasMs;     /* ... of the last prt_build_blas */
+    float lastTraceClosestMs; /* sum over the trace-closest launches of the last prt_record */
+    uint32_t lastTraceClosestLaunches;
+    uint32_t lastRecordLaunches;
+    uint32_t lastTlasLaunches;
+    uint32_t pad;
+} prt_timings;
+prt_status prt_get_timings(prt_ctx *ctx, prt_timings *out);
+
+/* BVH introspection for tests (sizes in elements) */
+typedef struct prt_bvh_stats {
+    uint32_t tlasNodes;
+    uint32_t blasNodesTotal;
+    uint64_t blasTrianglesTotal;
+    uint32_t blasCount;
+    uint32_t tlasInstances;
+} prt_bvh_stats;
+prt_status prt_get_bvh_stats(prt_ctx *ctx, prt_bvh_stats *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PRT_H */
