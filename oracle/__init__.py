@@ -1,0 +1,210 @@
+"""ctypes binding of the CPU oracle (oracle/liboracle.so). TEST INFRASTRUCTURE.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import
+this module. The product (prosper_b200, libprt_b200.so) never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "liboracle.so")
+_SOURCES = ["oracle.cpp", "oracle.h", "o_math.h", "o_shading.h", "o_scene.h", "o_bvh.h", "Makefile"]
+
+
+def build(force: bool = False) -> str:
+    """Compile liboracle.so with oracle/Makefile when it is missing or older than its sources."""
+    newest = max(os.path.getmtime(os.path.join(_HERE, s)) for s in _SOURCES)
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < newest:
+        subprocess.run(["make", "-C", _HERE, "-B", "liboracle.so"], check=True, capture_output=True)
+    return _LIB_PATH
+
+
+class _OrcTexture(C.Structure):
+    _fields_ = [("format", C.c_uint32), ("width", C.c_uint32), ("height", C.c_uint32), ("mipLevels", C.c_uint32),
+                ("data", C.c_void_p), ("dataBytes", C.c_uint64)]
+
+
+class _OrcScene(C.Structure):
+    _fields_ = [
+        ("geometryBufferCount", C.c_uint32), ("geometryBuffers", C.POINTER(C.c_void_p)),
+        ("geometryBufferBytes", C.POINTER(C.c_uint64)),
+        ("meshCount", C.c_uint32), ("metadatas", C.c_void_p), ("meshInfos", C.c_void_p),
+        ("materialCount", C.c_uint32), ("materials", C.c_void_p),
+        ("samplerCount", C.c_uint32), ("samplers", C.c_void_p),
+        ("textureCount", C.c_uint32), ("textures", C.POINTER(_OrcTexture)),
+        ("modelCount", C.c_uint32), ("modelOffsets", C.c_void_p), ("subModels", C.c_void_p),
+        ("instanceCount", C.c_uint32), ("tlasInstances", C.c_void_p),
+        ("drawInstanceCount", C.c_uint32), ("drawInstances", C.c_void_p),
+        ("transformCount", C.c_uint32), ("transforms", C.c_void_p),
+        ("directionalLight", C.c_void_p),
+        ("pointLightCount", C.c_uint32), ("pointLights", C.c_void_p),
+        ("spotLightCount", C.c_uint32), ("spotLights", C.c_void_p),
+        ("camera", C.c_void_p),
+        ("skyFaceSize", C.c_uint32), ("skyRgba16f", C.c_void_p),
+    ]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        l = C.CDLL(build())
+        l.orc_create.restype = C.c_void_p
+        l.orc_create.argtypes = [C.POINTER(_OrcScene), C.c_int]
+        l.orc_destroy.argtypes = [C.c_void_p]
+        l.orc_bvh_build_seconds.restype = C.c_double
+        l.orc_bvh_build_seconds.argtypes = [C.c_void_p]
+        l.orc_render.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_int,
+                                 C.c_void_p]
+        l.orc_trace_primary.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
+                                        C.c_int]
+        l.orc_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int,
+                                     C.c_void_p, C.c_void_p, C.c_int]
+        l.orc_pcg.restype = C.c_uint32
+        l.orc_pcg.argtypes = [C.c_uint32]
+        l.orc_rng_to_01.restype = C.c_float
+        l.orc_rng_to_01.argtypes = [C.c_uint32]
+        l.orc_vndf_pdf.restype = C.c_float
+        l.orc_vndf_pdf.argtypes = [C.c_void_p, C.c_void_p, C.c_float]
+        l.orc_sample_vndf.argtypes = [C.c_void_p, C.c_float, C.c_void_p, C.c_void_p]
+        l.orc_eval_brdf_times_nol.argtypes = [C.c_void_p] * 4 + [C.c_float, C.c_float, C.c_void_p]
+        l.orc_thin_lens_ray.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float,
+                                        C.c_void_p, C.c_void_p]
+        l.orc_half_to_float.restype = C.c_float
+        l.orc_half_to_float.argtypes = [C.c_uint16]
+        l.orc_float_to_half.restype = C.c_uint16
+        l.orc_float_to_half.argtypes = [C.c_float]
+        l.orc_srgb_to_linear.restype = C.c_float
+        l.orc_srgb_to_linear.argtypes = [C.c_float]
+        l.orc_bc7_decode_block.restype = C.c_int
+        l.orc_intersect_triangle.restype = C.c_int
+        l.orc_intersect_triangle.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_void_p]
+        l.orc_sample_texture.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_float, C.c_float, C.c_void_p]
+        l.orc_sample_sky.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        l.orc_unpack_snorm10.argtypes = [C.c_uint32, C.c_void_p]
+        _lib = l
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
+
+
+class Oracle:
+    """One oracle context over a SceneData (prosper_b200.scene_data). Keeps the arrays alive."""
+
+    def __init__(self, scene, brute_force: bool = False):
+        self.scene = scene
+        l = lib()
+        s = _OrcScene()
+        self._keep = []
+
+        def arr(a):
+            a = np.ascontiguousarray(a)
+            self._keep.append(a)
+            return a
+
+        bufs = [arr(b) for b in scene.geometry_buffers]
+        nb = len(bufs)
+        self._bufptrs = (C.c_void_p * nb)(*[b.ctypes.data for b in bufs])
+        self._bufbytes = (C.c_uint64 * nb)(*[b.nbytes for b in bufs])
+        s.geometryBufferCount = nb
+        s.geometryBuffers = C.cast(self._bufptrs, C.POINTER(C.c_void_p))
+        s.geometryBufferBytes = C.cast(self._bufbytes, C.POINTER(C.c_uint64))
+        s.meshCount = len(scene.metadatas)
+        s.metadatas = _p(arr(scene.metadatas))
+        s.meshInfos = _p(arr(scene.mesh_infos))
+        s.materialCount = len(scene.materials)
+        s.materials = _p(arr(scene.materials))
+        s.samplerCount = len(scene.samplers)
+        s.samplers = _p(arr(scene.samplers))
+        nt = len(scene.textures)
+        self._tex = (_OrcTexture * nt)()
+        for i, t in enumerate(scene.textures):
+            if t is None:
+                continue
+            d = arr(t.data)
+            self._tex[i] = _OrcTexture(t.format, t.width, t.height, t.mip_levels, d.ctypes.data, d.nbytes)
+        s.textureCount = nt
+        s.textures = C.cast(self._tex, C.POINTER(_OrcTexture))
+        s.modelCount = len(scene.model_offsets) - 1
+        s.modelOffsets = _p(arr(scene.model_offsets))
+        s.subModels = _p(arr(scene.sub_models))
+        s.instanceCount = len(scene.tlas_instances)
+        s.tlasInstances = _p(arr(scene.tlas_instances))
+        s.drawInstanceCount = len(scene.draw_instances)
+        s.drawInstances = _p(arr(scene.draw_instances))
+        s.transformCount = len(scene.transforms)
+        s.transforms = _p(arr(scene.transforms))
+        s.directionalLight = _p(arr(scene.directional_light.reshape(1)))
+        s.pointLightCount = len(scene.point_lights)
+        s.pointLights = _p(arr(scene.point_lights))
+        s.spotLightCount = len(scene.spot_lights)
+        s.spotLights = _p(arr(scene.spot_lights))
+        s.camera = _p(arr(scene.camera.reshape(1)))
+        s.skyFaceSize = scene.sky_face_size
+        s.skyRgba16f = _p(arr(scene.sky)) if scene.sky is not None else None
+        self._s = s
+        self._ctx = l.orc_create(C.byref(s), 1 if brute_force else 0)
+
+    def close(self):
+        if self._ctx:
+            lib().orc_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def bvh_build_seconds(self) -> float:
+        return lib().orc_bvh_build_seconds(self._ctx)
+
+    def render(self, pc, width, height, samples, rgba=None, threads=0):
+        """Returns (rgba float32 [h, w, 4], counters u64[4] = closest, shadow, shaded, pixel-samples)."""
+        if rgba is None:
+            rgba = np.zeros((height, width, 4), np.float32)
+        counters = np.zeros(4, np.uint64)
+        pc = np.ascontiguousarray(pc.reshape(1))
+        lib().orc_render(self._ctx, _p(pc), width, height, samples, _p(rgba), threads, _p(counters))
+        return rgba, counters
+
+    def trace_primary(self, pc, width, height, threads=0):
+        from prosper_b200.scene_data import HIT
+        hits = np.zeros(width * height, HIT)
+        margin = np.zeros(width * height, np.float32)
+        pc = np.ascontiguousarray(pc.reshape(1))
+        lib().orc_trace_primary(self._ctx, _p(pc), width, height, _p(hits), _p(margin), threads)
+        return hits, margin
+
+    def trace_rays(self, origin_tmin, dir_tmax, seeds=None, shadow=False, threads=0):
+        from prosper_b200.scene_data import HIT
+        o = np.ascontiguousarray(origin_tmin, np.float32)
+        d = np.ascontiguousarray(dir_tmax, np.float32)
+        n = o.shape[0]
+        sd = np.ascontiguousarray(seeds, np.uint32) if seeds is not None else np.zeros(n, np.uint32)
+        hits = np.zeros(n, HIT)
+        margin = np.zeros(n, np.float32)
+        lib().orc_trace_rays(self._ctx, _p(o), _p(d), _p(sd), n, 1 if shadow else 0, _p(hits), _p(margin), threads)
+        return hits, margin
+
+    def sample_texture(self, tex, smp, u, v):
+        out = np.zeros(4, np.float32)
+        lib().orc_sample_texture(self._ctx, tex, smp, u, v, _p(out))
+        return out
+
+    def sample_sky(self, d):
+        d = np.ascontiguousarray(d, np.float32)
+        out = np.zeros(3, np.float32)
+        lib().orc_sample_sky(self._ctx, _p(d), _p(out))
+        return out

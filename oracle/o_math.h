@@ -47,11 +47,16 @@ inline vec3 cross(vec3 a, vec3 b)
 inline float length(vec3 a) { return std::sqrt(dot(a, a)); }
 // normalize = v / sqrt(dot(v,v)) (division, not rsqrt): exact contract
 inline vec3 normalize(vec3 a) { return a / std::sqrt(dot(a, a)); }
-inline float saturate(float x) { return std::min(std::max(x, 0.0f), 1.0f); } // math.glsl:5
+// math.glsl:5. GLSL clamp() of a NaN is undefined; contract: NaN -> 0 (fmaxf drops the NaN), which is
+// what __saturatef does on the device.
+inline float saturate(float x) { return std::fmin(std::fmax(x, 0.0f), 1.0f); }
 inline float max3(vec3 v) { return std::max(std::max(v.x, v.y), v.z); }      // math.glsl:8
 inline vec3 vmax(vec3 a, vec3 b) { return {std::max(a.x, b.x), std::max(a.y, b.y), std::max(a.z, b.z)}; }
 inline vec3 vmin(vec3 a, vec3 b) { return {std::min(a.x, b.x), std::min(a.y, b.y), std::min(a.z, b.z)}; }
-inline vec3 clamp(vec3 v, float lo, float hi) { return vmin(vmax(v, {lo, lo, lo}), {hi, hi, hi}); }
+inline vec3 clamp(vec3 v, float lo, float hi) // NaN -> lo (same contract as saturate)
+{
+    return {std::fmin(std::fmax(v.x, lo), hi), std::fmin(std::fmax(v.y, lo), hi), std::fmin(std::fmax(v.z, lo), hi)};
+}
 inline vec3 mix(vec3 a, vec3 b, float t) { return a * (1.0f - t) + b * t; }
 inline vec3 reflect(vec3 i, vec3 n) { return i - n * (2.0f * dot(n, i)); }
 inline float sign(float x) { return x > 0.f ? 1.f : (x < 0.f ? -1.f : 0.f); }

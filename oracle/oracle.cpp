@@ -132,6 +132,9 @@ static vec3 sampleSky(const Scene &sc, vec3 d)
 {
     const uint32_t n = sc.s.skyFaceSize;
     if (n == 0 || sc.s.skyRgba16f == nullptr) return {0.f, 0.f, 0.f};
+    // A NaN direction (orthonormalBasis() of a normal with n.z == 0, sampling.glsl:41-42) is an
+    // undefined cube lookup in the reference; contract: it fetches black.
+    if (!std::isfinite(d.x) || !std::isfinite(d.y) || !std::isfinite(d.z)) return {0.f, 0.f, 0.f};
     const float ax = std::fabs(d.x), ay = std::fabs(d.y), az = std::fabs(d.z);
     uint32_t face;
     float sc_, tc, ma;
