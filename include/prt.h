@@ -36,7 +36,13 @@ typedef struct prt_config {
     uint32_t maxInstances;     /* TLAS capacity (World.cpp:838-876 reserveTlasInstances) */
     uint32_t flags;            /* PRT_CFG_* */
 } prt_config;
-enum { PRT_CFG_COUNTERS = 1u << 0 /* run the instrumented traversal kernels (untimed runs) */ };
+enum {
+    PRT_CFG_COUNTERS = 1u << 0,     /* run the instrumented traversal kernels (untimed runs) */
+    PRT_CFG_EXACT_FILTER = 1u << 1, /* material taps use the software bilinear of the any-hit stage
+                                       instead of the texture units' 8-bit-weight filter (parity tests) */
+    PRT_CFG_DECODE_BC7 = 1u << 2    /* expand BC7 payloads to RGBA8 arrays at upload (a CUDA kernel)
+                                       instead of sampling block-compressed CUDA arrays */
+};
 
 /* ---- lifetime: RtReference::init / ~RtReference (RtRef.cpp:90-120) ------------------------ */
 prt_status prt_create(const prt_config *cfg, prt_ctx **out);
@@ -122,6 +128,7 @@ typedef struct prt_counters {
     uint64_t textureTaps;   /* bilinear material/alpha fetches */
     uint64_t pixelSamples;  /* rgen invocations */
     uint64_t kernelLaunches;
+    uint64_t stackOverflows; /* traversal stack overflows (must stay 0; checked by the tests) */
 } prt_counters;
 prt_status prt_get_counters(prt_ctx *ctx, prt_counters *out);
 prt_status prt_reset_counters(prt_ctx *ctx);

@@ -98,60 +98,68 @@ def _p(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
 
 
+def pack_scene(scene):
+    """SceneData -> (orc_scene ctypes struct, list of objects that must outlive it)."""
+    s = _OrcScene()
+    keep = []
+
+    def arr(a):
+        a = np.ascontiguousarray(a)
+        keep.append(a)
+        return a
+
+    bufs = [arr(b) for b in scene.geometry_buffers]
+    nb = len(bufs)
+    bufptrs = (C.c_void_p * nb)(*[b.ctypes.data for b in bufs])
+    bufbytes = (C.c_uint64 * nb)(*[b.nbytes for b in bufs])
+    keep += [bufptrs, bufbytes]
+    s.geometryBufferCount = nb
+    s.geometryBuffers = C.cast(bufptrs, C.POINTER(C.c_void_p))
+    s.geometryBufferBytes = C.cast(bufbytes, C.POINTER(C.c_uint64))
+    s.meshCount = len(scene.metadatas)
+    s.metadatas = _p(arr(scene.metadatas))
+    s.meshInfos = _p(arr(scene.mesh_infos))
+    s.materialCount = len(scene.materials)
+    s.materials = _p(arr(scene.materials))
+    s.samplerCount = len(scene.samplers)
+    s.samplers = _p(arr(scene.samplers))
+    nt = len(scene.textures)
+    tex = (_OrcTexture * nt)()
+    keep.append(tex)
+    for i, t in enumerate(scene.textures):
+        if t is None:
+            continue
+        d = arr(t.data)
+        tex[i] = _OrcTexture(t.format, t.width, t.height, t.mip_levels, d.ctypes.data, d.nbytes)
+    s.textureCount = nt
+    s.textures = C.cast(tex, C.POINTER(_OrcTexture))
+    s.modelCount = len(scene.model_offsets) - 1
+    s.modelOffsets = _p(arr(scene.model_offsets))
+    s.subModels = _p(arr(scene.sub_models))
+    s.instanceCount = len(scene.tlas_instances)
+    s.tlasInstances = _p(arr(scene.tlas_instances))
+    s.drawInstanceCount = len(scene.draw_instances)
+    s.drawInstances = _p(arr(scene.draw_instances))
+    s.transformCount = len(scene.transforms)
+    s.transforms = _p(arr(scene.transforms))
+    s.directionalLight = _p(arr(scene.directional_light.reshape(1)))
+    s.pointLightCount = len(scene.point_lights)
+    s.pointLights = _p(arr(scene.point_lights))
+    s.spotLightCount = len(scene.spot_lights)
+    s.spotLights = _p(arr(scene.spot_lights))
+    s.camera = _p(arr(scene.camera.reshape(1)))
+    s.skyFaceSize = scene.sky_face_size
+    s.skyRgba16f = _p(arr(scene.sky)) if scene.sky is not None else None
+    return s, keep
+
+
 class Oracle:
     """One oracle context over a SceneData (prosper_b200.scene_data). Keeps the arrays alive."""
 
     def __init__(self, scene, brute_force: bool = False):
         self.scene = scene
         l = lib()
-        s = _OrcScene()
-        self._keep = []
-
-        def arr(a):
-            a = np.ascontiguousarray(a)
-            self._keep.append(a)
-            return a
-
-        bufs = [arr(b) for b in scene.geometry_buffers]
-        nb = len(bufs)
-        self._bufptrs = (C.c_void_p * nb)(*[b.ctypes.data for b in bufs])
-        self._bufbytes = (C.c_uint64 * nb)(*[b.nbytes for b in bufs])
-        s.geometryBufferCount = nb
-        s.geometryBuffers = C.cast(self._bufptrs, C.POINTER(C.c_void_p))
-        s.geometryBufferBytes = C.cast(self._bufbytes, C.POINTER(C.c_uint64))
-        s.meshCount = len(scene.metadatas)
-        s.metadatas = _p(arr(scene.metadatas))
-        s.meshInfos = _p(arr(scene.mesh_infos))
-        s.materialCount = len(scene.materials)
-        s.materials = _p(arr(scene.materials))
-        s.samplerCount = len(scene.samplers)
-        s.samplers = _p(arr(scene.samplers))
-        nt = len(scene.textures)
-        self._tex = (_OrcTexture * nt)()
-        for i, t in enumerate(scene.textures):
-            if t is None:
-                continue
-            d = arr(t.data)
-            self._tex[i] = _OrcTexture(t.format, t.width, t.height, t.mip_levels, d.ctypes.data, d.nbytes)
-        s.textureCount = nt
-        s.textures = C.cast(self._tex, C.POINTER(_OrcTexture))
-        s.modelCount = len(scene.model_offsets) - 1
-        s.modelOffsets = _p(arr(scene.model_offsets))
-        s.subModels = _p(arr(scene.sub_models))
-        s.instanceCount = len(scene.tlas_instances)
-        s.tlasInstances = _p(arr(scene.tlas_instances))
-        s.drawInstanceCount = len(scene.draw_instances)
-        s.drawInstances = _p(arr(scene.draw_instances))
-        s.transformCount = len(scene.transforms)
-        s.transforms = _p(arr(scene.transforms))
-        s.directionalLight = _p(arr(scene.directional_light.reshape(1)))
-        s.pointLightCount = len(scene.point_lights)
-        s.pointLights = _p(arr(scene.point_lights))
-        s.spotLightCount = len(scene.spot_lights)
-        s.spotLights = _p(arr(scene.spot_lights))
-        s.camera = _p(arr(scene.camera.reshape(1)))
-        s.skyFaceSize = scene.sky_face_size
-        s.skyRgba16f = _p(arr(scene.sky)) if scene.sky is not None else None
+        s, self._keep = pack_scene(scene)
         self._s = s
         self._ctx = l.orc_create(C.byref(s), 1 if brute_force else 0)
 

@@ -1,0 +1,86 @@
+// core_build.h -- per-primitive bodies of the builder's input stages (shared by the CUDA kernels in
+// kernels_build.cuh and the CPU kernel-logic simulator under tests/hostsim).
+#pragma once
+#include "core_bvh.h"
+#include "core_scene.h"
+#include "core_trace.h"
+
+namespace prt {
+
+// Host-compacted active instances (inactive ones, blasReference == 0, never reach the device:
+// World.cpp:898-905).
+struct TlasInput
+{
+    float transform[12]; // row-major 3x4 object -> world
+    uint32_t customIndexAndMask;
+    uint32_t index; // position in the caller's array
+    const WideNode *nodes;
+    const TriRec *tris;
+};
+
+// One BLAS triangle (World.cpp:617-668): fp16x4 positions, stride 8 (Mesh.hpp:11-12), through the
+// u16/u32 index buffer. Writes the triangle record and its unpadded box.
+HD void gatherTriangle(const SceneView &sv, uint32_t meshIndex, uint32_t p, uint32_t geometryIndex, uint32_t opaque, TriRec &t, V3 &lo,
+                       V3 &hi)
+{
+    const prt_geometry_metadata md = sv.metadatas[meshIndex];
+    const uint32_t i0 = loadIndex(sv, md.bufferIndex, md.indicesOffset, p * 3 + 0, md.usesShortIndices);
+    const uint32_t i1 = loadIndex(sv, md.bufferIndex, md.indicesOffset, p * 3 + 1, md.usesShortIndices);
+    const uint32_t i2 = loadIndex(sv, md.bufferIndex, md.indicesOffset, p * 3 + 2, md.usesShortIndices);
+    const V3 v0 = loadR16G16B16A16(sv, md.bufferIndex, md.positionsOffset, i0);
+    const V3 v1 = loadR16G16B16A16(sv, md.bufferIndex, md.positionsOffset, i1);
+    const V3 v2 = loadR16G16B16A16(sv, md.bufferIndex, md.positionsOffset, i2);
+    const V3 e1 = xsub3(v1, v0), e2 = xsub3(v2, v0);
+    t.v0[0] = v0.x; t.v0[1] = v0.y; t.v0[2] = v0.z; t.primitive = p;
+    t.e1[0] = e1.x; t.e1[1] = e1.y; t.e1[2] = e1.z; t.geometry = geometryIndex | (opaque << 31);
+    t.e2[0] = e2.x; t.e2[1] = e2.y; t.e2[2] = e2.z; t.pad = 0;
+    lo = vmin(v0, vmin(v1, v2));
+    hi = vmax(v0, vmax(v1, v2));
+}
+
+// Pads a primitive box (padMode 1: the oracle's rule for triangles, pad = max(max|coord| / 16384,
+// 1e-6), so a box never culls a triangle the exact test accepts) and returns its Morton key.
+HD uint64_t padBoxAndKey(Box &b, V3 sceneLo, V3 sceneHi, int padMode, uint64_t keyMask)
+{
+    if (padMode == 1)
+    {
+        const float maxAbs = fmaxf_(fmaxf_(fmaxf_(fabsf(sceneLo.x), fabsf(sceneHi.x)), fmaxf_(fabsf(sceneLo.y), fabsf(sceneHi.y))),
+                                    fmaxf_(fabsf(sceneLo.z), fabsf(sceneHi.z)));
+        const float pad = fmaxf_(maxAbs * (1.0f / 16384.0f), 1e-6f);
+        for (int a = 0; a < 3; ++a) { b.lo[a] -= pad; b.hi[a] += pad; }
+    }
+    const V3 c = (boxLo(b) + boxHi(b)) * 0.5f;
+    return mortonKey(c, sceneLo, sceneHi) & keyMask;
+}
+
+// One TLAS instance (World.cpp:878-928): exact world->object matrix + padded world box of the BLAS root.
+HD void tlasInstanceRecord(const TlasInput &ti, InstRec &r, V3 &lo, V3 &hi)
+{
+    invertTransformExact(ti.transform, r.w2o);
+    r.nodes = ti.nodes;
+    r.tris = ti.tris;
+    r.customIndex = ti.customIndexAndMask & 0xFFFFFFu;
+    r.mask = ti.customIndexAndMask >> 24;
+    r.index = ti.index;
+    r.pad = 0;
+    WideNode root;
+    loadNode(ti.nodes, root);
+    const Box ob = wideNodeBounds(root);
+    lo = {3.4e38f, 3.4e38f, 3.4e38f};
+    hi = {-3.4e38f, -3.4e38f, -3.4e38f};
+    const float *m = ti.transform;
+    for (int c = 0; c < 8; ++c)
+    {
+        const V3 p = {(c & 1) ? ob.hi[0] : ob.lo[0], (c & 2) ? ob.hi[1] : ob.lo[1], (c & 4) ? ob.hi[2] : ob.lo[2]};
+        const V3 w = {m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3], m[4] * p.x + m[5] * p.y + m[6] * p.z + m[7],
+                      m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11]};
+        lo = vmin(lo, w);
+        hi = vmax(hi, w);
+    }
+    const V3 e = hi - lo;
+    const float pad = fmaxf_(fmaxf_(e.x, fmaxf_(e.y, e.z)) * (1.0f / 16384.0f), 1e-6f);
+    lo = lo - V3{pad, pad, pad};
+    hi = hi + V3{pad, pad, pad};
+}
+
+} // namespace prt

@@ -1,0 +1,394 @@
+// core_bvh.h -- acceleration-structure data layout and the per-thread bodies of the builder kernels.
+//
+// Replaces what the Vulkan driver does behind vkCmdBuildAccelerationStructuresKHR for prosper
+// (BLAS: src/scene/World.cpp:585-747; TLAS, rebuilt every frame: World.cpp:749-802, 878-961).
+// Pipeline (kernels.cu wires these bodies to launches): primitive boxes -> 63-bit Morton keys ->
+// radix sort -> Karras hierarchy -> bottom-up refit -> surface-area-driven collapse into 8-wide
+// nodes -> quantised 80-byte nodes + primitive records in node order.
+#pragma once
+#include "hd.h"
+
+namespace prt {
+
+#if defined(__CUDA_ARCH__)
+HD uint32_t atomAdd(uint32_t *p, uint32_t v) { return atomicAdd(p, v); }
+HD void memFence() { __threadfence(); }
+#else
+HD uint32_t atomAdd(uint32_t *p, uint32_t v) { const uint32_t o = *p; *p = o + v; return o; }
+HD void memFence() {}
+#endif
+
+struct Box
+{
+    float lo[3];
+    float hi[3];
+};
+HD V3 boxLo(const Box &b) { return {b.lo[0], b.lo[1], b.lo[2]}; }
+HD V3 boxHi(const Box &b) { return {b.hi[0], b.hi[1], b.hi[2]}; }
+HD Box makeBox(V3 lo, V3 hi) { return Box{{lo.x, lo.y, lo.z}, {hi.x, hi.y, hi.z}}; }
+HD Box boxUnion(const Box &a, const Box &b) { return makeBox(vmin(boxLo(a), boxLo(b)), vmax(boxHi(a), boxHi(b))); }
+HD Box loadBoxL2(const Box *p)
+{
+#if defined(__CUDA_ARCH__)
+    Box b;
+    for (int k = 0; k < 3; ++k) { b.lo[k] = __ldcg(&p->lo[k]); b.hi[k] = __ldcg(&p->hi[k]); }
+    return b;
+#else
+    return *p;
+#endif
+}
+HD float boxHalfArea(const Box &b)
+{
+    const float ex = b.hi[0] - b.lo[0], ey = b.hi[1] - b.lo[1], ez = b.hi[2] - b.lo[2];
+    return ex * ey + ey * ez + ez * ex;
+}
+
+// Compressed 8-wide node, 80 bytes = five 128-bit loads (Ylitie/Karras/Laine 2017 layout).
+// Child boxes are quantised to 8 bits per plane on a per-node grid: plane = p + q * 2^(e-127).
+// meta[i]: 0 = empty slot; internal child: (1 << 5) | (24 + i); leaf: (unary count << 5) | first
+// primitive offset relative to primBase (offset + count <= 24). imask bit i = slot i is internal;
+// internal children are stored consecutively from childBase in slot order.
+struct alignas(16) WideNode
+{
+    float px, py, pz;
+    uint8_t ex, ey, ez, imask;
+    uint32_t childBase;
+    uint32_t primBase;
+    uint8_t meta[8];
+    uint8_t qlo[3][8];
+    uint8_t qhi[3][8];
+};
+static_assert(sizeof(WideNode) == 80, "WideNode is five 16-byte words");
+
+// Triangle record in node order, 48 bytes = three 128-bit loads. e1 = v1 - v0 and e2 = v2 - v0 are
+// the same single-rounding subtractions the exact ray/triangle test would do, hoisted to build time.
+struct alignas(16) TriRec
+{
+    float v0[3];
+    uint32_t primitive; // gl_PrimitiveID
+    float e1[3];
+    uint32_t geometry; // gl_GeometryIndexEXT | opaque << 31
+    float e2[3];
+    uint32_t pad;
+};
+static_assert(sizeof(TriRec) == 48, "TriRec");
+
+// Instance record in TLAS node order, 80 bytes = five 128-bit loads.
+struct alignas(16) InstRec
+{
+    float w2o[12];          // world -> object, row-major 3x4 (exact contract inverse)
+    const WideNode *nodes;  // BLAS root
+    const TriRec *tris;
+    uint32_t customIndex;   // first DrawInstance of the model instance (World.cpp:906-913)
+    uint32_t mask;
+    uint32_t index;         // position in the caller's instance array (tie-break key)
+    uint32_t pad;
+};
+static_assert(sizeof(InstRec) == 80, "InstRec");
+
+// ---- Morton keys ---------------------------------------------------------------------------------
+HD uint64_t expandBits21(uint32_t v)
+{
+    uint64_t x = v & 0x1FFFFFu;
+    x = (x | (x << 32)) & 0x001F00000000FFFFull;
+    x = (x | (x << 16)) & 0x001F0000FF0000FFull;
+    x = (x | (x << 8)) & 0x100F00F00F00F00Full;
+    x = (x | (x << 4)) & 0x10C30C30C30C30C3ull;
+    x = (x | (x << 2)) & 0x1249249249249249ull;
+    return x;
+}
+
+HD uint64_t mortonKey(V3 c, V3 lo, V3 hi)
+{
+    uint32_t q[3];
+    const float cc[3] = {c.x, c.y, c.z}, l[3] = {lo.x, lo.y, lo.z}, h[3] = {hi.x, hi.y, hi.z};
+    for (int a = 0; a < 3; ++a)
+    {
+        const float ext = h[a] - l[a];
+        float t = ext > 0.f ? (cc[a] - l[a]) / ext : 0.f;
+        t = fminf_(fmaxf_(t, 0.f), 1.f) * 2097152.0f;
+        const uint32_t v = (uint32_t)t;
+        q[a] = v > 2097151u ? 2097151u : v;
+    }
+    return (expandBits21(q[0]) << 2) | (expandBits21(q[1]) << 1) | expandBits21(q[2]);
+}
+
+// ---- binary hierarchy over the sorted keys (Karras 2012) ------------------------------------------
+// Node references: ref >= 0 is internal node `ref`; ref < 0 is the leaf at sorted position ~ref.
+struct Lbvh
+{
+    uint32_t count;       // primitives
+    const uint64_t *keys; // sorted
+    const uint32_t *order; // sorted position -> primitive index
+    const Box *primBox;   // by primitive index
+    int32_t *left;        // [count-1]
+    int32_t *right;
+    uint32_t *first;      // sorted range covered by the internal node
+    uint32_t *last;
+    int32_t *parentOfInternal; // [count-1], -1 for the root
+    int32_t *parentOfLeaf;     // [count]
+    Box *nodeBox;              // [count-1]
+    uint32_t *visit;           // [count-1], zeroed
+};
+
+HD int lbvhDelta(const Lbvh &t, int i, int j)
+{
+    if (j < 0 || j >= (int)t.count) return -1;
+    const uint64_t a = t.keys[i], b = t.keys[j];
+    if (a == b) return 64 + (31 - bfind((uint32_t)i ^ (uint32_t)j)); // tie-break on position
+    return clz64(a ^ b);
+}
+
+HD void lbvhBuildNode(const Lbvh &t, int i)
+{
+    const int d = (lbvhDelta(t, i, i + 1) - lbvhDelta(t, i, i - 1)) < 0 ? -1 : 1;
+    const int dmin = lbvhDelta(t, i, i - d);
+    int lmax = 2;
+    while (lbvhDelta(t, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int s = lmax / 2; s >= 1; s /= 2)
+        if (lbvhDelta(t, i, i + (l + s) * d) > dmin) l += s;
+    const int j = i + l * d;
+    const int dnode = lbvhDelta(t, i, j);
+    int s = 0;
+    int step = l;
+    do
+    {
+        step = (step + 1) >> 1;
+        if (lbvhDelta(t, i, i + (s + step) * d) > dnode) s += step;
+    } while (step > 1);
+    const int gamma = i + s * d + (d < 0 ? d : 0);
+    const int lo = i < j ? i : j, hi = i < j ? j : i;
+    t.first[i] = (uint32_t)lo;
+    t.last[i] = (uint32_t)hi;
+    if (lo == gamma) { t.left[i] = ~gamma; t.parentOfLeaf[gamma] = i; }
+    else { t.left[i] = gamma; t.parentOfInternal[gamma] = i; }
+    if (hi == gamma + 1) { t.right[i] = ~(gamma + 1); t.parentOfLeaf[gamma + 1] = i; }
+    else { t.right[i] = gamma + 1; t.parentOfInternal[gamma + 1] = i; }
+    if (i == 0) t.parentOfInternal[0] = -1;
+}
+
+HD Box lbvhRefBox(const Lbvh &t, int32_t ref) { return ref >= 0 ? t.nodeBox[ref] : t.primBox[t.order[~ref]]; }
+HD uint32_t lbvhRefCount(const Lbvh &t, int32_t ref) { return ref >= 0 ? t.last[ref] - t.first[ref] + 1u : 1u; }
+HD uint32_t lbvhRefFirst(const Lbvh &t, int32_t ref) { return ref >= 0 ? t.first[ref] : (uint32_t)~ref; }
+
+// One thread per leaf walks to the root; the second arrival at a node owns it (atomic visit flag).
+HD void lbvhRefitFromLeaf(const Lbvh &t, uint32_t leaf)
+{
+    int32_t node = t.parentOfLeaf[leaf];
+    while (node >= 0)
+    {
+        memFence();
+        if (atomAdd(&t.visit[node], 1u) == 0u) return;
+        memFence();
+        // the sibling's box was written by another thread: read it around L1
+        const Box a = t.left[node] >= 0 ? loadBoxL2(&t.nodeBox[t.left[node]]) : t.primBox[t.order[~t.left[node]]];
+        const Box b = t.right[node] >= 0 ? loadBoxL2(&t.nodeBox[t.right[node]]) : t.primBox[t.order[~t.right[node]]];
+        t.nodeBox[node] = boxUnion(a, b);
+        node = t.parentOfInternal[node];
+    }
+}
+
+// ---- collapse to 8-wide + quantise -----------------------------------------------------------------
+// Work item of the level-synchronous collapse: binary subtree `ref` becomes wide node `wide`.
+struct CollapseItem
+{
+    int32_t ref;
+    uint32_t wide;
+};
+
+struct Collapse
+{
+    Lbvh t;
+    uint32_t maxLeaf;      // primitives per leaf slot: 3 for a BLAS, 1 for the TLAS
+    WideNode *nodes;       // out
+    uint32_t *primOut;     // out: node-order position -> primitive index
+    uint32_t *nodeCount;   // atomic allocators (nodeCount starts at 1: the root)
+    uint32_t *primCount;
+    const CollapseItem *queueIn;
+    CollapseItem *queueOut;
+    uint32_t *queueOutCount;
+};
+
+// Smallest biased exponent byte e with 255 * 2^(e-127) >= ext.
+HD uint32_t gridExponent(float ext)
+{
+    if (!(ext > 0.f)) return 1u;
+    const float s = ext / 255.0f;
+    uint32_t bits = f2u(s);
+    uint32_t e = bits >> 23;
+    if (bits & 0x7FFFFFu) e += 1u;
+    if (e < 1u) e = 1u;
+    if (e > 254u) e = 254u;
+    return e;
+}
+
+// Conservative 8-bit quantisation of [lo, hi] on the grid p + q * scale. Returns false when hi does
+// not fit in 255 steps (caller bumps the exponent).
+HD bool quantisePlanes(float p, float scale, float lo, float hi, uint32_t &qlo, uint32_t &qhi)
+{
+    float fl = floorf((lo - p) / scale);
+    if (fl < 0.f) fl = 0.f;
+    if (fl > 255.f) fl = 255.f;
+    while (fl > 0.f && fl * scale + p > lo) fl -= 1.f;
+    float fh = ceilf((hi - p) / scale);
+    if (fh < 0.f) fh = 0.f;
+    while (fh <= 255.f && fh * scale + p < hi) fh += 1.f;
+    if (fh > 255.f) return false;
+    qlo = (uint32_t)fl;
+    qhi = (uint32_t)fh;
+    return true;
+}
+
+HD void collapseItem(const Collapse &c, uint32_t itemIndex)
+{
+    const CollapseItem item = c.queueIn[itemIndex];
+    const Lbvh &t = c.t;
+    int32_t ch[8];
+    int n = 0;
+    if (item.ref >= 0 && lbvhRefCount(t, item.ref) > c.maxLeaf)
+    {
+        ch[n++] = t.left[item.ref];
+        ch[n++] = t.right[item.ref];
+    }
+    else
+        ch[n++] = item.ref; // a tree that is a single leaf (count <= maxLeaf at the root)
+    // phase 1: open the largest-area child that is too big for a leaf slot; phase 2: use spare slots
+    // to split multi-primitive leaves (tighter boxes, same memory)
+    for (int phase = 0; phase < 2; ++phase)
+    {
+        while (n < 8)
+        {
+            int best = -1;
+            float bestArea = -1.f;
+            for (int i = 0; i < n; ++i)
+            {
+                if (ch[i] < 0) continue;
+                const bool big = lbvhRefCount(t, ch[i]) > c.maxLeaf;
+                if (phase == 0 && !big) continue;
+                const float a = boxHalfArea(t.nodeBox[ch[i]]);
+                if (a > bestArea) { bestArea = a; best = i; }
+            }
+            if (best < 0) break;
+            const int32_t r = ch[best];
+            ch[best] = t.left[r];
+            ch[n++] = t.right[r];
+        }
+    }
+    // boxes, node bounds
+    Box cb[8];
+    Box nb = lbvhRefBox(t, ch[0]);
+    cb[0] = nb;
+    for (int i = 1; i < n; ++i)
+    {
+        cb[i] = lbvhRefBox(t, ch[i]);
+        nb = boxUnion(nb, cb[i]);
+    }
+    // slot assignment (greedy on the Ylitie cost: child offset projected on the slot's octant diagonal)
+    const V3 nc = (boxLo(nb) + boxHi(nb)) * 0.5f;
+    float off[8][3];
+    for (int i = 0; i < n; ++i)
+    {
+        const V3 cc = (boxLo(cb[i]) + boxHi(cb[i])) * 0.5f - nc;
+        off[i][0] = cc.x; off[i][1] = cc.y; off[i][2] = cc.z;
+    }
+    int slotOf[8];
+    int childAt[8];
+    for (int i = 0; i < 8; ++i) { slotOf[i] = -1; childAt[i] = -1; }
+    for (int k = 0; k < n; ++k)
+    {
+        int bi = -1, bs = -1;
+        float bc = -3.4e38f;
+        for (int i = 0; i < n; ++i)
+        {
+            if (slotOf[i] >= 0) continue;
+            for (int s = 0; s < 8; ++s)
+            {
+                if (childAt[s] >= 0) continue;
+                const float cost = ((s & 1) ? off[i][0] : -off[i][0]) + ((s & 2) ? off[i][1] : -off[i][1]) +
+                                   ((s & 4) ? off[i][2] : -off[i][2]);
+                if (cost > bc) { bc = cost; bi = i; bs = s; }
+            }
+        }
+        slotOf[bi] = bs;
+        childAt[bs] = bi;
+    }
+    // allocate internal children and leaf primitives
+    uint32_t nInternal = 0, nPrims = 0;
+    for (int i = 0; i < n; ++i)
+    {
+        const uint32_t cnt = lbvhRefCount(t, ch[i]);
+        if (cnt > c.maxLeaf) nInternal++;
+        else nPrims += cnt;
+    }
+    const uint32_t childBase = nInternal ? atomAdd(c.nodeCount, nInternal) : 0u;
+    const uint32_t primBase = nPrims ? atomAdd(c.primCount, nPrims) : 0u;
+    const uint32_t queueBase = nInternal ? atomAdd(c.queueOutCount, nInternal) : 0u;
+    WideNode node;
+    node.px = nb.lo[0]; node.py = nb.lo[1]; node.pz = nb.lo[2];
+    node.childBase = childBase;
+    node.primBase = primBase;
+    uint32_t imask = 0, internalSeen = 0, primSeen = 0;
+    for (int s = 0; s < 8; ++s)
+    {
+        node.meta[s] = 0;
+        const int i = childAt[s];
+        if (i < 0) continue;
+        const uint32_t cnt = lbvhRefCount(t, ch[i]);
+        if (cnt > c.maxLeaf)
+        {
+            imask |= 1u << s;
+            node.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
+            c.queueOut[queueBase + internalSeen] = CollapseItem{ch[i], childBase + internalSeen};
+            internalSeen++;
+        }
+        else
+        {
+            const uint32_t first = lbvhRefFirst(t, ch[i]);
+            for (uint32_t k = 0; k < cnt; ++k) c.primOut[primBase + primSeen + k] = t.order[first + k];
+            node.meta[s] = (uint8_t)((((1u << cnt) - 1u) << 5) | primSeen);
+            primSeen += cnt;
+        }
+    }
+    node.imask = (uint8_t)imask;
+    // quantisation grid
+    uint32_t e[3];
+    const float plo[3] = {nb.lo[0], nb.lo[1], nb.lo[2]};
+    for (int a = 0; a < 3; ++a)
+    {
+        e[a] = gridExponent(nb.hi[a] - nb.lo[a]);
+        for (;;)
+        {
+            const float scale = u2f(e[a] << 23);
+            bool ok = true;
+            for (int s = 0; s < 8 && ok; ++s)
+            {
+                const int i = childAt[s];
+                uint32_t ql = 255, qh = 0;
+                if (i >= 0) ok = quantisePlanes(plo[a], scale, cb[i].lo[a], cb[i].hi[a], ql, qh);
+                node.qlo[a][s] = (uint8_t)ql;
+                node.qhi[a][s] = (uint8_t)qh;
+            }
+            if (ok || e[a] >= 254u) break;
+            e[a]++;
+        }
+    }
+    node.ex = (uint8_t)e[0]; node.ey = (uint8_t)e[1]; node.ez = (uint8_t)e[2];
+    c.nodes[item.wide] = node;
+}
+
+// Dequantised bounds of a wide node (root box of a BLAS for the TLAS builder; tests).
+HD Box wideNodeBounds(const WideNode &n)
+{
+    const float sx = u2f((uint32_t)n.ex << 23), sy = u2f((uint32_t)n.ey << 23), sz = u2f((uint32_t)n.ez << 23);
+    V3 lo = {3.4e38f, 3.4e38f, 3.4e38f}, hi = {-3.4e38f, -3.4e38f, -3.4e38f};
+    for (int s = 0; s < 8; ++s)
+    {
+        if (n.meta[s] == 0) continue;
+        lo = vmin(lo, V3{n.px + n.qlo[0][s] * sx, n.py + n.qlo[1][s] * sy, n.pz + n.qlo[2][s] * sz});
+        hi = vmax(hi, V3{n.px + n.qhi[0][s] * sx, n.py + n.qhi[1][s] * sy, n.pz + n.qhi[2][s] * sz});
+    }
+    return makeBox(lo, hi);
+}
+
+} // namespace prt

@@ -1,0 +1,354 @@
+// core_scene.h -- device view of the scene buffers and the fetch functions of
+// res/shader/scene/{geometry,instances,materials}.glsl, one function per GLSL function.
+#pragma once
+#include "hd.h"
+#include "../../include/prt_types.h"
+
+#ifdef __CUDACC__
+#include <cuda_runtime.h>
+#endif
+
+namespace prt {
+
+// One bindless slot = (texture, sampler) pair (materials.glsl:21-24, 37-38). `texels` is a point
+// sampled, unnormalised view used for the exact software bilinear (any-hit alpha decisions must
+// match the oracle bit for bit); `linear` is the hardware filtered view (material colour taps).
+struct TexSlot
+{
+#ifdef __CUDACC__
+    cudaTextureObject_t texels;
+    cudaTextureObject_t linear;
+#else
+    const uint8_t *rgba; // host simulator: decoded level 0
+    uint64_t unused;
+#endif
+    uint32_t width, height;
+    uint32_t magFilter; // 0 nearest, 1 linear
+    uint32_t addressU, addressV;
+    uint32_t valid;
+};
+
+struct SceneView
+{
+    const uint32_t *const *geometryBuffers;
+    const prt_geometry_metadata *metadatas;
+    const prt_material_data *materials;
+    const prt_draw_instance *drawInstances;
+    const prt_model_instance_transforms *transforms;
+    const TexSlot *texSlots; // [textureCount * samplerCount]
+    uint32_t textureCount, samplerCount;
+    const prt_directional_light *directional;
+    const prt_point_light *pointLights;
+    const prt_spot_light *spotLights;
+    uint32_t pointLightCount, spotLightCount;
+    const prt_camera_uniforms *camera;
+    const uint16_t *sky; // RGBA16F, 6 faces
+    uint32_t skyFaceSize;
+    uint32_t exactMaterialFilter; // 1: software bilinear for material taps too (parity tests)
+};
+
+// ---- scene/geometry.glsl ---------------------------------------------------------------------------
+HD uint32_t loadIndex(const SceneView &sv, uint32_t bufferIndex, uint32_t bufferOffset, uint32_t index, uint32_t usesShort)
+{ // geometry.glsl:51-59
+    if (usesShort == 1) return (uint32_t)((const uint16_t *)sv.geometryBuffers[bufferIndex])[bufferOffset + index];
+    return sv.geometryBuffers[bufferIndex][bufferOffset + index];
+}
+HD V2 unpackHalf2x16(uint32_t p) { return {halfToFloat((uint16_t)(p & 0xFFFFu)), halfToFloat((uint16_t)(p >> 16))}; }
+HD V2 loadR16G16(const SceneView &sv, uint32_t bufferIndex, uint32_t bufferOffset, uint32_t index)
+{ // geometry.glsl:71-80
+    if (bufferOffset == 0xFFFFFFFFu) return {0.f, 0.f};
+    return unpackHalf2x16(sv.geometryBuffers[bufferIndex][bufferOffset + index]);
+}
+HD V3 loadR16G16B16A16(const SceneView &sv, uint32_t bufferIndex, uint32_t bufferOffset, uint32_t index)
+{ // geometry.glsl:82-93
+    if (bufferOffset == 0xFFFFFFFFu) return {0.f, 0.f, 0.f};
+    const uint32_t *b = sv.geometryBuffers[bufferIndex] + bufferOffset + index * 2;
+    const V2 a = unpackHalf2x16(b[0]), c = unpackHalf2x16(b[1]);
+    return {a.x, a.y, c.x};
+}
+HD V3 unpackSnormR10G10B10(uint32_t packed)
+{ // geometry.glsl:95-103
+    const int32_t x = (int32_t)(packed << 22) >> 22;
+    const int32_t y = (int32_t)(packed << 12) >> 22;
+    const int32_t z = (int32_t)(packed << 2) >> 22;
+    const V3 v = vmax(V3{(float)x, (float)y, (float)z} / 511.f, V3{-1.f, -1.f, -1.f});
+    return normalize(v);
+}
+HD V3 loadR10G10B10Snorm(const SceneView &sv, uint32_t bufferIndex, uint32_t bufferOffset, uint32_t index)
+{ // geometry.glsl:105-114
+    if (bufferOffset == 0xFFFFFFFFu) return {0.f, 0.f, 0.f};
+    return unpackSnormR10G10B10(sv.geometryBuffers[bufferIndex][bufferOffset + index]);
+}
+HD V4 loadTangentWithSign(const SceneView &sv, uint32_t bufferIndex, uint32_t bufferOffset, uint32_t index)
+{ // geometry.glsl:116-127
+    if (bufferOffset == 0xFFFFFFFFu) return {0.f, 0.f, 0.f, 0.f};
+    const uint32_t packed = sv.geometryBuffers[bufferIndex][bufferOffset + index];
+    const V3 t = unpackSnormR10G10B10(packed);
+    return {t.x, t.y, t.z, (float)((int32_t)packed >> 30)};
+}
+
+struct Vertex // vertex.glsl:4-10
+{
+    V3 Position;
+    V3 Normal;
+    V4 Tangent;
+    V2 TexCoord0;
+};
+
+HD Vertex loadVertex(const SceneView &sv, const prt_geometry_metadata &m, uint32_t index)
+{ // geometry.glsl:220-234
+    Vertex r;
+    r.Position = loadR16G16B16A16(sv, m.bufferIndex, m.positionsOffset, index);
+    r.Normal = loadR10G10B10Snorm(sv, m.bufferIndex, m.normalsOffset, index);
+    r.Tangent = loadTangentWithSign(sv, m.bufferIndex, m.tangentsOffset, index);
+    r.TexCoord0 = loadR16G16(sv, m.bufferIndex, m.texCoord0sOffset, index);
+    return r;
+}
+HD Vertex loadVertexThroughIndexBuffer(const SceneView &sv, const prt_geometry_metadata &m, uint32_t index)
+{ // geometry.glsl:236-244
+    return loadVertex(sv, m, loadIndex(sv, m.bufferIndex, m.indicesOffset, index, m.usesShortIndices));
+}
+HD V2 loadUV(const SceneView &sv, uint32_t meshIndex, uint32_t index)
+{ // geometry.glsl:246-256
+    const prt_geometry_metadata &m = sv.metadatas[meshIndex];
+    const uint32_t vi = loadIndex(sv, m.bufferIndex, m.indicesOffset, index, m.usesShortIndices);
+    return loadR16G16(sv, m.bufferIndex, m.texCoord0sOffset, vi);
+}
+
+HD V2 bary2(V2 v0, V2 v1, V2 v2, float a, float b, float c)
+{
+    return {v0.x * a + v1.x * b + v2.x * c, v0.y * a + v1.y * b + v2.y * c};
+}
+HD V3 bary3(V3 v0, V3 v1, V3 v2, float a, float b, float c) { return v0 * a + v1 * b + v2 * c; }
+
+// The any-hit uv has to be bit-identical with the oracle's: single roundings, left to right.
+HD V2 interpolateUvExact(V2 v0, V2 v1, V2 v2, float bx, float by)
+{ // geometry.glsl:288-295
+    const float a = xsub(xsub(1.f, bx), by), b = bx, c = by;
+    return {xadd(xadd(xmul(v0.x, a), xmul(v1.x, b)), xmul(v2.x, c)),
+            xadd(xadd(xmul(v0.y, a), xmul(v1.y, b)), xmul(v2.y, c))};
+}
+
+HD Vertex interpolateVertex(const Vertex &v0, const Vertex &v1, const Vertex &v2, float bx, float by)
+{ // geometry.glsl:271-286
+    const float a = 1 - bx - by, b = bx, c = by;
+    Vertex r;
+    r.Position = bary3(v0.Position, v1.Position, v2.Position, a, b, c);
+    r.Normal = bary3(v0.Normal, v1.Normal, v2.Normal, a, b, c);
+    r.Tangent = {v0.Tangent.x * a + v1.Tangent.x * b + v2.Tangent.x * c, v0.Tangent.y * a + v1.Tangent.y * b + v2.Tangent.y * c,
+                 v0.Tangent.z * a + v1.Tangent.z * b + v2.Tangent.z * c, v0.Tangent.w * a + v1.Tangent.w * b + v2.Tangent.w * c};
+    r.TexCoord0 = bary2(v0.TexCoord0, v1.TexCoord0, v2.TexCoord0, a, b, c);
+    return r;
+}
+
+// scene/instances.glsl:36-53. GLSL `vec * mat`: result[i] = dot(vec, column i).
+HD Vertex transformVertex(const Vertex &v, const prt_model_instance_transforms &t)
+{
+    Vertex r;
+    const float(*m)[4] = t.modelToWorld;
+    const float(*nm)[4] = t.normalToWorld;
+    const V3 p = v.Position;
+    r.Position = {p.x * m[0][0] + p.y * m[0][1] + p.z * m[0][2] + m[0][3], p.x * m[1][0] + p.y * m[1][1] + p.z * m[1][2] + m[1][3],
+                  p.x * m[2][0] + p.y * m[2][1] + p.z * m[2][2] + m[2][3]};
+    const V3 n = v.Normal;
+    r.Normal = normalize(V3{n.x * nm[0][0] + n.y * nm[0][1] + n.z * nm[0][2], n.x * nm[1][0] + n.y * nm[1][1] + n.z * nm[1][2],
+                            n.x * nm[2][0] + n.y * nm[2][1] + n.z * nm[2][2]});
+    if (v.Tangent.w != 0)
+    {
+        const V3 g = {v.Tangent.x, v.Tangent.y, v.Tangent.z};
+        const V3 tw = normalize(V3{g.x * m[0][0] + g.y * m[0][1] + g.z * m[0][2], g.x * m[1][0] + g.y * m[1][1] + g.z * m[1][2],
+                                   g.x * m[2][0] + g.y * m[2][1] + g.z * m[2][2]});
+        r.Tangent = {tw.x, tw.y, tw.z, v.Tangent.w};
+    }
+    else
+        r.Tangent = v.Tangent;
+    r.TexCoord0 = v.TexCoord0;
+    return r;
+}
+
+// ---- texture fetch: texture() in a stage without derivatives = LOD 0, magnification filter
+// (materials.glsl:44; WorldData.cpp:686-720) ----------------------------------------------------------
+HD int wrapCoord(int i, int n, uint32_t mode)
+{
+    if (mode == PRT_ADDRESS_REPEAT)
+    {
+        i %= n;
+        return i < 0 ? i + n : i;
+    }
+    if (mode == PRT_ADDRESS_MIRRORED_REPEAT)
+    {
+        const int period = 2 * n;
+        i %= period;
+        if (i < 0) i += period;
+        return i < n ? i : period - 1 - i;
+    }
+    return i < 0 ? 0 : (i > n - 1 ? n - 1 : i);
+}
+
+HD V4 fetchTexel(const TexSlot &s, int x, int y)
+{
+#if defined(__CUDA_ARCH__)
+    const float4 t = tex2D<float4>(s.texels, (float)x + 0.5f, (float)y + 0.5f);
+    return {t.x, t.y, t.z, t.w};
+#elif defined(__CUDACC__)
+    (void)s; (void)x; (void)y;
+    return {0.f, 0.f, 0.f, 0.f};
+#else
+    const uint8_t *p = s.rgba + ((size_t)y * s.width + x) * 4;
+    return {p[0] / 255.f, p[1] / 255.f, p[2] / 255.f, p[3] / 255.f};
+#endif
+}
+
+// Software bilinear with the oracle's exact operation order (oracle.cpp sampleTexture).
+HD V4 sampleTextureExact(const TexSlot &s, V2 uv)
+{
+    const int w = (int)s.width, h = (int)s.height;
+    if (s.magFilter == PRT_FILTER_NEAREST)
+    {
+        const int x = wrapCoord((int)floorf(xmul(uv.x, (float)w)), w, s.addressU);
+        const int y = wrapCoord((int)floorf(xmul(uv.y, (float)h)), h, s.addressV);
+        return fetchTexel(s, x, y);
+    }
+    const float fx = xsub(xmul(uv.x, (float)w), 0.5f), fy = xsub(xmul(uv.y, (float)h), 0.5f);
+    const float x0f = floorf(fx), y0f = floorf(fy);
+    const float ax = xsub(fx, x0f), ay = xsub(fy, y0f);
+    const int x0 = wrapCoord((int)x0f, w, s.addressU), x1 = wrapCoord((int)x0f + 1, w, s.addressU);
+    const int y0 = wrapCoord((int)y0f, h, s.addressV), y1 = wrapCoord((int)y0f + 1, h, s.addressV);
+    const V4 t00 = fetchTexel(s, x0, y0), t10 = fetchTexel(s, x1, y0);
+    const V4 t01 = fetchTexel(s, x0, y1), t11 = fetchTexel(s, x1, y1);
+    const float bx = xsub(1.f, ax), by = xsub(1.f, ay);
+    auto lerp2 = [&](float c00, float c10, float c01, float c11) {
+        const float top = xadd(xmul(c00, bx), xmul(c10, ax));
+        const float bot = xadd(xmul(c01, bx), xmul(c11, ax));
+        return xadd(xmul(top, by), xmul(bot, ay));
+    };
+    return {lerp2(t00.x, t10.x, t01.x, t11.x), lerp2(t00.y, t10.y, t01.y, t11.y), lerp2(t00.z, t10.z, t01.z, t11.z),
+            lerp2(t00.w, t10.w, t01.w, t11.w)};
+}
+
+HD const TexSlot *texSlot(const SceneView &sv, uint32_t textureSampler)
+{
+    const uint32_t tex = textureSampler & 0xFFFFFFu, smp = textureSampler >> 24;
+    if (tex >= sv.textureCount) return nullptr;
+    const TexSlot *s = &sv.texSlots[(size_t)tex * sv.samplerCount + (smp < sv.samplerCount ? smp : 0)];
+    return s->valid ? s : nullptr;
+}
+
+HD V4 sampleTexture(const SceneView &sv, uint32_t textureSampler, V2 uv, bool exact)
+{
+    const TexSlot *s = texSlot(sv, textureSampler);
+    if (s == nullptr) return {1.f, 1.f, 1.f, 1.f};
+#if defined(__CUDA_ARCH__)
+    if (!exact)
+    {
+        const float4 t = tex2D<float4>(s->linear, uv.x, uv.y);
+        return {t.x, t.y, t.z, t.w};
+    }
+#else
+    (void)exact;
+#endif
+    return sampleTextureExact(*s, uv);
+}
+
+// ---- scene/materials.glsl ----------------------------------------------------------------------------
+struct Material // scene/material.glsl:4-16
+{
+    V3 albedo;
+    V3 normal;
+    float roughness;
+    float metallic;
+    float alpha;
+};
+
+HD float sRGBtoLinear(float x) // materials.glsl:26-29
+{
+    return x <= 0.04045f ? x / 12.92f : powf((x + 0.055f) / 1.055f, 2.4f);
+}
+
+HD Material sampleMaterial(const SceneView &sv, uint32_t index, V2 uv)
+{ // materials.glsl:47-119
+    const prt_material_data &data = sv.materials[index];
+    const bool exact = sv.exactMaterialFilter != 0;
+    Material ret;
+    ret.albedo = {0.f, 0.f, 0.f}; ret.normal = {0.f, 0.f, 0.f}; ret.roughness = 0.f; ret.metallic = 0.f; ret.alpha = 0.f;
+    V4 c = {1.f, 1.f, 1.f, 1.f};
+    if ((data.baseColorTextureSampler & 0xFFFFFFu) > 0)
+    {
+        const V4 s = sampleTexture(sv, data.baseColorTextureSampler, uv, exact);
+        c = {sRGBtoLinear(s.x), sRGBtoLinear(s.y), sRGBtoLinear(s.z), s.w};
+    }
+    c = {c.x * data.baseColorFactor[0], c.y * data.baseColorFactor[1], c.z * data.baseColorFactor[2], c.w * data.baseColorFactor[3]};
+    if (data.alphaMode == PRT_ALPHA_BLEND)
+        ret.alpha = c.w;
+    else
+    {
+        if (data.alphaMode == PRT_ALPHA_MASK && c.w < data.alphaCutoff)
+        {
+            ret.alpha = 0;
+            return ret;
+        }
+        ret.alpha = -1;
+    }
+    ret.albedo = {c.x, c.y, c.z};
+    if ((data.metallicRoughnessTextureSampler & 0xFFFFFFu) > 0)
+    {
+        const V4 mr = sampleTexture(sv, data.metallicRoughnessTextureSampler, uv, exact);
+        ret.roughness = mr.y * data.roughnessFactor;
+        ret.metallic = mr.z * data.metallicFactor;
+    }
+    else
+    {
+        ret.roughness = data.roughnessFactor;
+        ret.metallic = data.metallicFactor;
+    }
+    ret.roughness = fmaxf_(ret.roughness, 0.05f);
+    if ((data.normalTextureSampler & 0xFFFFFFu) > 0)
+    {
+        const V4 tn = sampleTexture(sv, data.normalTextureSampler, uv, exact);
+        ret.normal = V3{tn.x, tn.y, tn.z} * 2.f - V3{1.f, 1.f, 1.f};
+    }
+    else
+        ret.normal = {-2.f, -2.f, -2.f};
+    return ret;
+}
+
+// materials.glsl:121-147: the float overload of sRGBtoLinear IS applied to alpha here. Always the
+// exact software filter: this feeds the accept/ignore decision of scene.rahit.
+HD float sampleAlpha(const SceneView &sv, uint32_t index, V2 uv)
+{
+    const prt_material_data &data = sv.materials[index];
+    float linearAlpha = 1;
+    if ((data.baseColorTextureSampler & 0xFFFFFFu) > 0)
+        linearAlpha = sRGBtoLinear(sampleTexture(sv, data.baseColorTextureSampler, uv, true).w);
+    linearAlpha = xmul(linearAlpha, data.baseColorFactor[3]);
+    if (data.alphaMode == PRT_ALPHA_BLEND) return linearAlpha;
+    if (data.alphaMode == PRT_ALPHA_MASK && linearAlpha < data.alphaCutoff) return 0;
+    return -1;
+}
+
+HD uint32_t pcg(uint32_t v) // common/random.glsl:7-12
+{
+    const uint32_t state = v * 747796405u + 2891336453u;
+    const uint32_t word = ((state >> ((state >> 28u) + 4u)) ^ state) * 277803737u;
+    return (word >> 22u) ^ word;
+}
+
+// rt/scene.rahit:18-39. One u per RAY (payload.randomSeed is not advanced between candidates).
+HD bool anyHitAccept(const SceneView &sv, uint32_t drawInstanceIndex, uint32_t primitiveID, float bx, float by, uint32_t randomSeed)
+{
+    const prt_draw_instance &instance = sv.drawInstances[drawInstanceIndex];
+    const V2 uv0 = loadUV(sv, instance.meshIndex, primitiveID * 3 + 0);
+    const V2 uv1 = loadUV(sv, instance.meshIndex, primitiveID * 3 + 1);
+    const V2 uv2 = loadUV(sv, instance.meshIndex, primitiveID * 3 + 2);
+    const V2 uv = interpolateUvExact(uv0, uv1, uv2, bx, by);
+    const float alpha = sampleAlpha(sv, instance.materialIndex, uv);
+    if (alpha == 0) return false;
+    if (alpha > 0)
+    {
+        const float u = (float)pcg(randomSeed) / 4294967296.0f;
+        if (u > alpha) return false;
+    }
+    return true;
+}
+
+} // namespace prt

@@ -1,0 +1,293 @@
+// core_trace.h -- two-level traversal of the compressed 8-wide BVH: the CUDA stand-in for
+// traceRayEXT (main.rgen:57, 73) with scene.rchit / scene.rahit / scene.rmiss inlined.
+//
+// Results are independent of tree shape and traversal order by construction:
+//   * ray/triangle test and the world->object ray transform follow the exact contract (single
+//     roundings, fixed association) shared with the oracle,
+//   * closest hit = smallest t, ties broken by the smallest (instance, geometry, primitive),
+//   * box tests are conservative (quantised boxes only grow; slab interval widened by a few ulp),
+//   * any-hit acceptance uses one random number per RAY (scene.rahit:35), so it is order-free.
+#pragma once
+#include "core_bvh.h"
+#include "core_scene.h"
+
+namespace prt {
+
+constexpr uint32_t MISS_INDEX = 0xFFFFFFFFu; // main.rgen:47
+constexpr int TRACE_STACK = 64;
+
+struct HitRec
+{
+    uint32_t drawInstanceIndex; // scene.rchit:12: gl_InstanceCustomIndexEXT + gl_GeometryIndexEXT
+    uint32_t primitiveID;
+    float u, v; // barycentrics of v1, v2 (scene.rchit:8,14)
+    float t;
+    uint32_t instance; // tie-break keys, not part of the payload
+    uint32_t geometry;
+};
+
+struct TraceCounters
+{
+    uint32_t nodes, tris, instances, anyHits, overflow;
+};
+
+struct Accel
+{
+    const WideNode *tlasNodes; // nullptr = empty scene
+    const InstRec *instances;  // TLAS node order
+};
+
+struct NodeRay
+{
+    V3 o, d;   // exact ray in the current space
+    float ix, iy, iz; // reciprocal direction for the box test (zero components nudged)
+    uint32_t octinv;  // bit k set: direction non-negative on axis k
+};
+
+HD void setupNodeRay(NodeRay &r, V3 o, V3 d)
+{
+    r.o = o;
+    r.d = d;
+    const float eps = 1e-18f;
+    const float dx = fabsf(d.x) > eps ? d.x : (f2u(d.x) >> 31 ? -eps : eps);
+    const float dy = fabsf(d.y) > eps ? d.y : (f2u(d.y) >> 31 ? -eps : eps);
+    const float dz = fabsf(d.z) > eps ? d.z : (f2u(d.z) >> 31 ? -eps : eps);
+    r.ix = 1.0f / dx;
+    r.iy = 1.0f / dy;
+    r.iz = 1.0f / dz;
+    r.octinv = (dx >= 0.f ? 1u : 0u) | (dy >= 0.f ? 2u : 0u) | (dz >= 0.f ? 4u : 0u);
+}
+
+// EXACT CONTRACT: world -> object (oracle o_bvh.h transformPoint / transformVector)
+HD V3 xformPoint(const float *m, V3 p)
+{
+    return {xadd(xadd(xadd(xmul(m[0], p.x), xmul(m[1], p.y)), xmul(m[2], p.z)), m[3]),
+            xadd(xadd(xadd(xmul(m[4], p.x), xmul(m[5], p.y)), xmul(m[6], p.z)), m[7]),
+            xadd(xadd(xadd(xmul(m[8], p.x), xmul(m[9], p.y)), xmul(m[10], p.z)), m[11])};
+}
+HD V3 xformVector(const float *m, V3 d)
+{
+    return {xadd(xadd(xmul(m[0], d.x), xmul(m[1], d.y)), xmul(m[2], d.z)),
+            xadd(xadd(xmul(m[4], d.x), xmul(m[5], d.y)), xmul(m[6], d.z)),
+            xadd(xadd(xmul(m[8], d.x), xmul(m[9], d.y)), xmul(m[10], d.z))};
+}
+
+// EXACT CONTRACT: inverse of a row-major affine 3x4 (oracle o_bvh.h invertTransform)
+HD void invertTransformExact(const float *m, float *out)
+{
+    const float a = m[0], b = m[1], c = m[2];
+    const float d = m[4], e = m[5], f = m[6];
+    const float g = m[8], h = m[9], i = m[10];
+    const float c00 = xsub(xmul(e, i), xmul(f, h));
+    const float c01 = xsub(xmul(f, g), xmul(d, i));
+    const float c02 = xsub(xmul(d, h), xmul(e, g));
+    const float det = xadd(xadd(xmul(a, c00), xmul(b, c01)), xmul(c, c02));
+    const float i00 = xdiv(c00, det), i01 = xdiv(xsub(xmul(c, h), xmul(b, i)), det), i02 = xdiv(xsub(xmul(b, f), xmul(c, e)), det);
+    const float i10 = xdiv(c01, det), i11 = xdiv(xsub(xmul(a, i), xmul(c, g)), det), i12 = xdiv(xsub(xmul(c, d), xmul(a, f)), det);
+    const float i20 = xdiv(c02, det), i21 = xdiv(xsub(xmul(b, g), xmul(a, h)), det), i22 = xdiv(xsub(xmul(a, e), xmul(b, d)), det);
+    const float tx = m[3], ty = m[7], tz = m[11];
+    out[0] = i00; out[1] = i01; out[2] = i02;
+    out[3] = -xadd(xadd(xmul(i00, tx), xmul(i01, ty)), xmul(i02, tz));
+    out[4] = i10; out[5] = i11; out[6] = i12;
+    out[7] = -xadd(xadd(xmul(i10, tx), xmul(i11, ty)), xmul(i12, tz));
+    out[8] = i20; out[9] = i21; out[10] = i22;
+    out[11] = -xadd(xadd(xmul(i20, tx), xmul(i21, ty)), xmul(i22, tz));
+}
+
+// EXACT CONTRACT: Moeller-Trumbore, two-sided, no epsilon, open interval (oracle intersectTriangle)
+HD bool intersectTriangleExact(V3 o, V3 d, float tMin, float tMax, V3 v0, V3 e1, V3 e2, float &t, float &u, float &v)
+{
+    const V3 P = xcross(d, e2);
+    const float det = xdot(e1, P);
+    if (det == 0.0f) return false;
+    const float inv = xdiv(1.0f, det);
+    const V3 T = xsub3(o, v0);
+    const float uu = xmul(xdot(T, P), inv);
+    if (!(uu >= 0.0f) || uu > 1.0f) return false;
+    const V3 Q = xcross(T, e1);
+    const float vv = xmul(xdot(d, Q), inv);
+    if (!(vv >= 0.0f) || xadd(uu, vv) > 1.0f) return false;
+    const float tt = xmul(xdot(e2, Q), inv);
+    if (!(tt > tMin) || !(tt < tMax)) return false;
+    t = tt; u = uu; v = vv;
+    return true;
+}
+
+HD bool betterHit(float t, uint32_t inst, uint32_t geom, uint32_t prim, const HitRec &h)
+{
+    if (h.drawInstanceIndex == MISS_INDEX) return true;
+    if (t != h.t) return t < h.t;
+    if (inst != h.instance) return inst < h.instance;
+    if (geom != h.geometry) return geom < h.geometry;
+    return prim < h.primitiveID;
+}
+
+HD void loadNode(const WideNode *p, WideNode &n)
+{
+#if defined(__CUDA_ARCH__)
+    const uint4 *s = reinterpret_cast<const uint4 *>(p);
+    uint4 *d = reinterpret_cast<uint4 *>(&n);
+    d[0] = __ldg(s + 0); d[1] = __ldg(s + 1); d[2] = __ldg(s + 2); d[3] = __ldg(s + 3); d[4] = __ldg(s + 4);
+#else
+    n = *p;
+#endif
+}
+
+// Intersects the ray with the eight quantised child boxes. Returns the hit mask: internal children
+// in bits 24..31 at position 24 + (slot ^ octinv) (nearer octant = higher bit), leaf primitives in
+// bits 0..23.
+HD uint32_t intersectNode(const WideNode &n, const NodeRay &r, float tMin, float tMax)
+{
+    const float sx = u2f((uint32_t)n.ex << 23) * r.ix, sy = u2f((uint32_t)n.ey << 23) * r.iy, sz = u2f((uint32_t)n.ez << 23) * r.iz;
+    const float ox = (n.px - r.o.x) * r.ix, oy = (n.py - r.o.y) * r.iy, oz = (n.pz - r.o.z) * r.iz;
+    uint32_t mask = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int s = 0; s < 8; ++s)
+    {
+        const uint32_t meta = n.meta[s];
+        if (meta == 0) continue;
+        const float lx = (float)n.qlo[0][s], hx = (float)n.qhi[0][s];
+        const float ly = (float)n.qlo[1][s], hy = (float)n.qhi[1][s];
+        const float lz = (float)n.qlo[2][s], hz = (float)n.qhi[2][s];
+        const float x0 = lx * sx + ox, x1 = hx * sx + ox;
+        const float y0 = ly * sy + oy, y1 = hy * sy + oy;
+        const float z0 = lz * sz + oz, z1 = hz * sz + oz;
+        float tn = fmaxf_(fmaxf_(fminf_(x0, x1), fminf_(y0, y1)), fmaxf_(fminf_(z0, z1), tMin));
+        float tf = fminf_(fminf_(fmaxf_(x0, x1), fmaxf_(y0, y1)), fminf_(fmaxf_(z0, z1), tMax));
+        tn = tn - fabsf(tn) * 4e-7f;
+        tf = tf + fabsf(tf) * 4e-7f;
+        if (tn <= tf)
+        {
+            const uint32_t low5 = meta & 31u;
+            if ((meta & 0x18u) == 0x18u) mask |= 1u << (low5 ^ r.octinv);
+            else mask |= (meta >> 5) << low5;
+        }
+    }
+    return mask;
+}
+
+// traceRayEXT. SHADOW = gl_RayFlagsTerminateOnFirstHitEXT (main.rgen:52). Returns true on a hit.
+template <bool SHADOW, bool COUNT>
+HDNI bool traceRay(const Accel &as, const SceneView &sv, V3 o, V3 d, float tMin, float tMax, uint32_t seed, HitRec &best,
+                   TraceCounters *cnt)
+{
+    best.drawInstanceIndex = MISS_INDEX;
+    best.primitiveID = MISS_INDEX;
+    best.u = 0.f; best.v = 0.f; best.t = tMax; best.instance = MISS_INDEX; best.geometry = 0;
+    if (as.tlasNodes == nullptr) return false;
+
+    uint32_t stackX[TRACE_STACK], stackY[TRACE_STACK];
+    int sp = 0;
+    int blasSp = -1; // stack depth at BLAS entry; -1 while in the TLAS
+    NodeRay world, ray;
+    setupNodeRay(world, o, d);
+    ray = world;
+    const WideNode *nodes = as.tlasNodes;
+    const TriRec *tris = nullptr;
+    uint32_t instCustom = 0, instIndex = 0;
+    uint32_t gx = 0, gy = 0x80000000u; // node group: base index, hit bits | imask
+    uint32_t px = 0, py = 0;           // primitive group: base index, hit bits
+
+    for (;;)
+    {
+        if (gy & 0xFF000000u)
+        {
+            const int bit = bfind(gy);
+            const uint32_t imask = gy;
+            gy &= ~(1u << bit);
+            if (gy & 0xFF000000u)
+            {
+                if (sp < TRACE_STACK) { stackX[sp] = gx; stackY[sp] = gy; sp++; }
+                else if (COUNT) cnt->overflow++;
+            }
+            const uint32_t slot = ((uint32_t)bit - 24u) ^ ray.octinv;
+            const uint32_t rel = (uint32_t)popc(imask & 0xFFu & ((1u << slot) - 1u));
+            WideNode n;
+            loadNode(nodes + gx + rel, n);
+            if (COUNT) cnt->nodes++;
+            const float tFar = best.drawInstanceIndex == MISS_INDEX ? tMax : fminf_(tMax, best.t);
+            const uint32_t hits = intersectNode(n, ray, tMin, tFar);
+            gx = n.childBase;
+            gy = (hits & 0xFF000000u) | n.imask;
+            px = n.primBase;
+            py = hits & 0x00FFFFFFu;
+        }
+        else
+        {
+            px = gx; py = gy;
+            gx = 0; gy = 0;
+        }
+
+        while (py != 0)
+        {
+            const int pbit = bfind(py);
+            py &= ~(1u << pbit);
+            if (blasSp < 0)
+            {
+                // TLAS leaf: enter the instance (traversal state of the TLAS goes on the stack)
+                const InstRec &inst = as.instances[px + (uint32_t)pbit];
+                if (COUNT) cnt->instances++;
+                if ((inst.mask & 0xFFu) == 0) continue;
+                if (gy & 0xFF000000u)
+                {
+                    if (sp < TRACE_STACK) { stackX[sp] = gx; stackY[sp] = gy; sp++; }
+                    else if (COUNT) cnt->overflow++;
+                }
+                if (py != 0)
+                {
+                    if (sp < TRACE_STACK) { stackX[sp] = px; stackY[sp] = py; sp++; }
+                    else if (COUNT) cnt->overflow++;
+                }
+                blasSp = sp;
+                setupNodeRay(ray, xformPoint(inst.w2o, o), xformVector(inst.w2o, d));
+                nodes = inst.nodes;
+                tris = inst.tris;
+                instCustom = inst.customIndex;
+                instIndex = inst.index;
+                gx = 0; gy = 0x80000000u;
+                py = 0;
+                break;
+            }
+            const TriRec &tr = tris[px + (uint32_t)pbit];
+            if (COUNT) cnt->tris++;
+            float t, u, v;
+            if (!intersectTriangleExact(ray.o, ray.d, tMin, tMax, V3{tr.v0[0], tr.v0[1], tr.v0[2]}, V3{tr.e1[0], tr.e1[1], tr.e1[2]},
+                                        V3{tr.e2[0], tr.e2[1], tr.e2[2]}, t, u, v))
+                continue;
+            const uint32_t geom = tr.geometry & 0x7FFFFFFFu;
+            if (!betterHit(t, instIndex, geom, tr.primitive, best)) continue;
+            const uint32_t drawInstanceIndex = instCustom + geom;
+            if (!(tr.geometry >> 31))
+            {
+                if (COUNT) cnt->anyHits++;
+                if (!anyHitAccept(sv, drawInstanceIndex, tr.primitive, u, v, seed)) continue;
+            }
+            best.drawInstanceIndex = drawInstanceIndex;
+            best.primitiveID = tr.primitive;
+            best.u = u; best.v = v; best.t = t;
+            best.instance = instIndex;
+            best.geometry = geom;
+            if (SHADOW) return true;
+        }
+
+        if ((gy & 0xFF000000u) == 0)
+        {
+            if (sp == blasSp)
+            {
+                // BLAS exhausted: back to world space
+                blasSp = -1;
+                ray = world;
+                nodes = as.tlasNodes;
+            }
+            if (sp == 0) break;
+            sp--;
+            gx = stackX[sp];
+            gy = stackY[sp];
+        }
+    }
+    return best.drawInstanceIndex != MISS_INDEX;
+}
+
+} // namespace prt

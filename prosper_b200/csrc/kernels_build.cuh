@@ -1,0 +1,182 @@
+// kernels_build.cuh -- launches of the acceleration-structure builder (bodies in core_bvh.h).
+// BLAS: World::Impl::buildNextBlas (World.cpp:585-747). TLAS: updateTlasInstances + buildCurrentTlas
+// (World.cpp:878-928, 749-802), rebuilt from scratch every frame like the reference does.
+#pragma once
+#include "core_build.h"
+#include "kernels_sort.cuh"
+
+namespace prt {
+
+// order-preserving float <-> uint mapping for atomicMin/atomicMax on bounds
+__device__ __forceinline__ uint32_t floatOrdered(float f)
+{
+    const uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float orderedFloat(uint32_t k)
+{
+    const uint32_t b = (k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(b);
+#else
+    float f;
+    memcpy(&f, &b, 4);
+    return f;
+#endif
+}
+
+// bounds[0..2] = min xyz, bounds[3..5] = max xyz (ordered-uint encoding), bounds[6] = max |coord|
+struct BuildBounds
+{
+    uint32_t v[8];
+};
+
+__global__ void k_init_bounds(BuildBounds *b, uint32_t *counters, uint32_t nCounters)
+{
+    if (threadIdx.x < 3) b->v[threadIdx.x] = 0xFFFFFFFFu;
+    else if (threadIdx.x < 8) b->v[threadIdx.x] = 0u;
+    if (threadIdx.x < nCounters) counters[threadIdx.x] = 0u;
+}
+
+// Every lane of the warp must call this (invalid lanes pass valid = false).
+__device__ __forceinline__ void atomicBounds(BuildBounds *b, V3 lo, V3 hi, bool valid)
+{
+    const float l[3] = {lo.x, lo.y, lo.z}, h[3] = {hi.x, hi.y, hi.z};
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+    {
+        const uint32_t mn = __reduce_min_sync(0xFFFFFFFFu, valid ? floatOrdered(l[a]) : 0xFFFFFFFFu);
+        const uint32_t mx = __reduce_max_sync(0xFFFFFFFFu, valid ? floatOrdered(h[a]) : 0u);
+        if ((threadIdx.x & 31u) == 0u)
+        {
+            atomicMin(&b->v[a], mn);
+            atomicMax(&b->v[3 + a], mx);
+        }
+    }
+}
+
+// One launch per sub-model (= BLAS geometry, World.cpp:617-668): triangle records + unpadded boxes.
+__global__ void k_blas_gather(SceneView sv, uint32_t meshIndex, uint32_t primCount, uint32_t geometryIndex, uint32_t opaque,
+                              uint32_t outOffset, TriRec *__restrict__ tris, Box *__restrict__ boxes, BuildBounds *bounds)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= primCount)
+    {
+        atomicBounds(bounds, V3{0.f, 0.f, 0.f}, V3{0.f, 0.f, 0.f}, false);
+        return;
+    }
+    TriRec t;
+    V3 lo, hi;
+    gatherTriangle(sv, meshIndex, p, geometryIndex, opaque, t, lo, hi);
+    tris[outOffset + p] = t;
+    boxes[outOffset + p] = makeBox(lo, hi);
+    atomicBounds(bounds, lo, hi, true);
+}
+
+// Pads the primitive boxes (so a box never culls a triangle the exact test accepts: the oracle's
+// rule, pad = max(max|coord| / 16384, 1e-6)) and computes the Morton keys of the box centres.
+__global__ void k_pad_and_keys(Box *__restrict__ boxes, uint32_t n, const BuildBounds *__restrict__ bounds, int padMode,
+                               uint64_t keyMask, uint64_t *__restrict__ keys, uint32_t *__restrict__ order)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    V3 lo = {orderedFloat(bounds->v[0]), orderedFloat(bounds->v[1]), orderedFloat(bounds->v[2])};
+    V3 hi = {orderedFloat(bounds->v[3]), orderedFloat(bounds->v[4]), orderedFloat(bounds->v[5])};
+    Box b = boxes[i];
+    keys[i] = padBoxAndKey(b, lo, hi, padMode, keyMask);
+    if (padMode == 1) boxes[i] = b;
+    order[i] = i;
+}
+
+__global__ void k_lbvh_nodes(Lbvh t)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i + 1 >= t.count) return;
+    lbvhBuildNode(t, (int)i);
+    t.visit[i] = 0;
+}
+
+__global__ void k_lbvh_refit(Lbvh t)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= t.count) return;
+    lbvhRefitFromLeaf(t, i);
+}
+
+// One collapse level: items [0, *countIn) of queueIn. Launched with enough threads for the worst
+// case; the live count is read from device memory so the host never waits between levels.
+__global__ void k_collapse_level(Collapse c, const uint32_t *__restrict__ countIn)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= *countIn) return;
+    collapseItem(c, i);
+}
+
+// All levels in one block (TLAS: a few thousand instances, launch latency matters more than width).
+// queues = two arrays of capacity `queueCapacity` used alternately; queueCounts[l] = items of level l.
+__global__ void __launch_bounds__(1024) k_collapse_all_levels(Collapse c, CollapseItem *queueA, CollapseItem *queueB,
+                                                             uint32_t *queueCounts, uint32_t maxLevels)
+{
+    for (uint32_t level = 0; level + 1 < maxLevels; ++level)
+    {
+        const uint32_t count = __ldcg(&queueCounts[level]);
+        if (count == 0) break;
+        c.queueIn = (level & 1u) ? queueB : queueA;
+        c.queueOut = (level & 1u) ? queueA : queueB;
+        c.queueOutCount = &queueCounts[level + 1];
+        for (uint32_t i = threadIdx.x; i < count; i += blockDim.x) collapseItem(c, i);
+        __threadfence_block();
+        __syncthreads();
+    }
+}
+
+__global__ void k_collapse_seed(CollapseItem *queue, uint32_t *queueCounts, uint32_t levels, uint32_t *nodeCount,
+                                uint32_t *primCount, uint32_t primTotal)
+{
+    if (threadIdx.x == 0)
+    {
+        queue[0] = CollapseItem{primTotal > 1 ? 0 : ~0, 0u};
+        queueCounts[0] = 1;
+        *nodeCount = 1;
+        *primCount = 0;
+    }
+    for (uint32_t l = 1 + threadIdx.x; l < levels; l += blockDim.x) queueCounts[l] = 0;
+}
+
+__global__ void k_emit_tris(const uint32_t *__restrict__ primOut, uint32_t n, const TriRec *__restrict__ in, TriRec *__restrict__ out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 *s = reinterpret_cast<const uint4 *>(in + primOut[i]);
+    uint4 *d = reinterpret_cast<uint4 *>(out + i);
+    d[0] = s[0]; d[1] = s[1]; d[2] = s[2];
+}
+
+// ---- TLAS ------------------------------------------------------------------------------------------------
+__global__ void k_tlas_instances(const TlasInput *__restrict__ in, uint32_t n, InstRec *__restrict__ recs, Box *__restrict__ boxes,
+                                 BuildBounds *bounds)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+    {
+        atomicBounds(bounds, V3{0.f, 0.f, 0.f}, V3{0.f, 0.f, 0.f}, false);
+        return;
+    }
+    InstRec r;
+    V3 lo, hi;
+    tlasInstanceRecord(in[i], r, lo, hi);
+    recs[i] = r;
+    boxes[i] = makeBox(lo, hi);
+    atomicBounds(bounds, lo, hi, true);
+}
+
+__global__ void k_emit_instances(const uint32_t *__restrict__ primOut, uint32_t n, const InstRec *__restrict__ in, InstRec *__restrict__ out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 *s = reinterpret_cast<const uint4 *>(in + primOut[i]);
+    uint4 *d = reinterpret_cast<uint4 *>(out + i);
+    d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; d[3] = s[3]; d[4] = s[4];
+}
+
+} // namespace prt

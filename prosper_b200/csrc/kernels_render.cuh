@@ -1,0 +1,296 @@
+// kernels_render.cuh -- the wavefront form of res/shader/rt/reference/main.rgen.
+//
+// One rgen invocation (pixel, frameIndex) = one path with a fixed slot in the path-state arrays.
+// The bounce loop main.rgen:241-283 is cut at its two traceRayEXT calls into stages that communicate
+// through compacted queues in HBM:
+//   raygen -> [ trace_closest -> shade -> trace_shadow ] x maxBounces -> accumulate
+// Live counts stay in device memory (one counter per bounce), so the host enqueues the whole frame
+// without a single synchronisation. Compaction = warp ballot + one atomic per warp per queue.
+#pragma once
+#include "core_shade.h"
+#include "core_trace.h"
+
+namespace prt {
+
+constexpr int RENDER_THREADS = 128;
+constexpr uint32_t COUNT_SHADOW_BASE = 8; // counts[b] = closest rays of bounce b, counts[8 + b] = shadow rays
+
+struct PathBuffers
+{
+    uint4 *rng;          // per path: pcg_state.xyz
+    float4 *throughput;  // per path
+    float4 *color;       // per path: the rgen `color` accumulator
+    float4 *rayO[2];     // ray queues (ping-pong): origin.xyz, tMin
+    float4 *rayD[2];     // direction.xyz, tMax
+    uint2 *rayId[2];     // path index, payload.randomSeed
+    uint4 *hits;         // per closest-ray slot: drawInstanceIndex, primitiveID, bary bits
+    float4 *shadowO;     // shadow queue
+    float4 *shadowD;
+    uint2 *shadowId;
+    float4 *shadowC;     // contribution if unoccluded
+    uint32_t *counts;    // [16]
+};
+
+struct GlobalCounters
+{
+    unsigned long long closestRays, shadowRays, nodesVisited, trisTested, instancesEntered, anyHitCalls, shadedHits, textureTaps,
+        pixelSamples, stackOverflows;
+};
+
+__device__ __forceinline__ uint32_t appendSlot(uint32_t *counter, bool pred)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, pred);
+    if (m == 0) return 0;
+    const int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    return base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+}
+
+__device__ __forceinline__ void flushTraceCounters(GlobalCounters *g, const TraceCounters &c)
+{
+    const uint32_t n = __reduce_add_sync(0xFFFFFFFFu, c.nodes), t = __reduce_add_sync(0xFFFFFFFFu, c.tris);
+    const uint32_t i = __reduce_add_sync(0xFFFFFFFFu, c.instances), a = __reduce_add_sync(0xFFFFFFFFu, c.anyHits);
+    const uint32_t o = __reduce_add_sync(0xFFFFFFFFu, c.overflow);
+    if ((threadIdx.x & 31u) == 0)
+    {
+        if (n) atomicAdd(&g->nodesVisited, (unsigned long long)n);
+        if (t) atomicAdd(&g->trisTested, (unsigned long long)t);
+        if (i) atomicAdd(&g->instancesEntered, (unsigned long long)i);
+        if (a) atomicAdd(&g->anyHitCalls, (unsigned long long)a);
+        if (o) atomicAdd(&g->stackOverflows, (unsigned long long)o);
+    }
+}
+
+// main.rgen:225-240
+__global__ void __launch_bounds__(RENDER_THREADS)
+    k_raygen(SceneView sv, prt_reference_pc pc, uint32_t width, uint32_t height, uint32_t samples, PathBuffers pb)
+{
+    const uint32_t pixels = width * height;
+    const uint32_t total = pixels * samples;
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p == 0)
+    {
+        pb.counts[0] = total;
+        for (int i = 1; i < 16; ++i) pb.counts[i] = 0;
+    }
+    if (p >= total) return;
+    const uint32_t k = p / pixels, pix = p - k * pixels;
+    const uint32_t px = pix % width, py = pix / width;
+    const uint32_t frameIndex = (pc.frameIndex + k) % PRT_FRAME_PERIOD; // RtRef.cpp:170
+    Rng rng;
+    const Ray ray = generatePrimaryRay(sv, pc, frameIndex, px, py, width, height, rng);
+    pb.rng[p] = make_uint4(rng.state.x, rng.state.y, rng.state.z, 0u);
+    pb.throughput[p] = make_float4(1.f, 1.f, 1.f, 0.f);
+    pb.color[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+    pb.rayO[0][p] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.tMin);
+    pb.rayD[0][p] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.tMax);
+    pb.rayId[0][p] = make_uint2(p, pcg(rng.state.x ^ rng.state.z)); // main.rgen:71
+}
+
+// traceClosest, main.rgen:62-81
+template <bool COUNT>
+__global__ void __launch_bounds__(RENDER_THREADS)
+    k_trace_closest(Accel as, SceneView sv, PathBuffers pb, int q, uint32_t bounce, GlobalCounters *gc)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t count = pb.counts[bounce];
+    TraceCounters tc = {0, 0, 0, 0, 0};
+    if (slot < count)
+    {
+        const float4 o = pb.rayO[q][slot], d = pb.rayD[q][slot];
+        const uint2 id = pb.rayId[q][slot];
+        HitRec hit;
+        traceRay<false, COUNT>(as, sv, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, id.y, hit, &tc);
+        pb.hits[slot] = make_uint4(hit.drawInstanceIndex, hit.primitiveID, __float_as_uint(hit.u), __float_as_uint(hit.v));
+    }
+    if (COUNT) flushTraceCounters(gc, tc);
+}
+
+// One loop iteration of main.rgen:241-283 minus the traces.
+__global__ void __launch_bounds__(RENDER_THREADS)
+    k_shade(SceneView sv, prt_reference_pc pc, PathBuffers pb, int q, uint32_t bounce, GlobalCounters *gc, int countShaded)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t count = pb.counts[bounce];
+    ShadeResult r;
+    r.shadowRay = false;
+    r.alive = false;
+    uint32_t path = 0;
+    bool shaded = false;
+    Rng rng;
+    if (slot < count)
+    {
+        const uint4 h = pb.hits[slot];
+        const float4 d = pb.rayD[q][slot];
+        path = pb.rayId[q][slot].x;
+        const uint4 rs = pb.rng[path];
+        const float4 tp = pb.throughput[path];
+        const float4 cl = pb.color[path];
+        rng.state = {rs.x, rs.y, rs.z};
+        V3 throughput = {tp.x, tp.y, tp.z}, color = {cl.x, cl.y, cl.z};
+        shadePath(sv, pc, bounce, V3{d.x, d.y, d.z}, h.x, h.y, __uint_as_float(h.z), __uint_as_float(h.w), rng, throughput, color, r);
+        shaded = h.x != MISS_INDEX;
+        pb.color[path] = make_float4(color.x, color.y, color.z, 0.f);
+        if (r.alive)
+        {
+            pb.rng[path] = make_uint4(rng.state.x, rng.state.y, rng.state.z, 0u);
+            pb.throughput[path] = make_float4(throughput.x, throughput.y, throughput.z, 0.f);
+        }
+    }
+    const uint32_t ss = appendSlot(&pb.counts[COUNT_SHADOW_BASE + bounce], r.shadowRay);
+    if (r.shadowRay)
+    {
+        pb.shadowO[ss] = make_float4(r.shadowO.x, r.shadowO.y, r.shadowO.z, 0.1f); // main.rgen:217 tMin
+        pb.shadowD[ss] = make_float4(r.shadowD.x, r.shadowD.y, r.shadowD.z, r.shadowTMax);
+        pb.shadowId[ss] = make_uint2(path, r.shadowSeed);
+        pb.shadowC[ss] = make_float4(r.shadowContribution.x, r.shadowContribution.y, r.shadowContribution.z, 0.f);
+    }
+    const uint32_t ns = appendSlot(&pb.counts[bounce + 1], r.alive);
+    if (r.alive)
+    {
+        pb.rayO[q ^ 1][ns] = make_float4(r.next.o.x, r.next.o.y, r.next.o.z, r.next.tMin);
+        pb.rayD[q ^ 1][ns] = make_float4(r.next.d.x, r.next.d.y, r.next.d.z, r.next.tMax);
+        pb.rayId[q ^ 1][ns] = make_uint2(path, pcg(rng.state.x ^ rng.state.z));
+    }
+    if (countShaded)
+    {
+        const uint32_t n = __popc(__ballot_sync(0xFFFFFFFFu, shaded));
+        if ((threadIdx.x & 31u) == 0 && n) atomicAdd(&gc->shadedHits, (unsigned long long)n);
+    }
+}
+
+// shadow(), main.rgen:49-60, fused with the addBounce of evaluateDirectLighting's result
+template <bool COUNT>
+__global__ void __launch_bounds__(RENDER_THREADS)
+    k_trace_shadow(Accel as, SceneView sv, PathBuffers pb, uint32_t bounce, GlobalCounters *gc)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t count = pb.counts[COUNT_SHADOW_BASE + bounce];
+    TraceCounters tc = {0, 0, 0, 0, 0};
+    if (slot < count)
+    {
+        const float4 o = pb.shadowO[slot], d = pb.shadowD[slot];
+        const uint2 id = pb.shadowId[slot];
+        HitRec hit;
+        const bool occluded = traceRay<true, COUNT>(as, sv, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, id.y, hit, &tc);
+        if (!occluded)
+        {
+            const float4 c = pb.shadowC[slot];
+            float4 col = pb.color[id.x];
+            col.x += c.x; col.y += c.y; col.z += c.z;
+            pb.color[id.x] = col;
+        }
+    }
+    if (COUNT) flushTraceCounters(gc, tc);
+}
+
+// Adds the per-bounce live counts of the finished batch to the 64-bit totals.
+__global__ void k_tally(PathBuffers pb, GlobalCounters *gc, uint32_t pixelSamples)
+{
+    if (threadIdx.x == 0)
+    {
+        unsigned long long c = 0, s = 0;
+        for (uint32_t b = 0; b < MAX_BOUNCES; ++b)
+        {
+            c += pb.counts[b];
+            s += pb.counts[COUNT_SHADOW_BASE + b];
+        }
+        gc->closestRays += c;
+        gc->shadowRays += s;
+        gc->pixelSamples += pixelSamples;
+    }
+}
+
+// main.rgen:285-298, frame after frame in frameIndex order (the same order of operations as the
+// reference's one-frame-per-dispatch running mean).
+__global__ void k_accumulate(PathBuffers pb, float4 *__restrict__ accum, uint32_t pixels, uint32_t samples, uint32_t flags)
+{
+    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= pixels) return;
+    float4 h = accum[pix];
+    const bool accumulate = (flags >> 1) & 1u;
+    for (uint32_t k = 0; k < samples; ++k)
+    {
+        const float4 c = pb.color[k * pixels + pix];
+        const bool skipHistory = k == 0 && (flags & 1u);
+        if (skipHistory || !accumulate) h = make_float4(c.x, c.y, c.z, 1.f);
+        else
+        {
+            const float n = h.w + 1.f;
+            h.x = h.x + (c.x - h.x) / n;
+            h.y = h.y + (c.y - h.y) / n;
+            h.z = h.z + (c.z - h.z) / n;
+            h.w = n;
+        }
+    }
+    accum[pix] = h;
+}
+
+// The fp32 -> fp16 blit that produces Output::illumination (RtRef.cpp:336-377)
+__global__ void k_blit_f16(const float4 *__restrict__ accum, uint2 *__restrict__ out, uint32_t pixels)
+{
+    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= pixels) return;
+    const float4 c = accum[pix];
+    const uint32_t lo = (uint32_t)floatToHalf(c.x) | ((uint32_t)floatToHalf(c.y) << 16);
+    const uint32_t hi = (uint32_t)floatToHalf(c.z) | ((uint32_t)floatToHalf(c.w) << 16);
+    out[pix] = make_uint2(lo, hi);
+}
+
+// running mean (rgb, n) <-> sum (rgb * n, n) for the multi-GPU reduce
+__global__ void k_mean_to_sum(const float4 *__restrict__ accum, float4 *__restrict__ sum, uint32_t pixels)
+{
+    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= pixels) return;
+    const float4 c = accum[pix];
+    sum[pix] = make_float4(c.x * c.w, c.y * c.w, c.z * c.w, c.w);
+}
+__global__ void k_sum_to_mean(const float4 *__restrict__ sum, float4 *__restrict__ accum, uint32_t pixels)
+{
+    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= pixels) return;
+    const float4 s = sum[pix];
+    const float inv = s.w > 0.f ? 1.f / s.w : 0.f;
+    accum[pix] = make_float4(s.x * inv, s.y * inv, s.z * inv, s.w);
+}
+
+// prt_trace_rays: caller-supplied rays
+template <bool SHADOW>
+__global__ void __launch_bounds__(RENDER_THREADS)
+    k_trace_user(Accel as, SceneView sv, const float4 *__restrict__ o, const float4 *__restrict__ d, const uint32_t *__restrict__ seeds,
+                 uint32_t n, prt_hit *__restrict__ out, GlobalCounters *gc)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    TraceCounters tc = {0, 0, 0, 0, 0};
+    if (i < n)
+    {
+        const float4 oo = o[i], dd = d[i];
+        HitRec hit;
+        traceRay<SHADOW, true>(as, sv, V3{oo.x, oo.y, oo.z}, V3{dd.x, dd.y, dd.z}, oo.w, dd.w, seeds ? seeds[i] : 0u, hit, &tc);
+        prt_hit h;
+        h.drawInstanceIndex = hit.drawInstanceIndex;
+        h.primitiveID = hit.primitiveID;
+        h.bary[0] = hit.u;
+        h.bary[1] = hit.v;
+        out[i] = h;
+    }
+    flushTraceCounters(gc, tc);
+}
+
+__global__ void k_hits_to_records(const uint4 *__restrict__ hits, prt_hit *__restrict__ out, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 h = hits[i];
+    prt_hit r;
+    r.drawInstanceIndex = h.x;
+    r.primitiveID = h.y;
+    r.bary[0] = __uint_as_float(h.z);
+    r.bary[1] = __uint_as_float(h.w);
+    out[i] = r;
+}
+
+} // namespace prt

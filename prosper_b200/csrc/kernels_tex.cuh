@@ -1,0 +1,46 @@
+// kernels_tex.cuh -- texture-side kernels: BC7 -> RGBA8 expansion (PRT_CFG_DECODE_BC7 upload path) and
+// a texel probe used by the tests to pin what the texture units return against the software decode.
+#pragma once
+#include <cuda_runtime.h>
+#include "core_bc7.h"
+#include "core_scene.h"
+
+namespace prt {
+
+// One thread per 4x4 block of a BC7 level -> RGBA8 texels in a pitched linear image.
+__global__ void k_bc7_decode(const uint2 *__restrict__ blocks64, uint32_t blocksX, uint32_t blocksY, uint32_t width, uint32_t height,
+                             uint32_t *__restrict__ rgba)
+{
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= blocksX * blocksY) return;
+    const uint64_t *src = reinterpret_cast<const uint64_t *>(blocks64) + 2ull * b;
+    uint32_t px[16];
+    bc7DecodeBlock(src[0], src[1], px);
+    const uint32_t bx = b % blocksX, by = b / blocksX;
+    for (uint32_t y = 0; y < 4; ++y)
+        for (uint32_t x = 0; x < 4; ++x)
+        {
+            const uint32_t tx = bx * 4 + x, ty = by * 4 + y;
+            if (tx < width && ty < height) rgba[(size_t)ty * width + tx] = px[y * 4 + x];
+        }
+}
+
+// out[i] = texel (x, y) of the slot's point view and the slot's filtered view at (u, v)
+__global__ void k_probe_texels(TexSlot slot, const int2 *__restrict__ xy, uint32_t n, float4 *__restrict__ out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const V4 t = fetchTexel(slot, xy[i].x, xy[i].y);
+    out[i] = make_float4(t.x, t.y, t.z, t.w);
+}
+
+__global__ void k_probe_sample(SceneView sv, uint32_t textureSampler, const float2 *__restrict__ uv, uint32_t n, int exact,
+                               float4 *__restrict__ out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const V4 t = sampleTexture(sv, textureSampler, V2{uv[i].x, uv[i].y}, exact != 0);
+    out[i] = make_float4(t.x, t.y, t.z, t.w);
+}
+
+} // namespace prt

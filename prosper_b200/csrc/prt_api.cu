@@ -1,0 +1,1085 @@
+// prt_api.cu -- libprt_b200.so: the C ABI of include/prt.h over the sm_100a kernels.
+//
+// Host side of the drop-in boundary for render::RtReference (src/render/RtReference.{hpp,cpp}) and
+// the acceleration-structure half of scene::World (src/scene/World.cpp:538-961). No Vulkan, no CPU
+// fallback: every entry point fails with PRT_ERR_NO_DEVICE / PRT_ERR_CUDA when the GPU is missing.
+#include "../../include/prt.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels_build.cuh"
+#include "kernels_render.cuh"
+#include "kernels_tex.cuh"
+
+using namespace prt;
+
+static thread_local std::string g_lastError;
+
+static prt_status fail(prt_status st, const std::string &msg)
+{
+    g_lastError = msg;
+    return st;
+}
+
+#define CK(call)                                                                                                        \
+    do                                                                                                                  \
+    {                                                                                                                   \
+        const cudaError_t e__ = (call);                                                                                 \
+        if (e__ != cudaSuccess)                                                                                         \
+            return fail(PRT_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__) + " (" __FILE__ ":" +         \
+                                          std::to_string(__LINE__) + ")");                                              \
+    } while (0)
+#define CKS(expr)                                                                                                       \
+    do                                                                                                                  \
+    {                                                                                                                   \
+        const prt_status s__ = (expr);                                                                                  \
+        if (s__ != PRT_OK) return s__;                                                                                  \
+    } while (0)
+#define REQUIRE(cond, msg)                                                                                              \
+    do                                                                                                                  \
+    {                                                                                                                   \
+        if (!(cond)) return fail(PRT_ERR_INVALID, std::string(msg) + " [" #cond "]");                                   \
+    } while (0)
+
+static inline uint32_t blocksFor(uint64_t n, uint32_t threads) { return (uint32_t)std::max<uint64_t>(1, (n + threads - 1) / threads); }
+
+// Grow-only device array
+template <class T> struct DBuf
+{
+    T *p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t n)
+    {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        const cudaError_t e = cudaMalloc((void **)&p, std::max<size_t>(n, 1) * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+// Pinned bump ring for the per-frame uploads: the CUDA form of gfx::RingBuffer
+// (src/gfx/RingBuffer.hpp:14-76; RingBuffer.cpp:56-133): 256-byte aligned writes, wraps to 0, and
+// instead of asserting on a stomp it waits for the copies of the previous lap to retire.
+struct UploadRing
+{
+    uint8_t *base = nullptr;
+    size_t capacity = 0, head = 0;
+    cudaEvent_t lap = nullptr;
+    static constexpr size_t kAlignment = 256; // RingBuffer.hpp:18 sAlignment
+
+    cudaError_t init(size_t bytes)
+    {
+        capacity = bytes;
+        cudaError_t e = cudaHostAlloc((void **)&base, bytes, cudaHostAllocDefault);
+        if (e != cudaSuccess) return e;
+        return cudaEventCreateWithFlags(&lap, cudaEventDisableTiming);
+    }
+    void destroy()
+    {
+        if (base) cudaFreeHost(base);
+        if (lap) cudaEventDestroy(lap);
+        base = nullptr;
+    }
+    // Copies `bytes` from src into the ring and enqueues ring -> dst on `stream`.
+    cudaError_t upload(void *dst, const void *src, size_t bytes, cudaStream_t stream)
+    {
+        if (bytes == 0) return cudaSuccess;
+        if (bytes > capacity / 2) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream); // staged by the driver
+        size_t start = (head + kAlignment - 1) / kAlignment * kAlignment;
+        if (start + bytes > capacity)
+        {
+            // wrap: everything enqueued from the previous lap must retire before its bytes are reused
+            cudaError_t e = cudaEventRecord(lap, stream);
+            if (e != cudaSuccess) return e;
+            e = cudaEventSynchronize(lap);
+            if (e != cudaSuccess) return e;
+            start = 0;
+        }
+        memcpy(base + start, src, bytes);
+        head = start + bytes;
+        return cudaMemcpyAsync(dst, base + start, bytes, cudaMemcpyHostToDevice, stream);
+    }
+};
+
+struct TexRes
+{
+    cudaArray_t array = nullptr; // level 0 (texture() in the RT stages reads LOD 0, materials.glsl:44)
+    uint32_t width = 0, height = 0, format = 0, mipLevels = 0;
+};
+
+struct BlasRes
+{
+    WideNode *nodes = nullptr;
+    TriRec *tris = nullptr;
+    uint32_t nodeCount = 0, triCount = 0;
+    bool built = false;
+};
+
+struct prt_ctx
+{
+    prt_config cfg{};
+    cudaStream_t stream = nullptr;
+    UploadRing ring;
+
+    // scene data (WorldData buffers)
+    std::vector<uint32_t *> geomBufs;
+    DBuf<const uint32_t *> geomTable;
+    std::vector<prt_geometry_metadata> hMeta;
+    std::vector<prt_mesh_info> hInfo;
+    DBuf<prt_geometry_metadata> dMeta;
+    std::vector<prt_material_data> hMat;
+    DBuf<prt_material_data> dMat;
+    std::vector<prt_sampler_desc> hSamplers;
+    std::vector<TexRes> textures;
+    std::vector<TexSlot> hSlots;
+    DBuf<TexSlot> dSlots;
+    bool slotsDirty = true;
+    DBuf<uint16_t> dSky;
+    uint32_t skyFace = 0;
+    std::vector<uint32_t> modelOffsets;
+    std::vector<prt_sub_model> subModels;
+    std::vector<BlasRes> blas;
+
+    // per-frame rings
+    DBuf<prt_draw_instance> dDraw;
+    DBuf<prt_model_instance_transforms> dXf;
+    DBuf<prt_directional_light> dDir;
+    DBuf<prt_point_light> dPoints;
+    DBuf<prt_spot_light> dSpots;
+    uint32_t pointCount = 0, spotCount = 0;
+    DBuf<prt_camera_uniforms> dCam;
+    bool haveCamera = false, haveLights = false;
+
+    // TLAS
+    DBuf<WideNode> tlasNodes;
+    DBuf<InstRec> tlasInst;
+    uint32_t tlasInstances = 0;
+    std::vector<TlasInput> hTlasInput;
+
+    // builder scratch
+    DBuf<TriRec> bTris;
+    DBuf<InstRec> bInst;
+    DBuf<TlasInput> bTlasIn;
+    DBuf<Box> bBoxes, bNodeBox;
+    DBuf<uint64_t> bKeys[2];
+    DBuf<uint32_t> bOrder[2], bHist, bFirst, bLast, bVisit, bPrimOut, bScalars;
+    DBuf<int32_t> bLeft, bRight, bParentI, bParentL;
+    DBuf<CollapseItem> bQueue[2];
+    DBuf<WideNode> bNodes;
+    DBuf<BuildBounds> bBounds;
+
+    // path state
+    PathBuffers pb{};
+    uint64_t pathCapacity = 0;
+    DBuf<float4> accum, sum;
+    DBuf<uint2> f16;
+    DBuf<prt_hit> userHits;
+    DBuf<float4> userO, userD;
+    DBuf<uint32_t> userSeeds;
+    uint32_t accumWidth = 0, accumHeight = 0;
+    bool historyValid = false;
+    GlobalCounters *dCounters = nullptr;
+    uint64_t kernelLaunches = 0;
+
+    // timing
+    cudaEvent_t evRecord[2]{}, evTlas[2]{}, evBlas[2]{}, evTrace[2 * PRT_MAX_BOUNCES]{};
+    bool recordTimed = false, tlasTimed = false, blasTimed = false;
+    uint32_t lastTraceLaunches = 0, lastRecordLaunches = 0, lastTlasLaunches = 0;
+    bool traceTimed = false;
+
+    SceneView view() const
+    {
+        SceneView sv{};
+        sv.geometryBuffers = geomTable.p;
+        sv.metadatas = dMeta.p;
+        sv.materials = dMat.p;
+        sv.drawInstances = dDraw.p;
+        sv.transforms = dXf.p;
+        sv.texSlots = dSlots.p;
+        sv.textureCount = (uint32_t)textures.size();
+        sv.samplerCount = (uint32_t)std::max<size_t>(hSamplers.size(), 1);
+        sv.directional = dDir.p;
+        sv.pointLights = dPoints.p;
+        sv.spotLights = dSpots.p;
+        sv.pointLightCount = pointCount;
+        sv.spotLightCount = spotCount;
+        sv.camera = dCam.p;
+        sv.sky = skyFace ? dSky.p : nullptr;
+        sv.skyFaceSize = skyFace;
+        sv.exactMaterialFilter = (cfg.flags & PRT_CFG_EXACT_FILTER) ? 1u : 0u;
+        return sv;
+    }
+    Accel accel() const
+    {
+        Accel a{};
+        a.tlasNodes = tlasInstances ? tlasNodes.p : nullptr;
+        a.instances = tlasInst.p;
+        return a;
+    }
+};
+
+extern "C" const char *prt_last_error(void) { return g_lastError.c_str(); }
+
+// ---- lifetime: RtReference::init / ~RtReference (RtRef.cpp:90-120) ------------------------------------
+static prt_status allocPathBuffers(prt_ctx *c, uint64_t paths)
+{
+    if (paths <= c->pathCapacity) return PRT_OK;
+    PathBuffers &pb = c->pb;
+    void **ptrs[] = {(void **)&pb.rng,      (void **)&pb.throughput, (void **)&pb.color,   (void **)&pb.rayO[0], (void **)&pb.rayO[1],
+                     (void **)&pb.rayD[0],  (void **)&pb.rayD[1],    (void **)&pb.rayId[0], (void **)&pb.rayId[1], (void **)&pb.hits,
+                     (void **)&pb.shadowO,  (void **)&pb.shadowD,    (void **)&pb.shadowId, (void **)&pb.shadowC};
+    const size_t elem[] = {16, 16, 16, 16, 16, 16, 16, 8, 8, 16, 16, 16, 8, 16};
+    for (size_t i = 0; i < sizeof(elem) / sizeof(elem[0]); ++i)
+    {
+        if (*ptrs[i]) CK(cudaFree(*ptrs[i]));
+        *ptrs[i] = nullptr;
+        CK(cudaMalloc(ptrs[i], paths * elem[i]));
+    }
+    if (!pb.counts)
+    {
+        CK(cudaMalloc((void **)&pb.counts, 16 * sizeof(uint32_t)));
+        CK(cudaMemset(pb.counts, 0, 16 * sizeof(uint32_t)));
+    }
+    c->pathCapacity = paths;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_create(const prt_config *cfg, prt_ctx **out)
+{
+    if (!cfg || !out) return fail(PRT_ERR_INVALID, "prt_create: null argument");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+        return fail(PRT_ERR_NO_DEVICE, "prt_create: no CUDA device (this library has no CPU fallback)");
+    if (cfg->device < 0 || cfg->device >= count) return fail(PRT_ERR_NO_DEVICE, "prt_create: device ordinal out of range");
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major < 10) return fail(PRT_ERR_NO_DEVICE, std::string("prt_create: ") + prop.name + " is not an sm_100 device");
+    CK(cudaSetDevice(cfg->device));
+    prt_ctx *c = new prt_ctx;
+    c->cfg = *cfg;
+    if (c->cfg.samplesPerLaunch == 0) c->cfg.samplesPerLaunch = 1;
+    *out = c;
+    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CK(c->ring.init(32u << 20));
+    CK(cudaMalloc((void **)&c->dCounters, sizeof(GlobalCounters)));
+    CK(cudaMemset(c->dCounters, 0, sizeof(GlobalCounters)));
+    for (int i = 0; i < 2; ++i)
+    {
+        CK(cudaEventCreate(&c->evRecord[i]));
+        CK(cudaEventCreate(&c->evTlas[i]));
+        CK(cudaEventCreate(&c->evBlas[i]));
+    }
+    for (uint32_t i = 0; i < 2 * PRT_MAX_BOUNCES; ++i) CK(cudaEventCreate(&c->evTrace[i]));
+    CK(c->dDir.ensure(1));
+    CK(c->dCam.ensure(1));
+    CK(c->dPoints.ensure(PRT_MAX_POINT_LIGHTS));
+    CK(c->dSpots.ensure(PRT_MAX_SPOT_LIGHTS));
+    CK(c->bBounds.ensure(1));
+    CK(c->bScalars.ensure(256));
+    const uint64_t pixels = (uint64_t)cfg->maxWidth * cfg->maxHeight;
+    if (pixels)
+    {
+        CKS(allocPathBuffers(c, pixels * c->cfg.samplesPerLaunch));
+        CK(c->accum.ensure(pixels));
+        CK(cudaMemsetAsync(c->accum.p, 0, pixels * sizeof(float4), c->stream));
+    }
+    // the local-memory traversal stacks want L1 rather than shared memory
+    cudaFuncSetAttribute(k_trace_closest<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
+    cudaFuncSetAttribute(k_trace_shadow<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
+    CK(cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+extern "C" void prt_destroy(prt_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->cfg.device);
+    cudaDeviceSynchronize();
+    for (uint32_t *b : c->geomBufs)
+        if (b) cudaFree(b);
+    for (TexSlot &s : c->hSlots)
+    {
+        if (s.texels) cudaDestroyTextureObject(s.texels);
+        if (s.linear) cudaDestroyTextureObject(s.linear);
+    }
+    for (TexRes &t : c->textures)
+        if (t.array) cudaFreeArray(t.array);
+    for (BlasRes &b : c->blas)
+    {
+        if (b.nodes) cudaFree(b.nodes);
+        if (b.tris) cudaFree(b.tris);
+    }
+    PathBuffers &pb = c->pb;
+    void *ptrs[] = {pb.rng,      pb.throughput, pb.color,   pb.rayO[0], pb.rayO[1], pb.rayD[0],  pb.rayD[1], pb.rayId[0],
+                    pb.rayId[1], pb.hits,       pb.shadowO, pb.shadowD, pb.shadowId, pb.shadowC, pb.counts,  c->dCounters};
+    for (void *p : ptrs)
+        if (p) cudaFree(p);
+    c->geomTable.release(); c->dMeta.release(); c->dMat.release(); c->dSlots.release(); c->dSky.release();
+    c->dDraw.release(); c->dXf.release(); c->dDir.release(); c->dPoints.release(); c->dSpots.release(); c->dCam.release();
+    c->tlasNodes.release(); c->tlasInst.release();
+    c->bTris.release(); c->bInst.release(); c->bTlasIn.release(); c->bBoxes.release(); c->bNodeBox.release();
+    for (int i = 0; i < 2; ++i) { c->bKeys[i].release(); c->bOrder[i].release(); c->bQueue[i].release(); }
+    c->bHist.release(); c->bFirst.release(); c->bLast.release(); c->bVisit.release(); c->bPrimOut.release(); c->bScalars.release();
+    c->bLeft.release(); c->bRight.release(); c->bParentI.release(); c->bParentL.release(); c->bNodes.release(); c->bBounds.release();
+    c->accum.release(); c->sum.release(); c->f16.release(); c->userHits.release(); c->userO.release(); c->userD.release();
+    c->userSeeds.release();
+    for (int i = 0; i < 2; ++i)
+    {
+        if (c->evRecord[i]) cudaEventDestroy(c->evRecord[i]);
+        if (c->evTlas[i]) cudaEventDestroy(c->evTlas[i]);
+        if (c->evBlas[i]) cudaEventDestroy(c->evBlas[i]);
+    }
+    for (uint32_t i = 0; i < 2 * PRT_MAX_BOUNCES; ++i)
+        if (c->evTrace[i]) cudaEventDestroy(c->evTrace[i]);
+    c->ring.destroy();
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" void *prt_stream(prt_ctx *c) { return c ? (void *)c->stream : nullptr; }
+
+extern "C" prt_status prt_synchronize(prt_ctx *c)
+{
+    REQUIRE(c, "prt_synchronize");
+    CK(cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+// ---- scene data ------------------------------------------------------------------------------------------
+extern "C" prt_status prt_set_geometry_buffer(prt_ctx *c, uint32_t index, const void *data, uint64_t bytes)
+{
+    REQUIRE(c && data, "prt_set_geometry_buffer");
+    REQUIRE(bytes % 4 == 0, "geometry buffers are u32 arrays (WorldData.cpp:1271-1320)");
+    REQUIRE(index < 100, "at most 100 geometry buffers (WorldData.cpp:31)");
+    CK(cudaSetDevice(c->cfg.device));
+    if (c->geomBufs.size() <= index) c->geomBufs.resize(index + 1, nullptr);
+    if (c->geomBufs[index]) CK(cudaFree(c->geomBufs[index]));
+    c->geomBufs[index] = nullptr;
+    // 16 bytes of slack: loadIndex() on a short-index mesh may read the padding half-word
+    CK(cudaMalloc((void **)&c->geomBufs[index], bytes + 16));
+    CK(cudaMemcpyAsync(c->geomBufs[index], data, bytes, cudaMemcpyHostToDevice, c->stream));
+    CK(c->geomTable.ensure(100));
+    std::vector<const uint32_t *> table(100, nullptr);
+    for (size_t i = 0; i < c->geomBufs.size(); ++i) table[i] = c->geomBufs[i];
+    CK(cudaMemcpyAsync(c->geomTable.p, table.data(), 100 * sizeof(uint32_t *), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream)); // `table` and `data` may go away after return
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_set_meshes(prt_ctx *c, const prt_geometry_metadata *metadatas, const prt_mesh_info *infos, uint32_t count)
+{
+    REQUIRE(c && (count == 0 || (metadatas && infos)), "prt_set_meshes");
+    CK(cudaSetDevice(c->cfg.device));
+    c->hMeta.assign(metadatas, metadatas + count);
+    c->hInfo.assign(infos, infos + count);
+    CK(c->dMeta.ensure(count));
+    CK(c->ring.upload(c->dMeta.p, metadatas, count * sizeof(prt_geometry_metadata), c->stream));
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_set_materials(prt_ctx *c, const prt_material_data *materials, uint32_t count)
+{
+    REQUIRE(c && (count == 0 || materials), "prt_set_materials");
+    CK(cudaSetDevice(c->cfg.device));
+    c->hMat.assign(materials, materials + count);
+    CK(c->dMat.ensure(count));
+    CK(c->ring.upload(c->dMat.p, materials, count * sizeof(prt_material_data), c->stream));
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_set_samplers(prt_ctx *c, const prt_sampler_desc *samplers, uint32_t count)
+{
+    REQUIRE(c && (count == 0 || samplers), "prt_set_samplers");
+    REQUIRE(count <= 256, "sampler index is 8 bits (material_data.h:19-36)");
+    c->hSamplers.assign(samplers, samplers + count);
+    c->slotsDirty = true;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_set_texture(prt_ctx *c, uint32_t index, const prt_texture_desc *desc)
+{
+    REQUIRE(c && desc && desc->data, "prt_set_texture");
+    REQUIRE(index >= 1 && index < (1u << 24), "texture index 0 is the reserved 'no texture' slot (WorldData.cpp:727-741)");
+    REQUIRE(desc->width > 0 && desc->height > 0, "empty texture");
+    CK(cudaSetDevice(c->cfg.device));
+    if (c->textures.size() <= index) c->textures.resize(index + 1);
+    TexRes &t = c->textures[index];
+    if (t.array)
+    {
+        CK(cudaStreamSynchronize(c->stream));
+        CK(cudaFreeArray(t.array));
+        t.array = nullptr;
+    }
+    t.width = desc->width; t.height = desc->height; t.format = desc->format; t.mipLevels = desc->mipLevels;
+    const uint32_t bx = (desc->width + 3) / 4, by = (desc->height + 3) / 4;
+    if (desc->format == PRT_TEX_BC7_UNORM && !(c->cfg.flags & PRT_CFG_DECODE_BC7))
+    {
+        REQUIRE(desc->dataBytes >= (uint64_t)bx * by * 16, "BC7 payload shorter than level 0");
+        // stored UNORM, linearised in the shader after filtering (Texture.cpp:429-432)
+        const cudaChannelFormatDesc cd = cudaCreateChannelDesc<cudaChannelFormatKindUnsignedBlockCompressed7>();
+        CK(cudaMallocArray(&t.array, &cd, desc->width, desc->height));
+        CK(cudaMemcpy2DToArrayAsync(t.array, 0, 0, desc->data, (size_t)bx * 16, (size_t)bx * 16, by, cudaMemcpyHostToDevice, c->stream));
+    }
+    else
+    {
+        const cudaChannelFormatDesc cd = cudaCreateChannelDesc<uchar4>();
+        CK(cudaMallocArray(&t.array, &cd, desc->width, desc->height));
+        if (desc->format == PRT_TEX_BC7_UNORM)
+        {
+            REQUIRE(desc->dataBytes >= (uint64_t)bx * by * 16, "BC7 payload shorter than level 0");
+            DBuf<uint2> blocks;
+            DBuf<uint32_t> rgba;
+            CK(blocks.ensure((size_t)bx * by * 2));
+            CK(rgba.ensure((size_t)desc->width * desc->height));
+            CK(cudaMemcpyAsync(blocks.p, desc->data, (size_t)bx * by * 16, cudaMemcpyHostToDevice, c->stream));
+            k_bc7_decode<<<blocksFor((uint64_t)bx * by, 128), 128, 0, c->stream>>>(blocks.p, bx, by, desc->width, desc->height, rgba.p);
+            CK(cudaGetLastError());
+            CK(cudaMemcpy2DToArrayAsync(t.array, 0, 0, rgba.p, (size_t)desc->width * 4, (size_t)desc->width * 4, desc->height,
+                                        cudaMemcpyDeviceToDevice, c->stream));
+            CK(cudaStreamSynchronize(c->stream));
+            blocks.release();
+            rgba.release();
+        }
+        else
+        {
+            REQUIRE(desc->format == PRT_TEX_RGBA8_UNORM, "unknown texture format");
+            REQUIRE(desc->dataBytes >= (uint64_t)desc->width * desc->height * 4, "RGBA8 payload shorter than level 0");
+            CK(cudaMemcpy2DToArrayAsync(t.array, 0, 0, desc->data, (size_t)desc->width * 4, (size_t)desc->width * 4, desc->height,
+                                        cudaMemcpyHostToDevice, c->stream));
+        }
+    }
+    CK(cudaStreamSynchronize(c->stream)); // desc->data may go away after return
+    c->slotsDirty = true;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_set_sky_cubemap(prt_ctx *c, uint32_t faceSize, const void *rgba16f)
+{
+    REQUIRE(c, "prt_set_sky_cubemap");
+    CK(cudaSetDevice(c->cfg.device));
+    if (faceSize == 0 || rgba16f == nullptr)
+    {
+        c->skyFace = 0;
+        return PRT_OK;
+    }
+    const size_t n = (size_t)6 * faceSize * faceSize * 4;
+    CK(c->dSky.ensure(n));
+    CK(cudaMemcpyAsync(c->dSky.p, rgba16f, n * 2, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->skyFace = faceSize;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_set_models(prt_ctx *c, const uint32_t *offsets, const prt_sub_model *subModels, uint32_t modelCount)
+{
+    REQUIRE(c && offsets, "prt_set_models");
+    c->modelOffsets.assign(offsets, offsets + modelCount + 1);
+    const uint32_t n = offsets[modelCount];
+    REQUIRE(n == 0 || subModels, "prt_set_models: sub-models missing");
+    c->subModels.assign(subModels, subModels + n);
+    if (c->blas.size() < modelCount) c->blas.resize(modelCount);
+    return PRT_OK;
+}
+
+// (texture, sampler) -> CUDA texture objects; rebuilt lazily when textures or samplers changed
+static prt_status refreshTextureSlots(prt_ctx *c)
+{
+    if (!c->slotsDirty) return PRT_OK;
+    CK(cudaStreamSynchronize(c->stream));
+    for (TexSlot &s : c->hSlots)
+    {
+        if (s.texels) cudaDestroyTextureObject(s.texels);
+        if (s.linear) cudaDestroyTextureObject(s.linear);
+    }
+    std::vector<prt_sampler_desc> samplers = c->hSamplers;
+    if (samplers.empty()) samplers.push_back(prt_sampler_desc{PRT_FILTER_LINEAR, PRT_FILTER_LINEAR, PRT_ADDRESS_REPEAT, PRT_ADDRESS_REPEAT});
+    const size_t ns = samplers.size(), nt = c->textures.size();
+    c->hSlots.assign(nt * ns, TexSlot{});
+    auto addr = [](uint32_t m) {
+        return m == PRT_ADDRESS_REPEAT ? cudaAddressModeWrap : (m == PRT_ADDRESS_MIRRORED_REPEAT ? cudaAddressModeMirror : cudaAddressModeClamp);
+    };
+    for (size_t t = 0; t < nt; ++t)
+    {
+        const TexRes &tr = c->textures[t];
+        if (!tr.array) continue;
+        for (size_t s = 0; s < ns; ++s)
+        {
+            TexSlot &slot = c->hSlots[t * ns + s];
+            cudaResourceDesc rd{};
+            rd.resType = cudaResourceTypeArray;
+            rd.res.array.array = tr.array;
+            cudaTextureDesc td{};
+            td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+            td.filterMode = cudaFilterModePoint;
+            td.readMode = cudaReadModeNormalizedFloat;
+            td.normalizedCoords = 0;
+            CK(cudaCreateTextureObject(&slot.texels, &rd, &td, nullptr));
+            td.addressMode[0] = addr(samplers[s].addressU);
+            td.addressMode[1] = addr(samplers[s].addressV);
+            td.filterMode = samplers[s].magFilter == PRT_FILTER_NEAREST ? cudaFilterModePoint : cudaFilterModeLinear;
+            td.normalizedCoords = 1;
+            CK(cudaCreateTextureObject(&slot.linear, &rd, &td, nullptr));
+            slot.width = tr.width; slot.height = tr.height;
+            slot.magFilter = samplers[s].magFilter;
+            slot.addressU = samplers[s].addressU; slot.addressV = samplers[s].addressV;
+            slot.valid = 1;
+        }
+    }
+    CK(c->dSlots.ensure(std::max<size_t>(c->hSlots.size(), 1)));
+    if (!c->hSlots.empty())
+        CK(cudaMemcpyAsync(c->dSlots.p, c->hSlots.data(), c->hSlots.size() * sizeof(TexSlot), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->slotsDirty = false;
+    return PRT_OK;
+}
+
+// ---- acceleration structures -------------------------------------------------------------------------------
+// Shared back half of the BLAS and TLAS builds: boxes + bounds are in bBoxes/bBounds; produces the
+// wide nodes in bNodes and the node-order primitive permutation in bPrimOut.
+// bScalars layout: [0] nodeCount, [1] primCount, [8 .. 8 + MAX_LEVELS] per-level queue counts.
+static constexpr uint32_t kMaxLevels = 128;
+
+static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *launches)
+{
+    cudaStream_t st = c->stream;
+    for (int i = 0; i < 2; ++i)
+    {
+        CK(c->bKeys[i].ensure(n));
+        CK(c->bOrder[i].ensure(n));
+        CK(c->bQueue[i].ensure(n + 1));
+    }
+    const uint32_t sortBlocks = (n + SORT_TILE - 1) / SORT_TILE;
+    CK(c->bHist.ensure(256u * sortBlocks));
+    CK(c->bLeft.ensure(n)); CK(c->bRight.ensure(n)); CK(c->bFirst.ensure(n)); CK(c->bLast.ensure(n));
+    CK(c->bParentI.ensure(n)); CK(c->bParentL.ensure(n)); CK(c->bVisit.ensure(n)); CK(c->bNodeBox.ensure(n));
+    CK(c->bPrimOut.ensure(n)); CK(c->bNodes.ensure(n));
+
+    // TLAS keys keep the top 31 Morton bits (4 sort passes); BLAS keys all 63 (8 passes)
+    const uint64_t keyMask = tlas ? 0xFFFFFFFF00000000ull : ~0ull;
+    k_pad_and_keys<<<blocksFor(n, 256), 256, 0, st>>>(c->bBoxes.p, n, c->bBounds.p, tlas ? 0 : 1, keyMask, c->bKeys[0].p, c->bOrder[0].p);
+    *launches += 1;
+    const bool flipped = radixSortPairs(c->bKeys[0].p, c->bOrder[0].p, c->bKeys[1].p, c->bOrder[1].p, n, tlas ? 32 : 0, c->bHist.p, st, launches);
+    CK(cudaGetLastError());
+
+    Lbvh t{};
+    t.count = n;
+    t.keys = flipped ? c->bKeys[1].p : c->bKeys[0].p;
+    t.order = flipped ? c->bOrder[1].p : c->bOrder[0].p;
+    t.primBox = c->bBoxes.p;
+    t.left = c->bLeft.p; t.right = c->bRight.p; t.first = c->bFirst.p; t.last = c->bLast.p;
+    t.parentOfInternal = c->bParentI.p; t.parentOfLeaf = c->bParentL.p;
+    t.nodeBox = c->bNodeBox.p; t.visit = c->bVisit.p;
+    if (n > 1)
+    {
+        k_lbvh_nodes<<<blocksFor(n - 1, 256), 256, 0, st>>>(t);
+        k_lbvh_refit<<<blocksFor(n, 256), 256, 0, st>>>(t);
+        *launches += 2;
+    }
+    uint32_t *scal = c->bScalars.p;
+    k_collapse_seed<<<1, 128, 0, st>>>(c->bQueue[0].p, scal + 8, kMaxLevels + 1, scal + 0, scal + 1, n);
+    *launches += 1;
+    Collapse col{};
+    col.t = t;
+    col.maxLeaf = tlas ? 1u : 3u;
+    col.nodes = c->bNodes.p;
+    col.primOut = c->bPrimOut.p;
+    col.nodeCount = scal + 0;
+    col.primCount = scal + 1;
+    if (tlas && n <= 65536u)
+    {
+        k_collapse_all_levels<<<1, 1024, 0, st>>>(col, c->bQueue[0].p, c->bQueue[1].p, scal + 8, kMaxLevels);
+        *launches += 1;
+    }
+    else
+    {
+        for (uint32_t level = 0; level < kMaxLevels; ++level)
+        {
+            col.queueIn = c->bQueue[level & 1].p;
+            col.queueOut = c->bQueue[(level + 1) & 1].p;
+            col.queueOutCount = scal + 8 + level + 1;
+            k_collapse_level<<<blocksFor(n, 128), 128, 0, st>>>(col, scal + 8 + level);
+            *launches += 1;
+            if ((level & 7u) == 7u)
+            {
+                uint32_t next = 0;
+                CK(cudaMemcpyAsync(&next, scal + 8 + level + 1, 4, cudaMemcpyDeviceToHost, st));
+                CK(cudaStreamSynchronize(st));
+                if (next == 0) break;
+                REQUIRE(level + 1 < kMaxLevels, "BVH deeper than the collapse level budget");
+            }
+        }
+    }
+    CK(cudaGetLastError());
+    return PRT_OK;
+}
+
+// World::Impl::buildNextBlas (World.cpp:585-747): one BLAS per model, one geometry per sub-model,
+// OPAQUE flag from the mesh's material alpha mode (World.cpp:646-651).
+extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *outReference)
+{
+    REQUIRE(c, "prt_build_blas");
+    REQUIRE(modelIndex + 1 < c->modelOffsets.size(), "prt_build_blas: model index out of range (call prt_set_models first)");
+    CK(cudaSetDevice(c->cfg.device));
+    cudaStream_t st = c->stream;
+    BlasRes &b = c->blas[modelIndex];
+    if (b.nodes || b.tris)
+    {
+        CK(cudaStreamSynchronize(st));
+        if (b.nodes) CK(cudaFree(b.nodes));
+        if (b.tris) CK(cudaFree(b.tris));
+        b = BlasRes{};
+    }
+    uint64_t total = 0;
+    for (uint32_t g = c->modelOffsets[modelIndex]; g < c->modelOffsets[modelIndex + 1]; ++g)
+    {
+        const prt_sub_model &sm = c->subModels[g];
+        REQUIRE(sm.meshIndex < c->hInfo.size(), "sub-model mesh index out of range");
+        total += c->hInfo[sm.meshIndex].indexCount / 3;
+    }
+    REQUIRE(total < (1ull << 31), "model too large");
+    if (outReference) *outReference = (uint64_t)modelIndex + 1;
+    b.built = true;
+    if (total == 0) return PRT_OK;
+    const uint32_t n = (uint32_t)total;
+    CK(cudaEventRecord(c->evBlas[0], st));
+    uint32_t launches = 0;
+    CK(c->bTris.ensure(n));
+    CK(c->bBoxes.ensure(n));
+    k_init_bounds<<<1, 32, 0, st>>>(c->bBounds.p, c->bScalars.p, 8);
+    const SceneView sv = c->view();
+    uint32_t offset = 0;
+    for (uint32_t g = c->modelOffsets[modelIndex]; g < c->modelOffsets[modelIndex + 1]; ++g)
+    {
+        const prt_sub_model &sm = c->subModels[g];
+        const prt_mesh_info &info = c->hInfo[sm.meshIndex];
+        const uint32_t prims = info.indexCount / 3;
+        if (prims == 0) continue;
+        REQUIRE(info.materialIndex < c->hMat.size(), "mesh material index out of range");
+        const uint32_t opaque = c->hMat[info.materialIndex].alphaMode == PRT_ALPHA_OPAQUE ? 1u : 0u;
+        k_blas_gather<<<blocksFor(prims, 128), 128, 0, st>>>(sv, sm.meshIndex, prims, g - c->modelOffsets[modelIndex], opaque, offset,
+                                                             c->bTris.p, c->bBoxes.p, c->bBounds.p);
+        launches++;
+        offset += prims;
+    }
+    CK(cudaGetLastError());
+    CKS(buildHierarchy(c, n, false, &launches));
+    uint32_t counts[2] = {0, 0};
+    CK(cudaMemcpyAsync(counts, c->bScalars.p, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    REQUIRE(counts[1] == n, "collapse lost primitives");
+    b.nodeCount = counts[0];
+    b.triCount = n;
+    CK(cudaMalloc((void **)&b.nodes, (size_t)b.nodeCount * sizeof(WideNode)));
+    CK(cudaMalloc((void **)&b.tris, (size_t)n * sizeof(TriRec)));
+    CK(cudaMemcpyAsync(b.nodes, c->bNodes.p, (size_t)b.nodeCount * sizeof(WideNode), cudaMemcpyDeviceToDevice, st));
+    k_emit_tris<<<blocksFor(n, 256), 256, 0, st>>>(c->bPrimOut.p, n, c->bTris.p, b.tris);
+    launches++;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(c->evBlas[1], st));
+    c->blasTimed = true;
+    c->kernelLaunches += launches;
+    return PRT_OK;
+}
+
+// updateTlasInstances + buildCurrentTlas (World.cpp:878-928, 749-802): full rebuild, every frame.
+extern "C" prt_status prt_build_tlas(prt_ctx *c, const prt_tlas_instance *instances, uint32_t count)
+{
+    REQUIRE(c && (count == 0 || instances), "prt_build_tlas");
+    if (c->cfg.maxInstances) REQUIRE(count <= c->cfg.maxInstances, "more instances than prt_config.maxInstances");
+    CK(cudaSetDevice(c->cfg.device));
+    cudaStream_t st = c->stream;
+    std::vector<TlasInput> &in = c->hTlasInput;
+    in.clear();
+    for (uint32_t i = 0; i < count; ++i)
+    {
+        const prt_tlas_instance &ti = instances[i];
+        if (ti.blasReference == 0) continue; // inactive instance, World.cpp:898-905
+        const uint64_t model = ti.blasReference - 1;
+        REQUIRE(model < c->blas.size() && c->blas[model].built, "instance references a BLAS that was not built");
+        const BlasRes &b = c->blas[model];
+        if (b.triCount == 0) continue;
+        TlasInput t;
+        memcpy(t.transform, ti.transform, sizeof(t.transform));
+        t.customIndexAndMask = ti.customIndexAndMask;
+        t.index = i;
+        t.nodes = b.nodes;
+        t.tris = b.tris;
+        in.push_back(t);
+    }
+    const uint32_t n = (uint32_t)in.size();
+    CK(cudaEventRecord(c->evTlas[0], st));
+    uint32_t launches = 0;
+    c->tlasInstances = n;
+    if (n)
+    {
+        CK(c->bTlasIn.ensure(n));
+        CK(c->bInst.ensure(n));
+        CK(c->bBoxes.ensure(n));
+        CK(c->tlasNodes.ensure(n));
+        CK(c->tlasInst.ensure(n));
+        CK(c->ring.upload(c->bTlasIn.p, in.data(), (size_t)n * sizeof(TlasInput), st));
+        k_init_bounds<<<1, 32, 0, st>>>(c->bBounds.p, c->bScalars.p, 8);
+        k_tlas_instances<<<blocksFor(n, 128), 128, 0, st>>>(c->bTlasIn.p, n, c->bInst.p, c->bBoxes.p, c->bBounds.p);
+        launches += 2;
+        CKS(buildHierarchy(c, n, true, &launches));
+        // wide nodes <= n: copy the upper bound, the tail is never referenced
+        CK(cudaMemcpyAsync(c->tlasNodes.p, c->bNodes.p, (size_t)n * sizeof(WideNode), cudaMemcpyDeviceToDevice, st));
+        k_emit_instances<<<blocksFor(n, 128), 128, 0, st>>>(c->bPrimOut.p, n, c->bInst.p, c->tlasInst.p);
+        launches += 1;
+        CK(cudaGetLastError());
+    }
+    CK(cudaEventRecord(c->evTlas[1], st));
+    c->tlasTimed = true;
+    c->lastTlasLaunches = launches;
+    c->kernelLaunches += launches;
+    return PRT_OK;
+}
+
+// ---- per-frame rings: World::updateBuffers (World.cpp:468-536), Camera::updateBuffer --------------------------
+extern "C" prt_status prt_set_draw_instances(prt_ctx *c, const prt_draw_instance *instances, uint32_t count)
+{
+    REQUIRE(c && (count == 0 || instances), "prt_set_draw_instances");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(c->dDraw.ensure(count));
+    CK(c->ring.upload(c->dDraw.p, instances, (size_t)count * sizeof(prt_draw_instance), c->stream));
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_set_instance_transforms(prt_ctx *c, const prt_model_instance_transforms *t, uint32_t count)
+{
+    REQUIRE(c && (count == 0 || t), "prt_set_instance_transforms");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(c->dXf.ensure(count));
+    CK(c->ring.upload(c->dXf.p, t, (size_t)count * sizeof(prt_model_instance_transforms), c->stream));
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_set_lights(prt_ctx *c, const prt_directional_light *directional, const prt_point_light *points,
+                                     uint32_t pointCount, const prt_spot_light *spots, uint32_t spotCount)
+{
+    REQUIRE(c && directional, "prt_set_lights");
+    REQUIRE(pointCount <= PRT_MAX_POINT_LIGHTS && spotCount <= PRT_MAX_SPOT_LIGHTS, "light maxima (RtRef.cpp:429-430)");
+    REQUIRE((pointCount == 0 || points) && (spotCount == 0 || spots), "prt_set_lights: null array");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(c->ring.upload(c->dDir.p, directional, sizeof(prt_directional_light), c->stream));
+    CK(c->ring.upload(c->dPoints.p, points, (size_t)pointCount * sizeof(prt_point_light), c->stream));
+    CK(c->ring.upload(c->dSpots.p, spots, (size_t)spotCount * sizeof(prt_spot_light), c->stream));
+    c->pointCount = pointCount;
+    c->spotCount = spotCount;
+    c->haveLights = true;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_set_camera(prt_ctx *c, const prt_camera_uniforms *camera)
+{
+    REQUIRE(c && camera, "prt_set_camera");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(c->ring.upload(c->dCam.p, camera, sizeof(prt_camera_uniforms), c->stream));
+    c->haveCamera = true;
+    return PRT_OK;
+}
+
+// ---- the pass: RtReference::record (RtRef.cpp:161-383) ------------------------------------------------------------
+static prt_status checkRenderState(prt_ctx *c, const prt_reference_pc *pc, uint32_t width, uint32_t height)
+{
+    REQUIRE(pc, "null push constants");
+    REQUIRE(width > 0 && height > 0, "empty render area");
+    REQUIRE(c->haveCamera, "prt_set_camera has not been called");
+    REQUIRE(c->haveLights, "prt_set_lights has not been called");
+    REQUIRE(pc->maxBounces <= PRT_MAX_BOUNCES, "maxBounces above sMaxBounces (RtRef.hpp:22)");
+    REQUIRE(pc->drawType < PRT_DRAW_COUNT, "unknown draw type");
+    CKS(refreshTextureSlots(c));
+    return PRT_OK;
+}
+
+// Enqueues `samples` frames starting at pc.frameIndex as one wavefront batch.
+static prt_status renderBatch(prt_ctx *c, prt_reference_pc pc, uint32_t width, uint32_t height, uint32_t samples, bool accumulate,
+                              bool timeTrace)
+{
+    cudaStream_t st = c->stream;
+    const uint64_t total = (uint64_t)width * height * samples;
+    CKS(allocPathBuffers(c, total));
+    const SceneView sv = c->view();
+    const Accel as = c->accel();
+    const bool count = (c->cfg.flags & PRT_CFG_COUNTERS) != 0;
+    const uint32_t grid = blocksFor(total, RENDER_THREADS);
+    uint32_t launches = 0;
+    k_raygen<<<grid, RENDER_THREADS, 0, st>>>(sv, pc, width, height, samples, c->pb);
+    launches++;
+    const uint32_t bounces = std::min<uint32_t>(pc.maxBounces, PRT_MAX_BOUNCES);
+    const bool debugView = pc.drawType != PRT_DRAW_DEFAULT && pc.drawType != PRT_DRAW_MESHLET_ID;
+    for (uint32_t b = 0; b < bounces; ++b)
+    {
+        const int q = (int)(b & 1u);
+        if (timeTrace) CK(cudaEventRecord(c->evTrace[2 * b], st));
+        if (count) k_trace_closest<true><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters);
+        else k_trace_closest<false><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters);
+        if (timeTrace) CK(cudaEventRecord(c->evTrace[2 * b + 1], st));
+        k_shade<<<grid, RENDER_THREADS, 0, st>>>(sv, pc, c->pb, q, b, c->dCounters, count ? 1 : 0);
+        launches += 2;
+        if (debugView) break; // main.rgen:259-264: debug views stop at the first hit
+        if (count) k_trace_shadow<true><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters);
+        else k_trace_shadow<false><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters);
+        launches++;
+    }
+    if (timeTrace)
+    {
+        c->lastTraceLaunches = debugView ? std::min(bounces, 1u) : bounces;
+        c->traceTimed = true;
+    }
+    k_tally<<<1, 32, 0, st>>>(c->pb, c->dCounters, (uint32_t)total);
+    launches++;
+    if (accumulate)
+    {
+        k_accumulate<<<blocksFor((uint64_t)width * height, 256), 256, 0, st>>>(c->pb, c->accum.p, width * height, samples, pc.flags);
+        launches++;
+    }
+    CK(cudaGetLastError());
+    c->lastRecordLaunches += launches;
+    c->kernelLaunches += launches;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_record(prt_ctx *c, const prt_reference_pc *pcIn, uint32_t width, uint32_t height, uint32_t sampleCount)
+{
+    REQUIRE(c, "prt_record");
+    CK(cudaSetDevice(c->cfg.device));
+    CKS(checkRenderState(c, pcIn, width, height));
+    REQUIRE(sampleCount > 0, "sampleCount must be positive");
+    const uint64_t pixels = (uint64_t)width * height;
+    if (c->cfg.maxWidth && c->cfg.maxHeight) REQUIRE(pixels <= (uint64_t)c->cfg.maxWidth * c->cfg.maxHeight, "render area larger than prt_config");
+    prt_reference_pc pc = *pcIn;
+    // history is recreated on resize (RtRef.cpp:178-219): the first frame then ignores it
+    if (c->accumWidth != width || c->accumHeight != height || !c->historyValid)
+    {
+        CK(c->accum.ensure(pixels));
+        pc.flags |= PRT_FLAG_SKIP_HISTORY;
+        c->accumWidth = width;
+        c->accumHeight = height;
+    }
+    CK(cudaEventRecord(c->evRecord[0], c->stream));
+    c->lastRecordLaunches = 0;
+    const uint32_t perLaunch = std::max(1u, c->cfg.samplesPerLaunch);
+    uint32_t done = 0;
+    while (done < sampleCount)
+    {
+        const uint32_t k = std::min(perLaunch, sampleCount - done);
+        prt_reference_pc bpc = pc;
+        bpc.frameIndex = (pc.frameIndex + done) % PRT_FRAME_PERIOD; // RtRef.cpp:170
+        if (done > 0) bpc.flags &= ~(uint32_t)PRT_FLAG_SKIP_HISTORY;
+        CKS(renderBatch(c, bpc, width, height, k, true, done == 0));
+        done += k;
+    }
+    CK(cudaEventRecord(c->evRecord[1], c->stream));
+    c->recordTimed = true;
+    c->historyValid = true;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_output_f32_device(prt_ctx *c, const float **out)
+{
+    REQUIRE(c && out, "prt_output_f32_device");
+    REQUIRE(c->historyValid, "nothing recorded yet");
+    *out = reinterpret_cast<const float *>(c->accum.p);
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_read_output_f32(prt_ctx *c, float *dstHost, uint64_t dstBytes)
+{
+    REQUIRE(c && dstHost, "prt_read_output_f32");
+    REQUIRE(c->historyValid, "nothing recorded yet");
+    const uint64_t bytes = (uint64_t)c->accumWidth * c->accumHeight * 16;
+    REQUIRE(dstBytes >= bytes, "destination too small");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(dstHost, c->accum.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_read_illumination_f16(prt_ctx *c, void *dstHost, uint64_t dstBytes)
+{
+    REQUIRE(c && dstHost, "prt_read_illumination_f16");
+    REQUIRE(c->historyValid, "nothing recorded yet");
+    const uint32_t pixels = c->accumWidth * c->accumHeight;
+    REQUIRE(dstBytes >= (uint64_t)pixels * 8, "destination too small");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(c->f16.ensure(pixels));
+    k_blit_f16<<<blocksFor(pixels, 256), 256, 0, c->stream>>>(c->accum.p, c->f16.p, pixels);
+    c->kernelLaunches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dstHost, c->f16.p, (size_t)pixels * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_release_preserved(prt_ctx *c)
+{
+    REQUIRE(c, "prt_release_preserved");
+    c->historyValid = false; // RtRef.cpp:385-391
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_trace_primary(prt_ctx *c, const prt_reference_pc *pcIn, uint32_t width, uint32_t height, prt_hit *dstHost)
+{
+    REQUIRE(c && dstHost, "prt_trace_primary");
+    CK(cudaSetDevice(c->cfg.device));
+    CKS(checkRenderState(c, pcIn, width, height));
+    const uint64_t pixels = (uint64_t)width * height;
+    CKS(allocPathBuffers(c, pixels));
+    CK(c->userHits.ensure(pixels));
+    const SceneView sv = c->view();
+    const Accel as = c->accel();
+    cudaStream_t st = c->stream;
+    const uint32_t grid = blocksFor(pixels, RENDER_THREADS);
+    k_raygen<<<grid, RENDER_THREADS, 0, st>>>(sv, *pcIn, width, height, 1, c->pb);
+    k_trace_closest<true><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, 0, 0, c->dCounters);
+    k_hits_to_records<<<blocksFor(pixels, 256), 256, 0, st>>>(c->pb.hits, c->userHits.p, (uint32_t)pixels);
+    c->kernelLaunches += 3;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dstHost, c->userHits.p, pixels * sizeof(prt_hit), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_trace_rays(prt_ctx *c, const float *originTmin, const float *dirTmax, const uint32_t *seeds, uint32_t count,
+                                     int shadow, prt_hit *dstHost)
+{
+    REQUIRE(c && originTmin && dirTmax && dstHost, "prt_trace_rays");
+    CK(cudaSetDevice(c->cfg.device));
+    CKS(refreshTextureSlots(c));
+    if (count == 0) return PRT_OK;
+    cudaStream_t st = c->stream;
+    CK(c->userO.ensure(count)); CK(c->userD.ensure(count)); CK(c->userSeeds.ensure(count)); CK(c->userHits.ensure(count));
+    CK(cudaMemcpyAsync(c->userO.p, originTmin, (size_t)count * 16, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(c->userD.p, dirTmax, (size_t)count * 16, cudaMemcpyHostToDevice, st));
+    if (seeds) CK(cudaMemcpyAsync(c->userSeeds.p, seeds, (size_t)count * 4, cudaMemcpyHostToDevice, st));
+    const SceneView sv = c->view();
+    const Accel as = c->accel();
+    const uint32_t grid = blocksFor(count, RENDER_THREADS);
+    if (shadow) k_trace_user<true><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->userO.p, c->userD.p, seeds ? c->userSeeds.p : nullptr, count, c->userHits.p, c->dCounters);
+    else k_trace_user<false><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->userO.p, c->userD.p, seeds ? c->userSeeds.p : nullptr, count, c->userHits.p, c->dCounters);
+    c->kernelLaunches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dstHost, c->userHits.p, (size_t)count * sizeof(prt_hit), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return PRT_OK;
+}
+
+// ---- multi-GPU ------------------------------------------------------------------------------------------------------
+extern "C" prt_status prt_export_sum_device(prt_ctx *c, float **outSum)
+{
+    REQUIRE(c && outSum, "prt_export_sum_device");
+    REQUIRE(c->historyValid, "nothing recorded yet");
+    CK(cudaSetDevice(c->cfg.device));
+    const uint32_t pixels = c->accumWidth * c->accumHeight;
+    CK(c->sum.ensure(pixels));
+    k_mean_to_sum<<<blocksFor(pixels, 256), 256, 0, c->stream>>>(c->accum.p, c->sum.p, pixels);
+    c->kernelLaunches++;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(c->stream)); // the caller reduces it on its own (NCCL) stream
+    *outSum = reinterpret_cast<float *>(c->sum.p);
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_import_sum_device(prt_ctx *c, const float *sumDevice)
+{
+    REQUIRE(c && sumDevice, "prt_import_sum_device");
+    REQUIRE(c->accumWidth && c->accumHeight, "no render area yet");
+    CK(cudaSetDevice(c->cfg.device));
+    const uint32_t pixels = c->accumWidth * c->accumHeight;
+    k_sum_to_mean<<<blocksFor(pixels, 256), 256, 0, c->stream>>>(reinterpret_cast<const float4 *>(sumDevice), c->accum.p, pixels);
+    c->kernelLaunches++;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(c->stream));
+    c->historyValid = true;
+    return PRT_OK;
+}
+
+// ---- metrics -----------------------------------------------------------------------------------------------------------
+extern "C" prt_status prt_get_counters(prt_ctx *c, prt_counters *out)
+{
+    REQUIRE(c && out, "prt_get_counters");
+    CK(cudaSetDevice(c->cfg.device));
+    GlobalCounters g;
+    CK(cudaMemcpyAsync(&g, c->dCounters, sizeof(g), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    out->closestRays = g.closestRays; out->shadowRays = g.shadowRays; out->nodesVisited = g.nodesVisited;
+    out->trisTested = g.trisTested; out->instancesEntered = g.instancesEntered; out->anyHitCalls = g.anyHitCalls;
+    out->shadedHits = g.shadedHits; out->textureTaps = g.textureTaps; out->pixelSamples = g.pixelSamples;
+    out->kernelLaunches = c->kernelLaunches;
+    out->stackOverflows = g.stackOverflows;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_reset_counters(prt_ctx *c)
+{
+    REQUIRE(c, "prt_reset_counters");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemsetAsync(c->dCounters, 0, sizeof(GlobalCounters), c->stream));
+    c->kernelLaunches = 0;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_get_timings(prt_ctx *c, prt_timings *out)
+{
+    REQUIRE(c && out, "prt_get_timings");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    memset(out, 0, sizeof(*out));
+    if (c->recordTimed) CK(cudaEventElapsedTime(&out->lastRecordMs, c->evRecord[0], c->evRecord[1]));
+    if (c->tlasTimed) CK(cudaEventElapsedTime(&out->lastTlasMs, c->evTlas[0], c->evTlas[1]));
+    if (c->blasTimed) CK(cudaEventElapsedTime(&out->lastBlasMs, c->evBlas[0], c->evBlas[1]));
+    if (c->traceTimed)
+    {
+        float sum = 0.f;
+        for (uint32_t b = 0; b < c->lastTraceLaunches; ++b)
+        {
+            float ms = 0.f;
+            CK(cudaEventElapsedTime(&ms, c->evTrace[2 * b], c->evTrace[2 * b + 1]));
+            sum += ms;
+        }
+        out->lastTraceClosestMs = sum;
+        out->lastTraceClosestLaunches = c->lastTraceLaunches;
+    }
+    out->lastRecordLaunches = c->lastRecordLaunches;
+    out->lastTlasLaunches = c->lastTlasLaunches;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_get_bvh_stats(prt_ctx *c, prt_bvh_stats *out)
+{
+    REQUIRE(c && out, "prt_get_bvh_stats");
+    memset(out, 0, sizeof(*out));
+    out->tlasInstances = c->tlasInstances;
+    for (const BlasRes &b : c->blas)
+    {
+        if (!b.built) continue;
+        out->blasCount++;
+        out->blasNodesTotal += b.nodeCount;
+        out->blasTrianglesTotal += b.triCount;
+    }
+    if (c->tlasInstances)
+    {
+        uint32_t nodes = 0;
+        CK(cudaSetDevice(c->cfg.device));
+        CK(cudaMemcpyAsync(&nodes, c->bScalars.p, 4, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+        out->tlasNodes = nodes; // valid when the TLAS was the last structure built
+    }
+    return PRT_OK;
+}

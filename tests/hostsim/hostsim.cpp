@@ -1,0 +1,392 @@
+// tests/hostsim/hostsim.cpp -- TEST INFRASTRUCTURE: kernel-logic simulator.
+//
+// Compiles the per-thread bodies of the CUDA kernels (prosper_b200/csrc/core_*.h, the very same
+// source the sm_100a kernels are built from) with g++ and drives them serially, so the CPU-only CI
+// (`pytest -m "not gpu"`) exercises the GPU builder, the compressed-node traversal and the shading
+// stages against the oracle without a GPU. It is NOT a CPU fallback: nothing in prosper_b200/
+// loads it and libprt_b200.so does not contain it. What it cannot cover (radix sort, scans, warp
+// compaction, texture units) is covered by the `-m gpu` tests.
+#include "../../prosper_b200/csrc/core_bc7.h"
+#include "../../prosper_b200/csrc/core_build.h"
+#include "../../prosper_b200/csrc/core_shade.h"
+#include "../../oracle/oracle.h" // orc_scene: the scene description struct shared with the oracle binding
+
+#include <algorithm>
+#include <atomic>
+#include <thread>
+#include <vector>
+
+using namespace prt;
+
+namespace {
+
+struct HostBvh
+{
+    std::vector<WideNode> nodes;
+    std::vector<uint32_t> primOut;
+    uint32_t levels = 0;
+};
+
+HostBvh buildHierarchyHost(std::vector<Box> &boxes, V3 lo, V3 hi, bool tlas)
+{
+    const uint32_t n = (uint32_t)boxes.size();
+    HostBvh out;
+    std::vector<uint64_t> keys(n);
+    std::vector<uint32_t> order(n);
+    const uint64_t keyMask = tlas ? 0xFFFFFFFF00000000ull : ~0ull;
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        keys[i] = padBoxAndKey(boxes[i], lo, hi, tlas ? 0 : 1, keyMask);
+        order[i] = i;
+    }
+    // stand-in for the radix sort (stable, like the LSD passes)
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });
+    std::vector<uint64_t> sorted(n);
+    for (uint32_t i = 0; i < n; ++i) sorted[i] = keys[order[i]];
+    std::vector<int32_t> left(n), right(n), parentI(n), parentL(n);
+    std::vector<uint32_t> first(n), last(n), visit(n, 0);
+    std::vector<Box> nodeBox(n);
+    Lbvh t{};
+    t.count = n; t.keys = sorted.data(); t.order = order.data(); t.primBox = boxes.data();
+    t.left = left.data(); t.right = right.data(); t.first = first.data(); t.last = last.data();
+    t.parentOfInternal = parentI.data(); t.parentOfLeaf = parentL.data(); t.nodeBox = nodeBox.data(); t.visit = visit.data();
+    if (n > 1)
+    {
+        for (uint32_t i = 0; i + 1 < n; ++i) lbvhBuildNode(t, (int)i);
+        for (uint32_t i = 0; i < n; ++i) lbvhRefitFromLeaf(t, i);
+    }
+    out.nodes.resize(std::max(n, 1u));
+    out.primOut.resize(n);
+    uint32_t nodeCount = 1, primCount = 0;
+    std::vector<CollapseItem> qa(n + 1), qb(n + 1);
+    qa[0] = CollapseItem{n > 1 ? 0 : ~0, 0u};
+    uint32_t countIn = 1;
+    Collapse c{};
+    c.t = t; c.maxLeaf = tlas ? 1u : 3u; c.nodes = out.nodes.data(); c.primOut = out.primOut.data();
+    c.nodeCount = &nodeCount; c.primCount = &primCount;
+    for (uint32_t level = 0; countIn > 0; ++level)
+    {
+        uint32_t countOut = 0;
+        c.queueIn = (level & 1) ? qb.data() : qa.data();
+        c.queueOut = (level & 1) ? qa.data() : qb.data();
+        c.queueOutCount = &countOut;
+        for (uint32_t i = 0; i < countIn; ++i) collapseItem(c, i);
+        countIn = countOut;
+        out.levels = level + 1;
+    }
+    out.nodes.resize(nodeCount);
+    if (primCount != n) out.primOut.clear(); // signals a builder bug to the caller
+    return out;
+}
+
+struct HostBlas
+{
+    std::vector<WideNode> nodes;
+    std::vector<TriRec> tris;
+};
+
+} // namespace
+
+struct hs_ctx
+{
+    orc_scene s;
+    std::vector<std::vector<uint8_t>> decoded;
+    std::vector<TexSlot> slots;
+    std::vector<HostBlas> blas;
+    std::vector<WideNode> tlasNodes;
+    std::vector<InstRec> tlasInst;
+    SceneView sv{};
+    Accel as{};
+    uint32_t blasLevels = 0, tlasLevels = 0;
+    int buildError = 0;
+    std::atomic<uint64_t> nodes{0}, tris{0}, instances{0}, anyHits{0}, overflow{0};
+};
+
+static void flush(hs_ctx *c, const TraceCounters &tc)
+{
+    c->nodes += tc.nodes; c->tris += tc.tris; c->instances += tc.instances; c->anyHits += tc.anyHits; c->overflow += tc.overflow;
+}
+
+template <typename F> static void parallelFor(uint32_t count, int threads, F &&fn)
+{
+    int n = threads > 0 ? threads : (int)std::thread::hardware_concurrency();
+    n = std::max(1, std::min(n, (int)count));
+    std::atomic<uint32_t> next{0};
+    auto worker = [&]() {
+        for (;;)
+        {
+            const uint32_t i = next.fetch_add(1);
+            if (i >= count) break;
+            fn(i);
+        }
+    };
+    if (n == 1) { worker(); return; }
+    std::vector<std::thread> pool;
+    for (int i = 0; i < n; ++i) pool.emplace_back(worker);
+    for (auto &t : pool) t.join();
+}
+
+extern "C" {
+
+hs_ctx *hs_create(const orc_scene *scene, int exactMaterialFilter)
+{
+    hs_ctx *c = new hs_ctx;
+    c->s = *scene;
+    const orc_scene &s = c->s;
+    // textures: decode level 0 with the product's BC7 decoder
+    c->decoded.resize(s.textureCount);
+    const uint32_t ns = std::max(s.samplerCount, 1u);
+    c->slots.assign((size_t)s.textureCount * ns, TexSlot{});
+    for (uint32_t t = 0; t < s.textureCount; ++t)
+    {
+        const orc_texture &tx = s.textures[t];
+        if (!tx.data || !tx.width) continue;
+        std::vector<uint8_t> &img = c->decoded[t];
+        img.resize((size_t)tx.width * tx.height * 4);
+        if (tx.format == 0) memcpy(img.data(), tx.data, img.size());
+        else
+        {
+            const uint32_t bw = (tx.width + 3) / 4, bh = (tx.height + 3) / 4;
+            const uint64_t *blocks = (const uint64_t *)tx.data;
+            for (uint32_t b = 0; b < bw * bh; ++b)
+            {
+                uint32_t px[16];
+                bc7DecodeBlock(blocks[2 * b], blocks[2 * b + 1], px);
+                const uint32_t bx = b % bw, by = b / bw;
+                for (uint32_t y = 0; y < 4; ++y)
+                    for (uint32_t x = 0; x < 4; ++x)
+                        if (bx * 4 + x < tx.width && by * 4 + y < tx.height)
+                            memcpy(&img[((size_t)(by * 4 + y) * tx.width + bx * 4 + x) * 4], &px[y * 4 + x], 4);
+            }
+        }
+        for (uint32_t sm = 0; sm < ns; ++sm)
+        {
+            TexSlot &slot = c->slots[(size_t)t * ns + sm];
+            slot.rgba = img.data();
+            slot.width = tx.width; slot.height = tx.height;
+            const prt_sampler_desc sd = s.samplerCount ? ((const prt_sampler_desc *)s.samplers)[sm] : prt_sampler_desc{1, 1, 0, 0};
+            slot.magFilter = sd.magFilter; slot.addressU = sd.addressU; slot.addressV = sd.addressV;
+            slot.valid = 1;
+        }
+    }
+    SceneView &sv = c->sv;
+    sv.geometryBuffers = (const uint32_t *const *)s.geometryBuffers;
+    sv.metadatas = (const prt_geometry_metadata *)s.metadatas;
+    sv.materials = (const prt_material_data *)s.materials;
+    sv.drawInstances = (const prt_draw_instance *)s.drawInstances;
+    sv.transforms = (const prt_model_instance_transforms *)s.transforms;
+    sv.texSlots = c->slots.data();
+    sv.textureCount = s.textureCount;
+    sv.samplerCount = ns;
+    sv.directional = (const prt_directional_light *)s.directionalLight;
+    sv.pointLights = (const prt_point_light *)s.pointLights;
+    sv.spotLights = (const prt_spot_light *)s.spotLights;
+    sv.pointLightCount = s.pointLightCount;
+    sv.spotLightCount = s.spotLightCount;
+    sv.camera = (const prt_camera_uniforms *)s.camera;
+    sv.sky = (const uint16_t *)s.skyRgba16f;
+    sv.skyFaceSize = s.skyRgba16f ? s.skyFaceSize : 0;
+    sv.exactMaterialFilter = exactMaterialFilter ? 1u : 0u;
+
+    // BLAS per model (the k_blas_gather -> buildHierarchy -> k_emit_tris sequence of prt_build_blas)
+    const prt_mesh_info *infos = (const prt_mesh_info *)s.meshInfos;
+    const prt_sub_model *subs = (const prt_sub_model *)s.subModels;
+    c->blas.resize(s.modelCount);
+    for (uint32_t m = 0; m < s.modelCount; ++m)
+    {
+        std::vector<TriRec> tris;
+        std::vector<Box> boxes;
+        V3 lo = {3.4e38f, 3.4e38f, 3.4e38f}, hi = {-3.4e38f, -3.4e38f, -3.4e38f};
+        for (uint32_t g = s.modelOffsets[m]; g < s.modelOffsets[m + 1]; ++g)
+        {
+            const prt_mesh_info &info = infos[subs[g].meshIndex];
+            const uint32_t opaque = sv.materials[info.materialIndex].alphaMode == PRT_ALPHA_OPAQUE ? 1u : 0u;
+            for (uint32_t p = 0; p < info.indexCount / 3; ++p)
+            {
+                TriRec t;
+                V3 l, h;
+                gatherTriangle(sv, subs[g].meshIndex, p, g - s.modelOffsets[m], opaque, t, l, h);
+                tris.push_back(t);
+                boxes.push_back(makeBox(l, h));
+                lo = vmin(lo, l);
+                hi = vmax(hi, h);
+            }
+        }
+        if (tris.empty()) continue;
+        HostBvh h = buildHierarchyHost(boxes, lo, hi, false);
+        if (h.primOut.size() != tris.size()) { c->buildError = 1; continue; }
+        c->blasLevels = std::max(c->blasLevels, h.levels);
+        c->blas[m].nodes = std::move(h.nodes);
+        c->blas[m].tris.resize(tris.size());
+        for (size_t i = 0; i < tris.size(); ++i) c->blas[m].tris[i] = tris[h.primOut[i]];
+    }
+    // TLAS (prt_build_tlas)
+    const prt_tlas_instance *inst = (const prt_tlas_instance *)s.tlasInstances;
+    std::vector<InstRec> recs;
+    std::vector<Box> boxes;
+    V3 lo = {3.4e38f, 3.4e38f, 3.4e38f}, hi = {-3.4e38f, -3.4e38f, -3.4e38f};
+    for (uint32_t i = 0; i < s.instanceCount; ++i)
+    {
+        if (inst[i].blasReference == 0) continue;
+        const uint64_t model = inst[i].blasReference - 1;
+        if (model >= s.modelCount || c->blas[model].tris.empty()) continue;
+        TlasInput ti;
+        memcpy(ti.transform, inst[i].transform, sizeof(ti.transform));
+        ti.customIndexAndMask = inst[i].customIndexAndMask;
+        ti.index = i;
+        ti.nodes = c->blas[model].nodes.data();
+        ti.tris = c->blas[model].tris.data();
+        InstRec r;
+        V3 l, h;
+        tlasInstanceRecord(ti, r, l, h);
+        recs.push_back(r);
+        boxes.push_back(makeBox(l, h));
+        lo = vmin(lo, l);
+        hi = vmax(hi, h);
+    }
+    if (!recs.empty())
+    {
+        HostBvh h = buildHierarchyHost(boxes, lo, hi, true);
+        if (h.primOut.size() != recs.size()) c->buildError = 2;
+        else
+        {
+            c->tlasLevels = h.levels;
+            c->tlasNodes = std::move(h.nodes);
+            c->tlasInst.resize(recs.size());
+            for (size_t i = 0; i < recs.size(); ++i) c->tlasInst[i] = recs[h.primOut[i]];
+            c->as.tlasNodes = c->tlasNodes.data();
+            c->as.instances = c->tlasInst.data();
+        }
+    }
+    return c;
+}
+
+void hs_destroy(hs_ctx *c) { delete c; }
+
+// out[0..7]: buildError, blas wide nodes, blas tris, tlas wide nodes, tlas instances, blas levels, tlas levels, 0
+void hs_stats(hs_ctx *c, uint64_t *out)
+{
+    uint64_t bn = 0, bt = 0;
+    for (const HostBlas &b : c->blas) { bn += b.nodes.size(); bt += b.tris.size(); }
+    out[0] = (uint64_t)c->buildError; out[1] = bn; out[2] = bt; out[3] = c->tlasNodes.size(); out[4] = c->tlasInst.size();
+    out[5] = c->blasLevels; out[6] = c->tlasLevels; out[7] = 0;
+}
+
+// out[0..4]: nodes visited, triangles tested, instances entered, any-hit calls, stack overflows
+void hs_trace_counters(hs_ctx *c, uint64_t *out)
+{
+    out[0] = c->nodes; out[1] = c->tris; out[2] = c->instances; out[3] = c->anyHits; out[4] = c->overflow;
+}
+
+void hs_trace_primary(hs_ctx *c, const void *pcIn, uint32_t width, uint32_t height, prt_hit *hits, int threads)
+{
+    const prt_reference_pc pc = *(const prt_reference_pc *)pcIn;
+    parallelFor(height, threads, [&](uint32_t y) {
+        TraceCounters tc = {0, 0, 0, 0, 0};
+        for (uint32_t x = 0; x < width; ++x)
+        {
+            Rng rng;
+            const Ray ray = generatePrimaryRay(c->sv, pc, pc.frameIndex, x, y, width, height, rng);
+            HitRec h;
+            traceRay<false, true>(c->as, c->sv, ray.o, ray.d, ray.tMin, ray.tMax, pcg(rng.state.x ^ rng.state.z), h, &tc);
+            hits[(size_t)y * width + x] = prt_hit{h.drawInstanceIndex, h.primitiveID, {h.u, h.v}};
+        }
+        flush(c, tc);
+    });
+}
+
+void hs_trace_rays(hs_ctx *c, const float *originTmin, const float *dirTmax, const uint32_t *seeds, uint32_t count, int shadow,
+                   prt_hit *hits, int threads)
+{
+    const uint32_t chunk = 1024;
+    parallelFor((count + chunk - 1) / chunk, threads, [&](uint32_t r) {
+        TraceCounters tc = {0, 0, 0, 0, 0};
+        for (uint32_t i = r * chunk; i < std::min(count, (r + 1) * chunk); ++i)
+        {
+            const V3 o = {originTmin[i * 4], originTmin[i * 4 + 1], originTmin[i * 4 + 2]};
+            const V3 d = {dirTmax[i * 4], dirTmax[i * 4 + 1], dirTmax[i * 4 + 2]};
+            HitRec h;
+            if (shadow) traceRay<true, true>(c->as, c->sv, o, d, originTmin[i * 4 + 3], dirTmax[i * 4 + 3], seeds ? seeds[i] : 0u, h, &tc);
+            else traceRay<false, true>(c->as, c->sv, o, d, originTmin[i * 4 + 3], dirTmax[i * 4 + 3], seeds ? seeds[i] : 0u, h, &tc);
+            hits[i] = prt_hit{h.drawInstanceIndex, h.primitiveID, {h.u, h.v}};
+        }
+        flush(c, tc);
+    });
+}
+
+// The wavefront stages executed path by path: raygen -> [trace_closest -> shade -> trace_shadow] -> accumulate.
+// counters (optional, 4 x u64): closest rays, shadow rays, shaded hits, pixel samples.
+void hs_render(hs_ctx *c, const void *pcIn, uint32_t width, uint32_t height, uint32_t sampleCount, float *rgba, int threads,
+               uint64_t *counters)
+{
+    const prt_reference_pc pc0 = *(const prt_reference_pc *)pcIn;
+    std::atomic<uint64_t> closest{0}, shadowRays{0}, shaded{0};
+    parallelFor(height, threads, [&](uint32_t y) {
+        TraceCounters tc = {0, 0, 0, 0, 0};
+        uint64_t nc = 0, nsr = 0, nsh = 0;
+        for (uint32_t x = 0; x < width; ++x)
+        {
+            float *out = rgba + ((size_t)y * width + x) * 4;
+            for (uint32_t k = 0; k < sampleCount; ++k)
+            {
+                prt_reference_pc pc = pc0;
+                pc.frameIndex = (pc0.frameIndex + k) % PRT_FRAME_PERIOD;
+                if (k > 0) pc.flags &= ~1u;
+                Rng rng;
+                Ray ray = generatePrimaryRay(c->sv, pc, pc.frameIndex, x, y, width, height, rng);
+                uint32_t seed = pcg(rng.state.x ^ rng.state.z);
+                V3 throughput = {1.f, 1.f, 1.f}, color = {0.f, 0.f, 0.f};
+                const uint32_t bounces = std::min<uint32_t>(pc.maxBounces, MAX_BOUNCES);
+                for (uint32_t bounce = 0; bounce < bounces; ++bounce)
+                {
+                    HitRec h;
+                    traceRay<false, true>(c->as, c->sv, ray.o, ray.d, ray.tMin, ray.tMax, seed, h, &tc);
+                    nc++;
+                    ShadeResult r;
+                    shadePath(c->sv, pc, bounce, ray.d, h.drawInstanceIndex, h.primitiveID, h.u, h.v, rng, throughput, color, r);
+                    if (h.drawInstanceIndex != MISS_INDEX) nsh++;
+                    if (r.shadowRay)
+                    {
+                        HitRec sh;
+                        nsr++;
+                        if (!traceRay<true, true>(c->as, c->sv, r.shadowO, r.shadowD, 0.1f, r.shadowTMax, r.shadowSeed, sh, &tc))
+                            color = color + r.shadowContribution;
+                    }
+                    if (!r.alive) break;
+                    ray = r.next;
+                    seed = pcg(rng.state.x ^ rng.state.z);
+                }
+                if (flagSkipHistory(pc) || !flagAccumulate(pc))
+                {
+                    out[0] = color.x; out[1] = color.y; out[2] = color.z; out[3] = 1.f;
+                }
+                else
+                {
+                    const float n = out[3] + 1.f;
+                    out[0] = out[0] + (color.x - out[0]) / n;
+                    out[1] = out[1] + (color.y - out[1]) / n;
+                    out[2] = out[2] + (color.z - out[2]) / n;
+                    out[3] = n;
+                }
+            }
+        }
+        flush(c, tc);
+        closest += nc; shadowRays += nsr; shaded += nsh;
+    });
+    if (counters)
+    {
+        counters[0] += closest; counters[1] += shadowRays; counters[2] += shaded;
+        counters[3] += (uint64_t)width * height * sampleCount;
+    }
+}
+
+// unit entry points
+int hs_bc7_decode_block(const uint8_t block[16], uint8_t out[64])
+{
+    uint64_t lo, hi;
+    memcpy(&lo, block, 8);
+    memcpy(&hi, block + 8, 8);
+    return bc7DecodeBlock(lo, hi, (uint32_t *)out) ? 0 : -1;
+}
+
+} // extern "C"
