@@ -110,6 +110,21 @@ prt_status prt_trace_primary(prt_ctx *ctx, const prt_reference_pc *pc, uint32_t 
 prt_status prt_trace_rays(prt_ctx *ctx, const float *originTmin, const float *dirTmax,
                           const uint32_t *seeds, uint32_t count, int shadow, prt_hit *dstHost);
 
+/* Test hook: what the bindless slot `textureSampler` ((sampler << 24) | texture, material_data.h:19-36)
+ * returns. texelXY == NULL: texture() at `uv` (2 floats per sample) through the hardware filter
+ * (exact == 0) or the software bilinear of the any-hit stage (exact != 0); otherwise the raw texels at
+ * integer coordinates texelXY (2 ints per sample). outRgba = 4 floats per sample. HOST pointers. */
+prt_status prt_probe_texture(prt_ctx *ctx, uint32_t textureSampler, const float *uv, const int32_t *texelXY,
+                             uint32_t count, int exact, float *outRgba);
+
+/* Test hooks: read the built structures back (80-byte wide nodes, 48-byte triangle records, 80-byte
+ * instance records; layouts in prosper_b200/csrc/core_bvh.h) so the tests can validate the GPU
+ * builder's output structurally on the host. Pass NULL buffers to query the counts. */
+prt_status prt_debug_read_blas(prt_ctx *ctx, uint32_t modelIndex, void *nodesOut, uint64_t nodesBytes,
+                               void *trisOut, uint64_t trisBytes, uint32_t *nodeCount, uint32_t *triCount);
+prt_status prt_debug_read_tlas(prt_ctx *ctx, void *nodesOut, uint64_t nodesBytes, void *instOut,
+                               uint64_t instBytes, uint32_t *instanceCount);
+
 /* ---- multi-GPU: one ctx per rank, accumulation kept as sum + count ------------- */
 /* Device pointer to the fp32 RGBA *sum* image (rgb = sum of samples, a = count) suitable for
  * ncclReduce(sum); prt_resolve_sum turns a reduced sum back into the running-mean image. */

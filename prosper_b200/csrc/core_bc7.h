@@ -112,4 +112,66 @@ HD bool bc7DecodeBlock(uint64_t lo, uint64_t hi, uint32_t *out)
     return false;
 }
 
+// Random access to one texel (index 0..15, row-major in the block) without expanding the block: what the
+// software bilinear of the any-hit stage uses, straight from the BC7 payload in HBM.
+HD uint32_t bc7Field(uint64_t lo, uint64_t hi, uint32_t pos, uint32_t n)
+{
+    Bc7Bits br{lo, hi, pos};
+    return br.get(n);
+}
+
+HD uint32_t bc7DecodeTexel(uint64_t lo, uint64_t hi, uint32_t i)
+{
+    const uint32_t low = (uint32_t)lo;
+    if (low & 0x40u && !(low & 0x3Fu)) // mode 6: 0000001
+    {
+        const uint32_t p0 = bc7Field(lo, hi, 63, 1), p1 = bc7Field(lo, hi, 64, 1);
+        const uint32_t idx = i == 0 ? bc7Field(lo, hi, 65, 3) : bc7Field(lo, hi, 64 + 4 * i, 4);
+        const uint32_t w = bc7Weight(4, idx);
+        uint32_t px = 0;
+        for (uint32_t c = 0; c < 4; ++c)
+        {
+            const uint32_t e0 = (bc7Field(lo, hi, 7 + 14 * c, 7) << 1) | p0;
+            const uint32_t e1 = (bc7Field(lo, hi, 14 + 14 * c, 7) << 1) | p1;
+            px |= bc7Lerp(e0, e1, w) << (8 * c);
+        }
+        return px;
+    }
+    const bool mode4 = (low & 0x1Fu) == 0x10u, mode5 = (low & 0x3Fu) == 0x20u;
+    if (mode4 || mode5)
+    {
+        const uint32_t head = mode4 ? 5u : 6u; // mode bits
+        const uint32_t rot = bc7Field(lo, hi, head, 2);
+        const uint32_t idxMode = mode4 ? bc7Field(lo, hi, head + 2, 1) : 0u;
+        const uint32_t cb = mode4 ? 5u : 7u, ab = mode4 ? 6u : 8u;
+        const uint32_t colorPos = head + 2 + (mode4 ? 1u : 0u);
+        const uint32_t alphaPos = colorPos + 6 * cb;
+        const uint32_t idx0Pos = alphaPos + 2 * ab; // 2-bit stream: 31 bits
+        const uint32_t idx1Pos = idx0Pos + 31;
+        const uint32_t b1 = mode4 ? 3u : 2u;
+        const uint32_t a0 = i == 0 ? bc7Field(lo, hi, idx0Pos, 1) : bc7Field(lo, hi, idx0Pos + 2 * i - 1, 2);
+        const uint32_t a1 = i == 0 ? bc7Field(lo, hi, idx1Pos, b1 - 1) : bc7Field(lo, hi, idx1Pos + b1 * i - 1, b1);
+        uint32_t cw, aw;
+        if (mode5) { cw = bc7Weight(2, a0); aw = bc7Weight(2, a1); }
+        else if (idxMode == 0) { cw = bc7Weight(2, a0); aw = bc7Weight(3, a1); }
+        else { cw = bc7Weight(3, a1); aw = bc7Weight(2, a0); }
+        uint32_t ch[4];
+        for (uint32_t c = 0; c < 3; ++c)
+        {
+            const uint32_t v0 = bc7Field(lo, hi, colorPos + 2 * c * cb, cb), v1 = bc7Field(lo, hi, colorPos + (2 * c + 1) * cb, cb);
+            ch[c] = bc7Lerp((v0 << (8 - cb)) | (v0 >> (2 * cb - 8)), (v1 << (8 - cb)) | (v1 >> (2 * cb - 8)), cw);
+        }
+        const uint32_t v0 = bc7Field(lo, hi, alphaPos, ab), v1 = bc7Field(lo, hi, alphaPos + ab, ab);
+        ch[3] = bc7Lerp(ab == 8 ? v0 : ((v0 << 2) | (v0 >> 4)), ab == 8 ? v1 : ((v1 << 2) | (v1 >> 4)), aw);
+        if (rot >= 1 && rot <= 3)
+        {
+            const uint32_t t = ch[3];
+            ch[3] = ch[rot - 1];
+            ch[rot - 1] = t;
+        }
+        return ch[0] | (ch[1] << 8) | (ch[2] << 16) | (ch[3] << 24);
+    }
+    return 0;
+}
+
 } // namespace prt

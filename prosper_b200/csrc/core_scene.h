@@ -2,6 +2,7 @@
 // res/shader/scene/{geometry,instances,materials}.glsl, one function per GLSL function.
 #pragma once
 #include "hd.h"
+#include "core_bc7.h"
 #include "../../include/prt_types.h"
 
 #ifdef __CUDACC__
@@ -10,22 +11,30 @@
 
 namespace prt {
 
-// One bindless slot = (texture, sampler) pair (materials.glsl:21-24, 37-38). `texels` is a point
-// sampled, unnormalised view used for the exact software bilinear (any-hit alpha decisions must
-// match the oracle bit for bit); `linear` is the hardware filtered view (material colour taps).
+// One bindless slot = (texture, sampler) pair (materials.glsl:21-24, 37-38).
+//  * `payload` is level 0 of the texture as the texture cache stores it (BC7 blocks or RGBA8 texels) in
+//    HBM: the software bilinear of the any-hit stage decodes texels straight from it, so the
+//    accept/ignore decisions of scene.rahit are bit-identical with the oracle's and the traversal
+//    kernels contain no texture instruction at all;
+//  * `linear` is the hardware-filtered CUDA texture object over the same data (BC7 CUDA array), used for
+//    the material colour taps in the shade stage;
+//  * `texels` is a point-sampled view of that array, used only by the test probe that pins what the
+//    texture units decode against the software decode.
 struct TexSlot
 {
+    const uint8_t *payload;
 #ifdef __CUDACC__
-    cudaTextureObject_t texels;
     cudaTextureObject_t linear;
+    cudaTextureObject_t texels;
 #else
-    const uint8_t *rgba; // host simulator: decoded level 0
-    uint64_t unused;
+    uint64_t linear, texels;
 #endif
+    uint32_t format; // PRT_TEX_*
     uint32_t width, height;
     uint32_t magFilter; // 0 nearest, 1 linear
     uint32_t addressU, addressV;
     uint32_t valid;
+    uint32_t pad;
 };
 
 struct SceneView
@@ -185,18 +194,34 @@ HD int wrapCoord(int i, int n, uint32_t mode)
     return i < 0 ? 0 : (i > n - 1 ? n - 1 : i);
 }
 
+// texel (x, y) of level 0, decoded in software from the cached payload: unorm8 / 255 like the oracle
 HD V4 fetchTexel(const TexSlot &s, int x, int y)
 {
+    uint32_t px;
+    if (s.format == PRT_TEX_BC7_UNORM)
+    {
+        const uint32_t bw = (s.width + 3u) >> 2;
+        const uint8_t *blk = s.payload + ((size_t)((uint32_t)y >> 2) * bw + ((uint32_t)x >> 2)) * 16;
 #if defined(__CUDA_ARCH__)
-    const float4 t = tex2D<float4>(s.texels, (float)x + 0.5f, (float)y + 0.5f);
-    return {t.x, t.y, t.z, t.w};
-#elif defined(__CUDACC__)
-    (void)s; (void)x; (void)y;
-    return {0.f, 0.f, 0.f, 0.f};
+        const uint4 b = __ldg(reinterpret_cast<const uint4 *>(blk));
+        const uint64_t lo = (uint64_t)b.x | ((uint64_t)b.y << 32), hi = (uint64_t)b.z | ((uint64_t)b.w << 32);
 #else
-    const uint8_t *p = s.rgba + ((size_t)y * s.width + x) * 4;
-    return {p[0] / 255.f, p[1] / 255.f, p[2] / 255.f, p[3] / 255.f};
+        uint64_t lo, hi;
+        memcpy(&lo, blk, 8);
+        memcpy(&hi, blk + 8, 8);
 #endif
+        px = bc7DecodeTexel(lo, hi, (((uint32_t)y & 3u) << 2) | ((uint32_t)x & 3u));
+    }
+    else
+    {
+#if defined(__CUDA_ARCH__)
+        px = __ldg(reinterpret_cast<const uint32_t *>(s.payload) + (size_t)y * s.width + x);
+#else
+        memcpy(&px, s.payload + ((size_t)y * s.width + x) * 4, 4);
+#endif
+    }
+    return {xdiv((float)(px & 255u), 255.f), xdiv((float)((px >> 8) & 255u), 255.f), xdiv((float)((px >> 16) & 255u), 255.f),
+            xdiv((float)(px >> 24), 255.f)};
 }
 
 // Software bilinear with the oracle's exact operation order (oracle.cpp sampleTexture).
@@ -234,19 +259,11 @@ HD const TexSlot *texSlot(const SceneView &sv, uint32_t textureSampler)
     return s->valid ? s : nullptr;
 }
 
-HD V4 sampleTexture(const SceneView &sv, uint32_t textureSampler, V2 uv, bool exact)
+// texture() through the software filter
+HD V4 sampleTexture(const SceneView &sv, uint32_t textureSampler, V2 uv)
 {
     const TexSlot *s = texSlot(sv, textureSampler);
     if (s == nullptr) return {1.f, 1.f, 1.f, 1.f};
-#if defined(__CUDA_ARCH__)
-    if (!exact)
-    {
-        const float4 t = tex2D<float4>(s->linear, uv.x, uv.y);
-        return {t.x, t.y, t.z, t.w};
-    }
-#else
-    (void)exact;
-#endif
     return sampleTextureExact(*s, uv);
 }
 
@@ -265,16 +282,33 @@ HD float sRGBtoLinear(float x) // materials.glsl:26-29
     return x <= 0.04045f ? x / 12.92f : powf((x + 0.055f) / 1.055f, 2.4f);
 }
 
-HD Material sampleMaterial(const SceneView &sv, uint32_t index, V2 uv)
+// The three texture() results sampleMaterial needs (base colour, metallic-roughness, normal); a tap of
+// a material without that texture is never read.
+struct MaterialTaps
+{
+    V4 base, metallicRoughness, normal;
+};
+
+HD MaterialTaps softwareMaterialTaps(const SceneView &sv, uint32_t index, V2 uv)
+{
+    const prt_material_data &data = sv.materials[index];
+    MaterialTaps t;
+    t.base = t.metallicRoughness = t.normal = V4{1.f, 1.f, 1.f, 1.f};
+    if ((data.baseColorTextureSampler & 0xFFFFFFu) > 0) t.base = sampleTexture(sv, data.baseColorTextureSampler, uv);
+    if ((data.metallicRoughnessTextureSampler & 0xFFFFFFu) > 0) t.metallicRoughness = sampleTexture(sv, data.metallicRoughnessTextureSampler, uv);
+    if ((data.normalTextureSampler & 0xFFFFFFu) > 0) t.normal = sampleTexture(sv, data.normalTextureSampler, uv);
+    return t;
+}
+
+HD Material sampleMaterial(const SceneView &sv, uint32_t index, const MaterialTaps &taps)
 { // materials.glsl:47-119
     const prt_material_data &data = sv.materials[index];
-    const bool exact = sv.exactMaterialFilter != 0;
     Material ret;
     ret.albedo = {0.f, 0.f, 0.f}; ret.normal = {0.f, 0.f, 0.f}; ret.roughness = 0.f; ret.metallic = 0.f; ret.alpha = 0.f;
     V4 c = {1.f, 1.f, 1.f, 1.f};
     if ((data.baseColorTextureSampler & 0xFFFFFFu) > 0)
     {
-        const V4 s = sampleTexture(sv, data.baseColorTextureSampler, uv, exact);
+        const V4 s = taps.base;
         c = {sRGBtoLinear(s.x), sRGBtoLinear(s.y), sRGBtoLinear(s.z), s.w};
     }
     c = {c.x * data.baseColorFactor[0], c.y * data.baseColorFactor[1], c.z * data.baseColorFactor[2], c.w * data.baseColorFactor[3]};
@@ -292,9 +326,8 @@ HD Material sampleMaterial(const SceneView &sv, uint32_t index, V2 uv)
     ret.albedo = {c.x, c.y, c.z};
     if ((data.metallicRoughnessTextureSampler & 0xFFFFFFu) > 0)
     {
-        const V4 mr = sampleTexture(sv, data.metallicRoughnessTextureSampler, uv, exact);
-        ret.roughness = mr.y * data.roughnessFactor;
-        ret.metallic = mr.z * data.metallicFactor;
+        ret.roughness = taps.metallicRoughness.y * data.roughnessFactor;
+        ret.metallic = taps.metallicRoughness.z * data.metallicFactor;
     }
     else
     {
@@ -303,10 +336,7 @@ HD Material sampleMaterial(const SceneView &sv, uint32_t index, V2 uv)
     }
     ret.roughness = fmaxf_(ret.roughness, 0.05f);
     if ((data.normalTextureSampler & 0xFFFFFFu) > 0)
-    {
-        const V4 tn = sampleTexture(sv, data.normalTextureSampler, uv, exact);
-        ret.normal = V3{tn.x, tn.y, tn.z} * 2.f - V3{1.f, 1.f, 1.f};
-    }
+        ret.normal = V3{taps.normal.x, taps.normal.y, taps.normal.z} * 2.f - V3{1.f, 1.f, 1.f};
     else
         ret.normal = {-2.f, -2.f, -2.f};
     return ret;
@@ -319,7 +349,7 @@ HD float sampleAlpha(const SceneView &sv, uint32_t index, V2 uv)
     const prt_material_data &data = sv.materials[index];
     float linearAlpha = 1;
     if ((data.baseColorTextureSampler & 0xFFFFFFu) > 0)
-        linearAlpha = sRGBtoLinear(sampleTexture(sv, data.baseColorTextureSampler, uv, true).w);
+        linearAlpha = sRGBtoLinear(sampleTexture(sv, data.baseColorTextureSampler, uv).w);
     linearAlpha = xmul(linearAlpha, data.baseColorFactor[3]);
     if (data.alphaMode == PRT_ALPHA_BLEND) return linearAlpha;
     if (data.alphaMode == PRT_ALPHA_MASK && linearAlpha < data.alphaCutoff) return 0;

@@ -332,8 +332,15 @@ HD Ray generatePrimaryRay(const SceneView &sv, const prt_reference_pc &PC, uint3
     return pinholeCameraRay(*sv.camera, jitteredUV);
 }
 
-HD VisibleSurface evaluateSurface(const SceneView &sv, V3 rayD, uint32_t drawInstanceIndex, uint32_t primitiveID, float bx,
-                                  float by) // main.rgen:146-179
+// evaluateSurface, main.rgen:146-179, in two halves so that the shade kernel can fetch the material's
+// textures between them at a warp-convergent point (kernels_render.cuh).
+struct SurfaceGeom
+{
+    Vertex v; // interpolated, in world space
+    uint32_t materialIndex;
+};
+
+HD SurfaceGeom surfaceGeometry(const SceneView &sv, uint32_t drawInstanceIndex, uint32_t primitiveID, float bx, float by)
 {
     const prt_draw_instance &instance = sv.drawInstances[drawInstanceIndex];
     const prt_model_instance_transforms &trfn = sv.transforms[instance.modelInstanceIndex];
@@ -341,12 +348,20 @@ HD VisibleSurface evaluateSurface(const SceneView &sv, V3 rayD, uint32_t drawIns
     const Vertex v0 = loadVertexThroughIndexBuffer(sv, metadata, primitiveID * 3 + 0);
     const Vertex v1 = loadVertexThroughIndexBuffer(sv, metadata, primitiveID * 3 + 1);
     const Vertex v2 = loadVertexThroughIndexBuffer(sv, metadata, primitiveID * 3 + 2);
-    const Vertex v = transformVertex(interpolateVertex(v0, v1, v2, bx, by), trfn);
+    SurfaceGeom g;
+    g.v = transformVertex(interpolateVertex(v0, v1, v2, bx, by), trfn);
+    g.materialIndex = instance.materialIndex;
+    return g;
+}
+
+HD VisibleSurface evaluateSurface(const SceneView &sv, V3 rayD, const SurfaceGeom &g, const MaterialTaps &taps)
+{
+    const Vertex &v = g.v;
     VisibleSurface surface;
     surface.positionWS = v.Position;
     surface.invViewRayWS = -rayD;
     surface.uv = v.TexCoord0;
-    surface.material = sampleMaterial(sv, instance.materialIndex, v.TexCoord0);
+    surface.material = sampleMaterial(sv, g.materialIndex, taps);
     if (surface.material.normal.x != -2 && v.Tangent.w != 0)
         surface.normalWS = mappedNormal(surface.material.normal, v.Normal, V3{v.Tangent.x, v.Tangent.y, v.Tangent.z}, v.Tangent.w);
     else
@@ -427,8 +442,10 @@ struct ShadeResult
     Ray next;
 };
 
+// `geom` / `taps` are only read when the ray hit something (hitDrawInstance != MISS_INDEX).
 HDNI void shadePath(const SceneView &sv, const prt_reference_pc &PC, uint32_t bounce, V3 rayD, uint32_t hitDrawInstance,
-                    uint32_t hitPrimitive, float bx, float by, Rng &rng, V3 &throughput, V3 &color, ShadeResult &out)
+                    uint32_t hitPrimitive, const SurfaceGeom &geom, const MaterialTaps &taps, Rng &rng, V3 &throughput, V3 &color,
+                    ShadeResult &out)
 {
     out.shadowRay = false;
     out.alive = false;
@@ -437,7 +454,7 @@ HDNI void shadePath(const SceneView &sv, const prt_reference_pc &PC, uint32_t bo
         if (flagIBL(PC)) addBounce(PC, color, throughput * sampleSky(sv, rayD), bounce); // main.rgen:247-255
         return;
     }
-    const VisibleSurface surface = evaluateSurface(sv, rayD, hitDrawInstance, hitPrimitive, bx, by);
+    const VisibleSurface surface = evaluateSurface(sv, rayD, geom, taps);
     if (PC.drawType != PRT_DRAW_DEFAULT && PC.drawType != PRT_DRAW_MESHLET_ID)
     {
         color = debugColor(sv, PC.drawType, hitDrawInstance, hitPrimitive, surface); // main.rgen:259-264

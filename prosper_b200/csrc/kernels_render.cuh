@@ -109,6 +109,35 @@ __global__ void __launch_bounds__(RENDER_THREADS)
     if (COUNT) flushTraceCounters(gc, tc);
 }
 
+// texture() through the texture units for one tap of every lane of the warp. All 32 lanes must call
+// this together. The bindless handle differs from lane to lane; the loop hands the texture unit ONE
+// handle per iteration (the lowest pending lane's), so the fetch itself always sees a warp-uniform
+// handle. Besides being how the hardware wants it, this side-steps a ptxas 12.9 code-generation bug
+// we hit on sm_100a: in its own divergent-handle ("waterfall") loop the coordinate moves were sunk
+// into the loop over registers aliased with the result, corrupting .xy of lanes served earlier
+// (DESIGN.md section 6).
+__device__ __forceinline__ V4 warpTextureTap(const SceneView &sv, uint32_t textureSampler, bool wanted, V2 uv)
+{
+    V4 out = {1.f, 1.f, 1.f, 1.f};
+    const TexSlot *slot = wanted ? texSlot(sv, textureSampler) : nullptr;
+    unsigned long long handle = slot ? (unsigned long long)slot->linear : 0ull;
+    bool pending = handle != 0ull;
+    for (;;)
+    {
+        const uint32_t m = __ballot_sync(0xFFFFFFFFu, pending);
+        if (m == 0) break;
+        const int leader = __ffs(m) - 1;
+        const unsigned long long h = __shfl_sync(0xFFFFFFFFu, handle, leader);
+        if (pending && handle == h)
+        {
+            const float4 t = tex2D<float4>((cudaTextureObject_t)h, uv.x, uv.y);
+            out = V4{t.x, t.y, t.z, t.w};
+            pending = false;
+        }
+    }
+    return out;
+}
+
 // One loop iteration of main.rgen:241-283 minus the traces.
 __global__ void __launch_bounds__(RENDER_THREADS)
     k_shade(SceneView sv, prt_reference_pc pc, PathBuffers pb, int q, uint32_t bounce, GlobalCounters *gc, int countShaded)
@@ -119,20 +148,49 @@ __global__ void __launch_bounds__(RENDER_THREADS)
     r.shadowRay = false;
     r.alive = false;
     uint32_t path = 0;
-    bool shaded = false;
     Rng rng;
-    if (slot < count)
+    rng.state = {0u, 0u, 0u};
+    const bool active = slot < count;
+    uint4 h = make_uint4(MISS_INDEX, MISS_INDEX, 0u, 0u);
+    float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (active)
     {
-        const uint4 h = pb.hits[slot];
-        const float4 d = pb.rayD[q][slot];
+        h = pb.hits[slot];
+        d = pb.rayD[q][slot];
         path = pb.rayId[q][slot].x;
+    }
+    const bool shaded = active && h.x != MISS_INDEX;
+    SurfaceGeom geom;
+    geom.materialIndex = 0;
+    MaterialTaps taps;
+    taps.base = taps.metallicRoughness = taps.normal = V4{1.f, 1.f, 1.f, 1.f};
+    if (shaded) geom = surfaceGeometry(sv, h.x, h.y, __uint_as_float(h.z), __uint_as_float(h.w));
+    if (sv.exactMaterialFilter)
+    {
+        if (shaded) taps = softwareMaterialTaps(sv, geom.materialIndex, geom.v.TexCoord0);
+    }
+    else
+    {
+        // warp-convergent: every lane takes part in the three taps
+        uint32_t tb = 0, tm = 0, tn = 0;
+        if (shaded)
+        {
+            const prt_material_data &md = sv.materials[geom.materialIndex];
+            tb = md.baseColorTextureSampler; tm = md.metallicRoughnessTextureSampler; tn = md.normalTextureSampler;
+        }
+        const V2 uv = shaded ? geom.v.TexCoord0 : V2{0.f, 0.f};
+        taps.base = warpTextureTap(sv, tb, (tb & 0xFFFFFFu) > 0, uv);
+        taps.metallicRoughness = warpTextureTap(sv, tm, (tm & 0xFFFFFFu) > 0, uv);
+        taps.normal = warpTextureTap(sv, tn, (tn & 0xFFFFFFu) > 0, uv);
+    }
+    if (active)
+    {
         const uint4 rs = pb.rng[path];
         const float4 tp = pb.throughput[path];
         const float4 cl = pb.color[path];
         rng.state = {rs.x, rs.y, rs.z};
         V3 throughput = {tp.x, tp.y, tp.z}, color = {cl.x, cl.y, cl.z};
-        shadePath(sv, pc, bounce, V3{d.x, d.y, d.z}, h.x, h.y, __uint_as_float(h.z), __uint_as_float(h.w), rng, throughput, color, r);
-        shaded = h.x != MISS_INDEX;
+        shadePath(sv, pc, bounce, V3{d.x, d.y, d.z}, h.x, h.y, geom, taps, rng, throughput, color, r);
         pb.color[path] = make_float4(color.x, color.y, color.z, 0.f);
         if (r.alive)
         {

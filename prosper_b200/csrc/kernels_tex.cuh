@@ -25,22 +25,29 @@ __global__ void k_bc7_decode(const uint2 *__restrict__ blocks64, uint32_t blocks
         }
 }
 
-// out[i] = texel (x, y) of the slot's point view and the slot's filtered view at (u, v)
+// out[i] = texel xy[i] as the texture units decode it (point view of the CUDA array; uniform handle)
 __global__ void k_probe_texels(TexSlot slot, const int2 *__restrict__ xy, uint32_t n, float4 *__restrict__ out)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const V4 t = fetchTexel(slot, xy[i].x, xy[i].y);
-    out[i] = make_float4(t.x, t.y, t.z, t.w);
+    out[i] = tex2D<float4>(slot.texels, (float)xy[i].x + 0.5f, (float)xy[i].y + 0.5f);
 }
 
+// out[i] = texture() at uv[i]: software filter (exact != 0) or texture units (uniform handle)
 __global__ void k_probe_sample(SceneView sv, uint32_t textureSampler, const float2 *__restrict__ uv, uint32_t n, int exact,
                                float4 *__restrict__ out)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const V4 t = sampleTexture(sv, textureSampler, V2{uv[i].x, uv[i].y}, exact != 0);
-    out[i] = make_float4(t.x, t.y, t.z, t.w);
+    const TexSlot *s = texSlot(sv, textureSampler);
+    if (s == nullptr) { out[i] = make_float4(1.f, 1.f, 1.f, 1.f); return; }
+    if (exact)
+    {
+        const V4 t = sampleTextureExact(*s, V2{uv[i].x, uv[i].y});
+        out[i] = make_float4(t.x, t.y, t.z, t.w);
+    }
+    else
+        out[i] = tex2D<float4>(s->linear, uv[i].x, uv[i].y);
 }
 
 } // namespace prt

@@ -119,6 +119,7 @@ struct UploadRing
 struct TexRes
 {
     cudaArray_t array = nullptr; // level 0 (texture() in the RT stages reads LOD 0, materials.glsl:44)
+    uint8_t *payload = nullptr;  // level 0 as cached (BC7 blocks / RGBA8 texels) for the software filter
     uint32_t width = 0, height = 0, format = 0, mipLevels = 0;
 };
 
@@ -318,7 +319,10 @@ extern "C" void prt_destroy(prt_ctx *c)
         if (s.linear) cudaDestroyTextureObject(s.linear);
     }
     for (TexRes &t : c->textures)
+    {
         if (t.array) cudaFreeArray(t.array);
+        if (t.payload) cudaFree(t.payload);
+    }
     for (BlasRes &b : c->blas)
     {
         if (b.nodes) cudaFree(b.nodes);
@@ -424,6 +428,8 @@ extern "C" prt_status prt_set_texture(prt_ctx *c, uint32_t index, const prt_text
         CK(cudaStreamSynchronize(c->stream));
         CK(cudaFreeArray(t.array));
         t.array = nullptr;
+        if (t.payload) CK(cudaFree(t.payload));
+        t.payload = nullptr;
     }
     t.width = desc->width; t.height = desc->height; t.format = desc->format; t.mipLevels = desc->mipLevels;
     const uint32_t bx = (desc->width + 3) / 4, by = (desc->height + 3) / 4;
@@ -462,6 +468,11 @@ extern "C" prt_status prt_set_texture(prt_ctx *c, uint32_t index, const prt_text
             CK(cudaMemcpy2DToArrayAsync(t.array, 0, 0, desc->data, (size_t)desc->width * 4, (size_t)desc->width * 4, desc->height,
                                         cudaMemcpyHostToDevice, c->stream));
         }
+    }
+    {
+        const size_t bytes = desc->format == PRT_TEX_BC7_UNORM ? (size_t)bx * by * 16 : (size_t)desc->width * desc->height * 4;
+        CK(cudaMalloc((void **)&t.payload, bytes));
+        CK(cudaMemcpyAsync(t.payload, desc->data, bytes, cudaMemcpyHostToDevice, c->stream));
     }
     CK(cudaStreamSynchronize(c->stream)); // desc->data may go away after return
     c->slotsDirty = true;
@@ -534,6 +545,8 @@ static prt_status refreshTextureSlots(prt_ctx *c)
             td.filterMode = samplers[s].magFilter == PRT_FILTER_NEAREST ? cudaFilterModePoint : cudaFilterModeLinear;
             td.normalizedCoords = 1;
             CK(cudaCreateTextureObject(&slot.linear, &rd, &td, nullptr));
+            slot.payload = tr.payload;
+            slot.format = tr.format;
             slot.width = tr.width; slot.height = tr.height;
             slot.magFilter = samplers[s].magFilter;
             slot.addressU = samplers[s].addressU; slot.addressV = samplers[s].addressV;
@@ -1081,5 +1094,84 @@ extern "C" prt_status prt_get_bvh_stats(prt_ctx *c, prt_bvh_stats *out)
         CK(cudaStreamSynchronize(c->stream));
         out->tlasNodes = nodes; // valid when the TLAS was the last structure built
     }
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_probe_texture(prt_ctx *c, uint32_t textureSampler, const float *uv, const int32_t *texelXY, uint32_t count,
+                                        int exact, float *outRgba)
+{
+    REQUIRE(c && outRgba && (uv || texelXY), "prt_probe_texture");
+    if (count == 0) return PRT_OK;
+    CK(cudaSetDevice(c->cfg.device));
+    CKS(refreshTextureSlots(c));
+    cudaStream_t st = c->stream;
+    DBuf<float4> out;
+    DBuf<float2> in;
+    CK(out.ensure(count));
+    CK(in.ensure(count));
+    const SceneView sv = c->view();
+    if (texelXY)
+    {
+        const uint32_t tex = textureSampler & 0xFFFFFFu, smp = textureSampler >> 24;
+        REQUIRE(tex < c->textures.size() && c->textures[tex].array, "prt_probe_texture: no such texture");
+        const TexSlot slot = c->hSlots[(size_t)tex * sv.samplerCount + (smp < sv.samplerCount ? smp : 0)];
+        CK(cudaMemcpyAsync(in.p, texelXY, (size_t)count * 8, cudaMemcpyHostToDevice, st));
+        k_probe_texels<<<blocksFor(count, 128), 128, 0, st>>>(slot, reinterpret_cast<const int2 *>(in.p), count, out.p);
+    }
+    else
+    {
+        CK(cudaMemcpyAsync(in.p, uv, (size_t)count * 8, cudaMemcpyHostToDevice, st));
+        k_probe_sample<<<blocksFor(count, 128), 128, 0, st>>>(sv, textureSampler, in.p, count, exact, out.p);
+    }
+    c->kernelLaunches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(outRgba, out.p, (size_t)count * 16, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    out.release();
+    in.release();
+    return PRT_OK;
+}
+
+// ---- debug read-back of the built structures (tests validate the GPU builder's output on the host) --------
+extern "C" prt_status prt_debug_read_blas(prt_ctx *c, uint32_t modelIndex, void *nodesOut, uint64_t nodesBytes, void *trisOut,
+                                          uint64_t trisBytes, uint32_t *nodeCount, uint32_t *triCount)
+{
+    REQUIRE(c && modelIndex < c->blas.size(), "prt_debug_read_blas");
+    const BlasRes &b = c->blas[modelIndex];
+    if (nodeCount) *nodeCount = b.nodeCount;
+    if (triCount) *triCount = b.triCount;
+    CK(cudaSetDevice(c->cfg.device));
+    if (nodesOut)
+    {
+        REQUIRE(nodesBytes >= (uint64_t)b.nodeCount * sizeof(WideNode), "node buffer too small");
+        CK(cudaMemcpyAsync(nodesOut, b.nodes, (size_t)b.nodeCount * sizeof(WideNode), cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (trisOut)
+    {
+        REQUIRE(trisBytes >= (uint64_t)b.triCount * sizeof(TriRec), "triangle buffer too small");
+        CK(cudaMemcpyAsync(trisOut, b.tris, (size_t)b.triCount * sizeof(TriRec), cudaMemcpyDeviceToHost, c->stream));
+    }
+    CK(cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_debug_read_tlas(prt_ctx *c, void *nodesOut, uint64_t nodesBytes, void *instOut, uint64_t instBytes,
+                                          uint32_t *instanceCount)
+{
+    REQUIRE(c, "prt_debug_read_tlas");
+    const uint32_t n = c->tlasInstances;
+    if (instanceCount) *instanceCount = n;
+    CK(cudaSetDevice(c->cfg.device));
+    if (nodesOut && n)
+    {
+        REQUIRE(nodesBytes >= (uint64_t)n * sizeof(WideNode), "node buffer too small (instanceCount nodes)");
+        CK(cudaMemcpyAsync(nodesOut, c->tlasNodes.p, (size_t)n * sizeof(WideNode), cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (instOut && n)
+    {
+        REQUIRE(instBytes >= (uint64_t)n * sizeof(InstRec), "instance buffer too small");
+        CK(cudaMemcpyAsync(instOut, c->tlasInst.p, (size_t)n * sizeof(InstRec), cudaMemcpyDeviceToHost, c->stream));
+    }
+    CK(cudaStreamSynchronize(c->stream));
     return PRT_OK;
 }

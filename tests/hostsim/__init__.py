@@ -46,6 +46,7 @@ def lib():
         l.hs_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_int]
         l.hs_render.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_int, C.c_void_p]
         l.hs_bc7_decode_block.restype = C.c_int
+        l.hs_replace_blas.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
         _lib = l
     return _lib
 
@@ -70,6 +71,10 @@ class HostSim:
             self.close()
         except Exception:
             pass
+
+    def replace_blas(self, model, nodes, tris):
+        nodes, tris = np.ascontiguousarray(nodes), np.ascontiguousarray(tris)
+        lib().hs_replace_blas(self._ctx, model, _p(nodes), nodes.shape[0], _p(tris), tris.shape[0])
 
     def stats(self):
         out = np.zeros(8, np.uint64)

@@ -90,7 +90,6 @@ struct HostBlas
 struct hs_ctx
 {
     orc_scene s;
-    std::vector<std::vector<uint8_t>> decoded;
     std::vector<TexSlot> slots;
     std::vector<HostBlas> blas;
     std::vector<WideNode> tlasNodes;
@@ -126,6 +125,52 @@ template <typename F> static void parallelFor(uint32_t count, int threads, F &&f
     for (auto &t : pool) t.join();
 }
 
+static void buildTlasHost(hs_ctx *c)
+{
+    const orc_scene &s = c->s;
+    c->tlasNodes.clear();
+    c->tlasInst.clear();
+    c->as = Accel{};
+    // TLAS (prt_build_tlas)
+    const prt_tlas_instance *inst = (const prt_tlas_instance *)s.tlasInstances;
+    std::vector<InstRec> recs;
+    std::vector<Box> boxes;
+    V3 lo = {3.4e38f, 3.4e38f, 3.4e38f}, hi = {-3.4e38f, -3.4e38f, -3.4e38f};
+    for (uint32_t i = 0; i < s.instanceCount; ++i)
+    {
+        if (inst[i].blasReference == 0) continue;
+        const uint64_t model = inst[i].blasReference - 1;
+        if (model >= s.modelCount || c->blas[model].tris.empty()) continue;
+        TlasInput ti;
+        memcpy(ti.transform, inst[i].transform, sizeof(ti.transform));
+        ti.customIndexAndMask = inst[i].customIndexAndMask;
+        ti.index = i;
+        ti.nodes = c->blas[model].nodes.data();
+        ti.tris = c->blas[model].tris.data();
+        InstRec r;
+        V3 l, h;
+        tlasInstanceRecord(ti, r, l, h);
+        recs.push_back(r);
+        boxes.push_back(makeBox(l, h));
+        lo = vmin(lo, l);
+        hi = vmax(hi, h);
+    }
+    if (!recs.empty())
+    {
+        HostBvh h = buildHierarchyHost(boxes, lo, hi, true);
+        if (h.primOut.size() != recs.size()) c->buildError = 2;
+        else
+        {
+            c->tlasLevels = h.levels;
+            c->tlasNodes = std::move(h.nodes);
+            c->tlasInst.resize(recs.size());
+            for (size_t i = 0; i < recs.size(); ++i) c->tlasInst[i] = recs[h.primOut[i]];
+            c->as.tlasNodes = c->tlasNodes.data();
+            c->as.instances = c->tlasInst.data();
+        }
+    }
+}
+
 extern "C" {
 
 hs_ctx *hs_create(const orc_scene *scene, int exactMaterialFilter)
@@ -133,36 +178,18 @@ hs_ctx *hs_create(const orc_scene *scene, int exactMaterialFilter)
     hs_ctx *c = new hs_ctx;
     c->s = *scene;
     const orc_scene &s = c->s;
-    // textures: decode level 0 with the product's BC7 decoder
-    c->decoded.resize(s.textureCount);
+    // texture slots point at the cached payloads: the software filter decodes texels on the fly
     const uint32_t ns = std::max(s.samplerCount, 1u);
     c->slots.assign((size_t)s.textureCount * ns, TexSlot{});
     for (uint32_t t = 0; t < s.textureCount; ++t)
     {
         const orc_texture &tx = s.textures[t];
         if (!tx.data || !tx.width) continue;
-        std::vector<uint8_t> &img = c->decoded[t];
-        img.resize((size_t)tx.width * tx.height * 4);
-        if (tx.format == 0) memcpy(img.data(), tx.data, img.size());
-        else
-        {
-            const uint32_t bw = (tx.width + 3) / 4, bh = (tx.height + 3) / 4;
-            const uint64_t *blocks = (const uint64_t *)tx.data;
-            for (uint32_t b = 0; b < bw * bh; ++b)
-            {
-                uint32_t px[16];
-                bc7DecodeBlock(blocks[2 * b], blocks[2 * b + 1], px);
-                const uint32_t bx = b % bw, by = b / bw;
-                for (uint32_t y = 0; y < 4; ++y)
-                    for (uint32_t x = 0; x < 4; ++x)
-                        if (bx * 4 + x < tx.width && by * 4 + y < tx.height)
-                            memcpy(&img[((size_t)(by * 4 + y) * tx.width + bx * 4 + x) * 4], &px[y * 4 + x], 4);
-            }
-        }
         for (uint32_t sm = 0; sm < ns; ++sm)
         {
             TexSlot &slot = c->slots[(size_t)t * ns + sm];
-            slot.rgba = img.data();
+            slot.payload = (const uint8_t *)tx.data;
+            slot.format = tx.format;
             slot.width = tx.width; slot.height = tx.height;
             const prt_sampler_desc sd = s.samplerCount ? ((const prt_sampler_desc *)s.samplers)[sm] : prt_sampler_desc{1, 1, 0, 0};
             slot.magFilter = sd.magFilter; slot.addressU = sd.addressU; slot.addressV = sd.addressV;
@@ -220,48 +247,21 @@ hs_ctx *hs_create(const orc_scene *scene, int exactMaterialFilter)
         c->blas[m].tris.resize(tris.size());
         for (size_t i = 0; i < tris.size(); ++i) c->blas[m].tris[i] = tris[h.primOut[i]];
     }
-    // TLAS (prt_build_tlas)
-    const prt_tlas_instance *inst = (const prt_tlas_instance *)s.tlasInstances;
-    std::vector<InstRec> recs;
-    std::vector<Box> boxes;
-    V3 lo = {3.4e38f, 3.4e38f, 3.4e38f}, hi = {-3.4e38f, -3.4e38f, -3.4e38f};
-    for (uint32_t i = 0; i < s.instanceCount; ++i)
-    {
-        if (inst[i].blasReference == 0) continue;
-        const uint64_t model = inst[i].blasReference - 1;
-        if (model >= s.modelCount || c->blas[model].tris.empty()) continue;
-        TlasInput ti;
-        memcpy(ti.transform, inst[i].transform, sizeof(ti.transform));
-        ti.customIndexAndMask = inst[i].customIndexAndMask;
-        ti.index = i;
-        ti.nodes = c->blas[model].nodes.data();
-        ti.tris = c->blas[model].tris.data();
-        InstRec r;
-        V3 l, h;
-        tlasInstanceRecord(ti, r, l, h);
-        recs.push_back(r);
-        boxes.push_back(makeBox(l, h));
-        lo = vmin(lo, l);
-        hi = vmax(hi, h);
-    }
-    if (!recs.empty())
-    {
-        HostBvh h = buildHierarchyHost(boxes, lo, hi, true);
-        if (h.primOut.size() != recs.size()) c->buildError = 2;
-        else
-        {
-            c->tlasLevels = h.levels;
-            c->tlasNodes = std::move(h.nodes);
-            c->tlasInst.resize(recs.size());
-            for (size_t i = 0; i < recs.size(); ++i) c->tlasInst[i] = recs[h.primOut[i]];
-            c->as.tlasNodes = c->tlasNodes.data();
-            c->as.instances = c->tlasInst.data();
-        }
-    }
+    buildTlasHost(c);
     return c;
 }
 
 void hs_destroy(hs_ctx *c) { delete c; }
+
+// Swap in a BLAS built elsewhere (read back from the GPU with prt_debug_read_blas) and rebuild the TLAS:
+// lets the tests traverse the GPU builder's output with the CPU copy of the traversal code.
+void hs_replace_blas(hs_ctx *c, uint32_t model, const void *nodes, uint32_t nodeCount, const void *tris, uint32_t triCount)
+{
+    HostBlas &b = c->blas[model];
+    b.nodes.assign((const WideNode *)nodes, (const WideNode *)nodes + nodeCount);
+    b.tris.assign((const TriRec *)tris, (const TriRec *)tris + triCount);
+    buildTlasHost(c);
+}
 
 // out[0..7]: buildError, blas wide nodes, blas tris, tlas wide nodes, tlas instances, blas levels, tlas levels, 0
 void hs_stats(hs_ctx *c, uint64_t *out)
@@ -343,7 +343,14 @@ void hs_render(hs_ctx *c, const void *pcIn, uint32_t width, uint32_t height, uin
                     traceRay<false, true>(c->as, c->sv, ray.o, ray.d, ray.tMin, ray.tMax, seed, h, &tc);
                     nc++;
                     ShadeResult r;
-                    shadePath(c->sv, pc, bounce, ray.d, h.drawInstanceIndex, h.primitiveID, h.u, h.v, rng, throughput, color, r);
+                    SurfaceGeom geom;
+                    MaterialTaps taps;
+                    if (h.drawInstanceIndex != MISS_INDEX)
+                    {
+                        geom = surfaceGeometry(c->sv, h.drawInstanceIndex, h.primitiveID, h.u, h.v);
+                        taps = softwareMaterialTaps(c->sv, geom.materialIndex, geom.v.TexCoord0);
+                    }
+                    shadePath(c->sv, pc, bounce, ray.d, h.drawInstanceIndex, h.primitiveID, geom, taps, rng, throughput, color, r);
                     if (h.drawInstanceIndex != MISS_INDEX) nsh++;
                     if (r.shadowRay)
                     {

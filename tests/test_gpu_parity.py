@@ -1,0 +1,264 @@
+"""-m gpu: the CUDA path, called through the C ABI (libprt_b200.so), against the CPU oracle.
+
+Bar (BASELINE.json north_star): primary-ray (drawInstanceIndex, primitiveID) bit-exact, ties excluded;
+radiance within the stated tolerance at identical PCG seeds.
+"""
+import numpy as np
+import pytest
+
+import oracle
+from prosper_b200 import rt_reference as rt
+from prosper_b200 import scene_data as sd
+
+pytestmark = pytest.mark.gpu
+
+# any-hit decisions closer than this to their threshold are "ties" (device powf vs host pow differ by ulps)
+ALPHA_TIE_MARGIN = 1e-4
+
+
+def _world(scene, w, h, flags=rt.CFG_COUNTERS | rt.CFG_EXACT_FILTER, spl=1):
+    world = rt.World(scene, max_width=w, max_height=h, samples_per_launch=spl, flags=flags)
+    world.updateBuffers()
+    world.buildAccelerationStructures()
+    return world
+
+
+def _id_mismatch(a, b):
+    return (a["drawInstanceIndex"] != b["drawInstanceIndex"]) | (a["primitiveID"] != b["primitiveID"])
+
+
+def _check_primary(scene, w, h, frames=(1, 2, 4095)):
+    world = _world(scene, w, h)
+    orc = oracle.Oracle(scene)
+    for f in frames:
+        pc = sd.reference_pc(frame_index=f)
+        ho, margin = orc.trace_primary(pc, w, h)
+        hg = world.trace_primary(pc, w, h)
+        tie = margin < ALPHA_TIE_MARGIN
+        bad = _id_mismatch(ho, hg) & ~tie
+        assert bad.sum() == 0, f"frame {f}: {bad.sum()} primary hit IDs differ (first at {np.nonzero(bad)[0][:5]})"
+        assert tie.mean() < 1e-3
+        same = ~_id_mismatch(ho, hg)
+        assert np.array_equal(ho["bary"][same], hg["bary"][same]), "barycentrics must be bit-exact (exact contract)"
+    c = world.counters()
+    assert c["stackOverflows"] == 0
+    world.close()
+
+
+def test_primary_ids_test_scene(test_scene):
+    _check_primary(test_scene, 96, 64)
+
+
+def test_primary_ids_test_scene_bc7(test_scene_bc7):
+    _check_primary(test_scene_bc7, 96, 64)
+
+
+def test_primary_ids_helmet(small_helmet):
+    _check_primary(small_helmet, 128, 128, frames=(1,))
+
+
+def test_primary_ids_atrium(small_atrium):
+    _check_primary(small_atrium, 160, 90, frames=(1, 7))
+
+
+def test_primary_ids_atrium_instanced(small_atrium_instanced):
+    _check_primary(small_atrium_instanced, 160, 90, frames=(1,))
+
+
+def test_dof_primary(test_scene):
+    w, h = 96, 64
+    world = _world(test_scene, w, h)
+    orc = oracle.Oracle(test_scene)
+    flags = sd.FLAG_ACCUMULATE | sd.FLAG_CLAMP_INDIRECT | sd.FLAG_IBL | sd.FLAG_SKIP_HISTORY | sd.FLAG_DOF
+    pc = sd.reference_pc(frame_index=3, flags=flags, aperture=0.05, focus_distance=3.0, focal_len=0.035)
+    ho, margin = orc.trace_primary(pc, w, h)
+    hg = world.trace_primary(pc, w, h)
+    # thin-lens rays use cos/sin (not in the exact contract): IDs agree except on silhouettes
+    assert _id_mismatch(ho, hg).mean() < 0.01
+    world.close()
+
+
+def test_random_rays_closest_and_shadow(test_scene, small_atrium_instanced):
+    rng = np.random.default_rng(5)
+    for scene in (test_scene, small_atrium_instanced):
+        world = _world(scene, 64, 64)
+        orc = oracle.Oracle(scene)
+        n = 20000
+        o = np.zeros((n, 4), np.float32)
+        d = np.zeros((n, 4), np.float32)
+        o[:, :3] = rng.uniform(-3, 3, (n, 3)) + np.array([0, 2, 0])
+        v = rng.normal(size=(n, 3))
+        d[:, :3] = v / np.linalg.norm(v, axis=1, keepdims=True)
+        o[:, 3] = rng.uniform(0, 0.2, n)
+        d[:, 3] = np.where(rng.random(n) < 0.5, np.inf, rng.uniform(0.5, 10, n))
+        # axis-parallel and degenerate directions
+        d[:50, 0:3] = (0, -1, 0)
+        d[50:100, 0:3] = (1, 0, 0)
+        d[100:110, 0:3] = (0, 0, 0)
+        seeds = rng.integers(0, 2**32, n, dtype=np.uint64).astype(np.uint32)
+        ho, margin = orc.trace_rays(o, d, seeds)
+        hg = world.trace_rays(o, d, seeds)
+        bad = _id_mismatch(ho, hg) & ~(margin < ALPHA_TIE_MARGIN)
+        assert bad.sum() == 0
+        so, smargin = orc.trace_rays(o, d, seeds, shadow=True)
+        sg = world.trace_rays(o, d, seeds, shadow=True)
+        occ_o = so["drawInstanceIndex"] != sd.MISS
+        occ_g = sg["drawInstanceIndex"] != sd.MISS
+        assert ((occ_o != occ_g) & ~(smargin < ALPHA_TIE_MARGIN)).sum() == 0
+        assert world.counters()["stackOverflows"] == 0
+        world.close()
+
+
+def _rel_rmse(a, b, floor=1e-2):
+    la = a[..., :3] @ np.array([0.2126, 0.7152, 0.0722], np.float32)
+    lb = b[..., :3] @ np.array([0.2126, 0.7152, 0.0722], np.float32)
+    return float(np.sqrt(np.mean(((la - lb) / (np.abs(lb) + floor)) ** 2)))
+
+
+@pytest.mark.parametrize("spl", [1, 4])
+def test_render_exact_filter_matches_oracle(test_scene, spl):
+    """With the software filter on both sides only transcendental ulps differ: tight tolerance."""
+    w, h, spp = 96, 64, 8
+    world = _world(test_scene, w, h, spl=spl)
+    r = rt.RtReference()
+    r.init(world)
+    r.drawUi(maxBounces=4)
+    out = r.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=spp).illumination_f32()
+    ref, counters = oracle.Oracle(test_scene).render(sd.reference_pc(max_bounces=4), w, h, spp)
+    assert np.all(out[..., 3] == spp)
+    assert _rel_rmse(out, ref) < 0.02  # tolerance: 2 % relRMSE on luminance, floor 1e-2
+    assert abs(out[..., :3].mean() - ref[..., :3].mean()) < 0.005 * ref[..., :3].mean()
+    c = world.counters()
+    # rays differ only where a float-level difference flips a discrete decision
+    assert abs(c["closestRays"] - int(counters[0])) <= 0.002 * int(counters[0])
+    assert abs(c["shadowRays"] - int(counters[1])) <= 0.005 * int(counters[1])
+    assert c["pixelSamples"] == w * h * spp and c["stackOverflows"] == 0
+    world.close()
+
+
+def test_render_hardware_filter_within_tolerance(test_scene_bc7):
+    w, h, spp = 96, 64, 16
+    world = _world(test_scene_bc7, w, h, flags=0, spl=4)
+    r = rt.RtReference()
+    r.init(world)
+    r.drawUi(maxBounces=4)
+    out = r.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=spp).illumination_f32()
+    ref, _ = oracle.Oracle(test_scene_bc7).render(sd.reference_pc(max_bounces=4), w, h, spp)
+    assert _rel_rmse(out, ref) < 0.03
+    assert abs(out[..., :3].mean() - ref[..., :3].mean()) < 0.005 * ref[..., :3].mean()
+    world.close()
+
+
+def test_accumulation_semantics_and_f16_blit(test_scene):
+    w, h = 64, 48
+    world = _world(test_scene, w, h)
+    r = rt.RtReference()
+    r.init(world)
+    r.drawUi(maxBounces=2)
+    a = r.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=3).illumination_f32()
+    assert np.all(a[..., 3] == 3)
+    # two more frames continue the running mean (frameIndex 4, 5)
+    b = r.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=2).illumination_f32()
+    assert np.all(b[..., 3] == 5)
+    world2 = _world(test_scene, w, h)
+    r2 = rt.RtReference()
+    r2.init(world2)
+    r2.drawUi(maxBounces=2)
+    c = r2.record(world2, (0, 0, w, h), rt.Options(ibl=True), frames=5).illumination_f32()
+    assert np.array_equal(b, c), "3 + 2 frames must equal 5 frames (same frameIndex sequence, same order)"
+    out = r2.record(world2, (0, 0, w, h), rt.Options(ibl=True, colorDirty=True), frames=1)
+    d = out.illumination_f32()
+    assert np.all(d[..., 3] == 1), "colorDirty resets the history (RtRef.cpp:282-284)"
+    f16 = out.illumination()
+    assert np.array_equal(f16, d.astype(np.float16))
+    r2.releasePreserved(world2)
+    e = r2.record(world2, (0, 0, w, h), rt.Options(ibl=True), frames=1).illumination_f32()
+    assert np.all(e[..., 3] == 1)
+    world.close()
+    world2.close()
+
+
+def test_debug_draw_types(test_scene):
+    w, h = 64, 48
+    world = _world(test_scene, w, h)
+    orc = oracle.Oracle(test_scene)
+    for dt in (1, 3, 4, 5, 6, 7, 8, 9, 10):
+        r = rt.RtReference()
+        r.init(world)
+        out = r.record(world, (0, 0, w, h), rt.Options(ibl=True, drawType=dt, colorDirty=True), frames=1).illumination_f32()
+        ref, _ = orc.render(sd.reference_pc(draw_type=dt, max_bounces=6), w, h, 1)
+        assert np.mean(np.abs(out[..., :3] - ref[..., :3]) > 1e-3) < 0.01, f"draw type {dt}"
+    world.close()
+
+
+def test_texture_units_match_software_decode(test_scene_bc7):
+    """Pins what the texture units return for BC7 arrays against the spec decoder (oracle + product)."""
+    scene = test_scene_bc7
+    world = _world(scene, 32, 32, flags=0)
+    orc = oracle.Oracle(scene)
+    rng = np.random.default_rng(3)
+    for tex in range(1, len(scene.textures)):
+        for smp in range(len(scene.samplers)):
+            uv = rng.uniform(-1.5, 2.5, (512, 2)).astype(np.float32)
+            ts = (smp << 24) | tex
+            exact = world.probe_texture(ts, uv, True)
+            hw = world.probe_texture(ts, uv, False)
+            ref = np.array([orc.sample_texture(tex, smp, float(u), float(v)) for u, v in uv])
+            assert np.abs(exact - ref).max() < 1e-6, f"software filter, texture {tex} sampler {smp}"
+            if scene.samplers[smp]["magFilter"] == 1:
+                assert np.abs(hw - ref).max() < 2.5 / 256, f"hardware filter (8-bit weights), texture {tex} sampler {smp}"
+    world.close()
+
+
+def test_bc7_decode_upload_path_matches_native(test_scene_bc7):
+    w, h = 96, 64
+    a = _world(test_scene_bc7, w, h)
+    b = _world(test_scene_bc7, w, h, flags=rt.CFG_COUNTERS | rt.CFG_EXACT_FILTER | rt.CFG_DECODE_BC7)
+    pc = sd.reference_pc(frame_index=2)
+    ha, hb = a.trace_primary(pc, w, h), b.trace_primary(pc, w, h)
+    assert np.array_equal(ha, hb)
+    a.close()
+    b.close()
+
+
+def test_tlas_rebuild_with_moved_instances(small_atrium_instanced):
+    scene = small_atrium_instanced
+    w, h = 160, 90
+    world = _world(scene, w, h)
+    import copy
+    moved = copy.copy(scene)
+    moved.tlas_instances = scene.tlas_instances.copy()
+    moved.transforms = scene.transforms.copy()
+    for i in range(0, len(moved.tlas_instances), 3):
+        m = np.eye(4)
+        m[:3, :] = scene.tlas_instances[i]["transform"]
+        m = sd.trs((0.1 * (i % 5), 0.05, 0), (0, 1, 0), 0.2) @ m
+        moved.transforms[i] = sd.instance_transforms(m)
+        moved.tlas_instances[i]["transform"] = moved.transforms[i]["modelToWorld"]
+    world.updateBuffers(moved)
+    world.buildTlas(moved.tlas_instances)  # per-frame rebuild, BLAS untouched (World.cpp:749-802)
+    pc = sd.reference_pc()
+    hg = world.trace_primary(pc, w, h)
+    ho, margin = oracle.Oracle(moved).trace_primary(pc, w, h)
+    assert (_id_mismatch(ho, hg) & ~(margin < ALPHA_TIE_MARGIN)).sum() == 0
+    t = world.timings()
+    assert t["lastTlasMs"] > 0 and t["lastTlasLaunches"] > 0
+    world.close()
+
+
+def test_errors_are_loud(test_scene):
+    world = rt.World(test_scene, max_width=32, max_height=32)
+    pc = sd.reference_pc()
+    with pytest.raises(RuntimeError):
+        world.trace_primary(pc, 32, 32)  # camera / lights not set
+    world.updateBuffers()
+    world.buildAccelerationStructures()
+    with pytest.raises(RuntimeError):
+        rt.RtReference().record(world, (0, 0, 32, 32))  # before init
+    r = rt.RtReference()
+    r.init(world)
+    with pytest.raises(RuntimeError):
+        r.record(world, (1, 0, 32, 32))  # offset must be 0 (RtRef.cpp:327)
+    with pytest.raises(RuntimeError):
+        r.record(world, (0, 0, 64, 64))  # larger than prt_config
+    world.close()
