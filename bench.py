@@ -1,0 +1,456 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the RtReference path (BASELINE.json metric: Mrays/s and spp/s, 1080p
+Sponza-class scene, 4 bounces) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One STEP = one pass of the hot path over one batch: `--spp` (default 64) frames of the 1920x1080
+procedural atrium (BASELINE.json configs[1]; Sponza itself is not in the image)
+through RtReference.record, 4 bounces, reference defaults otherwise. A ray is one
+traceRayEXT equivalent (closest or shadow). Under torchrun every rank renders its own `spp` frame
+indices of the same image (weak scaling by sample) and one NCCL reduce of the fp32 sum
+image per step lands the result on rank 0, inside the timed region.
+
+Printed (rank 0, ONE JSON line): `value` = rays of all ranks / max-over-ranks device time with the scene
+and per-frame buffers resident in HBM; `e2e` = the same metric through the host-facing call sequence the
+reference's frame loop makes (World.updateBuffers + TLAS rebuild from host instance records + record +
+read-back of the fp16 illumination to host), host<->device copies inside the timed region;
+`roofline` for the dominant kernel (k_trace_closest) from the integer counters of an instrumented,
+untimed run of the same step; `cpu_baseline` = the CPU oracle (oracle/, kind "port") on a bounded sample.
+
+`--impl reference` times the CPU oracle alone (there is no buildable reference implementation of this
+path: it is GLSL on a Vulkan RT driver) on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WIDTH, HEIGHT, BOUNCES = 1920, 1080, 4
+SAMPLE_W, SAMPLE_H = 480, 270  # CPU sample: the same camera at 1/16 of the pixels
+METRIC = "Mrays/s (closest + shadow rays), 1080p Sponza-class atrium, 4 bounces"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
+    ap.add_argument("--spp", type=int, default=64, help="frames per step (configs[1]: 64)")
+    ap.add_argument("--samples-per-launch", type=int, default=4)
+    ap.add_argument("--tex-size", type=int, default=1024)
+    ap.add_argument("--detail", type=float, default=1.0)
+    ap.add_argument("--lights", type=int, default=0, help="configs[2]: 1024 point/spot lights")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    return ap.parse_args()
+
+
+def build_scene(args, width=WIDTH, height=HEIGHT):
+    from prosper_b200 import scene_zoo
+    return scene_zoo.atrium(width, height, seed=1, lights=args.lights, tex_size=args.tex_size, detail=args.detail)
+
+
+def workload_config(args, scene, n_gpus):
+    return {
+        "workload": f"atrium(seed=1) {scene.triangle_count} tris, {len(scene.textures) - 1} BC7 textures {args.tex_size}^2, "
+                    f"alpha-MASK foliage, {WIDTH}x{HEIGHT}, {args.spp} spp per step per GPU, {BOUNCES} bounces, "
+                    f"{len(scene.point_lights)}+{len(scene.spot_lights)} point/spot lights + sun + sky IBL",
+        "scene": "procedural stand-in for Sponza (BASELINE.json configs[1]); no Sponza asset in the image",
+        "width": WIDTH, "height": HEIGHT, "spp_per_step_per_gpu": args.spp, "max_bounces": BOUNCES,
+        "samples_per_launch": args.samples_per_launch,
+        "partition": "by sample (frame indices), scene replicated" if n_gpus > 1 else "single GPU",
+        "l2": "inputs larger than L2: path/ray/hit queues of one launch = "
+              f"{args.samples_per_launch * WIDTH * HEIGHT * 232 / 1e6:.0f} MB streamed per bounce (L2 126 MB)",
+    }
+
+
+# ---- clocks during the timed region (B200_PROFILING.md recipe) ---------------------------------------------------
+class ClockSampler:
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device = device
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        self.thread.join(timeout=2)
+        sm, smax, power, reasons = [], [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower() == "active":
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)), "power_w_max": float(max(power)),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---- CPU arm: the oracle on a bounded sample --------------------------------------------------------------------
+def cpu_sample_scene(args, scene=None):
+    """The same scene seen by the same camera at SAMPLE_W x SAMPLE_H: width and height enter the generator only
+    through the camera's aspect ratio, which the sample keeps, so the 1080p scene object serves both."""
+    return scene if scene is not None else build_scene(args, SAMPLE_W, SAMPLE_H)
+
+
+def oracle_step(orc, spp, frame_index):
+    """One bounded CPU step: `spp` frames of the sample. Returns (rays, pixel-samples, seconds)."""
+    from prosper_b200 import scene_data as sd
+    pc = sd.reference_pc(frame_index=frame_index, max_bounces=BOUNCES)
+    t = time.perf_counter()
+    _, cnt = orc.render(pc, SAMPLE_W, SAMPLE_H, spp, threads=0)  # threads=0: all hardware threads
+    dt = time.perf_counter() - t
+    return int(cnt[0] + cnt[1]), int(cnt[3]), dt
+
+
+def calibrate_oracle(orc, target_s=12.0):
+    """Chooses how many frames of the sample make about `target_s` seconds of CPU work."""
+    rays, _, dt = oracle_step(orc, 1, 1)
+    return max(1, min(64, int(target_s / max(dt, 1e-3)))), rays / dt / 1e6
+
+
+def cpu_baseline(args, scene=None):
+    import oracle
+    cores = os.cpu_count() or 1
+    orc = oracle.Oracle(cpu_sample_scene(args, scene))
+    spp, _ = calibrate_oracle(orc)
+    rays, samples, dt = oracle_step(orc, spp, 1)
+    out = {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "port",
+           "spp_per_s_1080p_equiv": samples / dt / (WIDTH * HEIGHT),
+           "bvh_build_s": orc.bvh_build_seconds,
+           "sample": f"{SAMPLE_W}x{SAMPLE_H} (same camera, 1/16 of the pixels) x {spp} spp, {BOUNCES} bounces, "
+                     f"{rays} rays in {dt:.1f} s, std::thread over {cores} hardware threads"}
+    orc.close()
+    return out
+
+
+def run_reference(args):
+    """--impl reference: the reference's own path cannot be built or run here (GLSL + Vulkan RT driver), so its CPU
+    arm is the oracle port, all host threads, on a bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    cores = os.cpu_count() or 1
+    scene = cpu_sample_scene(args)
+    orc = oracle.Oracle(scene)
+    total_steps = max(1, args.steps + args.warmup)
+    spp, _ = calibrate_oracle(orc, target_s=min(12.0, 150.0 / total_steps))
+    for w in range(args.warmup):
+        oracle_step(orc, spp, 1)
+    rays = samples = 0
+    secs = 0.0
+    for k in range(args.steps):
+        r, s, dt = oracle_step(orc, spp, 1 + k * spp)
+        rays += r; samples += s; secs += dt
+    orc.close()
+    value = rays / secs / 1e6
+    cfg = workload_config(args, build_scene_stub(scene), args.gpus)
+    sample = (f"{SAMPLE_W}x{SAMPLE_H} (same camera, 1/16 of the pixels) x {spp} spp per step, {BOUNCES} bounces, "
+              f"std::thread over {cores} hardware threads")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": secs / max(1, args.steps) * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+        "spp_per_s": samples / secs / (WIDTH * HEIGHT),
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "CPU oracle (port of the reference's shaders + its own BVH); the reference's GLSL/Vulkan path is "
+                "unavailable on this box",
+    }), flush=True)
+
+
+class build_scene_stub:
+    """workload_config wants the full-size scene's counts; the sample scene has the same geometry and textures."""
+
+    def __init__(self, scene):
+        self.triangle_count = scene.triangle_count
+        self.textures = scene.textures
+        self.point_lights = scene.point_lights
+        self.spot_lights = scene.spot_lights
+
+
+# ---- product arm ----------------------------------------------------------------------------------------------
+# Algorithmic bytes, per unit of work of the traversal kernels:
+B_RAY_IO = 32 + 8 + 16      # ray in (origin+tMin, dir+tMax), ray id (path, seed), hit record out
+B_NODE = 80                 # one compressed 8-wide node
+B_TRI = 48                  # one triangle record (v0, e1, e2 as 3 x float4 with ids in .w)
+B_INST = 80                 # one instance record (3x4 world->object, BLAS pointers, custom index)
+B_ANYHIT = 12 + 3 * 2 + 3 * 4 + 48 + 16  # draw instance + 3 u16 indices + 3 fp16x2 uvs + material + one BC7 block
+
+
+def traversal_bytes(c, shadow):
+    if shadow:
+        rays, nodes, tris, inst, ah = (c["shadowRays"], c["shadowNodesVisited"], c["shadowTrisTested"],
+                                       c["shadowInstancesEntered"], c["shadowAnyHitCalls"])
+        io = 32 + 8 + 16 + 16  # ray, id, contribution in; colour read-modify-write counted once
+    else:
+        rays = c["closestRays"]
+        nodes = c["nodesVisited"] - c["shadowNodesVisited"]
+        tris = c["trisTested"] - c["shadowTrisTested"]
+        inst = c["instancesEntered"] - c["shadowInstancesEntered"]
+        ah = c["anyHitCalls"] - c["shadowAnyHitCalls"]
+        io = B_RAY_IO
+    return rays * io + nodes * B_NODE + tris * B_TRI + inst * B_INST + ah * B_ANYHIT
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (copy bandwidth measured on this pool's B200)"
+    except (OSError, KeyError, ValueError):
+        return 6559.0, "fallback: B200_PROFILING.md measured copy bandwidth"
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from prosper_b200 import rt_reference as rt
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: prosper_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world_size > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if world_size * args.spp > rt.RtReference.sFramePeriod - 1:
+        raise RuntimeError("spp x ranks exceeds the reference's frame-index period (RtRef.cpp:31)")
+
+    scene = build_scene(args)
+    world = rt.World(scene, device=local_rank, max_width=WIDTH, max_height=HEIGHT,
+                     samples_per_launch=args.samples_per_launch, flags=0)
+    world.updateBuffers()
+    world.buildAccelerationStructures()
+    world.synchronize()
+    build_t = world.timings()
+    stream = torch.cuda.ExternalStream(world.stream_ptr(), device=torch.device("cuda", local_rank))
+    pass_ = rt.RtReference()
+    pass_.init(world)
+    pass_.drawUi(maxBounces=BOUNCES)
+    area = (0, 0, WIDTH, HEIGHT)
+    opts = rt.Options(ibl=True)
+    pixels = WIDTH * HEIGHT
+    torch.cuda.set_stream(stream)  # NCCL work and the timing events are ordered on the library's stream
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def render_step():
+        """rank g renders frame indices g*spp+1 .. (g+1)*spp into a fresh accumulation (RNG seed = (px, frameIndex),
+        main.rgen:229); N>1: one reduce of the (sum, count) image to rank 0."""
+        pass_.m_frameIndex = rank * args.spp
+        pass_.m_accumulationDirty = True
+        out = pass_.record(world, area, opts, frames=args.spp)
+        if world_size > 1:
+            summed = world.export_sum_tensor()  # fp32 (sum.rgb, count) image, zero-copy view of library memory
+            dist.reduce(summed, dst=0, op=dist.ReduceOp.SUM)  # the stream waits for the collective (blocking wait)
+            if rank == 0:
+                world.import_sum(summed.data_ptr())
+        return out
+
+    def e2e_step():
+        """What one reference frame loop iteration does around the pass: World::updateBuffers (ring uploads),
+        the per-frame TLAS rebuild from host instance records, record, and the consumer reading the fp16 image."""
+        world.updateBuffers()
+        world.buildTlas(scene.tlas_instances)
+        out = render_step()
+        img = out.illumination() if rank == 0 or world_size == 1 else None
+        world.synchronize()
+        return img
+
+    def max_over_ranks(x):
+        if world_size == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world_size == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # ---- device-resident timing -------------------------------------------------------------------------------
+    for _ in range(args.warmup):
+        render_step()
+    barrier()
+    world.reset_counters()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        render_step()
+    ev1.record(stream)
+    barrier()
+    wall_ms = (time.perf_counter() - wall0) * 1e3
+    step_ms = ev0.elapsed_time(ev1) / args.steps
+    t = world.timings()  # stage split of the LAST step
+    stage_ms = {"closest": t["lastTraceClosestMs"], "shade": t["lastShadeMs"], "shadow": t["lastTraceShadowMs"]}
+    stage_launches = {"closest": t["lastTraceClosestLaunches"], "shade": t["lastShadeLaunches"],
+                      "shadow": t["lastTraceShadowLaunches"]}
+    record_ms_last = t["lastRecordMs"]
+    clk = clocks.stop() if rank == 0 else None
+    c = world.counters()
+    rays_rank = c["closestRays"] + c["shadowRays"]
+    samples_rank = c["pixelSamples"]
+    launches = c["kernelLaunches"]
+    step_ms = max_over_ranks(step_ms)
+    rays_all = sum_over_ranks(rays_rank)
+    samples_all = sum_over_ranks(samples_rank)
+    value = rays_all / (step_ms * args.steps) / 1e3  # Mrays/s
+
+    # ---- end to end through the host-facing calls ----------------------------------------------------------------
+    for _ in range(min(args.warmup, 2)):
+        e2e_step()
+    barrier()
+    world.reset_counters()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    ce = world.counters()
+    e2e_rays = sum_over_ranks(ce["closestRays"] + ce["shadowRays"])
+    h2d = sum(int(a.nbytes) for a in (scene.draw_instances, scene.transforms, scene.directional_light, scene.point_lights,
+                                      scene.spot_lights, scene.camera, scene.tlas_instances))
+    h2d += 2 * 16  # light counts ride with the light arrays (World.cpp:500-536)
+    d2h = pixels * 8
+    e2e = {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+           "ms_per_step": e2e_s / args.steps * 1e3,
+           "path": "World.updateBuffers + World.buildTlas (host instance records) + RtReference.record + "
+                   "Output.illumination() fp16 read-back to host"}
+
+    # ---- TLAS rebuild metric ("ms per TLAS rebuild", App.cpp:575 BuildTLAS scope) ---------------------------------
+    tlas_ms = []
+    for _ in range(5):
+        world.buildTlas(scene.tlas_instances)
+        tlas_ms.append(world.timings()["lastTlasMs"])
+    tlas = {"ms_per_rebuild": float(np.median(tlas_ms)), "instances": int(len(scene.tlas_instances)),
+            "launches": int(world.timings()["lastTlasLaunches"]), "blas_build_ms_last": build_t["lastBlasMs"]}
+    world.close()
+
+    # ---- roofline of the dominant kernel from an instrumented (untimed) run of the same step -----------------------
+    roofline = None
+    breakdown = None
+    if rank == 0 and not args.no_roofline:
+        cw = rt.World(scene, device=local_rank, max_width=WIDTH, max_height=HEIGHT,
+                      samples_per_launch=args.samples_per_launch, flags=rt.CFG_COUNTERS)
+        cw.updateBuffers()
+        cw.buildAccelerationStructures()
+        cp = rt.RtReference()
+        cp.init(cw)
+        cp.drawUi(maxBounces=BOUNCES)
+        cp.m_frameIndex = 0
+        cp.record(cw, area, opts, frames=args.spp)
+        cw.synchronize()
+        cc = cw.counters()
+        stats = cw.bvh_stats()
+        cw.close()
+        peak, peak_src = measured_peak_gbs()
+        by_closest, by_shadow = traversal_bytes(cc, False), traversal_bytes(cc, True)
+        n_launch = max(1, stage_launches["closest"])
+        achieved = by_closest / (stage_ms["closest"] * 1e-3) / 1e9 if stage_ms["closest"] > 0 else 0.0
+        roofline = {"kernel": "k_trace_closest<false>", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": None,
+                    "algorithmic_bytes_per_launch": by_closest / n_launch,
+                    "avg_launch_ms": stage_ms["closest"] / n_launch, "launches_per_step": n_launch,
+                    "bytes_per_closest_ray": by_closest / max(1, cc["closestRays"]),
+                    "peak_source": peak_src, "frac_of_nominal_8000": achieved / 8000.0,
+                    "note": "algorithmic = requested bytes from exact integer counters (rays, 80 B nodes, 48 B triangles, "
+                            "80 B instances, any-hit fetches); L1/L2 serve most of them, so frac can exceed DRAM traffic"}
+        shadow_gbs = by_shadow / (stage_ms["shadow"] * 1e-3) / 1e9 if stage_ms["shadow"] > 0 else 0.0
+        breakdown = {"record_ms_last_step": record_ms_last, "stage_ms_last_step": stage_ms, "stage_launches": stage_launches,
+                     "shadow_algorithmic_gbs": shadow_gbs, "counters_per_step": cc, "bvh": stats,
+                     "nodes_per_closest_ray": (cc["nodesVisited"] - cc["shadowNodesVisited"]) / max(1, cc["closestRays"]),
+                     "tris_per_closest_ray": (cc["trisTested"] - cc["shadowTrisTested"]) / max(1, cc["closestRays"]),
+                     "nodes_per_shadow_ray": cc["shadowNodesVisited"] / max(1, cc["shadowRays"]),
+                     "tris_per_shadow_ray": cc["shadowTrisTested"] / max(1, cc["shadowRays"])}
+
+    cpu = None
+    if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(args, scene)
+
+    if world_size > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+    line = {
+        "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": workload_config(args, scene, world_size),
+        "spp_per_s": samples_all / pixels / (step_ms * args.steps * 1e-3),
+        "rays_per_step": rays_all / args.steps, "wall_ms_per_step": wall_ms / args.steps,
+        "e2e": e2e, "gpu_launches": int(launches), "clocks": clk, "tlas": tlas,
+    }
+    if roofline is not None:
+        line["roofline"] = roofline
+        line["breakdown"] = breakdown
+    if cpu is not None:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

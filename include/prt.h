@@ -144,6 +144,9 @@ typedef struct prt_counters {
     uint64_t pixelSamples;  /* rgen invocations */
     uint64_t kernelLaunches;
     uint64_t stackOverflows; /* traversal stack overflows (must stay 0; checked by the tests) */
+    /* the part of nodesVisited / trisTested / instancesEntered / anyHitCalls spent by shadow rays
+     * (so closest-ray traffic = total - shadow part; bench.py's per-kernel roofline needs the split) */
+    uint64_t shadowNodesVisited, shadowTrisTested, shadowInstancesEntered, shadowAnyHitCalls;
 } prt_counters;
 prt_status prt_get_counters(prt_ctx *ctx, prt_counters *out);
 prt_status prt_reset_counters(prt_ctx *ctx);
@@ -151,10 +154,14 @@ typedef struct prt_timings {
     float lastRecordMs;   /* CUDA-event time of the last prt_record ("RtReference" scope) */
     float lastTlasMs;     /* ... of the last prt_build_tlas ("BuildTLAS" scope) */
     float lastBlasMs;     /* ... of the last prt_build_blas */
-    float lastTraceClosestMs; /* sum over the trace-closest launches of the last prt_record */
+    float lastTraceClosestMs; /* sum over ALL trace-closest launches of the last prt_record */
     uint32_t lastTraceClosestLaunches;
     uint32_t lastRecordLaunches;
     uint32_t lastTlasLaunches;
+    float lastShadeMs;        /* likewise for the shade and trace-shadow stages */
+    uint32_t lastShadeLaunches;
+    float lastTraceShadowMs;
+    uint32_t lastTraceShadowLaunches;
     uint32_t pad;
 } prt_timings;
 prt_status prt_get_timings(prt_ctx *ctx, prt_timings *out);

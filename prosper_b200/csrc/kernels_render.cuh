@@ -34,7 +34,7 @@ struct PathBuffers
 struct GlobalCounters
 {
     unsigned long long closestRays, shadowRays, nodesVisited, trisTested, instancesEntered, anyHitCalls, shadedHits, textureTaps,
-        pixelSamples, stackOverflows;
+        pixelSamples, stackOverflows, shadowNodes, shadowTris, shadowInstances, shadowAnyHits;
 };
 
 __device__ __forceinline__ uint32_t appendSlot(uint32_t *counter, bool pred)
@@ -49,7 +49,7 @@ __device__ __forceinline__ uint32_t appendSlot(uint32_t *counter, bool pred)
     return base + (uint32_t)__popc(m & ((1u << lane) - 1u));
 }
 
-__device__ __forceinline__ void flushTraceCounters(GlobalCounters *g, const TraceCounters &c)
+__device__ __forceinline__ void flushTraceCounters(GlobalCounters *g, const TraceCounters &c, bool shadow = false)
 {
     const uint32_t n = __reduce_add_sync(0xFFFFFFFFu, c.nodes), t = __reduce_add_sync(0xFFFFFFFFu, c.tris);
     const uint32_t i = __reduce_add_sync(0xFFFFFFFFu, c.instances), a = __reduce_add_sync(0xFFFFFFFFu, c.anyHits);
@@ -61,6 +61,13 @@ __device__ __forceinline__ void flushTraceCounters(GlobalCounters *g, const Trac
         if (i) atomicAdd(&g->instancesEntered, (unsigned long long)i);
         if (a) atomicAdd(&g->anyHitCalls, (unsigned long long)a);
         if (o) atomicAdd(&g->stackOverflows, (unsigned long long)o);
+        if (shadow)
+        {
+            if (n) atomicAdd(&g->shadowNodes, (unsigned long long)n);
+            if (t) atomicAdd(&g->shadowTris, (unsigned long long)t);
+            if (i) atomicAdd(&g->shadowInstances, (unsigned long long)i);
+            if (a) atomicAdd(&g->shadowAnyHits, (unsigned long long)a);
+        }
     }
 }
 
@@ -165,6 +172,13 @@ __global__ void __launch_bounds__(RENDER_THREADS)
     MaterialTaps taps;
     taps.base = taps.metallicRoughness = taps.normal = V4{1.f, 1.f, 1.f, 1.f};
     if (shaded) geom = surfaceGeometry(sv, h.x, h.y, __uint_as_float(h.z), __uint_as_float(h.w));
+    uint32_t tapCount = 0;
+    if (shaded)
+    {
+        const prt_material_data &md = sv.materials[geom.materialIndex];
+        tapCount = ((md.baseColorTextureSampler & 0xFFFFFFu) > 0) + ((md.metallicRoughnessTextureSampler & 0xFFFFFFu) > 0) +
+                   ((md.normalTextureSampler & 0xFFFFFFu) > 0);
+    }
     if (sv.exactMaterialFilter)
     {
         if (shaded) taps = softwareMaterialTaps(sv, geom.materialIndex, geom.v.TexCoord0);
@@ -216,7 +230,9 @@ __global__ void __launch_bounds__(RENDER_THREADS)
     if (countShaded)
     {
         const uint32_t n = __popc(__ballot_sync(0xFFFFFFFFu, shaded));
+        const uint32_t tp = __reduce_add_sync(0xFFFFFFFFu, tapCount);
         if ((threadIdx.x & 31u) == 0 && n) atomicAdd(&gc->shadedHits, (unsigned long long)n);
+        if ((threadIdx.x & 31u) == 0 && tp) atomicAdd(&gc->textureTaps, (unsigned long long)tp);
     }
 }
 
@@ -242,7 +258,7 @@ __global__ void __launch_bounds__(RENDER_THREADS)
             pb.color[id.x] = col;
         }
     }
-    if (COUNT) flushTraceCounters(gc, tc);
+    if (COUNT) flushTraceCounters(gc, tc, true);
 }
 
 // Adds the per-bounce live counts of the finished batch to the 64-bit totals.
@@ -335,7 +351,7 @@ __global__ void __launch_bounds__(RENDER_THREADS)
         h.bary[1] = hit.v;
         out[i] = h;
     }
-    flushTraceCounters(gc, tc);
+    flushTraceCounters(gc, tc, SHADOW);
 }
 
 __global__ void k_hits_to_records(const uint4 *__restrict__ hits, prt_hit *__restrict__ out, uint32_t n)

@@ -198,10 +198,28 @@ struct prt_ctx
     uint64_t kernelLaunches = 0;
 
     // timing
-    cudaEvent_t evRecord[2]{}, evTlas[2]{}, evBlas[2]{}, evTrace[2 * PRT_MAX_BOUNCES]{};
+    cudaEvent_t evRecord[2]{}, evTlas[2]{}, evBlas[2]{};
     bool recordTimed = false, tlasTimed = false, blasTimed = false;
-    uint32_t lastTraceLaunches = 0, lastRecordLaunches = 0, lastTlasLaunches = 0;
-    bool traceTimed = false;
+    uint32_t lastRecordLaunches = 0, lastTlasLaunches = 0;
+    // per-stage timing of the last prt_record: an event between every two stage launches (pool grows on demand);
+    // stageOf[i] = stage of the launch between evStage[i] and evStage[i + 1] (0 closest, 1 shade, 2 shadow, 3 other)
+    std::vector<cudaEvent_t> evStage;
+    std::vector<uint8_t> stageOf;
+    uint32_t evUsed = 0;
+
+    cudaError_t mark(int stageOfNextLaunch)
+    {
+        if (evUsed == evStage.size())
+        {
+            cudaEvent_t e;
+            cudaError_t err = cudaEventCreate(&e);
+            if (err != cudaSuccess) return err;
+            evStage.push_back(e);
+            stageOf.push_back(3);
+        }
+        stageOf[evUsed] = (uint8_t)stageOfNextLaunch;
+        return cudaEventRecord(evStage[evUsed++], stream);
+    }
 
     SceneView view() const
     {
@@ -285,7 +303,6 @@ extern "C" prt_status prt_create(const prt_config *cfg, prt_ctx **out)
         CK(cudaEventCreate(&c->evTlas[i]));
         CK(cudaEventCreate(&c->evBlas[i]));
     }
-    for (uint32_t i = 0; i < 2 * PRT_MAX_BOUNCES; ++i) CK(cudaEventCreate(&c->evTrace[i]));
     CK(c->dDir.ensure(1));
     CK(c->dCam.ensure(1));
     CK(c->dPoints.ensure(PRT_MAX_POINT_LIGHTS));
@@ -348,8 +365,7 @@ extern "C" void prt_destroy(prt_ctx *c)
         if (c->evTlas[i]) cudaEventDestroy(c->evTlas[i]);
         if (c->evBlas[i]) cudaEventDestroy(c->evBlas[i]);
     }
-    for (uint32_t i = 0; i < 2 * PRT_MAX_BOUNCES; ++i)
-        if (c->evTrace[i]) cudaEventDestroy(c->evTrace[i]);
+    for (cudaEvent_t e : c->evStage) cudaEventDestroy(e);
     c->ring.destroy();
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -839,22 +855,19 @@ static prt_status renderBatch(prt_ctx *c, prt_reference_pc pc, uint32_t width, u
     for (uint32_t b = 0; b < bounces; ++b)
     {
         const int q = (int)(b & 1u);
-        if (timeTrace) CK(cudaEventRecord(c->evTrace[2 * b], st));
+        CK(c->mark(0));
         if (count) k_trace_closest<true><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters);
         else k_trace_closest<false><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters);
-        if (timeTrace) CK(cudaEventRecord(c->evTrace[2 * b + 1], st));
+        CK(c->mark(1));
         k_shade<<<grid, RENDER_THREADS, 0, st>>>(sv, pc, c->pb, q, b, c->dCounters, count ? 1 : 0);
         launches += 2;
         if (debugView) break; // main.rgen:259-264: debug views stop at the first hit
+        CK(c->mark(2));
         if (count) k_trace_shadow<true><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters);
         else k_trace_shadow<false><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters);
         launches++;
     }
-    if (timeTrace)
-    {
-        c->lastTraceLaunches = debugView ? std::min(bounces, 1u) : bounces;
-        c->traceTimed = true;
-    }
+    CK(c->mark(3));
     k_tally<<<1, 32, 0, st>>>(c->pb, c->dCounters, (uint32_t)total);
     launches++;
     if (accumulate)
@@ -887,6 +900,7 @@ extern "C" prt_status prt_record(prt_ctx *c, const prt_reference_pc *pcIn, uint3
     }
     CK(cudaEventRecord(c->evRecord[0], c->stream));
     c->lastRecordLaunches = 0;
+    c->evUsed = 0;
     const uint32_t perLaunch = std::max(1u, c->cfg.samplesPerLaunch);
     uint32_t done = 0;
     while (done < sampleCount)
@@ -1036,6 +1050,8 @@ extern "C" prt_status prt_get_counters(prt_ctx *c, prt_counters *out)
     out->shadedHits = g.shadedHits; out->textureTaps = g.textureTaps; out->pixelSamples = g.pixelSamples;
     out->kernelLaunches = c->kernelLaunches;
     out->stackOverflows = g.stackOverflows;
+    out->shadowNodesVisited = g.shadowNodes; out->shadowTrisTested = g.shadowTris;
+    out->shadowInstancesEntered = g.shadowInstances; out->shadowAnyHitCalls = g.shadowAnyHits;
     return PRT_OK;
 }
 
@@ -1057,17 +1073,22 @@ extern "C" prt_status prt_get_timings(prt_ctx *c, prt_timings *out)
     if (c->recordTimed) CK(cudaEventElapsedTime(&out->lastRecordMs, c->evRecord[0], c->evRecord[1]));
     if (c->tlasTimed) CK(cudaEventElapsedTime(&out->lastTlasMs, c->evTlas[0], c->evTlas[1]));
     if (c->blasTimed) CK(cudaEventElapsedTime(&out->lastBlasMs, c->evBlas[0], c->evBlas[1]));
-    if (c->traceTimed)
+    if (c->recordTimed)
     {
-        float sum = 0.f;
-        for (uint32_t b = 0; b < c->lastTraceLaunches; ++b)
+        float sums[3] = {0.f, 0.f, 0.f};
+        uint32_t n[3] = {0, 0, 0};
+        for (uint32_t i = 0; i + 1 < c->evUsed; ++i)
         {
+            const uint32_t stage = c->stageOf[i];
+            if (stage > 2) continue;
             float ms = 0.f;
-            CK(cudaEventElapsedTime(&ms, c->evTrace[2 * b], c->evTrace[2 * b + 1]));
-            sum += ms;
+            CK(cudaEventElapsedTime(&ms, c->evStage[i], c->evStage[i + 1]));
+            sums[stage] += ms;
+            n[stage]++;
         }
-        out->lastTraceClosestMs = sum;
-        out->lastTraceClosestLaunches = c->lastTraceLaunches;
+        out->lastTraceClosestMs = sums[0]; out->lastTraceClosestLaunches = n[0];
+        out->lastShadeMs = sums[1]; out->lastShadeLaunches = n[1];
+        out->lastTraceShadowMs = sums[2]; out->lastTraceShadowLaunches = n[2];
     }
     out->lastRecordLaunches = c->lastRecordLaunches;
     out->lastTlasLaunches = c->lastTlasLaunches;

@@ -41,13 +41,16 @@ class PrtTextureDesc(C.Structure):
 class PrtCounters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("closestRays", "shadowRays", "nodesVisited", "trisTested", "instancesEntered",
                                           "anyHitCalls", "shadedHits", "textureTaps", "pixelSamples", "kernelLaunches",
-                                          "stackOverflows")]
+                                          "stackOverflows", "shadowNodesVisited", "shadowTrisTested",
+                                          "shadowInstancesEntered", "shadowAnyHitCalls")]
 
 
 class PrtTimings(C.Structure):
     _fields_ = [("lastRecordMs", C.c_float), ("lastTlasMs", C.c_float), ("lastBlasMs", C.c_float),
                 ("lastTraceClosestMs", C.c_float), ("lastTraceClosestLaunches", C.c_uint32),
-                ("lastRecordLaunches", C.c_uint32), ("lastTlasLaunches", C.c_uint32), ("pad", C.c_uint32)]
+                ("lastRecordLaunches", C.c_uint32), ("lastTlasLaunches", C.c_uint32), ("lastShadeMs", C.c_float),
+                ("lastShadeLaunches", C.c_uint32), ("lastTraceShadowMs", C.c_float), ("lastTraceShadowLaunches", C.c_uint32),
+                ("pad", C.c_uint32)]
 
 
 class PrtBvhStats(C.Structure):
@@ -135,6 +138,7 @@ class World:
             self.handle = None
             raise RuntimeError(f"prt_create failed ({st}): {msg}")
         self.blas_references = np.zeros(len(scene.model_offsets) - 1, np.uint64)
+        self._accum_pixels = 0
         self._upload_static()
 
     # WorldData::init + uploadMeshDatas / uploadMaterialDatas (WorldData.cpp:307-586)
@@ -194,6 +198,33 @@ class World:
 
     def synchronize(self):
         _check(self.lib.prt_synchronize(self.handle))
+
+    def stream_ptr(self) -> int:
+        """The cudaStream_t every call of this context is ordered on (for torch.cuda.ExternalStream)."""
+        return int(self.lib.prt_stream(self.handle))
+
+    # ---- multi-GPU (SURVEY 8e): the accumulation as (sum.rgb, count), reduced by the caller over NCCL ----
+    def export_sum_ptr(self) -> int:
+        p = C.c_void_p()
+        _check(self.lib.prt_export_sum_device(self.handle, C.byref(p)))
+        return int(p.value)
+
+    def export_sum_tensor(self):
+        """Zero-copy torch view (fp32 [h*w*4], on this context's device) of the exported sum image."""
+        import torch
+
+        class _Dev:
+            pass
+        d = _Dev()
+        n = self.accum_pixels() * 4
+        d.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (self.export_sum_ptr(), False), "version": 2}
+        return torch.as_tensor(d, device=torch.device("cuda", self.device))
+
+    def import_sum(self, device_ptr: int):
+        _check(self.lib.prt_import_sum_device(self.handle, C.c_void_p(device_ptr)))
+
+    def accum_pixels(self) -> int:
+        return self._accum_pixels
 
     def counters(self) -> dict:
         c = PrtCounters()
@@ -354,6 +385,7 @@ class RtReference:
         skip = cameraChanged or options.colorDirty or self.m_accumulationDirty  # RtRef.cpp:282-284
         pc = self._pc(options, camera_params or {}, skip)
         _check(world.lib.prt_record(world.handle, _p(np.ascontiguousarray(pc.reshape(1))), w, h, frames))
+        world._accum_pixels = w * h
         self.m_frameIndex = (self.m_frameIndex + frames - 1) % self.sFramePeriod
         self.m_accumulationDirty = False
         return Output(w, h, world)

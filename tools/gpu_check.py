@@ -63,7 +63,7 @@ for flags, label in ((0, "timed"), (rt.CFG_COUNTERS, "counters")):
         c = world.counters(); tm = world.timings()
         rays = c["closestRays"] + c["shadowRays"]
         print(f"  [{label}] 4 spp wall {dt*1e3:.1f} ms, record {tm['lastRecordMs']:.1f} ms, rays {rays/1e6:.1f} M -> {rays/tm['lastRecordMs']/1e3:.1f} Mrays/s;"
-              f" closest(first batch) {tm['lastTraceClosestMs']:.2f} ms", c, flush=True)
+              f" closest {tm['lastTraceClosestMs']:.2f} ms", c, flush=True)
     if label == "timed":
         from prosper_b200 import imageio
         img = rt.Output(1920, 1080, world).illumination_f32()
