@@ -34,7 +34,9 @@ struct TexSlot
     uint32_t magFilter; // 0 nearest, 1 linear
     uint32_t addressU, addressV;
     uint32_t valid;
-    uint32_t pad;
+    uint32_t alphaOpaque;  // every level-0 texel has alpha 255: the alpha of any tap is the filter of ones
+    const uint8_t *alpha;  // level-0 alpha channel, one byte per texel exactly as the BC7/RGBA8 payload decodes
+                           // (built at upload, prt_set_texture); nullptr: decode the payload per tap
 };
 
 struct SceneView
@@ -251,6 +253,46 @@ HD V4 sampleTextureExact(const TexSlot &s, V2 uv)
             lerp2(t00.w, t10.w, t01.w, t11.w)};
 }
 
+// .w of sampleTextureExact, bit for bit: the same coordinates, texel values and filter arithmetic, but the four
+// texels come from the decoded alpha plane (or are the constant 1 for a texture without transparency) instead
+// of four software BC7 block decodes. This is what scene.rahit's sampleAlpha costs per candidate.
+HD float texelAlpha(const TexSlot &s, int x, int y)
+{
+    if (s.alphaOpaque) return 1.f; // xdiv(255, 255)
+    if (s.alpha == nullptr) return fetchTexel(s, x, y).w;
+#if defined(__CUDA_ARCH__)
+    return xdiv((float)__ldg(s.alpha + (size_t)y * s.width + x), 255.f);
+#else
+    return xdiv((float)s.alpha[(size_t)y * s.width + x], 255.f);
+#endif
+}
+
+HD float sampleTextureAlphaExact(const TexSlot &s, V2 uv)
+{
+    const int w = (int)s.width, h = (int)s.height;
+    if (s.magFilter == PRT_FILTER_NEAREST)
+    {
+        const int x = wrapCoord((int)floorf(xmul(uv.x, (float)w)), w, s.addressU);
+        const int y = wrapCoord((int)floorf(xmul(uv.y, (float)h)), h, s.addressV);
+        return texelAlpha(s, x, y);
+    }
+    const float fx = xsub(xmul(uv.x, (float)w), 0.5f), fy = xsub(xmul(uv.y, (float)h), 0.5f);
+    const float x0f = floorf(fx), y0f = floorf(fy);
+    const float ax = xsub(fx, x0f), ay = xsub(fy, y0f);
+    float c00 = 1.f, c10 = 1.f, c01 = 1.f, c11 = 1.f;
+    if (!s.alphaOpaque)
+    {
+        const int x0 = wrapCoord((int)x0f, w, s.addressU), x1 = wrapCoord((int)x0f + 1, w, s.addressU);
+        const int y0 = wrapCoord((int)y0f, h, s.addressV), y1 = wrapCoord((int)y0f + 1, h, s.addressV);
+        c00 = texelAlpha(s, x0, y0); c10 = texelAlpha(s, x1, y0);
+        c01 = texelAlpha(s, x0, y1); c11 = texelAlpha(s, x1, y1);
+    }
+    const float bx = xsub(1.f, ax), by = xsub(1.f, ay);
+    const float top = xadd(xmul(c00, bx), xmul(c10, ax));
+    const float bot = xadd(xmul(c01, bx), xmul(c11, ax));
+    return xadd(xmul(top, by), xmul(bot, ay));
+}
+
 HD const TexSlot *texSlot(const SceneView &sv, uint32_t textureSampler)
 {
     const uint32_t tex = textureSampler & 0xFFFFFFu, smp = textureSampler >> 24;
@@ -349,7 +391,10 @@ HD float sampleAlpha(const SceneView &sv, uint32_t index, V2 uv)
     const prt_material_data &data = sv.materials[index];
     float linearAlpha = 1;
     if ((data.baseColorTextureSampler & 0xFFFFFFu) > 0)
-        linearAlpha = sRGBtoLinear(sampleTexture(sv, data.baseColorTextureSampler, uv).w);
+    {
+        const TexSlot *s = texSlot(sv, data.baseColorTextureSampler);
+        linearAlpha = sRGBtoLinear(s ? sampleTextureAlphaExact(*s, uv) : 1.f);
+    }
     linearAlpha = xmul(linearAlpha, data.baseColorFactor[3]);
     if (data.alphaMode == PRT_ALPHA_BLEND) return linearAlpha;
     if (data.alphaMode == PRT_ALPHA_MASK && linearAlpha < data.alphaCutoff) return 0;

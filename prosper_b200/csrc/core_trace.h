@@ -168,125 +168,175 @@ HD uint32_t intersectNode(const WideNode &n, const NodeRay &r, float tMin, float
     return mask;
 }
 
-// traceRayEXT. SHADOW = gl_RayFlagsTerminateOnFirstHitEXT (main.rgen:52). Returns true on a hit.
+// Traversal state of one ray, resumable one step at a time so that the persistent trace kernels can
+// retire and refill lanes between steps (kernels_render.cuh); traceRay below runs it to completion.
+struct TraceState
+{
+    V3 o, d;         // world-space ray
+    float tMin, tMax;
+    uint32_t seed;   // payload.randomSeed (scene.rahit:35)
+    NodeRay ray;     // ray in the current space (world in the TLAS, object in a BLAS)
+    const WideNode *nodes;
+    const TriRec *tris;
+    uint32_t instCustom, instIndex;
+    uint32_t gx, gy; // node group: base index, hit bits | imask
+    uint32_t px, py; // primitive group: base index, hit bits
+    int sp;
+    int blasSp;      // stack depth at BLAS entry; -1 while in the TLAS
+    HitRec best;
+};
+// kept apart from TraceState so that the scalar state stays in registers (a dynamically indexed member
+// would drag the whole struct into local memory)
+struct TraceStack
+{
+    uint32_t x[TRACE_STACK], y[TRACE_STACK];
+};
+
+// Returns false when there is nothing to traverse (the ray is a miss).
+HD bool traceBegin(TraceState &s, const Accel &as, V3 o, V3 d, float tMin, float tMax, uint32_t seed)
+{
+    s.best.drawInstanceIndex = MISS_INDEX;
+    s.best.primitiveID = MISS_INDEX;
+    s.best.u = 0.f; s.best.v = 0.f; s.best.t = tMax; s.best.instance = MISS_INDEX; s.best.geometry = 0;
+    s.o = o; s.d = d; s.tMin = tMin; s.tMax = tMax; s.seed = seed;
+    s.sp = 0;
+    s.blasSp = -1;
+    setupNodeRay(s.ray, o, d);
+    s.nodes = as.tlasNodes;
+    s.tris = nullptr;
+    s.instCustom = 0; s.instIndex = 0;
+    s.gx = 0; s.gy = 0x80000000u;
+    s.px = 0; s.py = 0;
+    return as.tlasNodes != nullptr;
+}
+
+// One step of traceRayEXT = ONE item of work, so that the lanes of a warp stay in lock step on items of
+// similar cost: either one pending primitive of the current primitive group (a triangle test with its any-hit,
+// or entering an instance), or one node (take the nearest pending child of the current node group, intersect
+// its eight boxes). Pops when both groups are exhausted.
+// SHADOW = gl_RayFlagsTerminateOnFirstHitEXT (main.rgen:52). Returns true when the ray is finished.
+template <bool SHADOW, bool COUNT>
+HD bool traceStep(TraceState &s, TraceStack &st, const Accel &as, const SceneView &sv, TraceCounters *cnt)
+{
+    if (s.py != 0)
+    {
+        const int pbit = bfind(s.py);
+        s.py &= ~(1u << pbit);
+        if (s.blasSp < 0)
+        {
+            // TLAS leaf: enter the instance (traversal state of the TLAS goes on the stack)
+            const InstRec &inst = as.instances[s.px + (uint32_t)pbit];
+            if (COUNT) cnt->instances++;
+            if ((inst.mask & 0xFFu) != 0)
+            {
+                if (s.gy & 0xFF000000u)
+                {
+                    if (s.sp < TRACE_STACK) { st.x[s.sp] = s.gx; st.y[s.sp] = s.gy; s.sp++; }
+                    else if (COUNT) cnt->overflow++;
+                }
+                if (s.py != 0)
+                {
+                    if (s.sp < TRACE_STACK) { st.x[s.sp] = s.px; st.y[s.sp] = s.py; s.sp++; }
+                    else if (COUNT) cnt->overflow++;
+                }
+                s.blasSp = s.sp;
+                setupNodeRay(s.ray, xformPoint(inst.w2o, s.o), xformVector(inst.w2o, s.d));
+                s.nodes = inst.nodes;
+                s.tris = inst.tris;
+                s.instCustom = inst.customIndex;
+                s.instIndex = inst.index;
+                s.gx = 0; s.gy = 0x80000000u;
+                s.py = 0;
+                return false;
+            }
+        }
+        else
+        {
+            const TriRec &tr = s.tris[s.px + (uint32_t)pbit];
+            if (COUNT) cnt->tris++;
+            float t, u, v;
+            if (intersectTriangleExact(s.ray.o, s.ray.d, s.tMin, s.tMax, V3{tr.v0[0], tr.v0[1], tr.v0[2]}, V3{tr.e1[0], tr.e1[1], tr.e1[2]},
+                                       V3{tr.e2[0], tr.e2[1], tr.e2[2]}, t, u, v))
+            {
+                const uint32_t geom = tr.geometry & 0x7FFFFFFFu;
+                if (betterHit(t, s.instIndex, geom, tr.primitive, s.best))
+                {
+                    const uint32_t drawInstanceIndex = s.instCustom + geom;
+                    bool accept = true;
+                    if (!(tr.geometry >> 31))
+                    {
+                        if (COUNT) cnt->anyHits++;
+                        accept = anyHitAccept(sv, drawInstanceIndex, tr.primitive, u, v, s.seed);
+                    }
+                    if (accept)
+                    {
+                        s.best.drawInstanceIndex = drawInstanceIndex;
+                        s.best.primitiveID = tr.primitive;
+                        s.best.u = u; s.best.v = v; s.best.t = t;
+                        s.best.instance = s.instIndex;
+                        s.best.geometry = geom;
+                        if (SHADOW) return true;
+                    }
+                }
+            }
+        }
+    }
+    else if (s.gy & 0xFF000000u)
+    {
+        const int bit = bfind(s.gy);
+        const uint32_t imask = s.gy;
+        s.gy &= ~(1u << bit);
+        if (s.gy & 0xFF000000u)
+        {
+            if (s.sp < TRACE_STACK) { st.x[s.sp] = s.gx; st.y[s.sp] = s.gy; s.sp++; }
+            else if (COUNT) cnt->overflow++;
+        }
+        const uint32_t slot = ((uint32_t)bit - 24u) ^ s.ray.octinv;
+        const uint32_t rel = (uint32_t)popc(imask & 0xFFu & ((1u << slot) - 1u));
+        WideNode n;
+        loadNode(s.nodes + s.gx + rel, n);
+        if (COUNT) cnt->nodes++;
+        const float tFar = s.best.drawInstanceIndex == MISS_INDEX ? s.tMax : fminf_(s.tMax, s.best.t);
+        const uint32_t hits = intersectNode(n, s.ray, s.tMin, tFar);
+        s.gx = n.childBase;
+        s.gy = (hits & 0xFF000000u) | n.imask;
+        s.px = n.primBase;
+        s.py = hits & 0x00FFFFFFu;
+    }
+
+    if (s.py == 0 && (s.gy & 0xFF000000u) == 0)
+    {
+        if (s.sp == s.blasSp)
+        {
+            // BLAS exhausted: back to world space
+            s.blasSp = -1;
+            setupNodeRay(s.ray, s.o, s.d);
+            s.nodes = as.tlasNodes;
+        }
+        if (s.sp == 0) return true;
+        s.sp--;
+        s.gx = st.x[s.sp];
+        s.gy = st.y[s.sp];
+        if ((s.gy & 0xFF000000u) == 0)
+        {
+            // a postponed primitive group (pushed when an instance was entered)
+            s.px = s.gx; s.py = s.gy;
+            s.gx = 0; s.gy = 0;
+        }
+    }
+    return false;
+}
+
+// traceRayEXT to completion. Returns true on a hit.
 template <bool SHADOW, bool COUNT>
 HDNI bool traceRay(const Accel &as, const SceneView &sv, V3 o, V3 d, float tMin, float tMax, uint32_t seed, HitRec &best,
                    TraceCounters *cnt)
 {
-    best.drawInstanceIndex = MISS_INDEX;
-    best.primitiveID = MISS_INDEX;
-    best.u = 0.f; best.v = 0.f; best.t = tMax; best.instance = MISS_INDEX; best.geometry = 0;
-    if (as.tlasNodes == nullptr) return false;
-
-    uint32_t stackX[TRACE_STACK], stackY[TRACE_STACK];
-    int sp = 0;
-    int blasSp = -1; // stack depth at BLAS entry; -1 while in the TLAS
-    NodeRay world, ray;
-    setupNodeRay(world, o, d);
-    ray = world;
-    const WideNode *nodes = as.tlasNodes;
-    const TriRec *tris = nullptr;
-    uint32_t instCustom = 0, instIndex = 0;
-    uint32_t gx = 0, gy = 0x80000000u; // node group: base index, hit bits | imask
-    uint32_t px = 0, py = 0;           // primitive group: base index, hit bits
-
-    for (;;)
-    {
-        if (gy & 0xFF000000u)
-        {
-            const int bit = bfind(gy);
-            const uint32_t imask = gy;
-            gy &= ~(1u << bit);
-            if (gy & 0xFF000000u)
-            {
-                if (sp < TRACE_STACK) { stackX[sp] = gx; stackY[sp] = gy; sp++; }
-                else if (COUNT) cnt->overflow++;
-            }
-            const uint32_t slot = ((uint32_t)bit - 24u) ^ ray.octinv;
-            const uint32_t rel = (uint32_t)popc(imask & 0xFFu & ((1u << slot) - 1u));
-            WideNode n;
-            loadNode(nodes + gx + rel, n);
-            if (COUNT) cnt->nodes++;
-            const float tFar = best.drawInstanceIndex == MISS_INDEX ? tMax : fminf_(tMax, best.t);
-            const uint32_t hits = intersectNode(n, ray, tMin, tFar);
-            gx = n.childBase;
-            gy = (hits & 0xFF000000u) | n.imask;
-            px = n.primBase;
-            py = hits & 0x00FFFFFFu;
-        }
-        else
-        {
-            px = gx; py = gy;
-            gx = 0; gy = 0;
-        }
-
-        while (py != 0)
-        {
-            const int pbit = bfind(py);
-            py &= ~(1u << pbit);
-            if (blasSp < 0)
-            {
-                // TLAS leaf: enter the instance (traversal state of the TLAS goes on the stack)
-                const InstRec &inst = as.instances[px + (uint32_t)pbit];
-                if (COUNT) cnt->instances++;
-                if ((inst.mask & 0xFFu) == 0) continue;
-                if (gy & 0xFF000000u)
-                {
-                    if (sp < TRACE_STACK) { stackX[sp] = gx; stackY[sp] = gy; sp++; }
-                    else if (COUNT) cnt->overflow++;
-                }
-                if (py != 0)
-                {
-                    if (sp < TRACE_STACK) { stackX[sp] = px; stackY[sp] = py; sp++; }
-                    else if (COUNT) cnt->overflow++;
-                }
-                blasSp = sp;
-                setupNodeRay(ray, xformPoint(inst.w2o, o), xformVector(inst.w2o, d));
-                nodes = inst.nodes;
-                tris = inst.tris;
-                instCustom = inst.customIndex;
-                instIndex = inst.index;
-                gx = 0; gy = 0x80000000u;
-                py = 0;
-                break;
-            }
-            const TriRec &tr = tris[px + (uint32_t)pbit];
-            if (COUNT) cnt->tris++;
-            float t, u, v;
-            if (!intersectTriangleExact(ray.o, ray.d, tMin, tMax, V3{tr.v0[0], tr.v0[1], tr.v0[2]}, V3{tr.e1[0], tr.e1[1], tr.e1[2]},
-                                        V3{tr.e2[0], tr.e2[1], tr.e2[2]}, t, u, v))
-                continue;
-            const uint32_t geom = tr.geometry & 0x7FFFFFFFu;
-            if (!betterHit(t, instIndex, geom, tr.primitive, best)) continue;
-            const uint32_t drawInstanceIndex = instCustom + geom;
-            if (!(tr.geometry >> 31))
-            {
-                if (COUNT) cnt->anyHits++;
-                if (!anyHitAccept(sv, drawInstanceIndex, tr.primitive, u, v, seed)) continue;
-            }
-            best.drawInstanceIndex = drawInstanceIndex;
-            best.primitiveID = tr.primitive;
-            best.u = u; best.v = v; best.t = t;
-            best.instance = instIndex;
-            best.geometry = geom;
-            if (SHADOW) return true;
-        }
-
-        if ((gy & 0xFF000000u) == 0)
-        {
-            if (sp == blasSp)
-            {
-                // BLAS exhausted: back to world space
-                blasSp = -1;
-                ray = world;
-                nodes = as.tlasNodes;
-            }
-            if (sp == 0) break;
-            sp--;
-            gx = stackX[sp];
-            gy = stackY[sp];
-        }
-    }
+    TraceState s;
+    TraceStack st;
+    if (traceBegin(s, as, o, d, tMin, tMax, seed))
+        while (!traceStep<SHADOW, COUNT>(s, st, as, sv, cnt)) {}
+    best = s.best;
     return best.drawInstanceIndex != MISS_INDEX;
 }
 

@@ -14,6 +14,11 @@ namespace prt {
 
 constexpr int RENDER_THREADS = 128;
 constexpr uint32_t COUNT_SHADOW_BASE = 8; // counts[b] = closest rays of bounce b, counts[8 + b] = shadow rays
+constexpr uint32_t CURSOR_BASE = 16;      // counts[16 + i] = fetch cursor of the persistent trace kernel over queue i
+constexpr uint32_t COUNT_WORDS = 32;
+// Persistent trace kernels: a warp refills its retired lanes from the queue once fewer than this many
+// lanes are still traversing (Aila & Laine's dynamic fetch); below it, finished lanes idle until the refill.
+constexpr int TRACE_REFILL_BELOW = 22;
 
 struct PathBuffers
 {
@@ -81,7 +86,7 @@ __global__ void __launch_bounds__(RENDER_THREADS)
     if (p == 0)
     {
         pb.counts[0] = total;
-        for (int i = 1; i < 16; ++i) pb.counts[i] = 0;
+        for (uint32_t i = 1; i < COUNT_WORDS; ++i) pb.counts[i] = 0;
     }
     if (p >= total) return;
     const uint32_t k = p / pixels, pix = p - k * pixels;
@@ -97,21 +102,57 @@ __global__ void __launch_bounds__(RENDER_THREADS)
     pb.rayId[0][p] = make_uint2(p, pcg(rng.state.x ^ rng.state.z)); // main.rgen:71
 }
 
-// traceClosest, main.rgen:62-81
+// Hands the idle lanes of a warp their next queue slots: one atomic per warp per refill. Returns the slot of this
+// lane (>= count: nothing left); `exhausted` is warp-uniform and tells that the queue has no more work to hand out.
+__device__ __forceinline__ uint32_t fetchSlots(uint32_t *cursor, uint32_t count, bool idle, bool &exhausted)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t need = __ballot_sync(0xFFFFFFFFu, idle);
+    if (need == 0) return 0xFFFFFFFFu;
+    const int leader = __ffs(need) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)__popc(need));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    exhausted = base + (uint32_t)__popc(need) >= count;
+    return idle ? base + (uint32_t)__popc(need & ((1u << lane) - 1u)) : 0xFFFFFFFFu;
+}
+
+// traceClosest, main.rgen:62-81. Persistent warps over the closest-ray queue of `bounce`.
 template <bool COUNT>
 __global__ void __launch_bounds__(RENDER_THREADS)
     k_trace_closest(Accel as, SceneView sv, PathBuffers pb, int q, uint32_t bounce, GlobalCounters *gc)
 {
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t count = pb.counts[bounce];
+    uint32_t *cursor = &pb.counts[CURSOR_BASE + bounce];
     TraceCounters tc = {0, 0, 0, 0, 0};
-    if (slot < count)
+    TraceState s;
+    TraceStack st;
+    bool active = false, exhausted = false;
+    uint32_t slot = 0;
+    for (;;)
     {
-        const float4 o = pb.rayO[q][slot], d = pb.rayD[q][slot];
-        const uint2 id = pb.rayId[q][slot];
-        HitRec hit;
-        traceRay<false, COUNT>(as, sv, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, id.y, hit, &tc);
-        pb.hits[slot] = make_uint4(hit.drawInstanceIndex, hit.primitiveID, __float_as_uint(hit.u), __float_as_uint(hit.v));
+        if (!exhausted)
+        {
+            const uint32_t next = fetchSlots(cursor, count, !active, exhausted);
+            if (!active && next < count)
+            {
+                slot = next;
+                const float4 o = pb.rayO[q][slot], d = pb.rayD[q][slot];
+                active = traceBegin(s, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.rayId[q][slot].y);
+                if (!active) pb.hits[slot] = make_uint4(MISS_INDEX, MISS_INDEX, 0u, 0u);
+            }
+        }
+        if (!__any_sync(0xFFFFFFFFu, active)) break;
+        for (;;)
+        {
+            if (active && traceStep<false, COUNT>(s, st, as, sv, &tc))
+            {
+                pb.hits[slot] = make_uint4(s.best.drawInstanceIndex, s.best.primitiveID, __float_as_uint(s.best.u), __float_as_uint(s.best.v));
+                active = false;
+            }
+            const int live = __popc(__ballot_sync(0xFFFFFFFFu, active));
+            if (live == 0 || (!exhausted && live < TRACE_REFILL_BELOW)) break;
+        }
     }
     if (COUNT) flushTraceCounters(gc, tc);
 }
@@ -241,21 +282,46 @@ template <bool COUNT>
 __global__ void __launch_bounds__(RENDER_THREADS)
     k_trace_shadow(Accel as, SceneView sv, PathBuffers pb, uint32_t bounce, GlobalCounters *gc)
 {
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t count = pb.counts[COUNT_SHADOW_BASE + bounce];
+    uint32_t *cursor = &pb.counts[CURSOR_BASE + COUNT_SHADOW_BASE + bounce];
     TraceCounters tc = {0, 0, 0, 0, 0};
-    if (slot < count)
-    {
-        const float4 o = pb.shadowO[slot], d = pb.shadowD[slot];
-        const uint2 id = pb.shadowId[slot];
-        HitRec hit;
-        const bool occluded = traceRay<true, COUNT>(as, sv, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, id.y, hit, &tc);
-        if (!occluded)
+    TraceState s;
+    TraceStack st;
+    bool active = false, exhausted = false;
+    uint32_t slot = 0;
+    auto retire = [&]() {
+        if (s.best.drawInstanceIndex == MISS_INDEX) // unoccluded
         {
             const float4 c = pb.shadowC[slot];
-            float4 col = pb.color[id.x];
+            const uint32_t path = pb.shadowId[slot].x;
+            float4 col = pb.color[path];
             col.x += c.x; col.y += c.y; col.z += c.z;
-            pb.color[id.x] = col;
+            pb.color[path] = col;
+        }
+    };
+    for (;;)
+    {
+        if (!exhausted)
+        {
+            const uint32_t next = fetchSlots(cursor, count, !active, exhausted);
+            if (!active && next < count)
+            {
+                slot = next;
+                const float4 o = pb.shadowO[slot], d = pb.shadowD[slot];
+                active = traceBegin(s, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.shadowId[slot].y);
+                if (!active) retire();
+            }
+        }
+        if (!__any_sync(0xFFFFFFFFu, active)) break;
+        for (;;)
+        {
+            if (active && traceStep<true, COUNT>(s, st, as, sv, &tc))
+            {
+                retire();
+                active = false;
+            }
+            const int live = __popc(__ballot_sync(0xFFFFFFFFu, active));
+            if (live == 0 || (!exhausted && live < TRACE_REFILL_BELOW)) break;
         }
     }
     if (COUNT) flushTraceCounters(gc, tc, true);

@@ -25,6 +25,31 @@ __global__ void k_bc7_decode(const uint2 *__restrict__ blocks64, uint32_t blocks
         }
 }
 
+// Level-0 alpha plane for scene.rahit's sampleAlpha: one byte per texel, exactly the alpha the payload decodes to.
+// One thread per texel (BC7: 16 threads share a block fetch through L1). minAlpha collects the smallest alpha so
+// a texture without any transparency needs no plane at all.
+__global__ void k_alpha_plane(TexSlot slot, uint8_t *__restrict__ alpha, uint32_t *__restrict__ minAlpha)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t a = 255u;
+    if (i < slot.width * slot.height)
+    {
+        const uint32_t x = i % slot.width, y = i / slot.width;
+        if (slot.format == PRT_TEX_BC7_UNORM)
+        {
+            const uint32_t bw = (slot.width + 3u) >> 2;
+            const uint4 b = __ldg(reinterpret_cast<const uint4 *>(slot.payload + ((size_t)(y >> 2) * bw + (x >> 2)) * 16));
+            const uint64_t lo = (uint64_t)b.x | ((uint64_t)b.y << 32), hi = (uint64_t)b.z | ((uint64_t)b.w << 32);
+            a = bc7DecodeTexel(lo, hi, ((y & 3u) << 2) | (x & 3u)) >> 24;
+        }
+        else
+            a = __ldg(reinterpret_cast<const uint32_t *>(slot.payload) + i) >> 24;
+        alpha[i] = (uint8_t)a;
+    }
+    a = __reduce_min_sync(0xFFFFFFFFu, a);
+    if ((threadIdx.x & 31u) == 0 && a < 255u) atomicMin(minAlpha, a);
+}
+
 // out[i] = texel xy[i] as the texture units decode it (point view of the CUDA array; uniform handle)
 __global__ void k_probe_texels(TexSlot slot, const int2 *__restrict__ xy, uint32_t n, float4 *__restrict__ out)
 {

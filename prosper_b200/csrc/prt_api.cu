@@ -120,6 +120,8 @@ struct TexRes
 {
     cudaArray_t array = nullptr; // level 0 (texture() in the RT stages reads LOD 0, materials.glsl:44)
     uint8_t *payload = nullptr;  // level 0 as cached (BC7 blocks / RGBA8 texels) for the software filter
+    uint8_t *alpha = nullptr;    // level-0 alpha plane (k_alpha_plane); nullptr + alphaOpaque when all 255
+    bool alphaOpaque = false;
     uint32_t width = 0, height = 0, format = 0, mipLevels = 0;
 };
 
@@ -196,6 +198,7 @@ struct prt_ctx
     bool historyValid = false;
     GlobalCounters *dCounters = nullptr;
     uint64_t kernelLaunches = 0;
+    uint32_t traceBlocks = 148; // grid of the persistent trace kernels
 
     // timing
     cudaEvent_t evRecord[2]{}, evTlas[2]{}, evBlas[2]{};
@@ -271,8 +274,8 @@ static prt_status allocPathBuffers(prt_ctx *c, uint64_t paths)
     }
     if (!pb.counts)
     {
-        CK(cudaMalloc((void **)&pb.counts, 16 * sizeof(uint32_t)));
-        CK(cudaMemset(pb.counts, 0, 16 * sizeof(uint32_t)));
+        CK(cudaMalloc((void **)&pb.counts, COUNT_WORDS * sizeof(uint32_t)));
+        CK(cudaMemset(pb.counts, 0, COUNT_WORDS * sizeof(uint32_t)));
     }
     c->pathCapacity = paths;
     return PRT_OK;
@@ -319,6 +322,13 @@ extern "C" prt_status prt_create(const prt_config *cfg, prt_ctx **out)
     // the local-memory traversal stacks want L1 rather than shared memory
     cudaFuncSetAttribute(k_trace_closest<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
     cudaFuncSetAttribute(k_trace_shadow<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
+    {
+        // persistent trace kernels: one resident wave of blocks (SM count x blocks per SM)
+        int sms = 0, perSm = 0;
+        CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->cfg.device));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_trace_closest<false>, RENDER_THREADS, 0));
+        c->traceBlocks = (uint32_t)std::max(1, sms * std::max(1, perSm));
+    }
     CK(cudaStreamSynchronize(c->stream));
     return PRT_OK;
 }
@@ -339,6 +349,7 @@ extern "C" void prt_destroy(prt_ctx *c)
     {
         if (t.array) cudaFreeArray(t.array);
         if (t.payload) cudaFree(t.payload);
+        if (t.alpha) cudaFree(t.alpha);
     }
     for (BlasRes &b : c->blas)
     {
@@ -446,6 +457,9 @@ extern "C" prt_status prt_set_texture(prt_ctx *c, uint32_t index, const prt_text
         t.array = nullptr;
         if (t.payload) CK(cudaFree(t.payload));
         t.payload = nullptr;
+        if (t.alpha) CK(cudaFree(t.alpha));
+        t.alpha = nullptr;
+        t.alphaOpaque = false;
     }
     t.width = desc->width; t.height = desc->height; t.format = desc->format; t.mipLevels = desc->mipLevels;
     const uint32_t bx = (desc->width + 3) / 4, by = (desc->height + 3) / 4;
@@ -489,6 +503,28 @@ extern "C" prt_status prt_set_texture(prt_ctx *c, uint32_t index, const prt_text
         const size_t bytes = desc->format == PRT_TEX_BC7_UNORM ? (size_t)bx * by * 16 : (size_t)desc->width * desc->height * 4;
         CK(cudaMalloc((void **)&t.payload, bytes));
         CK(cudaMemcpyAsync(t.payload, desc->data, bytes, cudaMemcpyHostToDevice, c->stream));
+    }
+    {
+        // alpha plane for the any-hit stage (derived data like the BLAS; the payload stays the source of truth)
+        const size_t texels = (size_t)desc->width * desc->height;
+        REQUIRE(texels < (1ull << 32), "texture too large");
+        CK(cudaMalloc((void **)&t.alpha, texels));
+        uint32_t *minAlpha = c->bScalars.p + 250; // past the builder's per-level counts (bScalars holds 256)
+        const uint32_t init = 255u;
+        CK(cudaMemcpyAsync(minAlpha, &init, 4, cudaMemcpyHostToDevice, c->stream));
+        TexSlot view{};
+        view.payload = t.payload; view.format = t.format; view.width = t.width; view.height = t.height;
+        k_alpha_plane<<<blocksFor(texels, 256), 256, 0, c->stream>>>(view, t.alpha, minAlpha);
+        CK(cudaGetLastError());
+        uint32_t lowest = 0;
+        CK(cudaMemcpyAsync(&lowest, minAlpha, 4, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+        if (lowest == 255u)
+        {
+            CK(cudaFree(t.alpha));
+            t.alpha = nullptr;
+            t.alphaOpaque = true;
+        }
     }
     CK(cudaStreamSynchronize(c->stream)); // desc->data may go away after return
     c->slotsDirty = true;
@@ -562,6 +598,8 @@ static prt_status refreshTextureSlots(prt_ctx *c)
             td.normalizedCoords = 1;
             CK(cudaCreateTextureObject(&slot.linear, &rd, &td, nullptr));
             slot.payload = tr.payload;
+            slot.alpha = tr.alpha;
+            slot.alphaOpaque = tr.alphaOpaque ? 1u : 0u;
             slot.format = tr.format;
             slot.width = tr.width; slot.height = tr.height;
             slot.magFilter = samplers[s].magFilter;
@@ -847,6 +885,7 @@ static prt_status renderBatch(prt_ctx *c, prt_reference_pc pc, uint32_t width, u
     const Accel as = c->accel();
     const bool count = (c->cfg.flags & PRT_CFG_COUNTERS) != 0;
     const uint32_t grid = blocksFor(total, RENDER_THREADS);
+    const uint32_t tgrid = std::min(grid, c->traceBlocks);
     uint32_t launches = 0;
     k_raygen<<<grid, RENDER_THREADS, 0, st>>>(sv, pc, width, height, samples, c->pb);
     launches++;
@@ -856,15 +895,15 @@ static prt_status renderBatch(prt_ctx *c, prt_reference_pc pc, uint32_t width, u
     {
         const int q = (int)(b & 1u);
         CK(c->mark(0));
-        if (count) k_trace_closest<true><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters);
-        else k_trace_closest<false><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters);
+        if (count) k_trace_closest<true><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters);
+        else k_trace_closest<false><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters);
         CK(c->mark(1));
         k_shade<<<grid, RENDER_THREADS, 0, st>>>(sv, pc, c->pb, q, b, c->dCounters, count ? 1 : 0);
         launches += 2;
         if (debugView) break; // main.rgen:259-264: debug views stop at the first hit
         CK(c->mark(2));
-        if (count) k_trace_shadow<true><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters);
-        else k_trace_shadow<false><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters);
+        if (count) k_trace_shadow<true><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters);
+        else k_trace_shadow<false><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters);
         launches++;
     }
     CK(c->mark(3));
@@ -974,7 +1013,7 @@ extern "C" prt_status prt_trace_primary(prt_ctx *c, const prt_reference_pc *pcIn
     cudaStream_t st = c->stream;
     const uint32_t grid = blocksFor(pixels, RENDER_THREADS);
     k_raygen<<<grid, RENDER_THREADS, 0, st>>>(sv, *pcIn, width, height, 1, c->pb);
-    k_trace_closest<true><<<grid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, 0, 0, c->dCounters);
+    k_trace_closest<true><<<std::min(grid, c->traceBlocks), RENDER_THREADS, 0, st>>>(as, sv, c->pb, 0, 0, c->dCounters);
     k_hits_to_records<<<blocksFor(pixels, 256), 256, 0, st>>>(c->pb.hits, c->userHits.p, (uint32_t)pixels);
     c->kernelLaunches += 3;
     CK(cudaGetLastError());
