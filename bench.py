@@ -258,8 +258,8 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     if world_size > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    if world_size * args.spp > rt.RtReference.sFramePeriod - 1:
-        raise RuntimeError("spp x ranks exceeds the reference's frame-index period (RtRef.cpp:31)")
+    from prosper_b200 import partition
+    first_frame, _ = partition.rank_frames(rank, world_size, args.spp)
 
     scene = build_scene(args)
     world = rt.World(scene, device=local_rank, max_width=WIDTH, max_height=HEIGHT,
@@ -285,12 +285,12 @@ def run_ours(args):
     def render_step():
         """rank g renders frame indices g*spp+1 .. (g+1)*spp into a fresh accumulation (RNG seed = (px, frameIndex),
         main.rgen:229); N>1: one reduce of the (sum, count) image to rank 0."""
-        pass_.m_frameIndex = rank * args.spp
+        pass_.m_frameIndex = first_frame - 1  # record() pre-increments (RtRef.cpp:170)
         pass_.m_accumulationDirty = True
         out = pass_.record(world, area, opts, frames=args.spp)
         if world_size > 1:
             summed = world.export_sum_tensor()  # fp32 (sum.rgb, count) image, zero-copy view of library memory
-            dist.reduce(summed, dst=0, op=dist.ReduceOp.SUM)  # the stream waits for the collective (blocking wait)
+            partition.reduce_sum_image(summed, dst=0)  # blocking wait: the library stream waits for the collective
             if rank == 0:
                 world.import_sum(summed.data_ptr())
         return out
