@@ -275,7 +275,10 @@ def run_ours(args):
     area = (0, 0, WIDTH, HEIGHT)
     opts = rt.Options(ibl=True)
     pixels = WIDTH * HEIGHT
-    torch.cuda.set_stream(stream)  # NCCL work and the timing events are ordered on the library's stream
+    # N > 1: the (sum, count) image is exported into torch-owned memory and reduced on torch's stream; every
+    # hand-over between the library stream and torch's stream is a host synchronisation, so the CUDA events
+    # recorded on the library stream around the timed steps span the collective as well
+    reduced = torch.empty(pixels * 4, dtype=torch.float32, device="cuda") if world_size > 1 else None
 
     def barrier():
         if world_size > 1:
@@ -289,10 +292,11 @@ def run_ours(args):
         pass_.m_accumulationDirty = True
         out = pass_.record(world, area, opts, frames=args.spp)
         if world_size > 1:
-            summed = world.export_sum_tensor()  # fp32 (sum.rgb, count) image, zero-copy view of library memory
-            partition.reduce_sum_image(summed, dst=0)  # blocking wait: the library stream waits for the collective
+            world.export_sum_to(reduced.data_ptr())
+            partition.reduce_sum_image(reduced, dst=0)
+            torch.cuda.current_stream().synchronize()
             if rank == 0:
-                world.import_sum(summed.data_ptr())
+                world.import_sum(reduced.data_ptr())
         return out
 
     def e2e_step():
@@ -445,6 +449,8 @@ def run_ours(args):
 
 
 def main():
+    import faulthandler
+    faulthandler.enable()
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -130,6 +130,9 @@ prt_status prt_debug_read_tlas(prt_ctx *ctx, void *nodesOut, uint64_t nodesBytes
  * ncclReduce(sum); prt_resolve_sum turns a reduced sum back into the running-mean image. */
 prt_status prt_export_sum_device(prt_ctx *ctx, float **outSum);
 prt_status prt_import_sum_device(prt_ctx *ctx, const float *sumDevice);
+/* Same as prt_export_sum_device but writes the sum image into caller-owned DEVICE memory (width*height*16 B,
+ * e.g. a buffer registered with the caller's communicator) and returns once it is complete. */
+prt_status prt_export_sum_to_device(prt_ctx *ctx, float *dstDevice);
 
 /* ---- metrics (the reference's "RtReference"/"BuildTLAS" profiler scopes, App.cpp:575) ------ */
 typedef struct prt_counters {

@@ -1062,6 +1062,19 @@ extern "C" prt_status prt_export_sum_device(prt_ctx *c, float **outSum)
     return PRT_OK;
 }
 
+extern "C" prt_status prt_export_sum_to_device(prt_ctx *c, float *dstDevice)
+{
+    REQUIRE(c && dstDevice, "prt_export_sum_to_device");
+    REQUIRE(c->historyValid, "nothing recorded yet");
+    CK(cudaSetDevice(c->cfg.device));
+    const uint32_t pixels = c->accumWidth * c->accumHeight;
+    k_mean_to_sum<<<blocksFor(pixels, 256), 256, 0, c->stream>>>(c->accum.p, reinterpret_cast<float4 *>(dstDevice), pixels);
+    c->kernelLaunches++;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
 extern "C" prt_status prt_import_sum_device(prt_ctx *c, const float *sumDevice)
 {
     REQUIRE(c && sumDevice, "prt_import_sum_device");

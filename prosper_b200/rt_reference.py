@@ -65,6 +65,7 @@ ABI_SYMBOLS = (
     "prt_build_blas", "prt_build_tlas", "prt_set_draw_instances", "prt_set_instance_transforms", "prt_set_lights",
     "prt_set_camera", "prt_record", "prt_output_f32_device", "prt_read_illumination_f16", "prt_read_output_f32",
     "prt_release_preserved", "prt_trace_primary", "prt_trace_rays", "prt_export_sum_device", "prt_import_sum_device",
+    "prt_export_sum_to_device",
     "prt_get_counters", "prt_reset_counters", "prt_get_timings", "prt_get_bvh_stats", "prt_probe_texture",
     "prt_debug_read_blas", "prt_debug_read_tlas",
 )
@@ -97,7 +98,7 @@ def load_library():
             "prt_output_f32_device": [vp, C.POINTER(vp)], "prt_read_illumination_f16": [vp, vp, u64],
             "prt_read_output_f32": [vp, vp, u64], "prt_release_preserved": [vp], "prt_trace_primary": [vp, vp, u32, u32, vp],
             "prt_trace_rays": [vp, vp, vp, vp, u32, C.c_int, vp], "prt_export_sum_device": [vp, C.POINTER(vp)],
-            "prt_import_sum_device": [vp, vp], "prt_get_counters": [vp, C.POINTER(PrtCounters)], "prt_reset_counters": [vp],
+            "prt_import_sum_device": [vp, vp], "prt_export_sum_to_device": [vp, vp], "prt_get_counters": [vp, C.POINTER(PrtCounters)], "prt_reset_counters": [vp],
             "prt_get_timings": [vp, C.POINTER(PrtTimings)], "prt_get_bvh_stats": [vp, C.POINTER(PrtBvhStats)],
             "prt_probe_texture": [vp, u32, vp, vp, u32, C.c_int, vp],
             "prt_debug_read_blas": [vp, u32, vp, u64, vp, u64, C.POINTER(u32), C.POINTER(u32)],
@@ -209,22 +210,13 @@ class World:
         _check(self.lib.prt_export_sum_device(self.handle, C.byref(p)))
         return int(p.value)
 
-    def export_sum_tensor(self):
-        """Zero-copy torch view (fp32 [h*w*4], on this context's device) of the exported sum image."""
-        import torch
-
-        class _Dev:
-            pass
-        d = _Dev()
-        n = self.accum_pixels() * 4
-        d.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (self.export_sum_ptr(), False), "version": 2}
-        return torch.as_tensor(d, device=torch.device("cuda", self.device))
+    def export_sum_to(self, device_ptr: int):
+        """Writes the (sum.rgb, count) image into caller-owned device memory (complete on return)."""
+        _check(self.lib.prt_export_sum_to_device(self.handle, C.c_void_p(device_ptr)))
 
     def import_sum(self, device_ptr: int):
         _check(self.lib.prt_import_sum_device(self.handle, C.c_void_p(device_ptr)))
 
-    def accum_pixels(self) -> int:
-        return self._accum_pixels
 
     def counters(self) -> dict:
         c = PrtCounters()
