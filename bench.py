@@ -218,8 +218,8 @@ class build_scene_stub:
 B_RAY_IO = 32 + 8 + 16      # ray in (origin+tMin, dir+tMax), ray id (path, seed), hit record out
 B_NODE = 80                 # one compressed 8-wide node
 B_TRI = 48                  # one triangle record (v0, e1, e2 as 3 x float4 with ids in .w)
-B_INST = 80                 # one instance record (3x4 world->object, BLAS pointers, custom index)
-B_ANYHIT = 12 + 3 * 2 + 3 * 4 + 48 + 16  # draw instance + 3 u16 indices + 3 fp16x2 uvs + material + one BC7 block
+B_INST = 96                 # one instance record (3x4 world->object, BLAS pointers, custom index)
+B_ANYHIT = 32 + 32 + 4      # AlphaMat record + AlphaUv record + four alpha-plane texels
 
 
 def traversal_bytes(c, shadow):
@@ -262,6 +262,8 @@ def run_ours(args):
     first_frame, _ = partition.rank_frames(rank, world_size, args.spp)
 
     scene = build_scene(args)
+    if os.environ.get("PRT_EXPERIMENT_OPAQUE"):  # experiment only: no any-hit work at all (changes the image)
+        scene.materials["alphaMode"] = 0
     world = rt.World(scene, device=local_rank, max_width=WIDTH, max_height=HEIGHT,
                      samples_per_launch=args.samples_per_launch, flags=0)
     world.updateBuffers()
@@ -452,6 +454,7 @@ def main():
     import faulthandler
     faulthandler.enable()
     args = parse_args()
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -117,7 +117,7 @@ prt_status prt_trace_rays(prt_ctx *ctx, const float *originTmin, const float *di
 prt_status prt_probe_texture(prt_ctx *ctx, uint32_t textureSampler, const float *uv, const int32_t *texelXY,
                              uint32_t count, int exact, float *outRgba);
 
-/* Test hooks: read the built structures back (80-byte wide nodes, 48-byte triangle records, 80-byte
+/* Test hooks: read the built structures back (80-byte wide nodes, 48-byte triangle records, 96-byte
  * instance records; layouts in prosper_b200/csrc/core_bvh.h) so the tests can validate the GPU
  * builder's output structurally on the host. Pass NULL buffers to query the counts. */
 prt_status prt_debug_read_blas(prt_ctx *ctx, uint32_t modelIndex, void *nodesOut, uint64_t nodesBytes,

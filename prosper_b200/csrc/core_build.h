@@ -16,6 +16,7 @@ struct TlasInput
     uint32_t index; // position in the caller's array
     const WideNode *nodes;
     const TriRec *tris;
+    const AlphaUv *uvs;
 };
 
 // One BLAS triangle (World.cpp:617-668): fp16x4 positions, stride 8 (Mesh.hpp:11-12), through the
@@ -36,6 +37,14 @@ HD void gatherTriangle(const SceneView &sv, uint32_t meshIndex, uint32_t p, uint
     t.e2[0] = e2.x; t.e2[1] = e2.y; t.e2[2] = e2.z; t.pad = 0;
     lo = vmin(v0, vmin(v1, v2));
     hi = vmax(v0, vmax(v1, v2));
+}
+
+// The any-hit record of triangle p (scene.rahit:24-30: loadUV of its three corners).
+HD void gatherTriangleUvs(const SceneView &sv, uint32_t meshIndex, uint32_t p, AlphaUv &r)
+{
+    const V2 uv0 = loadUV(sv, meshIndex, p * 3 + 0), uv1 = loadUV(sv, meshIndex, p * 3 + 1), uv2 = loadUV(sv, meshIndex, p * 3 + 2);
+    r.uv[0] = uv0.x; r.uv[1] = uv0.y; r.uv[2] = uv1.x; r.uv[3] = uv1.y; r.uv[4] = uv2.x; r.uv[5] = uv2.y;
+    r.pad[0] = 0; r.pad[1] = 0;
 }
 
 // Pads a primitive box (padMode 1: the oracle's rule for triangles, pad = max(max|coord| / 16384,
@@ -63,6 +72,8 @@ HD void tlasInstanceRecord(const TlasInput &ti, InstRec &r, V3 &lo, V3 &hi)
     r.mask = ti.customIndexAndMask >> 24;
     r.index = ti.index;
     r.pad = 0;
+    r.uvs = ti.uvs;
+    r.pad2 = 0;
     WideNode root;
     loadNode(ti.nodes, root);
     const Box ob = wideNodeBounds(root);

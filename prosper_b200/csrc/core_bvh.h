@@ -73,7 +73,17 @@ struct alignas(16) TriRec
 };
 static_assert(sizeof(TriRec) == 48, "TriRec");
 
-// Instance record in TLAS node order, 80 bytes = five 128-bit loads.
+// Any-hit record of one triangle, parallel to the TriRec array (same index): the three texture coordinates the
+// any-hit stage would otherwise fetch through the draw instance, the mesh metadata and the index buffer
+// (scene.rahit:24-30 loadUV x 3). Filled for non-opaque geometry only. 32 bytes = two 128-bit loads.
+struct alignas(16) AlphaUv
+{
+    float uv[6]; // uv0.xy, uv1.xy, uv2.xy: the fp16x2 attributes widened to float (exact)
+    uint32_t pad[2];
+};
+static_assert(sizeof(AlphaUv) == 32, "AlphaUv");
+
+// Instance record in TLAS node order, 96 bytes = six 128-bit loads.
 struct alignas(16) InstRec
 {
     float w2o[12];          // world -> object, row-major 3x4 (exact contract inverse)
@@ -83,8 +93,10 @@ struct alignas(16) InstRec
     uint32_t mask;
     uint32_t index;         // position in the caller's instance array (tie-break key)
     uint32_t pad;
+    const AlphaUv *uvs;     // any-hit records of the BLAS (nullptr: fetch uvs through the scene buffers)
+    uint64_t pad2;
 };
-static_assert(sizeof(InstRec) == 80, "InstRec");
+static_assert(sizeof(InstRec) == 96, "InstRec");
 
 // ---- Morton keys ---------------------------------------------------------------------------------
 HD uint64_t expandBits21(uint32_t v)

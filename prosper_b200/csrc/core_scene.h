@@ -39,6 +39,25 @@ struct TexSlot
                            // (built at upload, prt_set_texture); nullptr: decode the payload per tap
 };
 
+// Everything scene.rahit's sampleAlpha needs for one draw instance, flattened into one 32-byte record (two
+// 128-bit loads) so the any-hit stage does not chase draw instance -> material -> texture slot. Derived data,
+// rebuilt by k_alpha_mats whenever draw instances, materials or textures change.
+struct alignas(16) AlphaMat
+{
+    const uint8_t *alpha; // level-0 alpha plane of the base colour texture (nullptr unless kind == PLANE)
+    uint32_t width, height;
+    uint32_t bits;        // see ALPHAMAT_*
+    float factor;         // baseColorFactor.a
+    float cutoff;         // alphaCutoff
+    uint32_t pad;
+};
+static_assert(sizeof(AlphaMat) == 32, "AlphaMat");
+constexpr uint32_t ALPHAMAT_TEXTURED = 1u;      // a valid base colour texture is bound
+constexpr uint32_t ALPHAMAT_TEX_OPAQUE = 2u;    // ... whose texels all have alpha 255
+constexpr uint32_t ALPHAMAT_NEAREST = 4u;       // mag filter
+constexpr uint32_t ALPHAMAT_ADDRU_SHIFT = 4, ALPHAMAT_ADDRV_SHIFT = 6, ALPHAMAT_MODE_SHIFT = 8;
+constexpr uint32_t ALPHAMAT_USABLE = 1u << 31;  // 0: this draw instance must take the generic any-hit path
+
 struct SceneView
 {
     const uint32_t *const *geometryBuffers;
@@ -56,6 +75,7 @@ struct SceneView
     const uint16_t *sky; // RGBA16F, 6 faces
     uint32_t skyFaceSize;
     uint32_t exactMaterialFilter; // 1: software bilinear for material taps too (parity tests)
+    const AlphaMat *alphaMats;    // [draw instance]; nullptr: generic any-hit path only
 };
 
 // ---- scene/geometry.glsl ---------------------------------------------------------------------------
@@ -183,6 +203,7 @@ HD int wrapCoord(int i, int n, uint32_t mode)
 {
     if (mode == PRT_ADDRESS_REPEAT)
     {
+        if ((n & (n - 1)) == 0) return i & (n - 1); // power of two: the same non-negative remainder
         i %= n;
         return i < 0 ? i + n : i;
     }
@@ -256,41 +277,48 @@ HD V4 sampleTextureExact(const TexSlot &s, V2 uv)
 // .w of sampleTextureExact, bit for bit: the same coordinates, texel values and filter arithmetic, but the four
 // texels come from the decoded alpha plane (or are the constant 1 for a texture without transparency) instead
 // of four software BC7 block decodes. This is what scene.rahit's sampleAlpha costs per candidate.
-HD float texelAlpha(const TexSlot &s, int x, int y)
+// `fallback` (may be nullptr) decodes the payload when no plane was built.
+HD float texelAlphaAt(const uint8_t *plane, const TexSlot *fallback, uint32_t width, int x, int y)
 {
-    if (s.alphaOpaque) return 1.f; // xdiv(255, 255)
-    if (s.alpha == nullptr) return fetchTexel(s, x, y).w;
+    if (plane == nullptr) return fallback ? fetchTexel(*fallback, x, y).w : 1.f;
 #if defined(__CUDA_ARCH__)
-    return xdiv((float)__ldg(s.alpha + (size_t)y * s.width + x), 255.f);
+    return xdiv((float)__ldg(plane + (size_t)y * width + x), 255.f);
 #else
-    return xdiv((float)s.alpha[(size_t)y * s.width + x], 255.f);
+    return xdiv((float)plane[(size_t)y * width + x], 255.f);
 #endif
 }
 
-HD float sampleTextureAlphaExact(const TexSlot &s, V2 uv)
+HD float alphaFilterExact(const uint8_t *plane, bool allOpaque, const TexSlot *fallback, uint32_t width, uint32_t height, bool nearest,
+                          uint32_t addressU, uint32_t addressV, V2 uv)
 {
-    const int w = (int)s.width, h = (int)s.height;
-    if (s.magFilter == PRT_FILTER_NEAREST)
+    const int w = (int)width, h = (int)height;
+    if (nearest)
     {
-        const int x = wrapCoord((int)floorf(xmul(uv.x, (float)w)), w, s.addressU);
-        const int y = wrapCoord((int)floorf(xmul(uv.y, (float)h)), h, s.addressV);
-        return texelAlpha(s, x, y);
+        if (allOpaque) return 1.f; // xdiv(255, 255)
+        const int x = wrapCoord((int)floorf(xmul(uv.x, (float)w)), w, addressU);
+        const int y = wrapCoord((int)floorf(xmul(uv.y, (float)h)), h, addressV);
+        return texelAlphaAt(plane, fallback, width, x, y);
     }
     const float fx = xsub(xmul(uv.x, (float)w), 0.5f), fy = xsub(xmul(uv.y, (float)h), 0.5f);
     const float x0f = floorf(fx), y0f = floorf(fy);
     const float ax = xsub(fx, x0f), ay = xsub(fy, y0f);
     float c00 = 1.f, c10 = 1.f, c01 = 1.f, c11 = 1.f;
-    if (!s.alphaOpaque)
+    if (!allOpaque)
     {
-        const int x0 = wrapCoord((int)x0f, w, s.addressU), x1 = wrapCoord((int)x0f + 1, w, s.addressU);
-        const int y0 = wrapCoord((int)y0f, h, s.addressV), y1 = wrapCoord((int)y0f + 1, h, s.addressV);
-        c00 = texelAlpha(s, x0, y0); c10 = texelAlpha(s, x1, y0);
-        c01 = texelAlpha(s, x0, y1); c11 = texelAlpha(s, x1, y1);
+        const int x0 = wrapCoord((int)x0f, w, addressU), x1 = wrapCoord((int)x0f + 1, w, addressU);
+        const int y0 = wrapCoord((int)y0f, h, addressV), y1 = wrapCoord((int)y0f + 1, h, addressV);
+        c00 = texelAlphaAt(plane, fallback, width, x0, y0); c10 = texelAlphaAt(plane, fallback, width, x1, y0);
+        c01 = texelAlphaAt(plane, fallback, width, x0, y1); c11 = texelAlphaAt(plane, fallback, width, x1, y1);
     }
     const float bx = xsub(1.f, ax), by = xsub(1.f, ay);
     const float top = xadd(xmul(c00, bx), xmul(c10, ax));
     const float bot = xadd(xmul(c01, bx), xmul(c11, ax));
     return xadd(xmul(top, by), xmul(bot, ay));
+}
+
+HD float sampleTextureAlphaExact(const TexSlot &s, V2 uv)
+{
+    return alphaFilterExact(s.alpha, s.alphaOpaque != 0, &s, s.width, s.height, s.magFilter == PRT_FILTER_NEAREST, s.addressU, s.addressV, uv);
 }
 
 HD const TexSlot *texSlot(const SceneView &sv, uint32_t textureSampler)
@@ -423,6 +451,58 @@ HD bool anyHitAccept(const SceneView &sv, uint32_t drawInstanceIndex, uint32_t p
         const float u = (float)pcg(randomSeed) / 4294967296.0f;
         if (u > alpha) return false;
     }
+    return true;
+}
+
+// The AlphaMat of one draw instance (k_alpha_mats; the CPU simulator calls it too).
+HD AlphaMat makeAlphaMat(const SceneView &sv, uint32_t drawInstanceIndex)
+{
+    const prt_draw_instance &instance = sv.drawInstances[drawInstanceIndex];
+    const prt_material_data &data = sv.materials[instance.materialIndex];
+    AlphaMat m;
+    m.alpha = nullptr; m.width = 1; m.height = 1; m.pad = 0;
+    m.factor = data.baseColorFactor[3];
+    m.cutoff = data.alphaCutoff;
+    m.bits = ALPHAMAT_USABLE | (data.alphaMode << ALPHAMAT_MODE_SHIFT);
+    if ((data.baseColorTextureSampler & 0xFFFFFFu) > 0)
+    {
+        const TexSlot *s = texSlot(sv, data.baseColorTextureSampler);
+        if (s != nullptr) // an unbound slot samples as 1 and sRGBtoLinear(1) == 1: the same as no texture
+        {
+            m.bits |= ALPHAMAT_TEXTURED | (s->magFilter == PRT_FILTER_NEAREST ? ALPHAMAT_NEAREST : 0u) |
+                      (s->addressU << ALPHAMAT_ADDRU_SHIFT) | (s->addressV << ALPHAMAT_ADDRV_SHIFT);
+            m.width = s->width; m.height = s->height;
+            if (s->alphaOpaque) m.bits |= ALPHAMAT_TEX_OPAQUE;
+            else if (s->alpha) m.alpha = s->alpha;
+            else m.bits &= ~ALPHAMAT_USABLE; // no alpha plane built: generic path decodes the payload
+        }
+    }
+    return m;
+}
+
+// anyHitAccept with the flattened records: bit-identical decisions (same uv interpolation, same filter, same
+// sRGB->linear, same comparisons), two 128-bit loads + four alpha bytes instead of the scene-buffer chase.
+HD bool anyHitAcceptFast(const AlphaMat &m, const AlphaUv &t, float bx, float by, uint32_t randomSeed)
+{
+    const V2 uv = interpolateUvExact(V2{t.uv[0], t.uv[1]}, V2{t.uv[2], t.uv[3]}, V2{t.uv[4], t.uv[5]}, bx, by);
+    float linearAlpha = 1;
+    if (m.bits & ALPHAMAT_TEXTURED)
+        linearAlpha = sRGBtoLinear(alphaFilterExact(m.alpha, (m.bits & ALPHAMAT_TEX_OPAQUE) != 0, nullptr, m.width, m.height,
+                                                    (m.bits & ALPHAMAT_NEAREST) != 0, (m.bits >> ALPHAMAT_ADDRU_SHIFT) & 3u,
+                                                    (m.bits >> ALPHAMAT_ADDRV_SHIFT) & 3u, uv));
+    linearAlpha = xmul(linearAlpha, m.factor);
+    const uint32_t mode = (m.bits >> ALPHAMAT_MODE_SHIFT) & 3u;
+    if (mode == PRT_ALPHA_BLEND)
+    {
+        if (linearAlpha == 0) return false;
+        if (linearAlpha > 0)
+        {
+            const float u = (float)pcg(randomSeed) / 4294967296.0f;
+            if (u > linearAlpha) return false;
+        }
+        return true;
+    }
+    if (mode == PRT_ALPHA_MASK && linearAlpha < m.cutoff) return false;
     return true;
 }
 

@@ -133,6 +133,31 @@ HD void loadNode(const WideNode *p, WideNode &n)
 #endif
 }
 
+HD AlphaMat loadAlphaMat(const AlphaMat *p)
+{
+#if defined(__CUDA_ARCH__)
+    AlphaMat m;
+    const uint4 *s = reinterpret_cast<const uint4 *>(p);
+    uint4 *d = reinterpret_cast<uint4 *>(&m);
+    d[0] = __ldg(s + 0); d[1] = __ldg(s + 1);
+    return m;
+#else
+    return *p;
+#endif
+}
+HD AlphaUv loadAlphaUv(const AlphaUv *p)
+{
+#if defined(__CUDA_ARCH__)
+    AlphaUv m;
+    const uint4 *s = reinterpret_cast<const uint4 *>(p);
+    uint4 *d = reinterpret_cast<uint4 *>(&m);
+    d[0] = __ldg(s + 0); d[1] = __ldg(s + 1);
+    return m;
+#else
+    return *p;
+#endif
+}
+
 // Intersects the ray with the eight quantised child boxes. Returns the hit mask: internal children
 // in bits 24..31 at position 24 + (slot ^ octinv) (nearer octant = higher bit), leaf primitives in
 // bits 0..23.
@@ -178,6 +203,7 @@ struct TraceState
     NodeRay ray;     // ray in the current space (world in the TLAS, object in a BLAS)
     const WideNode *nodes;
     const TriRec *tris;
+    const AlphaUv *uvs; // any-hit records of the current BLAS (may be nullptr)
     uint32_t instCustom, instIndex;
     uint32_t gx, gy; // node group: base index, hit bits | imask
     uint32_t px, py; // primitive group: base index, hit bits
@@ -204,6 +230,7 @@ HD bool traceBegin(TraceState &s, const Accel &as, V3 o, V3 d, float tMin, float
     setupNodeRay(s.ray, o, d);
     s.nodes = as.tlasNodes;
     s.tris = nullptr;
+    s.uvs = nullptr;
     s.instCustom = 0; s.instIndex = 0;
     s.gx = 0; s.gy = 0x80000000u;
     s.px = 0; s.py = 0;
@@ -243,6 +270,7 @@ HD bool traceStep(TraceState &s, TraceStack &st, const Accel &as, const SceneVie
                 setupNodeRay(s.ray, xformPoint(inst.w2o, s.o), xformVector(inst.w2o, s.d));
                 s.nodes = inst.nodes;
                 s.tris = inst.tris;
+                s.uvs = inst.uvs;
                 s.instCustom = inst.customIndex;
                 s.instIndex = inst.index;
                 s.gx = 0; s.gy = 0x80000000u;
@@ -266,7 +294,14 @@ HD bool traceStep(TraceState &s, TraceStack &st, const Accel &as, const SceneVie
                     if (!(tr.geometry >> 31))
                     {
                         if (COUNT) cnt->anyHits++;
-                        accept = anyHitAccept(sv, drawInstanceIndex, tr.primitive, u, v, s.seed);
+                        bool fast = s.uvs != nullptr && sv.alphaMats != nullptr;
+                        if (fast)
+                        {
+                            const AlphaMat am = loadAlphaMat(sv.alphaMats + drawInstanceIndex);
+                            fast = (am.bits & ALPHAMAT_USABLE) != 0;
+                            if (fast) accept = anyHitAcceptFast(am, loadAlphaUv(s.uvs + s.px + (uint32_t)pbit), u, v, s.seed);
+                        }
+                        if (!fast) accept = anyHitAccept(sv, drawInstanceIndex, tr.primitive, u, v, s.seed);
                     }
                     if (accept)
                     {

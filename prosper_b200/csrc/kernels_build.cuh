@@ -57,7 +57,8 @@ __device__ __forceinline__ void atomicBounds(BuildBounds *b, V3 lo, V3 hi, bool 
 
 // One launch per sub-model (= BLAS geometry, World.cpp:617-668): triangle records + unpadded boxes.
 __global__ void k_blas_gather(SceneView sv, uint32_t meshIndex, uint32_t primCount, uint32_t geometryIndex, uint32_t opaque,
-                              uint32_t outOffset, TriRec *__restrict__ tris, Box *__restrict__ boxes, BuildBounds *bounds)
+                              uint32_t outOffset, TriRec *__restrict__ tris, AlphaUv *__restrict__ uvs, Box *__restrict__ boxes,
+                              BuildBounds *bounds)
 {
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= primCount)
@@ -69,6 +70,9 @@ __global__ void k_blas_gather(SceneView sv, uint32_t meshIndex, uint32_t primCou
     V3 lo, hi;
     gatherTriangle(sv, meshIndex, p, geometryIndex, opaque, t, lo, hi);
     tris[outOffset + p] = t;
+    AlphaUv uv = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, {0u, 0u}};
+    if (!opaque) gatherTriangleUvs(sv, meshIndex, p, uv);
+    uvs[outOffset + p] = uv;
     boxes[outOffset + p] = makeBox(lo, hi);
     atomicBounds(bounds, lo, hi, true);
 }
@@ -143,13 +147,26 @@ __global__ void k_collapse_seed(CollapseItem *queue, uint32_t *queueCounts, uint
     for (uint32_t l = 1 + threadIdx.x; l < levels; l += blockDim.x) queueCounts[l] = 0;
 }
 
-__global__ void k_emit_tris(const uint32_t *__restrict__ primOut, uint32_t n, const TriRec *__restrict__ in, TriRec *__restrict__ out)
+__global__ void k_emit_tris(const uint32_t *__restrict__ primOut, uint32_t n, const TriRec *__restrict__ in, TriRec *__restrict__ out,
+                            const AlphaUv *__restrict__ uvIn, AlphaUv *__restrict__ uvOut)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const uint4 *s = reinterpret_cast<const uint4 *>(in + primOut[i]);
+    const uint32_t src = primOut[i];
+    const uint4 *s = reinterpret_cast<const uint4 *>(in + src);
     uint4 *d = reinterpret_cast<uint4 *>(out + i);
     d[0] = s[0]; d[1] = s[1]; d[2] = s[2];
+    const uint4 *us = reinterpret_cast<const uint4 *>(uvIn + src);
+    uint4 *ud = reinterpret_cast<uint4 *>(uvOut + i);
+    ud[0] = us[0]; ud[1] = us[1];
+}
+
+// AlphaMat table: one record per draw instance (any-hit stage)
+__global__ void k_alpha_mats(SceneView sv, uint32_t n, AlphaMat *__restrict__ out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = makeAlphaMat(sv, i);
 }
 
 // ---- TLAS ------------------------------------------------------------------------------------------------

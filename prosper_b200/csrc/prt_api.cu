@@ -129,6 +129,7 @@ struct BlasRes
 {
     WideNode *nodes = nullptr;
     TriRec *tris = nullptr;
+    AlphaUv *uvs = nullptr; // any-hit records, parallel to tris
     uint32_t nodeCount = 0, triCount = 0;
     bool built = false;
 };
@@ -176,6 +177,10 @@ struct prt_ctx
 
     // builder scratch
     DBuf<TriRec> bTris;
+    DBuf<AlphaUv> bUvs;
+    DBuf<AlphaMat> dAlphaMats; // per draw instance, rebuilt when draw instances / materials / textures change
+    uint32_t drawCount = 0;
+    bool alphaMatsDirty = true;
     DBuf<InstRec> bInst;
     DBuf<TlasInput> bTlasIn;
     DBuf<Box> bBoxes, bNodeBox;
@@ -244,6 +249,7 @@ struct prt_ctx
         sv.sky = skyFace ? dSky.p : nullptr;
         sv.skyFaceSize = skyFace;
         sv.exactMaterialFilter = (cfg.flags & PRT_CFG_EXACT_FILTER) ? 1u : 0u;
+        sv.alphaMats = (!alphaMatsDirty && drawCount) ? dAlphaMats.p : nullptr;
         return sv;
     }
     Accel accel() const
@@ -355,6 +361,7 @@ extern "C" void prt_destroy(prt_ctx *c)
     {
         if (b.nodes) cudaFree(b.nodes);
         if (b.tris) cudaFree(b.tris);
+        if (b.uvs) cudaFree(b.uvs);
     }
     PathBuffers &pb = c->pb;
     void *ptrs[] = {pb.rng,      pb.throughput, pb.color,   pb.rayO[0], pb.rayO[1], pb.rayD[0],  pb.rayD[1], pb.rayId[0],
@@ -364,7 +371,7 @@ extern "C" void prt_destroy(prt_ctx *c)
     c->geomTable.release(); c->dMeta.release(); c->dMat.release(); c->dSlots.release(); c->dSky.release();
     c->dDraw.release(); c->dXf.release(); c->dDir.release(); c->dPoints.release(); c->dSpots.release(); c->dCam.release();
     c->tlasNodes.release(); c->tlasInst.release();
-    c->bTris.release(); c->bInst.release(); c->bTlasIn.release(); c->bBoxes.release(); c->bNodeBox.release();
+    c->bTris.release(); c->bUvs.release(); c->dAlphaMats.release(); c->bInst.release(); c->bTlasIn.release(); c->bBoxes.release(); c->bNodeBox.release();
     for (int i = 0; i < 2; ++i) { c->bKeys[i].release(); c->bOrder[i].release(); c->bQueue[i].release(); }
     c->bHist.release(); c->bFirst.release(); c->bLast.release(); c->bVisit.release(); c->bPrimOut.release(); c->bScalars.release();
     c->bLeft.release(); c->bRight.release(); c->bParentI.release(); c->bParentL.release(); c->bNodes.release(); c->bBounds.release();
@@ -430,6 +437,7 @@ extern "C" prt_status prt_set_materials(prt_ctx *c, const prt_material_data *mat
     c->hMat.assign(materials, materials + count);
     CK(c->dMat.ensure(count));
     CK(c->ring.upload(c->dMat.p, materials, count * sizeof(prt_material_data), c->stream));
+    c->alphaMatsDirty = true;
     return PRT_OK;
 }
 
@@ -612,6 +620,23 @@ static prt_status refreshTextureSlots(prt_ctx *c)
         CK(cudaMemcpyAsync(c->dSlots.p, c->hSlots.data(), c->hSlots.size() * sizeof(TexSlot), cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     c->slotsDirty = false;
+    c->alphaMatsDirty = true;
+    return PRT_OK;
+}
+
+// The any-hit stage's per-draw-instance records (AlphaMat), stream-ordered after the uploads they derive from.
+static prt_status refreshAlphaMats(prt_ctx *c)
+{
+    if (!c->alphaMatsDirty) return PRT_OK;
+    if (c->drawCount && !c->hMat.empty())
+    {
+        CK(c->dAlphaMats.ensure(c->drawCount));
+        SceneView sv = c->view();
+        k_alpha_mats<<<blocksFor(c->drawCount, 128), 128, 0, c->stream>>>(sv, c->drawCount, c->dAlphaMats.p);
+        c->kernelLaunches++;
+        CK(cudaGetLastError());
+        c->alphaMatsDirty = false;
+    }
     return PRT_OK;
 }
 
@@ -704,11 +729,12 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
     CK(cudaSetDevice(c->cfg.device));
     cudaStream_t st = c->stream;
     BlasRes &b = c->blas[modelIndex];
-    if (b.nodes || b.tris)
+    if (b.nodes || b.tris || b.uvs)
     {
         CK(cudaStreamSynchronize(st));
         if (b.nodes) CK(cudaFree(b.nodes));
         if (b.tris) CK(cudaFree(b.tris));
+        if (b.uvs) CK(cudaFree(b.uvs));
         b = BlasRes{};
     }
     uint64_t total = 0;
@@ -726,6 +752,7 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
     CK(cudaEventRecord(c->evBlas[0], st));
     uint32_t launches = 0;
     CK(c->bTris.ensure(n));
+    CK(c->bUvs.ensure(n));
     CK(c->bBoxes.ensure(n));
     k_init_bounds<<<1, 32, 0, st>>>(c->bBounds.p, c->bScalars.p, 8);
     const SceneView sv = c->view();
@@ -739,7 +766,7 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
         REQUIRE(info.materialIndex < c->hMat.size(), "mesh material index out of range");
         const uint32_t opaque = c->hMat[info.materialIndex].alphaMode == PRT_ALPHA_OPAQUE ? 1u : 0u;
         k_blas_gather<<<blocksFor(prims, 128), 128, 0, st>>>(sv, sm.meshIndex, prims, g - c->modelOffsets[modelIndex], opaque, offset,
-                                                             c->bTris.p, c->bBoxes.p, c->bBounds.p);
+                                                             c->bTris.p, c->bUvs.p, c->bBoxes.p, c->bBounds.p);
         launches++;
         offset += prims;
     }
@@ -753,8 +780,9 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
     b.triCount = n;
     CK(cudaMalloc((void **)&b.nodes, (size_t)b.nodeCount * sizeof(WideNode)));
     CK(cudaMalloc((void **)&b.tris, (size_t)n * sizeof(TriRec)));
+    CK(cudaMalloc((void **)&b.uvs, (size_t)n * sizeof(AlphaUv)));
     CK(cudaMemcpyAsync(b.nodes, c->bNodes.p, (size_t)b.nodeCount * sizeof(WideNode), cudaMemcpyDeviceToDevice, st));
-    k_emit_tris<<<blocksFor(n, 256), 256, 0, st>>>(c->bPrimOut.p, n, c->bTris.p, b.tris);
+    k_emit_tris<<<blocksFor(n, 256), 256, 0, st>>>(c->bPrimOut.p, n, c->bTris.p, b.tris, c->bUvs.p, b.uvs);
     launches++;
     CK(cudaGetLastError());
     CK(cudaEventRecord(c->evBlas[1], st));
@@ -786,6 +814,7 @@ extern "C" prt_status prt_build_tlas(prt_ctx *c, const prt_tlas_instance *instan
         t.index = i;
         t.nodes = b.nodes;
         t.tris = b.tris;
+        t.uvs = b.uvs;
         in.push_back(t);
     }
     const uint32_t n = (uint32_t)in.size();
@@ -824,6 +853,8 @@ extern "C" prt_status prt_set_draw_instances(prt_ctx *c, const prt_draw_instance
     CK(cudaSetDevice(c->cfg.device));
     CK(c->dDraw.ensure(count));
     CK(c->ring.upload(c->dDraw.p, instances, (size_t)count * sizeof(prt_draw_instance), c->stream));
+    c->drawCount = count;
+    c->alphaMatsDirty = true;
     return PRT_OK;
 }
 
@@ -871,6 +902,7 @@ static prt_status checkRenderState(prt_ctx *c, const prt_reference_pc *pc, uint3
     REQUIRE(pc->maxBounces <= PRT_MAX_BOUNCES, "maxBounces above sMaxBounces (RtRef.hpp:22)");
     REQUIRE(pc->drawType < PRT_DRAW_COUNT, "unknown draw type");
     CKS(refreshTextureSlots(c));
+    CKS(refreshAlphaMats(c));
     return PRT_OK;
 }
 
@@ -1028,6 +1060,7 @@ extern "C" prt_status prt_trace_rays(prt_ctx *c, const float *originTmin, const 
     REQUIRE(c && originTmin && dirTmax && dstHost, "prt_trace_rays");
     CK(cudaSetDevice(c->cfg.device));
     CKS(refreshTextureSlots(c));
+    CKS(refreshAlphaMats(c));
     if (count == 0) return PRT_OK;
     cudaStream_t st = c->stream;
     CK(c->userO.ensure(count)); CK(c->userD.ensure(count)); CK(c->userSeeds.ensure(count)); CK(c->userHits.ensure(count));

@@ -23,7 +23,8 @@ import numpy as np
 from . import scene_data as sd
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libprt_b200.so")
+# PRT_LIB: an alternative build of the same library (kernel experiments); there is still no fallback
+LIB_PATH = os.environ.get("PRT_LIB") or os.path.join(_HERE, "libprt_b200.so")
 
 CFG_COUNTERS, CFG_EXACT_FILTER, CFG_DECODE_BC7 = 1, 2, 4
 
@@ -269,11 +270,11 @@ class World:
         return nodes, tris
 
     def read_tlas(self):
-        """(nodes uint8 [n, 80], instance records uint8 [n, 80]) of the current TLAS (test hook)."""
+        """(nodes uint8 [n, 80], instance records uint8 [n, 96]) of the current TLAS (test hook)."""
         n = C.c_uint32()
         _check(self.lib.prt_debug_read_tlas(self.handle, None, 0, None, 0, C.byref(n)))
         nodes = np.zeros((n.value, 80), np.uint8)
-        inst = np.zeros((n.value, 80), np.uint8)
+        inst = np.zeros((n.value, 96), np.uint8)
         if n.value:
             _check(self.lib.prt_debug_read_tlas(self.handle, _p(nodes), nodes.nbytes, _p(inst), inst.nbytes, None))
         return nodes, inst

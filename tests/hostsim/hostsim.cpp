@@ -83,6 +83,7 @@ struct HostBlas
 {
     std::vector<WideNode> nodes;
     std::vector<TriRec> tris;
+    std::vector<AlphaUv> uvs; // any-hit records, parallel to tris
 };
 
 } // namespace
@@ -91,6 +92,8 @@ struct hs_ctx
 {
     orc_scene s;
     std::vector<TexSlot> slots;
+    std::vector<std::vector<uint8_t>> alphaPlanes; // per texture (k_alpha_plane)
+    std::vector<AlphaMat> alphaMats;               // per draw instance (k_alpha_mats)
     std::vector<HostBlas> blas;
     std::vector<WideNode> tlasNodes;
     std::vector<InstRec> tlasInst;
@@ -125,6 +128,21 @@ template <typename F> static void parallelFor(uint32_t count, int threads, F &&f
     for (auto &t : pool) t.join();
 }
 
+// the any-hit records of a BLAS from its triangle records (what k_blas_gather + k_emit_tris leave behind)
+static void buildUvsHost(hs_ctx *c, uint32_t model)
+{
+    const orc_scene &s = c->s;
+    const prt_sub_model *subs = (const prt_sub_model *)s.subModels;
+    HostBlas &b = c->blas[model];
+    b.uvs.assign(b.tris.size(), AlphaUv{{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, {0u, 0u}});
+    for (size_t i = 0; i < b.tris.size(); ++i)
+    {
+        const TriRec &t = b.tris[i];
+        if (t.geometry >> 31) continue;
+        gatherTriangleUvs(c->sv, subs[s.modelOffsets[model] + (t.geometry & 0x7FFFFFFFu)].meshIndex, t.primitive, b.uvs[i]);
+    }
+}
+
 static void buildTlasHost(hs_ctx *c)
 {
     const orc_scene &s = c->s;
@@ -147,6 +165,7 @@ static void buildTlasHost(hs_ctx *c)
         ti.index = i;
         ti.nodes = c->blas[model].nodes.data();
         ti.tris = c->blas[model].tris.data();
+        ti.uvs = c->blas[model].uvs.data();
         InstRec r;
         V3 l, h;
         tlasInstanceRecord(ti, r, l, h);
@@ -181,10 +200,26 @@ hs_ctx *hs_create(const orc_scene *scene, int exactMaterialFilter)
     // texture slots point at the cached payloads: the software filter decodes texels on the fly
     const uint32_t ns = std::max(s.samplerCount, 1u);
     c->slots.assign((size_t)s.textureCount * ns, TexSlot{});
+    c->alphaPlanes.resize(s.textureCount);
     for (uint32_t t = 0; t < s.textureCount; ++t)
     {
         const orc_texture &tx = s.textures[t];
         if (!tx.data || !tx.width) continue;
+        // level-0 alpha plane (k_alpha_plane): one byte per texel as the payload decodes, dropped when all 255
+        std::vector<uint8_t> &plane = c->alphaPlanes[t];
+        plane.resize((size_t)tx.width * tx.height);
+        uint32_t lowest = 255;
+        {
+            TexSlot view{};
+            view.payload = (const uint8_t *)tx.data; view.format = tx.format; view.width = tx.width; view.height = tx.height;
+            for (uint32_t y = 0; y < tx.height; ++y)
+                for (uint32_t x = 0; x < tx.width; ++x)
+                {
+                    const uint32_t a = (uint32_t)(fetchTexel(view, (int)x, (int)y).w * 255.f + 0.5f);
+                    plane[(size_t)y * tx.width + x] = (uint8_t)a;
+                    lowest = std::min(lowest, a);
+                }
+        }
         for (uint32_t sm = 0; sm < ns; ++sm)
         {
             TexSlot &slot = c->slots[(size_t)t * ns + sm];
@@ -194,6 +229,8 @@ hs_ctx *hs_create(const orc_scene *scene, int exactMaterialFilter)
             const prt_sampler_desc sd = s.samplerCount ? ((const prt_sampler_desc *)s.samplers)[sm] : prt_sampler_desc{1, 1, 0, 0};
             slot.magFilter = sd.magFilter; slot.addressU = sd.addressU; slot.addressV = sd.addressV;
             slot.valid = 1;
+            slot.alphaOpaque = lowest == 255 ? 1u : 0u;
+            slot.alpha = lowest == 255 ? nullptr : plane.data();
         }
     }
     SceneView &sv = c->sv;
@@ -214,6 +251,10 @@ hs_ctx *hs_create(const orc_scene *scene, int exactMaterialFilter)
     sv.sky = (const uint16_t *)s.skyRgba16f;
     sv.skyFaceSize = s.skyRgba16f ? s.skyFaceSize : 0;
     sv.exactMaterialFilter = exactMaterialFilter ? 1u : 0u;
+    sv.alphaMats = nullptr;
+    c->alphaMats.resize(s.drawInstanceCount);
+    for (uint32_t i = 0; i < s.drawInstanceCount; ++i) c->alphaMats[i] = makeAlphaMat(sv, i);
+    sv.alphaMats = c->alphaMats.empty() ? nullptr : c->alphaMats.data();
 
     // BLAS per model (the k_blas_gather -> buildHierarchy -> k_emit_tris sequence of prt_build_blas)
     const prt_mesh_info *infos = (const prt_mesh_info *)s.meshInfos;
@@ -246,6 +287,7 @@ hs_ctx *hs_create(const orc_scene *scene, int exactMaterialFilter)
         c->blas[m].nodes = std::move(h.nodes);
         c->blas[m].tris.resize(tris.size());
         for (size_t i = 0; i < tris.size(); ++i) c->blas[m].tris[i] = tris[h.primOut[i]];
+        buildUvsHost(c, m);
     }
     buildTlasHost(c);
     return c;
@@ -260,6 +302,7 @@ void hs_replace_blas(hs_ctx *c, uint32_t model, const void *nodes, uint32_t node
     HostBlas &b = c->blas[model];
     b.nodes.assign((const WideNode *)nodes, (const WideNode *)nodes + nodeCount);
     b.tris.assign((const TriRec *)tris, (const TriRec *)tris + triCount);
+    buildUvsHost(c, model);
     buildTlasHost(c);
 }
 
