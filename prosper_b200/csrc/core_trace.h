@@ -8,6 +8,7 @@
 //   * box tests are conservative (quantised boxes only grow; slab interval widened by a few ulp),
 //   * any-hit acceptance uses one random number per RAY (scene.rahit:35), so it is order-free.
 #pragma once
+#include <cstring>
 #include "core_bvh.h"
 #include "core_scene.h"
 
@@ -165,6 +166,17 @@ HD uint32_t intersectNode(const WideNode &n, const NodeRay &r, float tMin, float
 {
     const float sx = u2f((uint32_t)n.ex << 23) * r.ix, sy = u2f((uint32_t)n.ey << 23) * r.iy, sz = u2f((uint32_t)n.ez << 23) * r.iz;
     const float ox = (n.px - r.o.x) * r.ix, oy = (n.py - r.o.y) * r.iy, oz = (n.pz - r.o.z) * r.iz;
+    // Entry/exit planes by ray octant instead of min/max per axis: with a non-negative direction the scaled
+    // step is non-negative and lo * s + o <= hi * s + o, so the near plane is `lo` (and vice versa) -- the same
+    // values min(x0, x1) / max(x0, x1) would pick. Branch-free so that the eight slots stay converged; an empty
+    // slot (meta == 0) contributes no bits whatever its planes say.
+    // (selected a 32-bit word at a time so that the node stays in registers)
+    uint32_t lo[6], hi[6];
+    memcpy(lo, n.qlo, 24);
+    memcpy(hi, n.qhi, 24);
+    const bool px = (r.octinv & 1u) != 0, py = (r.octinv & 2u) != 0, pz = (r.octinv & 4u) != 0;
+    const uint32_t nw[6] = {px ? lo[0] : hi[0], px ? lo[1] : hi[1], py ? lo[2] : hi[2], py ? lo[3] : hi[3], pz ? lo[4] : hi[4], pz ? lo[5] : hi[5]};
+    const uint32_t fw[6] = {px ? hi[0] : lo[0], px ? hi[1] : lo[1], py ? hi[2] : lo[2], py ? hi[3] : lo[3], pz ? hi[4] : lo[4], pz ? hi[5] : lo[5]};
     uint32_t mask = 0;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
@@ -172,23 +184,17 @@ HD uint32_t intersectNode(const WideNode &n, const NodeRay &r, float tMin, float
     for (int s = 0; s < 8; ++s)
     {
         const uint32_t meta = n.meta[s];
-        if (meta == 0) continue;
-        const float lx = (float)n.qlo[0][s], hx = (float)n.qhi[0][s];
-        const float ly = (float)n.qlo[1][s], hy = (float)n.qhi[1][s];
-        const float lz = (float)n.qlo[2][s], hz = (float)n.qhi[2][s];
-        const float x0 = lx * sx + ox, x1 = hx * sx + ox;
-        const float y0 = ly * sy + oy, y1 = hy * sy + oy;
-        const float z0 = lz * sz + oz, z1 = hz * sz + oz;
-        float tn = fmaxf_(fmaxf_(fminf_(x0, x1), fminf_(y0, y1)), fmaxf_(fminf_(z0, z1), tMin));
-        float tf = fminf_(fminf_(fmaxf_(x0, x1), fmaxf_(y0, y1)), fminf_(fmaxf_(z0, z1), tMax));
+        const int w = s >> 2, sh = (s & 3) * 8;
+        const float x0 = (float)((nw[0 + w] >> sh) & 255u) * sx + ox, x1 = (float)((fw[0 + w] >> sh) & 255u) * sx + ox;
+        const float y0 = (float)((nw[2 + w] >> sh) & 255u) * sy + oy, y1 = (float)((fw[2 + w] >> sh) & 255u) * sy + oy;
+        const float z0 = (float)((nw[4 + w] >> sh) & 255u) * sz + oz, z1 = (float)((fw[4 + w] >> sh) & 255u) * sz + oz;
+        float tn = fmaxf_(fmaxf_(x0, y0), fmaxf_(z0, tMin));
+        float tf = fminf_(fminf_(x1, y1), fminf_(z1, tMax));
         tn = tn - fabsf(tn) * 4e-7f;
         tf = tf + fabsf(tf) * 4e-7f;
-        if (tn <= tf)
-        {
-            const uint32_t low5 = meta & 31u;
-            if ((meta & 0x18u) == 0x18u) mask |= 1u << (low5 ^ r.octinv);
-            else mask |= (meta >> 5) << low5;
-        }
+        const uint32_t low5 = meta & 31u;
+        const uint32_t bits = ((meta & 0x18u) == 0x18u) ? (1u << (low5 ^ r.octinv)) : ((meta >> 5) << low5);
+        mask |= (tn <= tf) ? bits : 0u;
     }
     return mask;
 }

@@ -193,7 +193,8 @@ __global__ void k_emit_instances(const uint32_t *__restrict__ primOut, uint32_t 
     if (i >= n) return;
     const uint4 *s = reinterpret_cast<const uint4 *>(in + primOut[i]);
     uint4 *d = reinterpret_cast<uint4 *>(out + i);
-    d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; d[3] = s[3]; d[4] = s[4];
+    static_assert(sizeof(InstRec) == 6 * sizeof(uint4), "InstRec copy");
+    d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; d[3] = s[3]; d[4] = s[4]; d[5] = s[5];
 }
 
 } // namespace prt
