@@ -282,10 +282,12 @@ HD float texelAlphaAt(const uint8_t *plane, const TexSlot *fallback, uint32_t wi
 {
     if (plane == nullptr) return fallback ? fetchTexel(*fallback, x, y).w : 1.f;
 #if defined(__CUDA_ARCH__)
-    return xdiv((float)__ldg(plane + (size_t)y * width + x), 255.f);
+    const uint32_t a = __ldg(plane + (size_t)y * width + x);
 #else
-    return xdiv((float)plane[(size_t)y * width + x], 255.f);
+    const uint32_t a = plane[(size_t)y * width + x];
 #endif
+    // 0 / 255 and 255 / 255 without the division (its zero-dividend case is a slow path on the device)
+    return a == 0u ? 0.f : (a == 255u ? 1.f : xdiv((float)a, 255.f));
 }
 
 HD float alphaFilterExact(const uint8_t *plane, bool allOpaque, const TexSlot *fallback, uint32_t width, uint32_t height, bool nearest,
@@ -350,6 +352,14 @@ struct Material // scene/material.glsl:4-16
 HD float sRGBtoLinear(float x) // materials.glsl:26-29
 {
     return x <= 0.04045f ? x / 12.92f : powf((x + 0.055f) / 1.055f, 2.4f);
+}
+// The same function for the any-hit stage with its two most common arguments answered without the IEEE division's
+// zero-dividend slow path and without powf: 0 / 12.92 == 0 and powf(1.055 / 1.055, 2.4) == powf(1, 2.4) == 1 exactly.
+HD float sRGBtoLinearAlpha(float x)
+{
+    if (x == 0.f) return x;
+    if (x == 1.f) return 1.f;
+    return sRGBtoLinear(x);
 }
 
 // The three texture() results sampleMaterial needs (base colour, metallic-roughness, normal); a tap of
@@ -421,7 +431,7 @@ HD float sampleAlpha(const SceneView &sv, uint32_t index, V2 uv)
     if ((data.baseColorTextureSampler & 0xFFFFFFu) > 0)
     {
         const TexSlot *s = texSlot(sv, data.baseColorTextureSampler);
-        linearAlpha = sRGBtoLinear(s ? sampleTextureAlphaExact(*s, uv) : 1.f);
+        linearAlpha = sRGBtoLinearAlpha(s ? sampleTextureAlphaExact(*s, uv) : 1.f);
     }
     linearAlpha = xmul(linearAlpha, data.baseColorFactor[3]);
     if (data.alphaMode == PRT_ALPHA_BLEND) return linearAlpha;
@@ -487,7 +497,7 @@ HD bool anyHitAcceptFast(const AlphaMat &m, const AlphaUv &t, float bx, float by
     const V2 uv = interpolateUvExact(V2{t.uv[0], t.uv[1]}, V2{t.uv[2], t.uv[3]}, V2{t.uv[4], t.uv[5]}, bx, by);
     float linearAlpha = 1;
     if (m.bits & ALPHAMAT_TEXTURED)
-        linearAlpha = sRGBtoLinear(alphaFilterExact(m.alpha, (m.bits & ALPHAMAT_TEX_OPAQUE) != 0, nullptr, m.width, m.height,
+        linearAlpha = sRGBtoLinearAlpha(alphaFilterExact(m.alpha, (m.bits & ALPHAMAT_TEX_OPAQUE) != 0, nullptr, m.width, m.height,
                                                     (m.bits & ALPHAMAT_NEAREST) != 0, (m.bits >> ALPHAMAT_ADDRU_SHIFT) & 3u,
                                                     (m.bits >> ALPHAMAT_ADDRV_SHIFT) & 3u, uv));
     linearAlpha = xmul(linearAlpha, m.factor);

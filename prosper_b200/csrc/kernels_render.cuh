@@ -145,7 +145,13 @@ __global__ void __launch_bounds__(RENDER_THREADS)
         if (!__any_sync(0xFFFFFFFFu, active)) break;
         for (;;)
         {
-            if (active && traceStep<false, COUNT>(s, st, as, sv, &tc))
+            // Majority vote: a step is either a primitive item or a node item (traceStep); only the kind most live
+            // lanes are waiting for runs this iteration, the others wait for their turn, so each issued
+            // instruction serves at least half of the live lanes instead of both kinds running half empty.
+            const bool wantPrim = active && s.py != 0;
+            const int nPrim = __popc(__ballot_sync(0xFFFFFFFFu, wantPrim)), nAll = __popc(__ballot_sync(0xFFFFFFFFu, active));
+            const bool runPrim = 2 * nPrim >= nAll;
+            if (active && wantPrim == runPrim && traceStep<false, COUNT>(s, st, as, sv, &tc))
             {
                 pb.hits[slot] = make_uint4(s.best.drawInstanceIndex, s.best.primitiveID, __float_as_uint(s.best.u), __float_as_uint(s.best.v));
                 active = false;
@@ -315,7 +321,10 @@ __global__ void __launch_bounds__(RENDER_THREADS)
         if (!__any_sync(0xFFFFFFFFu, active)) break;
         for (;;)
         {
-            if (active && traceStep<true, COUNT>(s, st, as, sv, &tc))
+            const bool wantPrim = active && s.py != 0; // majority vote, see k_trace_closest
+            const int nPrim = __popc(__ballot_sync(0xFFFFFFFFu, wantPrim)), nAll = __popc(__ballot_sync(0xFFFFFFFFu, active));
+            const bool runPrim = 2 * nPrim >= nAll;
+            if (active && wantPrim == runPrim && traceStep<true, COUNT>(s, st, as, sv, &tc))
             {
                 retire();
                 active = false;
