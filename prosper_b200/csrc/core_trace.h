@@ -203,41 +203,75 @@ HD uint32_t intersectNode(const WideNode &n, const NodeRay &r, float tMin, float
 // retire and refill lanes between steps (kernels_render.cuh); traceRay below runs it to completion.
 struct TraceState
 {
-    V3 o, d;         // world-space ray
     float tMin, tMax;
-    uint32_t seed;   // payload.randomSeed (scene.rahit:35)
     NodeRay ray;     // ray in the current space (world in the TLAS, object in a BLAS)
     const WideNode *nodes;
     const TriRec *tris;
-    const AlphaUv *uvs; // any-hit records of the current BLAS (may be nullptr)
-    uint32_t instCustom, instIndex;
+    uint32_t instIndex;
     uint32_t gx, gy; // node group: base index, hit bits | imask
     uint32_t px, py; // primitive group: base index, hit bits
     int sp;
     int blasSp;      // stack depth at BLAS entry; -1 while in the TLAS
     HitRec best;
 };
+// Rarely read part of the traversal state (instance entry/exit, any-hit): lives next to the stack in local
+// memory so that it does not hold registers across the hot node / triangle loop.
+struct TraceCold
+{
+    V3 o, d;            // world-space ray
+    uint32_t seed;      // payload.randomSeed (scene.rahit:35)
+    uint32_t instCustom;
+    const AlphaUv *uvs; // any-hit records of the current BLAS (may be nullptr)
+};
+
 // kept apart from TraceState so that the scalar state stays in registers (a dynamically indexed member
 // would drag the whole struct into local memory)
 struct TraceStack
 {
     uint32_t x[TRACE_STACK], y[TRACE_STACK];
+    TraceCold cold;
+    HD void put(int i, uint32_t a, uint32_t b) { x[i] = a; y[i] = b; }
+    HD void get(int i, uint32_t &a, uint32_t &b) const { a = x[i]; b = y[i]; }
 };
 
+#if defined(__CUDACC__)
+// The first TRACE_SMEM_STACK entries of every thread's stack live in shared memory ([entry][thread], 8-byte
+// columns: conflict-free), deeper ones in a per-thread local array that is almost never touched.
+constexpr int TRACE_SMEM_STACK = 12;
+struct SharedTraceStack
+{
+    uint2 *column; // &smem[0][threadIdx.x]
+    uint32_t stride; // threads per block
+    uint32_t ox[TRACE_STACK - TRACE_SMEM_STACK], oy[TRACE_STACK - TRACE_SMEM_STACK];
+    TraceCold cold;
+    __device__ __forceinline__ void put(int i, uint32_t a, uint32_t b)
+    {
+        if (i < TRACE_SMEM_STACK) column[(uint32_t)i * stride] = make_uint2(a, b);
+        else { ox[i - TRACE_SMEM_STACK] = a; oy[i - TRACE_SMEM_STACK] = b; }
+    }
+    __device__ __forceinline__ void get(int i, uint32_t &a, uint32_t &b) const
+    {
+        if (i < TRACE_SMEM_STACK) { const uint2 v = column[(uint32_t)i * stride]; a = v.x; b = v.y; }
+        else { a = ox[i - TRACE_SMEM_STACK]; b = oy[i - TRACE_SMEM_STACK]; }
+    }
+};
+#endif
+
 // Returns false when there is nothing to traverse (the ray is a miss).
-HD bool traceBegin(TraceState &s, const Accel &as, V3 o, V3 d, float tMin, float tMax, uint32_t seed)
+template <class Stack>
+HD bool traceBegin(TraceState &s, Stack &st, const Accel &as, V3 o, V3 d, float tMin, float tMax, uint32_t seed)
 {
     s.best.drawInstanceIndex = MISS_INDEX;
     s.best.primitiveID = MISS_INDEX;
     s.best.u = 0.f; s.best.v = 0.f; s.best.t = tMax; s.best.instance = MISS_INDEX; s.best.geometry = 0;
-    s.o = o; s.d = d; s.tMin = tMin; s.tMax = tMax; s.seed = seed;
+    st.cold.o = o; st.cold.d = d; st.cold.seed = seed; st.cold.instCustom = 0; st.cold.uvs = nullptr;
+    s.tMin = tMin; s.tMax = tMax;
     s.sp = 0;
     s.blasSp = -1;
     setupNodeRay(s.ray, o, d);
     s.nodes = as.tlasNodes;
     s.tris = nullptr;
-    s.uvs = nullptr;
-    s.instCustom = 0; s.instIndex = 0;
+    s.instIndex = 0;
     s.gx = 0; s.gy = 0x80000000u;
     s.px = 0; s.py = 0;
     return as.tlasNodes != nullptr;
@@ -248,8 +282,8 @@ HD bool traceBegin(TraceState &s, const Accel &as, V3 o, V3 d, float tMin, float
 // or entering an instance), or one node (take the nearest pending child of the current node group, intersect
 // its eight boxes). Pops when both groups are exhausted.
 // SHADOW = gl_RayFlagsTerminateOnFirstHitEXT (main.rgen:52). Returns true when the ray is finished.
-template <bool SHADOW, bool COUNT>
-HD bool traceStep(TraceState &s, TraceStack &st, const Accel &as, const SceneView &sv, TraceCounters *cnt)
+template <bool SHADOW, bool COUNT, class Stack>
+HD bool traceStep(TraceState &s, Stack &st, const Accel &as, const SceneView &sv, TraceCounters *cnt)
 {
     if (s.py != 0)
     {
@@ -264,20 +298,20 @@ HD bool traceStep(TraceState &s, TraceStack &st, const Accel &as, const SceneVie
             {
                 if (s.gy & 0xFF000000u)
                 {
-                    if (s.sp < TRACE_STACK) { st.x[s.sp] = s.gx; st.y[s.sp] = s.gy; s.sp++; }
+                    if (s.sp < TRACE_STACK) { st.put(s.sp, s.gx, s.gy); s.sp++; }
                     else if (COUNT) cnt->overflow++;
                 }
                 if (s.py != 0)
                 {
-                    if (s.sp < TRACE_STACK) { st.x[s.sp] = s.px; st.y[s.sp] = s.py; s.sp++; }
+                    if (s.sp < TRACE_STACK) { st.put(s.sp, s.px, s.py); s.sp++; }
                     else if (COUNT) cnt->overflow++;
                 }
                 s.blasSp = s.sp;
-                setupNodeRay(s.ray, xformPoint(inst.w2o, s.o), xformVector(inst.w2o, s.d));
+                setupNodeRay(s.ray, xformPoint(inst.w2o, st.cold.o), xformVector(inst.w2o, st.cold.d));
                 s.nodes = inst.nodes;
                 s.tris = inst.tris;
-                s.uvs = inst.uvs;
-                s.instCustom = inst.customIndex;
+                st.cold.uvs = inst.uvs;
+                st.cold.instCustom = inst.customIndex;
                 s.instIndex = inst.index;
                 s.gx = 0; s.gy = 0x80000000u;
                 s.py = 0;
@@ -295,19 +329,21 @@ HD bool traceStep(TraceState &s, TraceStack &st, const Accel &as, const SceneVie
                 const uint32_t geom = tr.geometry & 0x7FFFFFFFu;
                 if (betterHit(t, s.instIndex, geom, tr.primitive, s.best))
                 {
-                    const uint32_t drawInstanceIndex = s.instCustom + geom;
+                    const uint32_t drawInstanceIndex = st.cold.instCustom + geom;
                     bool accept = true;
                     if (!(tr.geometry >> 31))
                     {
                         if (COUNT) cnt->anyHits++;
-                        bool fast = s.uvs != nullptr && sv.alphaMats != nullptr;
+                        const AlphaUv *uvs = st.cold.uvs;
+                        const uint32_t seed = st.cold.seed;
+                        bool fast = uvs != nullptr && sv.alphaMats != nullptr;
                         if (fast)
                         {
                             const AlphaMat am = loadAlphaMat(sv.alphaMats + drawInstanceIndex);
                             fast = (am.bits & ALPHAMAT_USABLE) != 0;
-                            if (fast) accept = anyHitAcceptFast(am, loadAlphaUv(s.uvs + s.px + (uint32_t)pbit), u, v, s.seed);
+                            if (fast) accept = anyHitAcceptFast(am, loadAlphaUv(uvs + s.px + (uint32_t)pbit), u, v, seed);
                         }
-                        if (!fast) accept = anyHitAccept(sv, drawInstanceIndex, tr.primitive, u, v, s.seed);
+                        if (!fast) accept = anyHitAccept(sv, drawInstanceIndex, tr.primitive, u, v, seed);
                     }
                     if (accept)
                     {
@@ -329,7 +365,7 @@ HD bool traceStep(TraceState &s, TraceStack &st, const Accel &as, const SceneVie
         s.gy &= ~(1u << bit);
         if (s.gy & 0xFF000000u)
         {
-            if (s.sp < TRACE_STACK) { st.x[s.sp] = s.gx; st.y[s.sp] = s.gy; s.sp++; }
+            if (s.sp < TRACE_STACK) { st.put(s.sp, s.gx, s.gy); s.sp++; }
             else if (COUNT) cnt->overflow++;
         }
         const uint32_t slot = ((uint32_t)bit - 24u) ^ s.ray.octinv;
@@ -351,13 +387,12 @@ HD bool traceStep(TraceState &s, TraceStack &st, const Accel &as, const SceneVie
         {
             // BLAS exhausted: back to world space
             s.blasSp = -1;
-            setupNodeRay(s.ray, s.o, s.d);
+            setupNodeRay(s.ray, st.cold.o, st.cold.d);
             s.nodes = as.tlasNodes;
         }
         if (s.sp == 0) return true;
         s.sp--;
-        s.gx = st.x[s.sp];
-        s.gy = st.y[s.sp];
+        st.get(s.sp, s.gx, s.gy);
         if ((s.gy & 0xFF000000u) == 0)
         {
             // a postponed primitive group (pushed when an instance was entered)
@@ -375,7 +410,7 @@ HDNI bool traceRay(const Accel &as, const SceneView &sv, V3 o, V3 d, float tMin,
 {
     TraceState s;
     TraceStack st;
-    if (traceBegin(s, as, o, d, tMin, tMax, seed))
+    if (traceBegin(s, st, as, o, d, tMin, tMax, seed))
         while (!traceStep<SHADOW, COUNT>(s, st, as, sv, cnt)) {}
     best = s.best;
     return best.drawInstanceIndex != MISS_INDEX;

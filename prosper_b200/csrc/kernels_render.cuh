@@ -18,7 +18,16 @@ constexpr uint32_t CURSOR_BASE = 16;      // counts[16 + i] = fetch cursor of th
 constexpr uint32_t COUNT_WORDS = 32;
 // Persistent trace kernels: a warp refills its retired lanes from the queue once fewer than this many
 // lanes are still traversing (Aila & Laine's dynamic fetch); below it, finished lanes idle until the refill.
-constexpr int TRACE_REFILL_BELOW = 22;
+#ifndef PRT_TRACE_REFILL_BELOW
+#define PRT_TRACE_REFILL_BELOW 22
+#endif
+#ifndef PRT_TRACE_SMEM_STACK
+#define PRT_TRACE_SMEM_STACK 0
+#endif
+#ifndef PRT_TRACE_MIN_BLOCKS
+#define PRT_TRACE_MIN_BLOCKS 8
+#endif
+constexpr int TRACE_REFILL_BELOW = PRT_TRACE_REFILL_BELOW;
 
 struct PathBuffers
 {
@@ -119,14 +128,21 @@ __device__ __forceinline__ uint32_t fetchSlots(uint32_t *cursor, uint32_t count,
 
 // traceClosest, main.rgen:62-81. Persistent warps over the closest-ray queue of `bounce`.
 template <bool COUNT>
-__global__ void __launch_bounds__(RENDER_THREADS)
+__global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
     k_trace_closest(Accel as, SceneView sv, PathBuffers pb, int q, uint32_t bounce, GlobalCounters *gc)
 {
     const uint32_t count = pb.counts[bounce];
     uint32_t *cursor = &pb.counts[CURSOR_BASE + bounce];
     TraceCounters tc = {0, 0, 0, 0, 0};
     TraceState s;
-    TraceStack st;
+#if PRT_TRACE_SMEM_STACK
+    __shared__ uint2 stackMem[TRACE_SMEM_STACK * RENDER_THREADS];
+    SharedTraceStack st;
+    st.column = stackMem + threadIdx.x;
+    st.stride = RENDER_THREADS;
+#else
+    TraceStack st; // per-thread local memory, L1-resident: measured faster than the shared-memory variant
+#endif
     bool active = false, exhausted = false;
     uint32_t slot = 0;
     for (;;)
@@ -138,7 +154,7 @@ __global__ void __launch_bounds__(RENDER_THREADS)
             {
                 slot = next;
                 const float4 o = pb.rayO[q][slot], d = pb.rayD[q][slot];
-                active = traceBegin(s, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.rayId[q][slot].y);
+                active = traceBegin(s, st, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.rayId[q][slot].y);
                 if (!active) pb.hits[slot] = make_uint4(MISS_INDEX, MISS_INDEX, 0u, 0u);
             }
         }
@@ -285,14 +301,21 @@ __global__ void __launch_bounds__(RENDER_THREADS)
 
 // shadow(), main.rgen:49-60, fused with the addBounce of evaluateDirectLighting's result
 template <bool COUNT>
-__global__ void __launch_bounds__(RENDER_THREADS)
+__global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
     k_trace_shadow(Accel as, SceneView sv, PathBuffers pb, uint32_t bounce, GlobalCounters *gc)
 {
     const uint32_t count = pb.counts[COUNT_SHADOW_BASE + bounce];
     uint32_t *cursor = &pb.counts[CURSOR_BASE + COUNT_SHADOW_BASE + bounce];
     TraceCounters tc = {0, 0, 0, 0, 0};
     TraceState s;
-    TraceStack st;
+#if PRT_TRACE_SMEM_STACK
+    __shared__ uint2 stackMem[TRACE_SMEM_STACK * RENDER_THREADS];
+    SharedTraceStack st;
+    st.column = stackMem + threadIdx.x;
+    st.stride = RENDER_THREADS;
+#else
+    TraceStack st; // per-thread local memory, L1-resident: measured faster than the shared-memory variant
+#endif
     bool active = false, exhausted = false;
     uint32_t slot = 0;
     auto retire = [&]() {
@@ -314,7 +337,7 @@ __global__ void __launch_bounds__(RENDER_THREADS)
             {
                 slot = next;
                 const float4 o = pb.shadowO[slot], d = pb.shadowD[slot];
-                active = traceBegin(s, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.shadowId[slot].y);
+                active = traceBegin(s, st, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.shadowId[slot].y);
                 if (!active) retire();
             }
         }

@@ -325,9 +325,6 @@ extern "C" prt_status prt_create(const prt_config *cfg, prt_ctx **out)
         CK(c->accum.ensure(pixels));
         CK(cudaMemsetAsync(c->accum.p, 0, pixels * sizeof(float4), c->stream));
     }
-    // the local-memory traversal stacks want L1 rather than shared memory
-    cudaFuncSetAttribute(k_trace_closest<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
-    cudaFuncSetAttribute(k_trace_shadow<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
     {
         // persistent trace kernels: one resident wave of blocks (SM count x blocks per SM)
         int sms = 0, perSm = 0;
