@@ -40,8 +40,10 @@ enum {
     PRT_CFG_COUNTERS = 1u << 0,     /* run the instrumented traversal kernels (untimed runs) */
     PRT_CFG_EXACT_FILTER = 1u << 1, /* material taps use the software bilinear of the any-hit stage
                                        instead of the texture units' 8-bit-weight filter (parity tests) */
-    PRT_CFG_DECODE_BC7 = 1u << 2    /* expand BC7 payloads to RGBA8 arrays at upload (a CUDA kernel)
+    PRT_CFG_DECODE_BC7 = 1u << 2,   /* expand BC7 payloads to RGBA8 arrays at upload (a CUDA kernel)
                                        instead of sampling block-compressed CUDA arrays */
+    PRT_CFG_PLOC = 1u << 3          /* BLAS topology by PLOC (agglomerative, surface-area driven) instead of the
+                                       Karras Morton hierarchy; same collapse, same results, different tree */
 };
 
 /* ---- lifetime: RtReference::init / ~RtReference (RtRef.cpp:90-120) ------------------------ */

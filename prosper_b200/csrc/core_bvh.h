@@ -201,6 +201,103 @@ HD void lbvhRefitFromLeaf(const Lbvh &t, uint32_t leaf)
     }
 }
 
+// ---- PLOC: parallel locally-ordered clustering (Meister & Bittner 2018) --------------------------------
+// Bottom-up agglomerative build over the Morton-sorted primitives: every cluster looks `radius` positions to
+// both sides for the neighbour that minimises the surface area of the merged box, mutual nearest neighbours
+// merge, the cluster array is compacted (order preserved) and the search repeats until one cluster is left.
+// Produces the same binary-tree arrays as the Karras builder (left/right/parents/nodeBox, root = node 0) with a
+// surface-area-driven topology; plocFinish* then renumber the leaves in depth-first order so that every subtree
+// covers a contiguous range [first, last] again, which is what the collapse wants.
+struct Ploc
+{
+    Lbvh t;              // t.visit holds the subtree sizes while building; t.first/last are written at the end
+    const int32_t *refIn; // clusters of this iteration, in spatial order
+    const Box *boxIn;
+    int32_t *refOut;      // compacted clusters of the next iteration
+    Box *boxOut;
+    uint32_t *nearest;    // [count]
+    int32_t *mergedRef;   // [count] result of the merge step before compaction (PLOC_DROPPED = slot vanishes)
+    Box *mergedBox;
+    uint32_t *nodeAlloc;  // internal nodes created so far
+    uint32_t radius;
+};
+constexpr int32_t PLOC_DROPPED = 0x7FFFFFFF;
+
+HD uint32_t plocRefSize(const Lbvh &t, int32_t ref) { return ref >= 0 ? t.visit[ref] : 1u; }
+
+HD void plocNearest(const Ploc &p, uint32_t i, uint32_t m)
+{
+    const Box b = p.boxIn[i];
+    const uint32_t lo = i > p.radius ? i - p.radius : 0u, hi = i + p.radius < m ? i + p.radius : m - 1u;
+    float best = 3.4e38f;
+    uint32_t bj = i;
+    for (uint32_t j = lo; j <= hi; ++j)
+    {
+        if (j == i) continue;
+        const float a = boxHalfArea(boxUnion(b, p.boxIn[j]));
+        if (a < best) { best = a; bj = j; } // ties keep the lower j: the globally best pair is always mutual
+    }
+    p.nearest[i] = bj;
+}
+
+HD void plocMerge(const Ploc &p, uint32_t i, uint32_t m)
+{
+    const uint32_t j = p.nearest[i];
+    if (m > 1u && p.nearest[j] == i)
+    {
+        if (i > j) { p.mergedRef[i] = PLOC_DROPPED; return; }
+        const Lbvh &t = p.t;
+        // nodes are numbered downwards so that the last merge (the root) is node 0
+        const int32_t node = (int32_t)(t.count - 2u - atomAdd(p.nodeAlloc, 1u));
+        const int32_t l = p.refIn[i], r = p.refIn[j];
+        t.left[node] = l; t.right[node] = r;
+        if (l >= 0) t.parentOfInternal[l] = node; else t.parentOfLeaf[~l] = node;
+        if (r >= 0) t.parentOfInternal[r] = node; else t.parentOfLeaf[~r] = node;
+        t.parentOfInternal[node] = -1;
+        const Box u = boxUnion(p.boxIn[i], p.boxIn[j]);
+        t.nodeBox[node] = u;
+        t.visit[node] = plocRefSize(t, l) + plocRefSize(t, r);
+        p.mergedRef[i] = node;
+        p.mergedBox[i] = u;
+        return;
+    }
+    p.mergedRef[i] = p.refIn[i];
+    p.mergedBox[i] = p.boxIn[i];
+}
+
+// Start of the depth-first leaf range of `ref`: the sizes of all left siblings on the way to the root.
+HD uint32_t plocRangeStart(const Lbvh &t, int32_t ref)
+{
+    uint32_t start = 0;
+    int32_t node = ref >= 0 ? t.parentOfInternal[ref] : t.parentOfLeaf[~ref];
+    while (node >= 0)
+    {
+        if (t.right[node] == ref) start += plocRefSize(t, t.left[node]);
+        ref = node;
+        node = t.parentOfInternal[node];
+    }
+    return start;
+}
+// one call per old sorted position: its depth-first position and the re-ordered primitive index
+HD void plocFinishLeaf(const Lbvh &t, uint32_t oldPos, uint32_t *newPos, uint32_t *orderOut)
+{
+    const uint32_t pos = plocRangeStart(t, ~(int32_t)oldPos);
+    newPos[oldPos] = pos;
+    orderOut[pos] = t.order[oldPos];
+}
+// one call per internal node, after every plocFinishLeaf: range + leaf references in the new numbering
+HD void plocFinishNode(const Lbvh &t, uint32_t node, const uint32_t *newPos)
+{
+    const uint32_t start = plocRangeStart(t, (int32_t)node);
+    t.first[node] = start;
+    t.last[node] = start + t.visit[node] - 1u;
+}
+HD void plocRelabelNode(const Lbvh &t, uint32_t node, const uint32_t *newPos)
+{
+    if (t.left[node] < 0) t.left[node] = ~(int32_t)newPos[~t.left[node]];
+    if (t.right[node] < 0) t.right[node] = ~(int32_t)newPos[~t.right[node]];
+}
+
 // ---- collapse to 8-wide + quantise -----------------------------------------------------------------
 // Work item of the level-synchronous collapse: binary subtree `ref` becomes wide node `wide`.
 struct CollapseItem

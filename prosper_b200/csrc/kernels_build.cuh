@@ -107,6 +107,114 @@ __global__ void k_lbvh_refit(Lbvh t)
     lbvhRefitFromLeaf(t, i);
 }
 
+// ---- PLOC (core_bvh.h): per iteration nearest -> merge (+ per-block survivor counts) -> block offsets -> scatter.
+// The live cluster count stays in device memory (counts[it & 1]), so iterations are enqueued without host waits.
+constexpr int PLOC_THREADS = 256;
+
+__global__ void k_ploc_init(Lbvh t, int32_t *ref, Box *box, uint32_t *counts, uint32_t *nodeAlloc)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { counts[0] = t.count; counts[1] = 0; *nodeAlloc = 0; }
+    if (i >= t.count) return;
+    ref[i] = ~(int32_t)i;
+    box[i] = t.primBox[t.order[i]];
+    t.parentOfLeaf[i] = -1;
+}
+
+__global__ void __launch_bounds__(PLOC_THREADS) k_ploc_nearest(Ploc p, const uint32_t *__restrict__ count)
+{
+    const uint32_t m = *count, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m <= 1u || i >= m) return;
+    plocNearest(p, i, m);
+}
+
+// merge + count of surviving clusters per block
+__global__ void __launch_bounds__(PLOC_THREADS) k_ploc_merge(Ploc p, const uint32_t *__restrict__ count, uint32_t *__restrict__ blockCounts)
+{
+    const uint32_t m = *count, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m <= 1u) return;
+    bool keep = false;
+    if (i < m)
+    {
+        plocMerge(p, i, m);
+        keep = p.mergedRef[i] != PLOC_DROPPED;
+    }
+    const int n = __syncthreads_count(keep);
+    if (threadIdx.x == 0) blockCounts[blockIdx.x] = (uint32_t)n;
+}
+
+// exclusive scan of the per-block counts (one block; the array is count / 256 long) + next live count
+__global__ void __launch_bounds__(1024) k_ploc_offsets(const uint32_t *__restrict__ count, uint32_t *__restrict__ blockCounts, uint32_t *__restrict__ nextCount)
+{
+    __shared__ uint32_t warpSums[32];
+    __shared__ uint32_t carry;
+    const uint32_t m = *count;
+    if (m <= 1u) { if (threadIdx.x == 0) *nextCount = m; return; }
+    const uint32_t blocks = (m + PLOC_THREADS - 1) / PLOC_THREADS;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < blocks; base += blockDim.x)
+    {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = i < blocks ? blockCounts[i] : 0u;
+        uint32_t x = v;
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o); if ((threadIdx.x & 31) >= o) x += y; }
+        if ((threadIdx.x & 31) == 31) warpSums[threadIdx.x >> 5] = x;
+        __syncthreads();
+        if (threadIdx.x < 32)
+        {
+            uint32_t w = warpSums[threadIdx.x], z = w;
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, z, o); if ((int)threadIdx.x >= o) z += y; }
+            warpSums[threadIdx.x] = z - w; // exclusive
+        }
+        __syncthreads();
+        const uint32_t excl = carry + warpSums[threadIdx.x >> 5] + x - v;
+        if (i < blocks) blockCounts[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *nextCount = carry;
+}
+
+__global__ void __launch_bounds__(PLOC_THREADS) k_ploc_scatter(Ploc p, const uint32_t *__restrict__ count, const uint32_t *__restrict__ blockOffsets)
+{
+    __shared__ uint32_t warpBase[PLOC_THREADS / 32];
+    const uint32_t m = *count, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m <= 1u) return;
+    const bool keep = i < m && p.mergedRef[i] != PLOC_DROPPED;
+    const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, keep);
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (lane == 0) warpBase[warp] = (uint32_t)__popc(ballot);
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        uint32_t run = 0;
+        for (int w = 0; w < PLOC_THREADS / 32; ++w) { const uint32_t c = warpBase[w]; warpBase[w] = run; run += c; }
+    }
+    __syncthreads();
+    if (keep)
+    {
+        const uint32_t dst = blockOffsets[blockIdx.x] + warpBase[warp] + (uint32_t)__popc(ballot & ((1u << lane) - 1u));
+        p.refOut[dst] = p.mergedRef[i];
+        p.boxOut[dst] = p.mergedBox[i];
+    }
+}
+
+__global__ void k_ploc_finish_leaves(Lbvh t, uint32_t *newPos, uint32_t *orderOut)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= t.count) return;
+    plocFinishLeaf(t, i, newPos, orderOut);
+}
+__global__ void k_ploc_finish_nodes(Lbvh t, const uint32_t *newPos)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i + 1 >= t.count) return;
+    plocFinishNode(t, i, newPos);
+    plocRelabelNode(t, i, newPos);
+}
+
 // One collapse level: items [0, *countIn) of queueIn. Launched with enough threads for the worst
 // case; the live count is read from device memory so the host never waits between levels.
 __global__ void k_collapse_level(Collapse c, const uint32_t *__restrict__ countIn)

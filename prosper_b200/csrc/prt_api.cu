@@ -188,6 +188,10 @@ struct prt_ctx
     DBuf<uint32_t> bOrder[2], bHist, bFirst, bLast, bVisit, bPrimOut, bScalars;
     DBuf<int32_t> bLeft, bRight, bParentI, bParentL;
     DBuf<CollapseItem> bQueue[2];
+    // PLOC scratch (BLAS builds)
+    DBuf<int32_t> bPlocRef[2], bPlocMergedRef;
+    DBuf<Box> bPlocBox[2], bPlocMergedBox;
+    DBuf<uint32_t> bPlocNearest, bPlocBlocks, bNewPos;
     DBuf<WideNode> bNodes;
     DBuf<BuildBounds> bBounds;
 
@@ -370,6 +374,8 @@ extern "C" void prt_destroy(prt_ctx *c)
     c->tlasNodes.release(); c->tlasInst.release();
     c->bTris.release(); c->bUvs.release(); c->dAlphaMats.release(); c->bInst.release(); c->bTlasIn.release(); c->bBoxes.release(); c->bNodeBox.release();
     for (int i = 0; i < 2; ++i) { c->bKeys[i].release(); c->bOrder[i].release(); c->bQueue[i].release(); }
+    for (int i = 0; i < 2; ++i) { c->bPlocRef[i].release(); c->bPlocBox[i].release(); }
+    c->bPlocMergedRef.release(); c->bPlocMergedBox.release(); c->bPlocNearest.release(); c->bPlocBlocks.release(); c->bNewPos.release();
     c->bHist.release(); c->bFirst.release(); c->bLast.release(); c->bVisit.release(); c->bPrimOut.release(); c->bScalars.release();
     c->bLeft.release(); c->bRight.release(); c->bParentI.release(); c->bParentL.release(); c->bNodes.release(); c->bBounds.release();
     c->accum.release(); c->sum.release(); c->f16.release(); c->userHits.release(); c->userO.release(); c->userD.release();
@@ -642,6 +648,9 @@ static prt_status refreshAlphaMats(prt_ctx *c)
 // wide nodes in bNodes and the node-order primitive permutation in bPrimOut.
 // bScalars layout: [0] nodeCount, [1] primCount, [8 .. 8 + MAX_LEVELS] per-level queue counts.
 static constexpr uint32_t kMaxLevels = 128;
+#ifndef PRT_PLOC_RADIUS
+#define PRT_PLOC_RADIUS 16
+#endif
 
 static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *launches)
 {
@@ -673,18 +682,64 @@ static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *la
     t.left = c->bLeft.p; t.right = c->bRight.p; t.first = c->bFirst.p; t.last = c->bLast.p;
     t.parentOfInternal = c->bParentI.p; t.parentOfLeaf = c->bParentL.p;
     t.nodeBox = c->bNodeBox.p; t.visit = c->bVisit.p;
-    if (n > 1)
+    uint32_t *scal = c->bScalars.p;
+    if (n > 1 && !tlas && (c->cfg.flags & PRT_CFG_PLOC))
+    {
+        // BLAS: PLOC (surface-area-driven topology). Scalars: [240], [241] live cluster counts (ping-pong), [242] nodes made.
+        for (int i = 0; i < 2; ++i) { CK(c->bPlocRef[i].ensure(n)); CK(c->bPlocBox[i].ensure(n)); }
+        CK(c->bPlocMergedRef.ensure(n)); CK(c->bPlocMergedBox.ensure(n)); CK(c->bPlocNearest.ensure(n)); CK(c->bNewPos.ensure(n));
+        CK(c->bPlocBlocks.ensure(blocksFor(n, PLOC_THREADS)));
+        uint32_t *counts = scal + 240, *nodeAlloc = scal + 242;
+        k_ploc_init<<<blocksFor(n, 256), 256, 0, st>>>(t, c->bPlocRef[0].p, c->bPlocBox[0].p, counts, nodeAlloc);
+        *launches += 1;
+        Ploc p{};
+        p.t = t;
+        p.nearest = c->bPlocNearest.p; p.mergedRef = c->bPlocMergedRef.p; p.mergedBox = c->bPlocMergedBox.p;
+        p.nodeAlloc = nodeAlloc;
+        p.radius = PRT_PLOC_RADIUS;
+        uint32_t bound = n; // host-side upper bound of the live cluster count
+        bool done = false;
+        for (uint32_t it = 0; it < 4096u && !done; ++it)
+        {
+            const int a = (int)(it & 1u), b = a ^ 1;
+            p.refIn = c->bPlocRef[a].p; p.boxIn = c->bPlocBox[a].p; p.refOut = c->bPlocRef[b].p; p.boxOut = c->bPlocBox[b].p;
+            const uint32_t grid = blocksFor(bound, PLOC_THREADS);
+            k_ploc_nearest<<<grid, PLOC_THREADS, 0, st>>>(p, counts + a);
+            k_ploc_merge<<<grid, PLOC_THREADS, 0, st>>>(p, counts + a, c->bPlocBlocks.p);
+            k_ploc_offsets<<<1, 1024, 0, st>>>(counts + a, c->bPlocBlocks.p, counts + b);
+            k_ploc_scatter<<<grid, PLOC_THREADS, 0, st>>>(p, counts + a, c->bPlocBlocks.p);
+            *launches += 4;
+            if ((it & 3u) == 3u)
+            {
+                uint32_t live = 0;
+                CK(cudaMemcpyAsync(&live, counts + b, 4, cudaMemcpyDeviceToHost, st));
+                CK(cudaStreamSynchronize(st));
+                REQUIRE(live >= 1 && live <= bound, "PLOC cluster count out of range");
+                bound = live;
+                done = live == 1;
+            }
+        }
+        REQUIRE(done, "PLOC did not converge");
+        uint32_t *orderOut = flipped ? c->bOrder[0].p : c->bOrder[1].p;
+        k_ploc_finish_leaves<<<blocksFor(n, 256), 256, 0, st>>>(t, c->bNewPos.p, orderOut);
+        k_ploc_finish_nodes<<<blocksFor(n - 1, 256), 256, 0, st>>>(t, c->bNewPos.p);
+        *launches += 2;
+        t.order = orderOut;
+    }
+    else if (n > 1)
     {
         k_lbvh_nodes<<<blocksFor(n - 1, 256), 256, 0, st>>>(t);
         k_lbvh_refit<<<blocksFor(n, 256), 256, 0, st>>>(t);
         *launches += 2;
     }
-    uint32_t *scal = c->bScalars.p;
     k_collapse_seed<<<1, 128, 0, st>>>(c->bQueue[0].p, scal + 8, kMaxLevels + 1, scal + 0, scal + 1, n);
     *launches += 1;
     Collapse col{};
     col.t = t;
-    col.maxLeaf = tlas ? 1u : 3u;
+#ifndef PRT_BLAS_MAX_LEAF
+#define PRT_BLAS_MAX_LEAF 3
+#endif
+    col.maxLeaf = tlas ? 1u : (uint32_t)PRT_BLAS_MAX_LEAF;
     col.nodes = c->bNodes.p;
     col.primOut = c->bPrimOut.p;
     col.nodeCount = scal + 0;

@@ -27,7 +27,7 @@ struct HostBvh
     uint32_t levels = 0;
 };
 
-HostBvh buildHierarchyHost(std::vector<Box> &boxes, V3 lo, V3 hi, bool tlas)
+HostBvh buildHierarchyHost(std::vector<Box> &boxes, V3 lo, V3 hi, bool tlas, bool ploc = false)
 {
     const uint32_t n = (uint32_t)boxes.size();
     HostBvh out;
@@ -50,7 +50,35 @@ HostBvh buildHierarchyHost(std::vector<Box> &boxes, V3 lo, V3 hi, bool tlas)
     t.count = n; t.keys = sorted.data(); t.order = order.data(); t.primBox = boxes.data();
     t.left = left.data(); t.right = right.data(); t.first = first.data(); t.last = last.data();
     t.parentOfInternal = parentI.data(); t.parentOfLeaf = parentL.data(); t.nodeBox = nodeBox.data(); t.visit = visit.data();
-    if (n > 1)
+    std::vector<uint32_t> orderOut(n), newPos(n);
+    if (n > 1 && !tlas && ploc)
+    {
+        // PLOC, the k_ploc_* sequence of buildHierarchy (prt_api.cu) with the compaction done serially
+        std::vector<int32_t> ref[2] = {std::vector<int32_t>(n), std::vector<int32_t>(n)}, mergedRef(n);
+        std::vector<Box> box[2] = {std::vector<Box>(n), std::vector<Box>(n)}, mergedBox(n);
+        std::vector<uint32_t> nearest(n);
+        uint32_t nodeAlloc = 0, m = n;
+        for (uint32_t i = 0; i < n; ++i) { ref[0][i] = ~(int32_t)i; box[0][i] = boxes[order[i]]; parentL[i] = -1; }
+        Ploc p{};
+        p.t = t; p.nearest = nearest.data(); p.mergedRef = mergedRef.data(); p.mergedBox = mergedBox.data();
+        p.nodeAlloc = &nodeAlloc; p.radius = 16;
+        for (uint32_t it = 0; m > 1; ++it)
+        {
+            const int a = (int)(it & 1u), b = a ^ 1;
+            p.refIn = ref[a].data(); p.boxIn = box[a].data(); p.refOut = ref[b].data(); p.boxOut = box[b].data();
+            for (uint32_t i = 0; i < m; ++i) plocNearest(p, i, m);
+            for (uint32_t i = 0; i < m; ++i) plocMerge(p, i, m);
+            uint32_t next = 0;
+            for (uint32_t i = 0; i < m; ++i)
+                if (mergedRef[i] != PLOC_DROPPED) { ref[b][next] = mergedRef[i]; box[b][next] = mergedBox[i]; next++; }
+            if (next >= m) break; // no progress: a builder bug, caught by the prim-count check below
+            m = next;
+        }
+        for (uint32_t i = 0; i < n; ++i) plocFinishLeaf(t, i, newPos.data(), orderOut.data());
+        for (uint32_t i = 0; i + 1 < n; ++i) { plocFinishNode(t, i, newPos.data()); plocRelabelNode(t, i, newPos.data()); }
+        t.order = orderOut.data();
+    }
+    else if (n > 1)
     {
         for (uint32_t i = 0; i + 1 < n; ++i) lbvhBuildNode(t, (int)i);
         for (uint32_t i = 0; i < n; ++i) lbvhRefitFromLeaf(t, i);
@@ -192,8 +220,11 @@ static void buildTlasHost(hs_ctx *c)
 
 extern "C" {
 
-hs_ctx *hs_create(const orc_scene *scene, int exactMaterialFilter)
+// flags: bit 0 = software filter for material taps (PRT_CFG_EXACT_FILTER), bit 1 = PLOC builder (PRT_CFG_PLOC)
+hs_ctx *hs_create(const orc_scene *scene, int flags)
 {
+    const int exactMaterialFilter = flags & 1;
+    const bool ploc = (flags & 2) != 0;
     hs_ctx *c = new hs_ctx;
     c->s = *scene;
     const orc_scene &s = c->s;
@@ -281,7 +312,7 @@ hs_ctx *hs_create(const orc_scene *scene, int exactMaterialFilter)
             }
         }
         if (tris.empty()) continue;
-        HostBvh h = buildHierarchyHost(boxes, lo, hi, false);
+        HostBvh h = buildHierarchyHost(boxes, lo, hi, false, ploc);
         if (h.primOut.size() != tris.size()) { c->buildError = 1; continue; }
         c->blasLevels = std::max(c->blasLevels, h.levels);
         c->blas[m].nodes = std::move(h.nodes);

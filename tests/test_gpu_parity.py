@@ -65,6 +65,21 @@ def test_primary_ids_atrium_instanced(small_atrium_instanced):
     _check_primary(small_atrium_instanced, 160, 90, frames=(1,))
 
 
+def test_primary_ids_ploc_builder(small_atrium_instanced):
+    # PRT_CFG_PLOC: another BLAS topology, the same hit records (results do not depend on the tree)
+    scene, (w, h) = small_atrium_instanced, (160, 90)
+    world = rt.World(scene, max_width=w, max_height=h, flags=rt.CFG_COUNTERS | rt.CFG_PLOC)
+    world.updateBuffers()
+    world.buildAccelerationStructures()
+    orc = oracle.Oracle(scene)
+    pc = sd.reference_pc(frame_index=2)
+    ho, margin = orc.trace_primary(pc, w, h)
+    hg = world.trace_primary(pc, w, h)
+    assert (_id_mismatch(ho, hg) & ~(margin < ALPHA_TIE_MARGIN)).sum() == 0
+    assert world.counters()["stackOverflows"] == 0
+    world.close()
+
+
 def test_dof_primary(test_scene):
     w, h = 96, 64
     world = _world(test_scene, w, h)
