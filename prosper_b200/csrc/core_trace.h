@@ -222,7 +222,10 @@ struct TraceCold
     uint32_t seed;      // payload.randomSeed (scene.rahit:35)
     uint32_t instCustom;
     const AlphaUv *uvs; // any-hit records of the current BLAS (may be nullptr)
+    float pendT, pendU, pendV; // candidate waiting for its any-hit test (TRACE_PENDING set in TraceState::px)
+    uint32_t pendTri;          // its index in the BLAS triangle array
 };
+constexpr uint32_t TRACE_PENDING = 0x80000000u;
 
 // kept apart from TraceState so that the scalar state stays in registers (a dynamically indexed member
 // would drag the whole struct into local memory)
@@ -278,14 +281,48 @@ HD bool traceBegin(TraceState &s, Stack &st, const Accel &as, V3 o, V3 d, float 
 }
 
 // One step of traceRayEXT = ONE item of work, so that the lanes of a warp stay in lock step on items of
-// similar cost: either one pending primitive of the current primitive group (a triangle test with its any-hit,
-// or entering an instance), or one node (take the nearest pending child of the current node group, intersect
-// its eight boxes). Pops when both groups are exhausted.
+// similar cost: the any-hit test of a parked candidate, or one pending primitive of the current primitive group
+// (a triangle test, or entering an instance), or one node (take the nearest pending child of the current node
+// group, intersect its eight boxes). Pops when both groups are exhausted. traceItemKind tells which it will be.
 // SHADOW = gl_RayFlagsTerminateOnFirstHitEXT (main.rgen:52). Returns true when the ray is finished.
+HD int traceItemKind(const TraceState &s) { return (s.px & TRACE_PENDING) ? 2 : (s.py != 0 ? 1 : 0); }
+
 template <bool SHADOW, bool COUNT, class Stack>
 HD bool traceStep(TraceState &s, Stack &st, const Accel &as, const SceneView &sv, TraceCounters *cnt)
 {
-    if (s.py != 0)
+    if (s.px & TRACE_PENDING)
+    {
+        // scene.rahit for the candidate parked by the triangle item below (its own item kind, so that the lanes of
+        // a warp run the alpha test together instead of one or two at a time inside the triangle item)
+        s.px &= ~TRACE_PENDING;
+        const uint32_t tri = st.cold.pendTri;
+        const float t = st.cold.pendT, u = st.cold.pendU, v = st.cold.pendV;
+        const TriRec &tr = s.tris[tri];
+        const uint32_t geom = tr.geometry & 0x7FFFFFFFu;
+        const uint32_t drawInstanceIndex = st.cold.instCustom + geom;
+        if (COUNT) cnt->anyHits++;
+        const AlphaUv *uvs = st.cold.uvs;
+        const uint32_t seed = st.cold.seed;
+        bool accept = true;
+        bool fast = uvs != nullptr && sv.alphaMats != nullptr;
+        if (fast)
+        {
+            const AlphaMat am = loadAlphaMat(sv.alphaMats + drawInstanceIndex);
+            fast = (am.bits & ALPHAMAT_USABLE) != 0;
+            if (fast) accept = anyHitAcceptFast(am, loadAlphaUv(uvs + tri), u, v, seed);
+        }
+        if (!fast) accept = anyHitAccept(sv, drawInstanceIndex, tr.primitive, u, v, seed);
+        if (accept)
+        {
+            s.best.drawInstanceIndex = drawInstanceIndex;
+            s.best.primitiveID = tr.primitive;
+            s.best.u = u; s.best.v = v; s.best.t = t;
+            s.best.instance = s.instIndex;
+            s.best.geometry = geom;
+            if (SHADOW) return true;
+        }
+    }
+    else if (s.py != 0)
     {
         const int pbit = bfind(s.py);
         s.py &= ~(1u << pbit);
@@ -329,31 +366,20 @@ HD bool traceStep(TraceState &s, Stack &st, const Accel &as, const SceneView &sv
                 const uint32_t geom = tr.geometry & 0x7FFFFFFFu;
                 if (betterHit(t, s.instIndex, geom, tr.primitive, s.best))
                 {
-                    const uint32_t drawInstanceIndex = st.cold.instCustom + geom;
-                    bool accept = true;
                     if (!(tr.geometry >> 31))
                     {
-                        if (COUNT) cnt->anyHits++;
-                        const AlphaUv *uvs = st.cold.uvs;
-                        const uint32_t seed = st.cold.seed;
-                        bool fast = uvs != nullptr && sv.alphaMats != nullptr;
-                        if (fast)
-                        {
-                            const AlphaMat am = loadAlphaMat(sv.alphaMats + drawInstanceIndex);
-                            fast = (am.bits & ALPHAMAT_USABLE) != 0;
-                            if (fast) accept = anyHitAcceptFast(am, loadAlphaUv(uvs + s.px + (uint32_t)pbit), u, v, seed);
-                        }
-                        if (!fast) accept = anyHitAccept(sv, drawInstanceIndex, tr.primitive, u, v, seed);
+                        // non-opaque geometry: park the candidate, its any-hit test is the lane's next item
+                        st.cold.pendT = t; st.cold.pendU = u; st.cold.pendV = v;
+                        st.cold.pendTri = s.px + (uint32_t)pbit;
+                        s.px |= TRACE_PENDING;
+                        return false;
                     }
-                    if (accept)
-                    {
-                        s.best.drawInstanceIndex = drawInstanceIndex;
-                        s.best.primitiveID = tr.primitive;
-                        s.best.u = u; s.best.v = v; s.best.t = t;
-                        s.best.instance = s.instIndex;
-                        s.best.geometry = geom;
-                        if (SHADOW) return true;
-                    }
+                    s.best.drawInstanceIndex = st.cold.instCustom + geom;
+                    s.best.primitiveID = tr.primitive;
+                    s.best.u = u; s.best.v = v; s.best.t = t;
+                    s.best.instance = s.instIndex;
+                    s.best.geometry = geom;
+                    if (SHADOW) return true;
                 }
             }
         }

@@ -126,6 +126,16 @@ __device__ __forceinline__ uint32_t fetchSlots(uint32_t *cursor, uint32_t count,
     return idle ? base + (uint32_t)__popc(need & ((1u << lane) - 1u)) : 0xFFFFFFFFu;
 }
 
+// The item kind (0 node, 1 primitive, 2 any-hit; -1 idle) most lanes of the warp want next. Ties go to the later
+// stage, which frees lanes for the earlier ones. Never returns a kind nobody wants unless the warp is idle.
+__device__ __forceinline__ int pluralityKind(int kind)
+{
+    const int n0 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 0)), n1 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1));
+    const int n2 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 2));
+    if (n2 >= n1 && n2 >= n0 && n2 > 0) return 2;
+    return n1 >= n0 && n1 > 0 ? 1 : 0;
+}
+
 // traceClosest, main.rgen:62-81. Persistent warps over the closest-ray queue of `bounce`.
 template <bool COUNT>
 __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
@@ -161,13 +171,12 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
         if (!__any_sync(0xFFFFFFFFu, active)) break;
         for (;;)
         {
-            // Majority vote: a step is either a primitive item or a node item (traceStep); only the kind most live
-            // lanes are waiting for runs this iteration, the others wait for their turn, so each issued
-            // instruction serves at least half of the live lanes instead of both kinds running half empty.
-            const bool wantPrim = active && s.py != 0;
-            const int nPrim = __popc(__ballot_sync(0xFFFFFFFFu, wantPrim)), nAll = __popc(__ballot_sync(0xFFFFFFFFu, active));
-            const bool runPrim = 2 * nPrim >= nAll;
-            if (active && wantPrim == runPrim && traceStep<false, COUNT>(s, st, as, sv, &tc))
+            // Plurality vote: a step is one any-hit test, one primitive item or one node item (traceStep); only the
+            // kind most live lanes are waiting for runs this iteration and the others wait for their turn, so an
+            // issued instruction serves a large share of the live lanes instead of three kinds running mostly empty.
+            const int kind = active ? traceItemKind(s) : -1;
+            const int run = pluralityKind(kind);
+            if (kind == run && traceStep<false, COUNT>(s, st, as, sv, &tc))
             {
                 pb.hits[slot] = make_uint4(s.best.drawInstanceIndex, s.best.primitiveID, __float_as_uint(s.best.u), __float_as_uint(s.best.v));
                 active = false;
@@ -344,10 +353,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
         if (!__any_sync(0xFFFFFFFFu, active)) break;
         for (;;)
         {
-            const bool wantPrim = active && s.py != 0; // majority vote, see k_trace_closest
-            const int nPrim = __popc(__ballot_sync(0xFFFFFFFFu, wantPrim)), nAll = __popc(__ballot_sync(0xFFFFFFFFu, active));
-            const bool runPrim = 2 * nPrim >= nAll;
-            if (active && wantPrim == runPrim && traceStep<true, COUNT>(s, st, as, sv, &tc))
+            const int kind = active ? traceItemKind(s) : -1; // plurality vote, see k_trace_closest
+            const int run = pluralityKind(kind);
+            if (kind == run && traceStep<true, COUNT>(s, st, as, sv, &tc))
             {
                 retire();
                 active = false;
