@@ -7,7 +7,12 @@ h = rows[hi]
 ie, te = h.index("Instructions Executed"), h.index("Thread Instructions Executed")
 si = h.index("Source")
 samp = h.index("# Samples") if "# Samples" in h else None
-inst = [(r[si].strip(), int(r[ie]), int(r[te]), int(r[samp]) if samp is not None else 0) for r in rows[hi + 1:] if len(r) > te]
+body = []
+for r in rows[hi + 1:]:  # the first kernel table only
+    if not r or r[0] in ("Kernel Name", "Address"):
+        break
+    body.append(r)
+inst = [(r[si].strip(), int(r[ie]), int(r[te]), int(r[samp]) if samp is not None else 0) for r in body if len(r) > te]
 loc, cur = [], ("?", 0)
 for line in open(sys.argv[2]):
     m = re.search(r'//## File "(.*)", line (\d+)', line)
