@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--lights", type=int, default=0, help="configs[2]: 1024 point/spot lights")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-stress", action="store_true", help="skip the 10k-instance TLAS rebuild measurement")
+    ap.add_argument("--stress-instances", type=int, default=10000)
     return ap.parse_args()
 
 
@@ -403,7 +405,7 @@ def run_ours(args):
     for _ in range(5):
         world.buildTlas(scene.tlas_instances)
         tlas_ms.append(world.timings()["lastTlasMs"])
-    tlas = {"ms_per_rebuild": float(np.median(tlas_ms)), "instances": int(len(scene.tlas_instances)),
+    tlas = {"atrium_ms_per_rebuild": float(np.median(tlas_ms)), "atrium_instances": int(len(scene.tlas_instances)),
             "launches": int(world.timings()["lastTlasLaunches"]), "blas_build_ms_last": build_t["lastBlasMs"]}
     world.close()
 
@@ -445,6 +447,39 @@ def run_ours(args):
                      "tris_per_closest_ray": (cc["trisTested"] - cc["shadowTrisTested"]) / max(1, cc["closestRays"]),
                      "nodes_per_shadow_ray": cc["shadowNodesVisited"] / max(1, cc["shadowRays"]),
                      "tris_per_shadow_ray": cc["shadowTrisTested"] / max(1, cc["shadowRays"])}
+
+    # ---- TLAS rebuild at scale: BASELINE.json configs[4] (10k instances, ~100 M instanced triangles) ------------------
+    if rank == 0 and not args.no_stress:
+        from prosper_b200 import scene_zoo
+        st_scene = scene_zoo.stress(WIDTH, HEIGHT, instances=args.stress_instances)
+        sw = rt.World(st_scene, device=local_rank, max_width=WIDTH, max_height=HEIGHT, samples_per_launch=2, flags=0)
+        sw.updateBuffers()
+        sw.buildAccelerationStructures()
+        ms, wall = [], []
+        for _ in range(12):
+            sw.synchronize()
+            t0 = time.perf_counter()
+            sw.buildTlas(st_scene.tlas_instances)  # host instance records -> ring upload -> rebuild
+            sw.synchronize()
+            wall.append((time.perf_counter() - t0) * 1e3)
+            ms.append(sw.timings()["lastTlasMs"])
+        sp = rt.RtReference()
+        sp.init(sw)
+        sp.drawUi(maxBounces=BOUNCES)
+        for _ in range(2):
+            sw.reset_counters()
+            sp.m_frameIndex = 0
+            sp.m_accumulationDirty = True
+            sp.record(sw, area, opts, frames=4)
+            sw.synchronize()
+        sc, stt = sw.counters(), sw.timings()
+        tlas.update({"ms_per_rebuild": float(np.median(ms[2:])), "wall_ms_per_rebuild_from_host_records": float(np.median(wall[2:])),
+                     "instances": int(len(st_scene.tlas_instances)), "launches": int(stt["lastTlasLaunches"]),
+                     "scene": f"{st_scene.name}: {st_scene.instanced_triangle_count} instanced triangles, "
+                              f"{st_scene.triangle_count} unique", "bytes_per_instance_uploaded": 64,
+                     "stress_mrays_s": (sc["closestRays"] + sc["shadowRays"]) / stt["lastRecordMs"] / 1e3,
+                     "stress_sample": "1920x1080 x 4 spp, 4 bounces"})
+        sw.close()
 
     cpu = None
     if rank == 0 and world_size == 1 and not args.no_cpu_baseline:

@@ -196,3 +196,32 @@ def atrium(width=1920, height=1080, seed=1, lights=0, fmt=TEX_BC7, tex_size=1024
                    sky=procedural_sky(64))
     sc.name = "atrium" if not lights else f"atrium+{lights}lights"
     return sc
+
+
+def stress(width=1920, height=1080, instances=10000, seed=5, mesh_tris=10000, models=4):
+    """C5 stand-in: `instances` random-TRS instances of `models` ~`mesh_tris`-triangle meshes (about
+    instances x mesh_tris instanced triangles, ~100 M at the defaults) for TLAS rebuild timing and the
+    two-level traversal sweep. Untextured opaque materials, sun + sky."""
+    rng = np.random.default_rng(seed)
+    sb = SceneBuilder("stress")
+    mats = [sb.add_material(make_material(base_color=(*c, 1.0), roughness=r, metallic=m))
+            for c, r, m in (((0.8, 0.3, 0.25), 0.6, 0.0), ((0.3, 0.7, 0.35), 0.4, 0.0), ((0.3, 0.4, 0.8), 0.8, 0.0),
+                            ((0.85, 0.8, 0.6), 0.3, 1.0))]
+    nu = max(8, int(round(np.sqrt(mesh_tris / 2.0 * 1.03))))
+    nv = max(6, int(round(mesh_tris / 2.0 / nu)))
+    ids = [sb.add_model([(bumpy_sphere(0.5, nu, nv, 0.12 + 0.04 * k, 5.0 + 2 * k, 0.3 * k, (1, 1 + 0.2 * k, 1)), mats[k % len(mats)])])
+           for k in range(models)]
+    side = max(4.0, 1.6 * instances ** (1.0 / 3.0))  # keeps the instance density constant
+    pos = rng.uniform((-side, 0.5, -side), (side, side * 0.6 + 1.0, side), (instances, 3))
+    axis = rng.normal(size=(instances, 3))
+    axis /= np.linalg.norm(axis, axis=1, keepdims=True)
+    ang = rng.uniform(0, 2 * np.pi, instances)
+    scl = rng.uniform(0.5, 1.5, (instances, 3))
+    for i in range(instances):
+        sb.add_instance(ids[i % models], trs(tuple(pos[i]), tuple(axis[i]), float(ang[i]), tuple(scl[i])))
+    floor = sb.add_model([(plane(4 * side, 4 * side, 8, 8, (8, 8)), mats[3])])
+    sb.add_instance(floor)
+    cam = make_camera((-1.6 * side, side * 0.8, 1.9 * side), (0, side * 0.3, 0), width, height)
+    sc = sb.finish(cam, directional=((3, 2.8, 2.5, 0), (-0.3, -1, -0.2, 0)), sky=procedural_sky(64))
+    sc.name = f"stress({instances})"
+    return sc

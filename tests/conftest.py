@@ -41,3 +41,9 @@ def small_atrium():
 def small_atrium_instanced():
     from prosper_b200 import scene_zoo
     return scene_zoo.atrium(160, 90, tex_size=64, detail=0.08, bake=False, lights=32)
+
+
+@pytest.fixture(scope="session")
+def small_stress():
+    from prosper_b200 import scene_zoo
+    return scene_zoo.stress(160, 90, instances=150, mesh_tris=600)

@@ -65,6 +65,11 @@ def test_primary_ids_atrium_instanced(small_atrium_instanced):
     _check_primary(small_atrium_instanced, 160, 90, frames=(1,))
 
 
+def test_primary_ids_stress_instances(small_stress):
+    # 151 instances of 4 BLASes with random rotation + non-uniform scale: the two-level path of BASELINE configs[4]
+    _check_primary(small_stress, 160, 90, frames=(1, 5))
+
+
 def test_primary_ids_ploc_builder(small_atrium_instanced):
     # PRT_CFG_PLOC: another BLAS topology, the same hit records (results do not depend on the tree)
     scene, (w, h) = small_atrium_instanced, (160, 90)

@@ -15,7 +15,8 @@ def _mism(a, b):
 
 
 @pytest.mark.parametrize("fixture,w,h", [("test_scene", 96, 64), ("test_scene_bc7", 96, 64), ("small_helmet", 128, 128),
-                                         ("small_atrium", 160, 90), ("small_atrium_instanced", 160, 90)])
+                                         ("small_atrium", 160, 90), ("small_atrium_instanced", 160, 90),
+                                         ("small_stress", 160, 90)])
 def test_builder_and_traversal_bit_exact(fixture, w, h, request):
     scene = request.getfixturevalue(fixture)
     orc, hs = oracle.Oracle(scene), hostsim.HostSim(scene)
