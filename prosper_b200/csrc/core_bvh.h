@@ -351,7 +351,13 @@ HD bool quantisePlanes(float p, float scale, float lo, float hi, uint32_t &qlo, 
 
 HD void collapseItem(const Collapse &c, uint32_t itemIndex)
 {
+#if defined(__CUDA_ARCH__)
+    // written by other SMs one level earlier: read around L1
+    const uint2 raw = __ldcg(reinterpret_cast<const uint2 *>(c.queueIn + itemIndex));
+    const CollapseItem item = {(int32_t)raw.x, raw.y};
+#else
     const CollapseItem item = c.queueIn[itemIndex];
+#endif
     const Lbvh &t = c.t;
     int32_t ch[8];
     int n = 0;

@@ -2,6 +2,7 @@
 // BLAS: World::Impl::buildNextBlas (World.cpp:585-747). TLAS: updateTlasInstances + buildCurrentTlas
 // (World.cpp:878-928, 749-802), rebuilt from scratch every frame like the reference does.
 #pragma once
+#include <cooperative_groups.h>
 #include "core_build.h"
 #include "kernels_sort.cuh"
 
@@ -239,6 +240,26 @@ __global__ void __launch_bounds__(1024) k_collapse_all_levels(Collapse c, Collap
         for (uint32_t i = threadIdx.x; i < count; i += blockDim.x) collapseItem(c, i);
         __threadfence_block();
         __syncthreads();
+    }
+}
+
+// All levels in one cooperative launch (TLAS with thousands of instances): the blocks of the grid share every
+// level's queue and meet at a grid barrier between levels, so the host enqueues ONE kernel whatever the depth.
+__global__ void __launch_bounds__(128) k_collapse_all_levels_grid(Collapse c, CollapseItem *queueA, CollapseItem *queueB,
+                                                                  uint32_t *queueCounts, uint32_t maxLevels)
+{
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    const uint32_t stride = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
+    for (uint32_t level = 0; level + 1 < maxLevels; ++level)
+    {
+        const uint32_t count = __ldcg(&queueCounts[level]);
+        if (count == 0) break; // grid-uniform: every thread reads the same finished counter
+        c.queueIn = (level & 1u) ? queueB : queueA;
+        c.queueOut = (level & 1u) ? queueA : queueB;
+        c.queueOutCount = &queueCounts[level + 1];
+        for (uint32_t i = tid; i < count; i += stride) collapseItem(c, i);
+        __threadfence();
+        grid.sync();
     }
 }
 

@@ -208,6 +208,7 @@ struct prt_ctx
     GlobalCounters *dCounters = nullptr;
     uint64_t kernelLaunches = 0;
     uint32_t traceBlocks = 148; // grid of the persistent trace kernels
+    uint32_t coopBlocks = 0;    // co-resident blocks of k_collapse_all_levels_grid (0: cooperative launch unsupported)
 
     // timing
     cudaEvent_t evRecord[2]{}, evTlas[2]{}, evBlas[2]{};
@@ -335,6 +336,10 @@ extern "C" prt_status prt_create(const prt_config *cfg, prt_ctx **out)
         CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->cfg.device));
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_trace_closest<false>, RENDER_THREADS, 0));
         c->traceBlocks = (uint32_t)std::max(1, sms * std::max(1, perSm));
+        int coop = 0, perSmCollapse = 0;
+        CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->cfg.device));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSmCollapse, k_collapse_all_levels_grid, 128, 0));
+        c->coopBlocks = coop ? (uint32_t)(sms * std::max(0, perSmCollapse)) : 0u;
     }
     CK(cudaStreamSynchronize(c->stream));
     return PRT_OK;
@@ -744,9 +749,20 @@ static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *la
     col.primOut = c->bPrimOut.p;
     col.nodeCount = scal + 0;
     col.primCount = scal + 1;
-    if (tlas && n <= 65536u)
+    if (tlas && n <= 512u)
     {
         k_collapse_all_levels<<<1, 1024, 0, st>>>(col, c->bQueue[0].p, c->bQueue[1].p, scal + 8, kMaxLevels);
+        *launches += 1;
+    }
+    else if (tlas && c->coopBlocks > 0)
+    {
+        // one cooperative launch for all levels: enough blocks for the widest level, never more than are co-resident
+        CollapseItem *qa = c->bQueue[0].p, *qb = c->bQueue[1].p;
+        uint32_t *counts = scal + 8;
+        uint32_t maxLevels = kMaxLevels;
+        void *args[] = {&col, &qa, &qb, &counts, &maxLevels};
+        const uint32_t blocks = std::min<uint32_t>(c->coopBlocks, blocksFor((n + 3) / 4, 128));
+        CK(cudaLaunchCooperativeKernel((const void *)k_collapse_all_levels_grid, dim3(blocks), dim3(128), args, 0, st));
         *launches += 1;
     }
     else
