@@ -192,7 +192,7 @@ def run_reference(args):
     cfg = workload_config(args, build_scene_stub(scene), args.gpus)
     sample = (f"{SAMPLE_W}x{SAMPLE_H} (same camera, 1/16 of the pixels) x {spp} spp per step, {BOUNCES} bounces, "
               f"std::thread over {cores} hardware threads")
-    print(json.dumps({
+    _emit({
         "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": secs / max(1, args.steps) * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
@@ -202,7 +202,7 @@ def run_reference(args):
         "gpu_launches": 0,
         "note": "CPU oracle (port of the reference's shaders + its own BVH); the reference's GLSL/Vulkan path is "
                 "unavailable on this box",
-    }), flush=True)
+    })
 
 
 class build_scene_stub:
@@ -503,14 +503,27 @@ def run_ours(args):
         line["breakdown"] = breakdown
     if cpu is not None:
         line["cpu_baseline"] = cpu
-    print(json.dumps(line), flush=True)
+    _emit(line)
+
+
+_emit = None
 
 
 def main():
     import faulthandler
     faulthandler.enable()
     args = parse_args()
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line
+    # keep stdout to the ONE JSON line: library chatter (e.g. NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+    global _emit
+
+    def _emit(obj):
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        print(json.dumps(obj), flush=True)
+        os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
