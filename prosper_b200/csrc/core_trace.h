@@ -301,10 +301,19 @@ HD bool traceBegin(TraceState &s, Stack &st, const Accel &as, V3 o, V3 d, float 
 // group, intersect its eight boxes). Pops when both groups are exhausted. traceItemKind tells which it will be.
 // SHADOW = gl_RayFlagsTerminateOnFirstHitEXT (main.rgen:52). Returns true when the ray is finished.
 HD int traceItemKind(const TraceState &s) { return (s.px & TRACE_PENDING) ? 2 : (s.py != 0 ? 1 : 0); }
+// A lane with pending primitives AND pending nodes may serve either kind: postponing its primitive group (it goes
+// on the stack) is legal because the result does not depend on traversal order.
+HD bool traceCanPostpone(const TraceState &s) { return !(s.px & TRACE_PENDING) && s.py != 0 && (s.gy & 0xFF000000u) != 0; }
 
+// preferNode: take a node item even though primitives are pending (only meaningful when traceCanPostpone(s)).
 template <bool SHADOW, bool COUNT, class Stack>
-HD bool traceStep(TraceState &s, Stack &st, const Accel &as, const SceneView &sv, TraceCounters *cnt)
+HD bool traceStep(TraceState &s, Stack &st, const Accel &as, const SceneView &sv, TraceCounters *cnt, bool preferNode = false)
 {
+    if (preferNode && traceCanPostpone(s))
+    {
+        if (s.sp < TRACE_STACK) { st.put(s.sp, s.px, s.py); s.sp++; s.py = 0; }
+        // (a full stack keeps the primitives first: nothing is lost, only the order stays as it was)
+    }
     if (s.px & TRACE_PENDING)
     {
         // scene.rahit for the candidate parked by the triangle item below (its own item kind, so that the lanes of

@@ -24,6 +24,9 @@ constexpr uint32_t COUNT_WORDS = 32;
 #ifndef PRT_TRACE_SMEM_STACK
 #define PRT_TRACE_SMEM_STACK 0
 #endif
+#ifndef PRT_TRACE_POSTPONE
+#define PRT_TRACE_POSTPONE 0 // measured: postponing primitive groups costs pruning, 586 vs 687 Mrays/s
+#endif
 #ifndef PRT_TRACE_MIN_BLOCKS
 #define PRT_TRACE_MIN_BLOCKS 8
 #endif
@@ -128,12 +131,17 @@ __device__ __forceinline__ uint32_t fetchSlots(uint32_t *cursor, uint32_t count,
 
 // The item kind (0 node, 1 primitive, 2 any-hit; -1 idle) most lanes of the warp want next. Ties go to the later
 // stage, which frees lanes for the earlier ones. Never returns a kind nobody wants unless the warp is idle.
-__device__ __forceinline__ int pluralityKind(int kind)
+// `flexible` lanes (kind 1 that could also take a node item, traceCanPostpone) do not vote: they join whichever of
+// node / primitive wins, which is what lifts the lanes per issued instruction.
+__device__ __forceinline__ int pluralityKind(int kind, bool flexible)
 {
-    const int n0 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 0)), n1 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1));
+    const int n0 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 0));
+    const int n1 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1 && !flexible));
     const int n2 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 2));
-    if (n2 >= n1 && n2 >= n0 && n2 > 0) return 2;
-    return n1 >= n0 && n1 > 0 ? 1 : 0;
+    const int nf = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1 && flexible));
+    if (n2 > 0 && n2 >= n1 + nf && n2 >= n0 + nf) return 2;
+    if (n0 + n1 + nf == 0) return 2;
+    return n1 > n0 ? 1 : (n0 > 0 ? 0 : 1);
 }
 
 // traceClosest, main.rgen:62-81. Persistent warps over the closest-ray queue of `bounce`.
@@ -175,8 +183,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
             // kind most live lanes are waiting for runs this iteration and the others wait for their turn, so an
             // issued instruction serves a large share of the live lanes instead of three kinds running mostly empty.
             const int kind = active ? traceItemKind(s) : -1;
-            const int run = pluralityKind(kind);
-            if (kind == run && traceStep<false, COUNT>(s, st, as, sv, &tc))
+            const bool flexible = PRT_TRACE_POSTPONE && active && traceCanPostpone(s);
+            const int run = pluralityKind(kind, flexible);
+            if ((kind == run || (flexible && run == 0)) && traceStep<false, COUNT>(s, st, as, sv, &tc, run == 0))
             {
                 pb.hits[slot] = make_uint4(s.best.drawInstanceIndex, s.best.primitiveID, __float_as_uint(s.best.u), __float_as_uint(s.best.v));
                 active = false;
@@ -354,8 +363,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
         for (;;)
         {
             const int kind = active ? traceItemKind(s) : -1; // plurality vote, see k_trace_closest
-            const int run = pluralityKind(kind);
-            if (kind == run && traceStep<true, COUNT>(s, st, as, sv, &tc))
+            const bool flexible = PRT_TRACE_POSTPONE && active && traceCanPostpone(s);
+            const int run = pluralityKind(kind, flexible);
+            if ((kind == run || (flexible && run == 0)) && traceStep<true, COUNT>(s, st, as, sv, &tc, run == 0))
             {
                 retire();
                 active = false;

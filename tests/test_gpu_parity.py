@@ -70,6 +70,42 @@ def test_primary_ids_stress_instances(small_stress):
     _check_primary(small_stress, 160, 90, frames=(1, 5))
 
 
+def test_full_size_atrium_primary_ids_and_properties():
+    """BASELINE.json configs[1] at its full size (257,884 triangles, 1920x1080): primary hit IDs against the oracle on
+    every pixel, then size-independent properties of the 4-bounce render (sample count, 2 + 1 frames == 3 frames)."""
+    from prosper_b200 import scene_zoo
+    w, h = 1920, 1080
+    scene = scene_zoo.atrium(w, h, seed=1, tex_size=256)
+    world = rt.World(scene, max_width=w, max_height=h, samples_per_launch=2, flags=rt.CFG_COUNTERS)
+    world.updateBuffers()
+    world.buildAccelerationStructures()
+    orc = oracle.Oracle(scene)
+    pc = sd.reference_pc(frame_index=1)
+    ho, margin = orc.trace_primary(pc, w, h)
+    hg = world.trace_primary(pc, w, h)
+    tie = margin < ALPHA_TIE_MARGIN
+    bad = _id_mismatch(ho, hg) & ~tie
+    assert bad.sum() == 0, f"{bad.sum()} of {w * h} primary hit IDs differ"
+    assert tie.mean() < 1e-3
+    same = ~_id_mismatch(ho, hg)
+    assert np.array_equal(ho["bary"][same], hg["bary"][same])
+    assert (ho["drawInstanceIndex"] != sd.MISS).mean() > 0.9  # the camera looks down the nave
+    r = rt.RtReference()
+    r.init(world)
+    r.drawUi(maxBounces=4)
+    a = r.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=2).illumination_f32()
+    a = r.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=1).illumination_f32()
+    r2 = rt.RtReference()
+    r2.init(world)
+    r2.drawUi(maxBounces=4)
+    b = r2.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=3).illumination_f32()
+    assert np.all(a[..., 3] == 3) and np.array_equal(a, b)
+    assert np.isfinite(a).all() and a[..., :3].min() >= 0
+    c = world.counters()
+    assert c["stackOverflows"] == 0 and c["pixelSamples"] == 6 * w * h
+    world.close()
+
+
 def test_primary_ids_ploc_builder(small_atrium_instanced):
     # PRT_CFG_PLOC: another BLAS topology, the same hit records (results do not depend on the tree)
     scene, (w, h) = small_atrium_instanced, (160, 90)
