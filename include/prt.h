@@ -67,6 +67,11 @@ prt_status prt_set_samplers(prt_ctx *ctx, const prt_sampler_desc *samplers, uint
 /* texture `index` >= 1 of the bindless table (Texture.cpp:369-489); index 0 is the reserved
  * "no texture" slot (WorldData.cpp:727-741) */
 prt_status prt_set_texture(prt_ctx *ctx, uint32_t index, const prt_texture_desc *desc);
+/* Texture-cache build (Texture.cpp:213-296 `compress`, where prosper calls ispc_texcomp's CompressBlocksBC7): encodes
+ * one RGBA8 level (width, height multiples of 4; HOST memory) into BC7 blocks (width/4 * height/4 * 16 B; HOST) with a
+ * CUDA kernel. The blocks are what prt_set_texture(PRT_TEX_BC7_UNORM) and the .dds cache take. */
+prt_status prt_encode_bc7(prt_ctx *ctx, const void *rgba8, uint32_t width, uint32_t height, void *blocksOut,
+                          uint64_t blocksBytes);
 /* skybox cubemap, RGBA16F, faces +X,-X,+Y,-Y,+Z,-Z (Texture.cpp:595-601; skybox.glsl:4) */
 prt_status prt_set_sky_cubemap(prt_ctx *ctx, uint32_t faceSize, const void *rgba16f);
 /* models: sub-models of model m are subModels[offsets[m] .. offsets[m+1]) */

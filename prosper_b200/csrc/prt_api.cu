@@ -547,6 +547,29 @@ extern "C" prt_status prt_set_texture(prt_ctx *c, uint32_t index, const prt_text
     return PRT_OK;
 }
 
+extern "C" prt_status prt_encode_bc7(prt_ctx *c, const void *rgba8, uint32_t width, uint32_t height, void *blocksOut, uint64_t blocksBytes)
+{
+    REQUIRE(c && rgba8 && blocksOut, "prt_encode_bc7");
+    REQUIRE(width > 0 && height > 0 && (width & 3u) == 0 && (height & 3u) == 0,
+            "BC7 levels are whole 4x4 blocks (Texture.cpp:229-237 falls back to RGBA8 otherwise)");
+    const size_t nBlocks = (size_t)(width / 4) * (height / 4);
+    REQUIRE(blocksBytes >= nBlocks * 16, "block buffer too small");
+    CK(cudaSetDevice(c->cfg.device));
+    DBuf<uint32_t> src;
+    DBuf<uint2> dst;
+    CK(src.ensure((size_t)width * height));
+    CK(dst.ensure(nBlocks * 2));
+    CK(cudaMemcpyAsync(src.p, rgba8, (size_t)width * height * 4, cudaMemcpyHostToDevice, c->stream));
+    k_bc7_encode_mode6<<<blocksFor(nBlocks, 64), 64, 0, c->stream>>>(src.p, width, height, dst.p);
+    c->kernelLaunches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(blocksOut, dst.p, nBlocks * 16, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    src.release();
+    dst.release();
+    return PRT_OK;
+}
+
 extern "C" prt_status prt_set_sky_cubemap(prt_ctx *c, uint32_t faceSize, const void *rgba16f)
 {
     REQUIRE(c, "prt_set_sky_cubemap");

@@ -66,7 +66,7 @@ ABI_SYMBOLS = (
     "prt_build_blas", "prt_build_tlas", "prt_set_draw_instances", "prt_set_instance_transforms", "prt_set_lights",
     "prt_set_camera", "prt_record", "prt_output_f32_device", "prt_read_illumination_f16", "prt_read_output_f32",
     "prt_release_preserved", "prt_trace_primary", "prt_trace_rays", "prt_export_sum_device", "prt_import_sum_device",
-    "prt_export_sum_to_device",
+    "prt_export_sum_to_device", "prt_encode_bc7",
     "prt_get_counters", "prt_reset_counters", "prt_get_timings", "prt_get_bvh_stats", "prt_probe_texture",
     "prt_debug_read_blas", "prt_debug_read_tlas",
 )
@@ -99,7 +99,8 @@ def load_library():
             "prt_output_f32_device": [vp, C.POINTER(vp)], "prt_read_illumination_f16": [vp, vp, u64],
             "prt_read_output_f32": [vp, vp, u64], "prt_release_preserved": [vp], "prt_trace_primary": [vp, vp, u32, u32, vp],
             "prt_trace_rays": [vp, vp, vp, vp, u32, C.c_int, vp], "prt_export_sum_device": [vp, C.POINTER(vp)],
-            "prt_import_sum_device": [vp, vp], "prt_export_sum_to_device": [vp, vp], "prt_get_counters": [vp, C.POINTER(PrtCounters)], "prt_reset_counters": [vp],
+            "prt_import_sum_device": [vp, vp], "prt_export_sum_to_device": [vp, vp],
+            "prt_encode_bc7": [vp, vp, u32, u32, vp, u64], "prt_get_counters": [vp, C.POINTER(PrtCounters)], "prt_reset_counters": [vp],
             "prt_get_timings": [vp, C.POINTER(PrtTimings)], "prt_get_bvh_stats": [vp, C.POINTER(PrtBvhStats)],
             "prt_probe_texture": [vp, u32, vp, vp, u32, C.c_int, vp],
             "prt_debug_read_blas": [vp, u32, vp, u64, vp, u64, C.POINTER(u32), C.POINTER(u32)],
@@ -257,6 +258,16 @@ class World:
         uv = np.ascontiguousarray(uv, np.float32)
         out = np.zeros((uv.shape[0], 4), np.float32)
         _check(self.lib.prt_probe_texture(self.handle, texture_sampler, _p(uv), None, uv.shape[0], 1 if exact else 0, _p(out)))
+        return out
+
+    def encode_bc7(self, rgba: np.ndarray) -> np.ndarray:
+        """Texture-cache build step (Texture.cpp:213-296): RGBA8 [h, w, 4] -> BC7 blocks (uint8), on the GPU."""
+        img = np.ascontiguousarray(rgba, np.uint8)
+        h, w, ch = img.shape
+        if ch != 4:
+            raise RuntimeError("encode_bc7 wants RGBA8")
+        out = np.zeros((w // 4) * (h // 4) * 16, np.uint8)
+        _check(self.lib.prt_encode_bc7(self.handle, _p(img), w, h, _p(out), out.nbytes))
         return out
 
     def read_blas(self, model: int):
