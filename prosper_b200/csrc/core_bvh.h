@@ -359,15 +359,33 @@ HD void collapseItem(const Collapse &c, uint32_t itemIndex)
     const CollapseItem item = c.queueIn[itemIndex];
 #endif
     const Lbvh &t = c.t;
+    // children of the wide node with their box, area and primitive count fetched ONCE when they enter the set
+    // (the open-largest loop below used to re-read every child's box and range on every round)
     int32_t ch[8];
+    Box cb[8];
+    float carea[8];
+    uint32_t ccnt[8];
     int n = 0;
+    auto add = [&](int32_t ref) {
+        ch[n] = ref;
+        cb[n] = lbvhRefBox(t, ref);
+        carea[n] = boxHalfArea(cb[n]);
+        ccnt[n] = lbvhRefCount(t, ref);
+        n++;
+    };
+    auto replace = [&](int i, int32_t ref) {
+        ch[i] = ref;
+        cb[i] = lbvhRefBox(t, ref);
+        carea[i] = boxHalfArea(cb[i]);
+        ccnt[i] = lbvhRefCount(t, ref);
+    };
     if (item.ref >= 0 && lbvhRefCount(t, item.ref) > c.maxLeaf)
     {
-        ch[n++] = t.left[item.ref];
-        ch[n++] = t.right[item.ref];
+        add(t.left[item.ref]);
+        add(t.right[item.ref]);
     }
     else
-        ch[n++] = item.ref; // a tree that is a single leaf (count <= maxLeaf at the root)
+        add(item.ref); // a tree that is a single leaf (count <= maxLeaf at the root)
     // phase 1: open the largest-area child that is too big for a leaf slot; phase 2: use spare slots
     // to split multi-primitive leaves (tighter boxes, same memory)
     for (int phase = 0; phase < 2; ++phase)
@@ -379,26 +397,19 @@ HD void collapseItem(const Collapse &c, uint32_t itemIndex)
             for (int i = 0; i < n; ++i)
             {
                 if (ch[i] < 0) continue;
-                const bool big = lbvhRefCount(t, ch[i]) > c.maxLeaf;
-                if (phase == 0 && !big) continue;
-                const float a = boxHalfArea(t.nodeBox[ch[i]]);
-                if (a > bestArea) { bestArea = a; best = i; }
+                if (phase == 0 && !(ccnt[i] > c.maxLeaf)) continue;
+                if (carea[i] > bestArea) { bestArea = carea[i]; best = i; }
             }
             if (best < 0) break;
             const int32_t r = ch[best];
-            ch[best] = t.left[r];
-            ch[n++] = t.right[r];
+            const int32_t l2 = t.left[r], r2 = t.right[r];
+            replace(best, l2);
+            add(r2);
         }
     }
-    // boxes, node bounds
-    Box cb[8];
-    Box nb = lbvhRefBox(t, ch[0]);
-    cb[0] = nb;
-    for (int i = 1; i < n; ++i)
-    {
-        cb[i] = lbvhRefBox(t, ch[i]);
-        nb = boxUnion(nb, cb[i]);
-    }
+    // node bounds
+    Box nb = cb[0];
+    for (int i = 1; i < n; ++i) nb = boxUnion(nb, cb[i]);
     // slot assignment (greedy on the Ylitie cost: child offset projected on the slot's octant diagonal)
     const V3 nc = (boxLo(nb) + boxHi(nb)) * 0.5f;
     float off[8][3];
@@ -432,7 +443,7 @@ HD void collapseItem(const Collapse &c, uint32_t itemIndex)
     uint32_t nInternal = 0, nPrims = 0;
     for (int i = 0; i < n; ++i)
     {
-        const uint32_t cnt = lbvhRefCount(t, ch[i]);
+        const uint32_t cnt = ccnt[i];
         if (cnt > c.maxLeaf) nInternal++;
         else nPrims += cnt;
     }
@@ -449,7 +460,7 @@ HD void collapseItem(const Collapse &c, uint32_t itemIndex)
         node.meta[s] = 0;
         const int i = childAt[s];
         if (i < 0) continue;
-        const uint32_t cnt = lbvhRefCount(t, ch[i]);
+        const uint32_t cnt = ccnt[i];
         if (cnt > c.maxLeaf)
         {
             imask |= 1u << s;
