@@ -225,3 +225,70 @@ def stress(width=1920, height=1080, instances=10000, seed=5, mesh_tris=10000, mo
     sc = sb.finish(cam, directional=((3, 2.8, 2.5, 0), (-0.3, -1, -0.2, 0)), sky=procedural_sky(64))
     sc.name = f"stress({instances})"
     return sc
+
+
+def district(width=3840, height=2160, seed=4, detail=1.0, animated=1024):
+    """C4 stand-in ("Bistro-scale"): a street grid of facade / roof / tree models, ~3.5 M unique triangles at
+    detail=1 over ~1300 instances, the first `animated` of which are meant to be moved every frame (see
+    district_frame) so that the TLAS is rebuilt per frame. Untextured materials, sun + sky."""
+    rng = np.random.default_rng(seed)
+    sb = SceneBuilder("district")
+    d = lambda n: max(3, int(round(n * np.sqrt(detail))))
+    mats = [sb.add_material(make_material(base_color=(*c, 1.0), roughness=r, metallic=m))
+            for c, r, m in (((0.7, 0.66, 0.6), 0.8, 0.0), ((0.5, 0.3, 0.25), 0.7, 0.0), ((0.35, 0.4, 0.45), 0.5, 0.0),
+                            ((0.2, 0.45, 0.2), 0.9, 0.0), ((0.8, 0.8, 0.85), 0.25, 1.0))]
+    models = []
+    for k in range(16):  # facades: bumpy boxes, ~190k triangles each at detail=1
+        hgt = 6.0 + 3.0 * (k % 4)
+        wall = lambda u, v, s, k=k, hgt=hgt: np.stack(
+            [(u - 0.5) * 8.0, v * hgt, np.full_like(u, 4.0) + 0.15 * np.sin(u * (20 + 3 * k)) * np.sin(v * (14 + k))], -1)
+        parts = []
+        for q in range(4):
+            p, n, uv, t, idx = param_surface(lambda u, v: wall(u, v, 1.0), d(160), d(150), (4, 4))
+            c, s_ = np.cos(q * np.pi / 2), np.sin(q * np.pi / 2)
+            rot = np.array([[c, 0, s_], [0, 1, 0], [-s_, 0, c]], np.float32)
+            parts.append((p @ rot.T, n @ rot.T, uv, np.concatenate([t[:, :3] @ rot.T, t[:, 3:4]], 1), idx))
+        models.append(sb.add_model([(merge(parts), mats[k % 3]), (box(8.2, 0.4, 8.2, 2), mats[4])]))
+    trees = [sb.add_model([(bumpy_sphere(1.6, d(160), d(120), 0.35, 9.0 + k, 0.4 * k, (1, 1.4, 1)), mats[3]),
+                           (cylinder(0.25, 2.0, d(16), d(4)), mats[1])]) for k in range(8)]
+    grid, pitch = 18, 14.0
+    cells = [(i, j) for i in range(grid) for j in range(grid)]
+    rng.shuffle(cells)
+    for n, (i, j) in enumerate(cells):
+        x, z = (i - grid / 2 + 0.5) * pitch, (j - grid / 2 + 0.5) * pitch
+        sb.add_instance(models[n % len(models)], trs((x, 0, z), (0, 1, 0), 0.5 * np.pi * (n % 4)))
+    for n in range(1000):
+        i, j = rng.integers(0, grid, 2)
+        x, z = (i - grid / 2) * pitch + rng.uniform(-1, 1), (j - grid / 2 + 0.5) * pitch + rng.uniform(-5, 5)
+        sb.add_instance(trees[n % len(trees)], trs((x, 2.0, z), (0, 1, 0), float(rng.uniform(0, 6.28)), (1, float(rng.uniform(0.8, 1.5)), 1)))
+    # the moving instances come first in the arrays: reorder so that district_frame can rotate [0, animated)
+    sb.instances = sb.instances[::-1]
+    ground = sb.add_model([(plane(grid * pitch, grid * pitch, 64, 64, (32, 32)), mats[0])])
+    sb.add_instance(ground)
+    half = grid * pitch / 2
+    cam = make_camera((-half * 0.9, 22.0, half * 0.95), (0, 4.0, 0), width, height)
+    sc = sb.finish(cam, directional=((3, 2.8, 2.5, 0), (-0.4, -1, -0.3, 0)), sky=procedural_sky(64))
+    sc.name = "district"
+    sc.animated = min(animated, len(sc.tlas_instances) - 1)
+    return sc
+
+
+def district_frame(scene, frame: int):
+    """Per-frame update of an animated scene (World::updateAnimations + updateScene, World.cpp:349-466): rotates the first
+    `scene.animated` instances about Y by 0.02 rad per frame around their own origin and rewrites their
+    ModelInstanceTransforms and TLAS instance records in place (linear keyframes of a rotation track)."""
+    from .scene_data import instance_transforms
+    n = scene.animated
+    base = getattr(scene, "_base_m2w", None)
+    if base is None:
+        base = scene.transforms["modelToWorld"][:n].copy()  # [n, 3, 4]
+        scene._base_m2w = base
+    a = 0.02 * frame
+    c, s = np.cos(a), np.sin(a)
+    ry = np.array([[c, 0, s, 0], [0, 1, 0, 0], [-s, 0, c, 0], [0, 0, 0, 1]], np.float64)
+    for i in range(n):
+        m = np.eye(4)
+        m[:3, :4] = base[i]
+        t = instance_transforms(m @ ry)
+        scene.transforms[i] = t
+        scene.tlas_instances[i]["transform"] = t["modelToWorld"]

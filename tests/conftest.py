@@ -47,3 +47,9 @@ def small_atrium_instanced():
 def small_stress():
     from prosper_b200 import scene_zoo
     return scene_zoo.stress(160, 90, instances=150, mesh_tris=600)
+
+
+@pytest.fixture(scope="session")
+def small_district():
+    from prosper_b200 import scene_zoo
+    return scene_zoo.district(160, 90, detail=0.002, animated=1000)
