@@ -363,3 +363,52 @@ def test_animated_district_tlas_rebuild_per_frame(small_district):
         assert (_id_mismatch(ho, hg) & ~(margin < ALPHA_TIE_MARGIN)).sum() == 0, f"frame {frame}"
     assert world.counters()["stackOverflows"] == 0
     world.close()
+
+
+def test_degenerate_inputs_on_gpu(small_stress):
+    """Edge cases through the C ABI: single-triangle model, 40 coincident triangles (Morton ties -> lowest primitive
+    wins), inactive instances (blasReference 0, World.cpp:898-905), zero visibility mask, and an empty TLAS."""
+    import copy
+    from prosper_b200.scenes import SceneBuilder, procedural_sky
+    from prosper_b200.scene_data import make_camera, make_material
+    sb = SceneBuilder("degenerate")
+    m = sb.add_material(make_material((0.5, 0.5, 0.5, 1)))
+    tri = (np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32), np.tile([0, 0, 1], (3, 1)).astype(np.float32),
+           np.zeros((3, 2), np.float32), np.tile([1, 0, 0, 1], (3, 1)).astype(np.float32), np.array([0, 1, 2], np.uint32))
+    one = sb.add_model([(tri, m)])
+    many = sb.add_model([((np.tile(tri[0], (40, 1)), np.tile(tri[1], (40, 1)), np.tile(tri[2], (40, 1)), np.tile(tri[3], (40, 1)),
+                           np.arange(120, dtype=np.uint32)), m)])
+    sb.add_instance(one)
+    sb.add_instance(many, sd.trs((1.5, 0, 0)))
+    scene = sb.finish(make_camera((0.8, 0.4, 3), (0.8, 0.4, 0), 48, 32), sky=procedural_sky(8))
+    pc = sd.reference_pc()
+    world = _world(scene, 48, 32)
+    ho, margin = oracle.Oracle(scene).trace_primary(pc, 48, 32)
+    hg = world.trace_primary(pc, 48, 32)
+    assert np.array_equal(ho, hg)
+    assert hg["primitiveID"][hg["drawInstanceIndex"] == 1].max() == 0  # exact tie -> lowest primitive
+    # empty TLAS: every ray misses and the image is the sky
+    empty = scene.tlas_instances.copy()
+    empty["blasReference"] = 0
+    world.buildTlas(empty)
+    assert np.all(world.trace_primary(pc, 48, 32)["drawInstanceIndex"] == sd.MISS)
+    r = rt.RtReference()
+    r.init(world)
+    img = r.record(world, (0, 0, 48, 32), rt.Options(ibl=True), frames=2).illumination_f32()
+    scene_empty = copy.copy(scene)
+    scene_empty.tlas_instances = empty
+    ref, _ = oracle.Oracle(scene_empty).render(sd.reference_pc(max_bounces=6), 48, 32, 2)
+    assert np.allclose(img, ref, rtol=1e-5, atol=1e-6)
+    world.close()
+
+    # inactive and masked-out instances in a many-instance scene
+    scene2 = copy.deepcopy(small_stress)
+    scene2.tlas_instances["blasReference"][::3] = 0  # inactive
+    masked = scene2.tlas_instances["customIndexAndMask"][1::3]
+    scene2.tlas_instances["customIndexAndMask"][1::3] = masked & 0x00FFFFFF  # mask 0: never hit (gl_RayFlags mask 0xFF)
+    world = _world(scene2, 160, 90)
+    ho, margin = oracle.Oracle(scene2).trace_primary(pc, 160, 90)
+    hg = world.trace_primary(pc, 160, 90)
+    assert (_id_mismatch(ho, hg) & ~(margin < ALPHA_TIE_MARGIN)).sum() == 0
+    assert world.counters()["stackOverflows"] == 0
+    world.close()
