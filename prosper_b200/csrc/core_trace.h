@@ -40,6 +40,7 @@ struct Accel
 {
     const WideNode *tlasNodes; // nullptr = empty scene
     const InstRec *instances;  // TLAS node order
+    uint32_t instanceCount;    // 1: rays start inside the only instance (its BLAS root culls what the TLAS root would)
 };
 
 struct NodeRay
@@ -277,7 +278,8 @@ struct SharedTraceStack
 
 // Returns false when there is nothing to traverse (the ray is a miss).
 template <class Stack>
-HD bool traceBegin(TraceState &s, Stack &st, const Accel &as, V3 o, V3 d, float tMin, float tMax, uint32_t seed)
+HD bool traceBegin(TraceState &s, Stack &st, const Accel &as, V3 o, V3 d, float tMin, float tMax, uint32_t seed,
+                   TraceCounters *cnt = nullptr)
 {
     s.best.drawInstanceIndex = MISS_INDEX;
     s.best.primitiveID = MISS_INDEX;
@@ -292,7 +294,22 @@ HD bool traceBegin(TraceState &s, Stack &st, const Accel &as, V3 o, V3 d, float 
     s.instIndex = 0;
     s.gx = 0; s.gy = 0x80000000u;
     s.px = 0; s.py = 0;
-    return as.tlasNodes != nullptr;
+    if (as.tlasNodes == nullptr) return false;
+    if (as.instanceCount == 1u)
+    {
+        // single-instance scene (a baked glTF such as Sponza): skip the one-node TLAS
+        const InstRec &inst = as.instances[0];
+        if (cnt) cnt->instances++;
+        if ((inst.mask & 0xFFu) == 0) return false;
+        s.blasSp = 0;
+        setupNodeRay(s.ray, xformPoint(inst.w2o, o), xformVector(inst.w2o, d));
+        s.nodes = inst.nodes;
+        s.tris = inst.tris;
+        st.cold.uvs = inst.uvs;
+        st.cold.instCustom = inst.customIndex;
+        s.instIndex = inst.index;
+    }
+    return true;
 }
 
 // One step of traceRayEXT = ONE item of work, so that the lanes of a warp stay in lock step on items of
@@ -446,6 +463,7 @@ HD bool traceStep(TraceState &s, Stack &st, const Accel &as, const SceneView &sv
 
     if (s.py == 0 && (s.gy & 0xFF000000u) == 0)
     {
+        if (s.sp == 0) return true;
         if (s.sp == s.blasSp)
         {
             // BLAS exhausted: back to world space
@@ -453,7 +471,6 @@ HD bool traceStep(TraceState &s, Stack &st, const Accel &as, const SceneView &sv
             setupNodeRay(s.ray, st.cold.o, st.cold.d);
             s.nodes = as.tlasNodes;
         }
-        if (s.sp == 0) return true;
         s.sp--;
         st.get(s.sp, s.gx, s.gy);
         if ((s.gy & 0xFF000000u) == 0)
@@ -473,7 +490,7 @@ HDNI bool traceRay(const Accel &as, const SceneView &sv, V3 o, V3 d, float tMin,
 {
     TraceState s;
     TraceStack st;
-    if (traceBegin(s, st, as, o, d, tMin, tMax, seed))
+    if (traceBegin(s, st, as, o, d, tMin, tMax, seed, COUNT ? cnt : nullptr))
         while (!traceStep<SHADOW, COUNT>(s, st, as, sv, cnt)) {}
     best = s.best;
     return best.drawInstanceIndex != MISS_INDEX;

@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
             {
                 slot = next;
                 const float4 o = pb.rayO[q][slot], d = pb.rayD[q][slot];
-                active = traceBegin(s, st, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.rayId[q][slot].y);
+                active = traceBegin(s, st, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.rayId[q][slot].y, COUNT ? &tc : nullptr);
                 if (!active) pb.hits[slot] = make_uint4(MISS_INDEX, MISS_INDEX, 0u, 0u);
             }
         }
@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
             {
                 slot = next;
                 const float4 o = pb.shadowO[slot], d = pb.shadowD[slot];
-                active = traceBegin(s, st, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.shadowId[slot].y);
+                active = traceBegin(s, st, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.shadowId[slot].y, COUNT ? &tc : nullptr);
                 if (!active) retire();
             }
         }

@@ -262,6 +262,7 @@ struct prt_ctx
         Accel a{};
         a.tlasNodes = tlasInstances ? tlasNodes.p : nullptr;
         a.instances = tlasInst.p;
+        a.instanceCount = tlasInstances;
         return a;
     }
 };

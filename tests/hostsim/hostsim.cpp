@@ -214,6 +214,7 @@ static void buildTlasHost(hs_ctx *c)
             for (size_t i = 0; i < recs.size(); ++i) c->tlasInst[i] = recs[h.primOut[i]];
             c->as.tlasNodes = c->tlasNodes.data();
             c->as.instances = c->tlasInst.data();
+            c->as.instanceCount = (uint32_t)c->tlasInst.size();
         }
     }
 }
