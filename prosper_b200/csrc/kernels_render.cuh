@@ -129,18 +129,24 @@ __device__ __forceinline__ uint32_t fetchSlots(uint32_t *cursor, uint32_t count,
     return idle ? base + (uint32_t)__popc(need & ((1u << lane) - 1u)) : 0xFFFFFFFFu;
 }
 
-// The item kind (0 node, 1 primitive, 2 any-hit; -1 idle) most lanes of the warp want next. Ties go to the later
-// stage, which frees lanes for the earlier ones. Never returns a kind nobody wants unless the warp is idle.
-// `flexible` lanes (kind 1 that could also take a node item, traceCanPostpone) do not vote: they join whichever of
-// node / primitive wins, which is what lifts the lanes per issued instruction.
-__device__ __forceinline__ int pluralityKind(int kind, bool flexible)
+// The item kind (0 node, 1 primitive, 2 any-hit; -1 idle) most lanes of the warp want next; `live` = lanes with a ray.
+// Ties go to the later stage, which frees lanes for the earlier ones. `flexible` lanes (kind 1 that could also take
+// a node item, traceCanPostpone; only with PRT_TRACE_POSTPONE) do not vote: they join whichever of node /
+// primitive wins.
+__device__ __forceinline__ int pluralityKind(int kind, bool flexible, int &live)
 {
     const int n0 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 0));
-    const int n1 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1 && !flexible));
     const int n2 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 2));
+#if PRT_TRACE_POSTPONE
+    const int n1 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1 && !flexible));
     const int nf = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1 && flexible));
+#else
+    const int n1 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1));
+    const int nf = 0;
+    (void)flexible;
+#endif
+    live = n0 + n1 + n2 + nf;
     if (n2 > 0 && n2 >= n1 + nf && n2 >= n0 + nf) return 2;
-    if (n0 + n1 + nf == 0) return 2;
     return n1 > n0 ? 1 : (n0 > 0 ? 0 : 1);
 }
 
@@ -184,14 +190,14 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
             // issued instruction serves a large share of the live lanes instead of three kinds running mostly empty.
             const int kind = active ? traceItemKind(s) : -1;
             const bool flexible = PRT_TRACE_POSTPONE && active && traceCanPostpone(s);
-            const int run = pluralityKind(kind, flexible);
+            int live;
+            const int run = pluralityKind(kind, flexible, live);
+            if (live == 0 || (!exhausted && live < TRACE_REFILL_BELOW)) break; // refill (or finish) before the next item
             if ((kind == run || (flexible && run == 0)) && traceStep<false, COUNT>(s, st, as, sv, &tc, run == 0))
             {
                 pb.hits[slot] = make_uint4(s.best.drawInstanceIndex, s.best.primitiveID, __float_as_uint(s.best.u), __float_as_uint(s.best.v));
                 active = false;
             }
-            const int live = __popc(__ballot_sync(0xFFFFFFFFu, active));
-            if (live == 0 || (!exhausted && live < TRACE_REFILL_BELOW)) break;
         }
     }
     if (COUNT) flushTraceCounters(gc, tc);
@@ -364,14 +370,14 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
         {
             const int kind = active ? traceItemKind(s) : -1; // plurality vote, see k_trace_closest
             const bool flexible = PRT_TRACE_POSTPONE && active && traceCanPostpone(s);
-            const int run = pluralityKind(kind, flexible);
+            int live;
+            const int run = pluralityKind(kind, flexible, live);
+            if (live == 0 || (!exhausted && live < TRACE_REFILL_BELOW)) break;
             if ((kind == run || (flexible && run == 0)) && traceStep<true, COUNT>(s, st, as, sv, &tc, run == 0))
             {
                 retire();
                 active = false;
             }
-            const int live = __popc(__ballot_sync(0xFFFFFFFFu, active));
-            if (live == 0 || (!exhausted && live < TRACE_REFILL_BELOW)) break;
         }
     }
     if (COUNT) flushTraceCounters(gc, tc, true);
