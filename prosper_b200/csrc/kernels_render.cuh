@@ -135,13 +135,15 @@ __device__ __forceinline__ uint32_t fetchSlots(uint32_t *cursor, uint32_t count,
 // primitive wins.
 __device__ __forceinline__ int pluralityKind(int kind, bool flexible, int &live)
 {
+#if PRT_TRACE_POSTPONE
     const int n0 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 0));
     const int n2 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 2));
-#if PRT_TRACE_POSTPONE
     const int n1 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1 && !flexible));
     const int nf = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1 && flexible));
 #else
-    const int n1 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1));
+    // the three counts in one warp reduction: lane contributes 1 << (10 * kind)
+    const uint32_t sum = __reduce_add_sync(0xFFFFFFFFu, kind < 0 ? 0u : 1u << (10 * kind));
+    const int n0 = (int)(sum & 1023u), n1 = (int)((sum >> 10) & 1023u), n2 = (int)(sum >> 20);
     const int nf = 0;
     (void)flexible;
 #endif
