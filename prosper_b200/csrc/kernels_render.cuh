@@ -19,7 +19,7 @@ constexpr uint32_t COUNT_WORDS = 32;
 // Persistent trace kernels: a warp refills its retired lanes from the queue once fewer than this many
 // lanes are still traversing (Aila & Laine's dynamic fetch); below it, finished lanes idle until the refill.
 #ifndef PRT_TRACE_REFILL_BELOW
-#define PRT_TRACE_REFILL_BELOW 22
+#define PRT_TRACE_REFILL_BELOW 26
 #endif
 #ifndef PRT_TRACE_SMEM_STACK
 #define PRT_TRACE_SMEM_STACK 0
