@@ -323,15 +323,20 @@ HD int traceItemKind(const TraceState &s) { return (s.px & TRACE_PENDING) ? 2 : 
 HD bool traceCanPostpone(const TraceState &s) { return !(s.px & TRACE_PENDING) && s.py != 0 && (s.gy & 0xFF000000u) != 0; }
 
 // preferNode: take a node item even though primitives are pending (only meaningful when traceCanPostpone(s)).
+// kind: the caller's knowledge of traceItemKind(s) (-1: look it up). The trace kernels pass the warp-uniform kind
+// their vote selected, which turns the three-way choice below into a uniform branch.
 template <bool SHADOW, bool COUNT, class Stack>
-HD bool traceStep(TraceState &s, Stack &st, const Accel &as, const SceneView &sv, TraceCounters *cnt, bool preferNode = false)
+HD bool traceStep(TraceState &s, Stack &st, const Accel &as, const SceneView &sv, TraceCounters *cnt, bool preferNode = false,
+                  int kind = -1)
 {
     if (preferNode && traceCanPostpone(s))
     {
         if (s.sp < TRACE_STACK) { st.put(s.sp, s.px, s.py); s.sp++; s.py = 0; }
         // (a full stack keeps the primitives first: nothing is lost, only the order stays as it was)
+        kind = 0;
     }
-    if (s.px & TRACE_PENDING)
+    if (kind < 0) kind = traceItemKind(s);
+    if (kind == 2)
     {
         // scene.rahit for the candidate parked by the triangle item below (its own item kind, so that the lanes of
         // a warp run the alpha test together instead of one or two at a time inside the triangle item)
@@ -363,7 +368,7 @@ HD bool traceStep(TraceState &s, Stack &st, const Accel &as, const SceneView &sv
             if (SHADOW) return true;
         }
     }
-    else if (s.py != 0)
+    else if (kind == 1)
     {
         const int pbit = bfind(s.py);
         s.py &= ~(1u << pbit);

@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
             int live;
             const int run = pluralityKind(kind, flexible, live);
             if (live == 0 || (!exhausted && live < TRACE_REFILL_BELOW)) break; // refill (or finish) before the next item
-            if ((kind == run || (flexible && run == 0)) && traceStep<false, COUNT>(s, st, as, sv, &tc, run == 0))
+            if ((kind == run || (flexible && run == 0)) && traceStep<false, COUNT>(s, st, as, sv, &tc, PRT_TRACE_POSTPONE && run == 0, PRT_TRACE_POSTPONE ? -1 : run))
             {
                 pb.hits[slot] = make_uint4(s.best.drawInstanceIndex, s.best.primitiveID, __float_as_uint(s.best.u), __float_as_uint(s.best.v));
                 active = false;
@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
             int live;
             const int run = pluralityKind(kind, flexible, live);
             if (live == 0 || (!exhausted && live < TRACE_REFILL_BELOW)) break;
-            if ((kind == run || (flexible && run == 0)) && traceStep<true, COUNT>(s, st, as, sv, &tc, run == 0))
+            if ((kind == run || (flexible && run == 0)) && traceStep<true, COUNT>(s, st, as, sv, &tc, PRT_TRACE_POSTPONE && run == 0, PRT_TRACE_POSTPONE ? -1 : run))
             {
                 retire();
                 active = false;
