@@ -103,20 +103,21 @@ HD void invertTransformExact(const float *m, float *out)
 // EXACT CONTRACT: Moeller-Trumbore, two-sided, no epsilon, open interval (oracle intersectTriangle)
 HD bool intersectTriangleExact(V3 o, V3 d, float tMin, float tMax, V3 v0, V3 e1, V3 e2, float &t, float &u, float &v)
 {
+    // Straight-line form: the lanes of a warp test different triangles, so the early exits of the textbook version
+    // never save the warp anything; every value is computed with the same operations in the same order and the
+    // decision is one conjunction (a zero determinant makes inv infinite, which the comparisons below reject, and is
+    // excluded explicitly as before).
     const V3 P = xcross(d, e2);
     const float det = xdot(e1, P);
-    if (det == 0.0f) return false;
     const float inv = xdiv(1.0f, det);
     const V3 T = xsub3(o, v0);
     const float uu = xmul(xdot(T, P), inv);
-    if (!(uu >= 0.0f) || uu > 1.0f) return false;
     const V3 Q = xcross(T, e1);
     const float vv = xmul(xdot(d, Q), inv);
-    if (!(vv >= 0.0f) || xadd(uu, vv) > 1.0f) return false;
     const float tt = xmul(xdot(e2, Q), inv);
-    if (!(tt > tMin) || !(tt < tMax)) return false;
+    const bool hit = (det != 0.0f) & (uu >= 0.0f) & !(uu > 1.0f) & (vv >= 0.0f) & !(xadd(uu, vv) > 1.0f) & (tt > tMin) & (tt < tMax);
     t = tt; u = uu; v = vv;
-    return true;
+    return hit;
 }
 
 HD bool betterHit(float t, uint32_t inst, uint32_t geom, uint32_t prim, const HitRec &h)
