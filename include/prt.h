@@ -72,6 +72,17 @@ prt_status prt_set_texture(prt_ctx *ctx, uint32_t index, const prt_texture_desc 
  * CUDA kernel. The blocks are what prt_set_texture(PRT_TEX_BC7_UNORM) and the .dds cache take. */
 prt_status prt_encode_bc7(prt_ctx *ctx, const void *rgba8, uint32_t width, uint32_t height, void *blocksOut,
                           uint64_t blocksBytes);
+
+/* Display transform (render::ToneMap, src/render/ToneMap.cpp + res/shader/tone_map.comp).
+ * prt_set_tone_map_lut = ToneMap::init (ToneMap.cpp:31-42): the dim^3 3D table in DXGI R9G9B9E5_SHAREDEXP texels, x
+ * fastest -- the payload of res/texture/tony_mc_mapface.dds (dim 48) as it lies in the file; HOST memory.
+ * prt_tone_map = ToneMap::record (63-134): exposure, HSV contrast, Tony McMapface, 1/2.2 gamma over the current
+ * Output::illumination (the fp16-rounded running mean) into R8G8B8A8 unorm, width*height*4 bytes of HOST memory;
+ * prt_tone_map_device leaves the image on the GPU (valid until the next tone-map call), ordered on the stream. */
+typedef struct prt_tone_map_pc { float exposure; float contrast; } prt_tone_map_pc; /* push_constants/tone_map.h */
+prt_status prt_set_tone_map_lut(prt_ctx *ctx, const uint32_t *rgb9e5, uint32_t dim);
+prt_status prt_tone_map(prt_ctx *ctx, const prt_tone_map_pc *pc, void *dstHost, uint64_t dstBytes);
+prt_status prt_tone_map_device(prt_ctx *ctx, const prt_tone_map_pc *pc, const uint32_t **out);
 /* skybox cubemap, RGBA16F, faces +X,-X,+Y,-Y,+Z,-Z (Texture.cpp:595-601; skybox.glsl:4) */
 prt_status prt_set_sky_cubemap(prt_ctx *ctx, uint32_t faceSize, const void *rgba16f);
 /* models: sub-models of model m are subModels[offsets[m] .. offsets[m+1]) */

@@ -90,6 +90,10 @@ def lib():
         l.orc_sample_texture.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_float, C.c_float, C.c_void_p]
         l.orc_sample_sky.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         l.orc_unpack_snorm10.argtypes = [C.c_uint32, C.c_void_p]
+        l.orc_tone_map.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_float, C.c_float, C.c_void_p, C.c_uint32, C.c_void_p]
+        l.orc_tone_map.restype = None
+        l.orc_decode_rgb9e5.argtypes = [C.c_uint32, C.c_void_p]
+        l.orc_decode_rgb9e5.restype = None
         _lib = l
     return _lib
 
@@ -216,3 +220,20 @@ class Oracle:
         out = np.zeros(3, np.float32)
         lib().orc_sample_sky(self._ctx, _p(d), _p(out))
         return out
+
+
+def tone_map(illumination_f16: np.ndarray, exposure: float, contrast: float, lut_rgb9e5: np.ndarray) -> np.ndarray:
+    """tone_map.comp over an RGBA16F image [h, w, 4] -> RGBA8 [h, w, 4]."""
+    img = np.ascontiguousarray(illumination_f16, np.float16)
+    h, w, _ = img.shape
+    lut = np.ascontiguousarray(lut_rgb9e5, np.uint32).reshape(-1)
+    dim = round(lut.size ** (1.0 / 3.0))
+    out = np.zeros((h, w, 4), np.uint8)
+    lib().orc_tone_map(_p(img.view(np.uint16)), w, h, exposure, contrast, _p(lut), dim, _p(out))
+    return out
+
+
+def decode_rgb9e5(texel: int) -> np.ndarray:
+    out = np.zeros(3, np.float32)
+    lib().orc_decode_rgb9e5(int(texel), _p(out))
+    return out

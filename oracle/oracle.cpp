@@ -974,3 +974,95 @@ int orc_intersect_triangle(const float o[3], const float d[3], float tmin, float
 void orc_invert_transform(const float m[12], float out[12]) { invertTransform(m, out); }
 
 } // extern "C"
+
+// ---- display transform (tone_map.comp) ----
+namespace {
+// GLSL mod
+float modGlsl(float a, float b) { return a - b * std::floor(a / b); }
+// DXGI R9G9B9E5_SHAREDEXP: value = mantissa / 512 * 2^(exponent - 15)
+void rgb9e5(uint32_t t, float rgb[3])
+{
+    const float scale = std::ldexp(1.0f, (int)(t >> 27) - 15 - 9);
+    for (int ch = 0; ch < 3; ++ch) rgb[ch] = (float)((t >> (9 * ch)) & 511u) * scale;
+}
+// linear filter, clamp to edge, LOD 0 (Vulkan spec "Texel filtering": i0 = floor(u - 0.5), weight = frac(u - 0.5))
+void lutFetch(const uint32_t *lut, int dim, const float uvw[3], float rgb[3])
+{
+    int lo[3], hi[3];
+    float fr[3];
+    for (int a = 0; a < 3; ++a)
+    {
+        const float u = uvw[a] * (float)dim - 0.5f;
+        const float fl = std::floor(u);
+        fr[a] = u - fl;
+        if (!(fr[a] >= 0.f)) fr[a] = 0.f;
+        long i = std::isnan(fl) ? 0 : (fl < -1.f ? -1 : (fl > (float)dim ? dim : (long)fl));
+        lo[a] = (int)std::min<long>(std::max<long>(i, 0), dim - 1);
+        hi[a] = (int)std::min<long>(std::max<long>(i + 1, 0), dim - 1);
+    }
+    rgb[0] = rgb[1] = rgb[2] = 0.f;
+    for (int corner = 0; corner < 8; ++corner)
+    {
+        const int xi = (corner & 1) ? hi[0] : lo[0];
+        const int yi = (corner & 2) ? hi[1] : lo[1];
+        const int zi = (corner & 4) ? hi[2] : lo[2];
+        const float wx = (corner & 1) ? fr[0] : 1.f - fr[0];
+        const float wy = (corner & 2) ? fr[1] : 1.f - fr[1];
+        const float wz = (corner & 4) ? fr[2] : 1.f - fr[2];
+        float texel[3];
+        rgb9e5(lut[((size_t)zi * dim + yi) * dim + xi], texel);
+        const float w = wx * wy * wz;
+        for (int ch = 0; ch < 3; ++ch) rgb[ch] += w * texel[ch];
+    }
+}
+uint8_t unorm8(float v)
+{
+    if (std::isnan(v) || v <= 0.f) return 0;
+    if (v >= 1.f) return 255;
+    return (uint8_t)std::nearbyint(v * 255.f); // round to nearest even
+}
+} // namespace
+
+extern "C" void orc_decode_rgb9e5(uint32_t texel, float out[3]) { rgb9e5(texel, out); }
+
+extern "C" void orc_tone_map(const uint16_t *img, uint32_t width, uint32_t height, float exposure, float contrast,
+                             const uint32_t *lut, uint32_t dim, uint8_t *out)
+{
+    for (size_t p = 0; p < (size_t)width * height; ++p)
+    {
+        // tone_map.comp:39-43
+        float r = halfToFloat(img[4 * p + 0]) * exposure;
+        float g = halfToFloat(img[4 * p + 1]) * exposure;
+        float b = halfToFloat(img[4 * p + 2]) * exposure;
+        // math.glsl:18-42
+        const float value = std::max(std::max(r, g), b);
+        const float low = std::min(std::min(r, g), b);
+        const float chroma = value - low;
+        float hue = 0.f;
+        if (chroma != 0.f)
+        {
+            if (value == r) hue = modGlsl((g - b) / chroma, 6.f);
+            else if (value == g) hue = (b - r) / chroma + 2.f;
+            else hue = (r - g) / chroma + 4.f;
+        }
+        const float sat = value == 0.f ? 0.f : chroma / value;
+        // tone_map.comp:50
+        const float v2 = std::pow(value, contrast);
+        // math.glsl:45-77
+        const float c2 = v2 * sat;
+        const float x = c2 * (1.f - std::fabs(modGlsl(hue, 2.f) - 1.f));
+        const int sector = hue < 1.f ? 0 : hue < 2.f ? 1 : hue < 3.f ? 2 : hue < 4.f ? 3 : hue < 5.f ? 4 : 5;
+        static const int pick[6][3] = {{0, 1, 2}, {1, 0, 2}, {2, 0, 1}, {2, 1, 0}, {1, 2, 0}, {0, 2, 1}}; // 0 chroma, 1 x, 2 zero
+        const float parts[3] = {c2, x, 0.f};
+        const float m = v2 - c2;
+        const float rgb[3] = {parts[pick[sector][0]] + m, parts[pick[sector][1]] + m, parts[pick[sector][2]] + m};
+        // tone_map.comp:17-27
+        const float dims = (float)dim;
+        float uvw[3], mapped[3];
+        for (int ch = 0; ch < 3; ++ch) uvw[ch] = rgb[ch] / (rgb[ch] + 1.f) * ((dims - 1.f) / dims) + 0.5f / dims;
+        lutFetch(lut, (int)dim, uvw, mapped);
+        // tone_map.comp:57-61
+        for (int ch = 0; ch < 3; ++ch) out[4 * p + ch] = unorm8(std::pow(mapped[ch], 1.f / 2.2f));
+        out[4 * p + 3] = 255;
+    }
+}

@@ -114,6 +114,14 @@ int orc_intersect_triangle(const float o[3], const float d[3], float tmin, float
 /* world->object of a row-major 3x4 (exact contract); out = 12 floats row-major */
 void orc_invert_transform(const float m[12], float out[12]);
 
+/* Display transform: res/shader/tone_map.comp:17-62 with rgbToHsv / hsvToRgb of common/math.glsl:18-77 over an
+ * RGBA16F illumination image; lut = dim^3 R9G9B9E5 texels (tony_mc_mapface.dds payload), sampled trilinearly with
+ * clamp-to-edge; out = RGBA8 unorm (ToneMap.cpp:77). */
+void orc_tone_map(const uint16_t *illuminationF16, uint32_t width, uint32_t height, float exposure, float contrast,
+                  const uint32_t *lutRgb9e5, uint32_t dim, uint8_t *outRgba8);
+/* one R9G9B9E5_SHAREDEXP texel -> rgb */
+void orc_decode_rgb9e5(uint32_t texel, float out[3]);
+
 #ifdef __cplusplus
 }
 #endif

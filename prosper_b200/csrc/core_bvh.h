@@ -349,6 +349,10 @@ HD bool quantisePlanes(float p, float scale, float lo, float hi, uint32_t &qlo, 
     return true;
 }
 
+#ifndef PRT_BOTTOM_CAP
+#define PRT_BOTTOM_CAP 0
+#endif
+
 HD void collapseItem(const Collapse &c, uint32_t itemIndex)
 {
 #if defined(__CUDA_ARCH__)
@@ -388,6 +392,15 @@ HD void collapseItem(const Collapse &c, uint32_t itemIndex)
         add(item.ref); // a tree that is a single leaf (count <= maxLeaf at the root)
     // phase 1: open the largest-area child that is too big for a leaf slot; phase 2: use spare slots
     // to split multi-primitive leaves (tighter boxes, same memory)
+#if PRT_BOTTOM_CAP
+    // a subtree that fits one wide node's leaf storage is kept whole (it becomes ONE bottom node) instead of
+    // being opened from above into several sparse ones
+    const uint32_t total = item.ref >= 0 ? lbvhRefCount(t, item.ref) : 1u;
+    const uint32_t cap = (uint32_t)PRT_BOTTOM_CAP * c.maxLeaf;
+    const uint32_t openAbove = total > cap ? cap : c.maxLeaf;
+#else
+    const uint32_t openAbove = c.maxLeaf;
+#endif
     for (int phase = 0; phase < 2; ++phase)
     {
         while (n < 8)
@@ -397,7 +410,8 @@ HD void collapseItem(const Collapse &c, uint32_t itemIndex)
             for (int i = 0; i < n; ++i)
             {
                 if (ch[i] < 0) continue;
-                if (phase == 0 && !(ccnt[i] > c.maxLeaf)) continue;
+                if (phase == 0 && !(ccnt[i] > openAbove)) continue;
+                if (phase == 1 && ccnt[i] > c.maxLeaf) continue;
                 if (carea[i] > bestArea) { bestArea = carea[i]; best = i; }
             }
             if (best < 0) break;

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include "core_bc7.h"
 #include "core_scene.h"
+#include "core_tonemap.h"
 
 namespace prt {
 
@@ -178,6 +179,29 @@ __global__ void k_probe_sample(SceneView sv, uint32_t textureSampler, const floa
     }
     else
         out[i] = tex2D<float4>(s->linear, uv[i].x, uv[i].y);
+}
+
+
+// ---- display transform: tone_map.comp over Output::illumination -> RGBA8 unorm ----
+__global__ void k_decode_rgb9e5(const uint32_t *__restrict__ in, LutTexel *__restrict__ out, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const V3 c = decodeRgb9e5(in[i]);
+    out[i] = LutTexel{c.x, c.y, c.z, 1.f};
+}
+
+// One thread per pixel: 16 B in, 4 B out, eight LUT taps that stay in L1/L2 (the 48^3 table is 1.7 MB decoded).
+// The pass reads the fp16 illumination image in the reference (RtRef.cpp:336-377 blits to R16G16B16A16 first), so
+// the fp32 running mean goes through the same rounding here instead of through a separate blit launch.
+__global__ void k_tone_map(const float4 *__restrict__ accum, ToneLut lut, float exposure, float contrast,
+                           uint32_t *__restrict__ out, uint32_t pixels)
+{
+    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= pixels) return;
+    const float4 c = accum[pix];
+    const V3 color{halfToFloat(floatToHalf(c.x)), halfToFloat(floatToHalf(c.y)), halfToFloat(floatToHalf(c.z))};
+    out[pix] = toneMapPixel(lut, color, exposure, contrast);
 }
 
 } // namespace prt

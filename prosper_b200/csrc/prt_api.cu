@@ -200,6 +200,9 @@ struct prt_ctx
     uint64_t pathCapacity = 0;
     DBuf<float4> accum, sum;
     DBuf<uint2> f16;
+    DBuf<LutTexel> toneLut; // decoded 3D LUT of the display transform (8(f)3)
+    uint32_t toneLutDim = 0;
+    DBuf<uint32_t> ldr;
     DBuf<prt_hit> userHits;
     DBuf<float4> userO, userD;
     DBuf<uint32_t> userSeeds;
@@ -1114,6 +1117,59 @@ extern "C" prt_status prt_read_illumination_f16(prt_ctx *c, void *dstHost, uint6
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(dstHost, c->f16.p, (size_t)pixels * 8, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_set_tone_map_lut(prt_ctx *c, const uint32_t *rgb9e5, uint32_t dim)
+{
+    REQUIRE(c && rgb9e5, "prt_set_tone_map_lut");
+    REQUIRE(dim >= 2 && dim <= 256, "LUT edge must be in [2, 256] (the shipped table is 48)");
+    CK(cudaSetDevice(c->cfg.device));
+    const size_t n = (size_t)dim * dim * dim;
+    DBuf<uint32_t> raw;
+    CK(raw.ensure(n));
+    CK(c->toneLut.ensure(n));
+    CK(cudaMemcpyAsync(raw.p, rgb9e5, n * 4, cudaMemcpyHostToDevice, c->stream));
+    k_decode_rgb9e5<<<blocksFor(n, 256), 256, 0, c->stream>>>(raw.p, c->toneLut.p, (uint32_t)n);
+    c->kernelLaunches++;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(c->stream));
+    raw.release();
+    c->toneLutDim = dim;
+    return PRT_OK;
+}
+
+static prt_status toneMapLaunch(prt_ctx *c, const prt_tone_map_pc *pc, uint32_t &pixels)
+{
+    REQUIRE(c->historyValid, "nothing recorded yet");
+    REQUIRE(c->toneLutDim != 0, "prt_set_tone_map_lut first (ToneMap::init loads it, ToneMap.cpp:37-39)");
+    pixels = c->accumWidth * c->accumHeight;
+    CK(cudaSetDevice(c->cfg.device));
+    CK(c->ldr.ensure(pixels));
+    const ToneLut lut{c->toneLut.p, c->toneLutDim};
+    k_tone_map<<<blocksFor(pixels, 256), 256, 0, c->stream>>>(c->accum.p, lut, pc->exposure, pc->contrast, c->ldr.p, pixels);
+    c->kernelLaunches++;
+    CK(cudaGetLastError());
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_tone_map(prt_ctx *c, const prt_tone_map_pc *pc, void *dstHost, uint64_t dstBytes)
+{
+    REQUIRE(c && pc && dstHost, "prt_tone_map");
+    uint32_t pixels = 0;
+    CKS(toneMapLaunch(c, pc, pixels));
+    REQUIRE(dstBytes >= (uint64_t)pixels * 4, "destination too small");
+    CK(cudaMemcpyAsync(dstHost, c->ldr.p, (size_t)pixels * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_tone_map_device(prt_ctx *c, const prt_tone_map_pc *pc, const uint32_t **out)
+{
+    REQUIRE(c && pc && out, "prt_tone_map_device");
+    uint32_t pixels = 0;
+    CKS(toneMapLaunch(c, pc, pixels));
+    *out = c->ldr.p;
     return PRT_OK;
 }
 

@@ -66,7 +66,7 @@ ABI_SYMBOLS = (
     "prt_build_blas", "prt_build_tlas", "prt_set_draw_instances", "prt_set_instance_transforms", "prt_set_lights",
     "prt_set_camera", "prt_record", "prt_output_f32_device", "prt_read_illumination_f16", "prt_read_output_f32",
     "prt_release_preserved", "prt_trace_primary", "prt_trace_rays", "prt_export_sum_device", "prt_import_sum_device",
-    "prt_export_sum_to_device", "prt_encode_bc7",
+    "prt_export_sum_to_device", "prt_encode_bc7", "prt_set_tone_map_lut", "prt_tone_map", "prt_tone_map_device",
     "prt_get_counters", "prt_reset_counters", "prt_get_timings", "prt_get_bvh_stats", "prt_probe_texture",
     "prt_debug_read_blas", "prt_debug_read_tlas",
 )
@@ -100,6 +100,7 @@ def load_library():
             "prt_read_output_f32": [vp, vp, u64], "prt_release_preserved": [vp], "prt_trace_primary": [vp, vp, u32, u32, vp],
             "prt_trace_rays": [vp, vp, vp, vp, u32, C.c_int, vp], "prt_export_sum_device": [vp, C.POINTER(vp)],
             "prt_import_sum_device": [vp, vp], "prt_export_sum_to_device": [vp, vp],
+            "prt_set_tone_map_lut": [vp, vp, u32], "prt_tone_map": [vp, vp, vp, u64], "prt_tone_map_device": [vp, vp, C.POINTER(vp)],
             "prt_encode_bc7": [vp, vp, u32, u32, vp, u64], "prt_get_counters": [vp, C.POINTER(PrtCounters)], "prt_reset_counters": [vp],
             "prt_get_timings": [vp, C.POINTER(PrtTimings)], "prt_get_bvh_stats": [vp, C.POINTER(PrtBvhStats)],
             "prt_probe_texture": [vp, u32, vp, vp, u32, C.c_int, vp],
@@ -270,6 +271,21 @@ class World:
         _check(self.lib.prt_encode_bc7(self.handle, _p(img), w, h, _p(out), out.nbytes))
         return out
 
+    def set_tone_map_lut(self, lut_rgb9e5: np.ndarray):
+        """ToneMap::init (ToneMap.cpp:31-42): the dim^3 R9G9B9E5 table of tone_map.comp (uint32, x fastest)."""
+        lut = np.ascontiguousarray(lut_rgb9e5, np.uint32).reshape(-1)
+        dim = round(lut.size ** (1.0 / 3.0))
+        if dim ** 3 != lut.size:
+            raise RuntimeError("the tone-map LUT must be a cube")
+        _check(self.lib.prt_set_tone_map_lut(self.handle, _p(lut), dim))
+
+    def tone_map(self, exposure: float, contrast: float) -> np.ndarray:
+        """ToneMap::record (ToneMap.cpp:63-134) over the current illumination -> RGBA8 [h, w, 4]."""
+        pc = np.array([exposure, contrast], np.float32)
+        out = np.zeros(self._accum_pixels * 4, np.uint8)
+        _check(self.lib.prt_tone_map(self.handle, _p(pc), _p(out), out.nbytes))
+        return out
+
     def read_blas(self, model: int):
         """(nodes uint8 [n, 80], tris uint8 [t, 48]) of the BLAS of `model` (test hook)."""
         nn, nt = C.c_uint32(), C.c_uint32()
@@ -397,3 +413,32 @@ class RtReference:
     def releasePreserved(self, world: World):
         _check(world.lib.prt_release_preserved(world.handle))  # RtRef.cpp:385-391
         self.m_accumulationDirty = True
+
+
+class ToneMap:
+    """render::ToneMap (src/render/ToneMap.hpp, ToneMap.cpp): the display transform after the path tracer."""
+
+    def __init__(self):
+        self.m_initialized = False
+        self.m_exposure = 1.0  # ToneMap.hpp defaults, push_constants/tone_map.h
+        self.m_contrast = 1.0
+
+    def init(self, world: World, lut_rgb9e5: np.ndarray):
+        """ToneMap.cpp:31-42; `lut_rgb9e5` is the payload of res/texture/tony_mc_mapface.dds (tonemap.read_lut_dds)."""
+        if self.m_initialized:
+            raise RuntimeError("ToneMap::init called twice")
+        world.set_tone_map_lut(lut_rgb9e5)
+        self.m_initialized = True
+
+    def drawUi(self, exposure=None, contrast=None):
+        """ToneMap.cpp:54-60: both sliders are clamped to [0.001, 10000]."""
+        if exposure is not None:
+            self.m_exposure = min(max(float(exposure), 0.001), 10000.0)
+        if contrast is not None:
+            self.m_contrast = min(max(float(contrast), 0.001), 10000.0)
+
+    def record(self, world: World, inColor: Output) -> np.ndarray:
+        """ToneMap.cpp:63-134: returns Output::toneMapped as RGBA8 [h, w, 4]."""
+        if not self.m_initialized:
+            raise RuntimeError("ToneMap::record before init")
+        return world.tone_map(self.m_exposure, self.m_contrast).reshape(inColor.height, inColor.width, 4)
