@@ -73,6 +73,15 @@ prt_status prt_set_texture(prt_ctx *ctx, uint32_t index, const prt_texture_desc 
 prt_status prt_encode_bc7(prt_ctx *ctx, const void *rgba8, uint32_t width, uint32_t height, void *blocksOut,
                           uint64_t blocksBytes);
 
+/* Texture-cache build, the whole chain of `compress` (Texture.cpp:213-296) on the GPU: RGBA8 level 0 (HOST) -> mip
+ * levels (generateMipLevels, 165-211; 2x2 box, colour in linear light when colorSpace == 0 = sRGB, 1 = linear) ->
+ * BC7 blocks per level, or plain RGBA8 levels when a kept level is not whole 4x4 blocks (229-237). Levels are the
+ * full chain minus the last two (217-225). dataOut (HOST) receives the levels back to back exactly as utils::Dds::data
+ * holds them (Dds.cpp:95-133), so writeDds / prosper_b200.dds.write_dds can store it unchanged. */
+prt_status prt_compress_texture(prt_ctx *ctx, const void *rgba8, uint32_t width, uint32_t height, uint32_t colorSpace,
+                                uint32_t generateMipMaps, void *dataOut, uint64_t dataBytes, uint32_t *formatOut,
+                                uint32_t *mipLevelCountOut);
+
 /* Display transform (render::ToneMap, src/render/ToneMap.cpp + res/shader/tone_map.comp).
  * prt_set_tone_map_lut = ToneMap::init (ToneMap.cpp:31-42): the dim^3 3D table in DXGI R9G9B9E5_SHAREDEXP texels, x
  * fastest -- the payload of res/texture/tony_mc_mapface.dds (dim 48) as it lies in the file; HOST memory.

@@ -204,4 +204,48 @@ __global__ void k_tone_map(const float4 *__restrict__ accum, ToneLut lut, float 
     out[pix] = toneMapPixel(lut, color, exposure, contrast);
 }
 
+// ---- texture-cache build: the mip chain of generateMipLevels (Texture.cpp:165-211) ----
+// One thread per destination texel: 2x2 box over the parent level (edge-clamped for odd parents), colour averaged in
+// linear light when the texture is sRGB (stbir_resize_uint8_srgb's colour handling; alpha is always linear), back to 8
+// bits by searching the midpoint table -- table lookups and three additions in a fixed order, so the result is
+// bit-identical to the numpy restatement the tests hold. toLinear[256], midpoints[255] (midpoints[b] = the linear value
+// halfway between codes b and b+1).
+__device__ __forceinline__ uint32_t boxEncode(float v, const float *__restrict__ midpoints)
+{
+    uint32_t lo = 0, hi = 255; // smallest b with v < midpoints[b], or 255
+    while (lo < hi)
+    {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (v < midpoints[mid]) hi = mid;
+        else lo = mid + 1;
+    }
+    return lo;
+}
+__global__ void k_downsample_box(const uint32_t *__restrict__ src, uint32_t sw, uint32_t sh, uint32_t *__restrict__ dst,
+                                 uint32_t dw, uint32_t dh, const float *__restrict__ toLinear,
+                                 const float *__restrict__ midpoints, const float *__restrict__ alphaMidpoints, int srgb)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= dw * dh) return;
+    const uint32_t x = i % dw, y = i / dw;
+    const uint32_t x0 = min(2 * x, sw - 1), x1 = min(2 * x + 1, sw - 1), y0 = min(2 * y, sh - 1), y1 = min(2 * y + 1, sh - 1);
+    const uint32_t t[4] = {src[y0 * sw + x0], src[y0 * sw + x1], src[y1 * sw + x0], src[y1 * sw + x1]};
+    uint32_t out = 0;
+#pragma unroll
+    for (int ch = 0; ch < 4; ++ch)
+    {
+        const bool lin = !srgb || ch == 3;
+        float v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+        {
+            const uint32_t b = (t[k] >> (8 * ch)) & 0xFFu;
+            v[k] = lin ? (float)b : toLinear[b];
+        }
+        const float mean = __fmul_rn(__fadd_rn(__fadd_rn(v[0], v[1]), __fadd_rn(v[2], v[3])), 0.25f);
+        out |= boxEncode(mean, lin ? alphaMidpoints : midpoints) << (8 * ch);
+    }
+    dst[i] = out;
+}
+
 } // namespace prt

@@ -203,6 +203,7 @@ struct prt_ctx
     DBuf<LutTexel> toneLut; // decoded 3D LUT of the display transform (8(f)3)
     uint32_t toneLutDim = 0;
     DBuf<uint32_t> ldr;
+    DBuf<float> mipTables; // sRGB decode [256], sRGB midpoints [255], linear midpoints [255] (8(f)1 mip chain)
     DBuf<prt_hit> userHits;
     DBuf<float4> userO, userD;
     DBuf<uint32_t> userSeeds;
@@ -571,6 +572,82 @@ extern "C" prt_status prt_encode_bc7(prt_ctx *c, const void *rgba8, uint32_t wid
     CK(cudaStreamSynchronize(c->stream));
     src.release();
     dst.release();
+    return PRT_OK;
+}
+
+// getMipCount (Utils.hpp:144-148)
+static uint32_t mipCountFor(uint32_t maxDimension) { uint32_t n = 0; while (maxDimension) { n++; maxDimension >>= 1; } return n; }
+
+extern "C" prt_status prt_compress_texture(prt_ctx *c, const void *rgba8, uint32_t width, uint32_t height, uint32_t colorSpace,
+                                           uint32_t generateMipMaps, void *dataOut, uint64_t dataBytes, uint32_t *formatOut,
+                                           uint32_t *mipLevelCountOut)
+{
+    REQUIRE(c && rgba8 && dataOut && formatOut && mipLevelCountOut, "prt_compress_texture");
+    REQUIRE(width > 0 && height > 0 && width <= 16384 && height <= 16384, "texture extent out of range");
+    REQUIRE(colorSpace <= 1, "colorSpace is 0 (sRGB) or 1 (linear), TextureColorSpace in Texture.hpp");
+    // Texture.cpp:217-237: full chain minus the 2x2 and 1x1 levels; BC7 only when every kept level is whole 4x4 blocks
+    const uint32_t full = generateMipMaps ? mipCountFor(std::max(width, height)) : 1u;
+    const uint32_t levels = full > 2 ? full - 2 : 1u;
+    bool bc7 = true;
+    for (uint32_t i = 0; i < levels; ++i)
+        if ((std::max(width >> i, 1u) % 4) != 0 || (std::max(height >> i, 1u) % 4) != 0) bc7 = false;
+    std::vector<uint64_t> rawOff(levels), outOff(levels);
+    uint64_t rawTexels = 0, outBytes = 0;
+    for (uint32_t i = 0; i < levels; ++i)
+    {
+        const uint64_t w = std::max(width >> i, 1u), h = std::max(height >> i, 1u);
+        rawOff[i] = rawTexels;
+        outOff[i] = outBytes;
+        rawTexels += w * h;
+        outBytes += bc7 ? (w / 4) * (h / 4) * 16 : w * h * 4; // Dds::Dds, Dds.cpp:95-133
+    }
+    REQUIRE(dataBytes >= outBytes, "destination too small for the level chain");
+    CK(cudaSetDevice(c->cfg.device));
+    if (c->mipTables.cap == 0)
+    {
+        // sRGB decode table and the midpoints between neighbouring codes, in double then rounded once
+        std::vector<float> t(256 + 255 + 255);
+        auto lin = [](double s) { return s <= 0.04045 ? s / 12.92 : std::pow((s + 0.055) / 1.055, 2.4); };
+        for (int b = 0; b < 256; ++b) t[b] = (float)lin(b / 255.0);
+        for (int b = 0; b < 255; ++b) t[256 + b] = (float)lin((b + 0.5) / 255.0);
+        for (int b = 0; b < 255; ++b) t[511 + b] = (float)b + 0.5f;
+        CK(c->mipTables.ensure(t.size()));
+        CK(cudaMemcpyAsync(c->mipTables.p, t.data(), t.size() * 4, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+    }
+    DBuf<uint32_t> raw;
+    DBuf<uint2> blocks;
+    CK(raw.ensure(rawTexels));
+    if (bc7)
+    {
+        CK(blocks.ensure(outBytes / 8));
+    }
+    CK(cudaMemcpyAsync(raw.p, rgba8, (size_t)width * height * 4, cudaMemcpyHostToDevice, c->stream));
+    for (uint32_t i = 0; i < levels; ++i)
+    {
+        const uint32_t w = std::max(width >> i, 1u), h = std::max(height >> i, 1u);
+        if (i > 0)
+        {
+            const uint32_t pw = std::max(width >> (i - 1), 1u), ph = std::max(height >> (i - 1), 1u);
+            k_downsample_box<<<blocksFor((size_t)w * h, 256), 256, 0, c->stream>>>(
+                raw.p + rawOff[i - 1], pw, ph, raw.p + rawOff[i], w, h, c->mipTables.p, c->mipTables.p + 256,
+                c->mipTables.p + 511, colorSpace == 0);
+            c->kernelLaunches++;
+        }
+        if (bc7)
+        {
+            const size_t nBlocks = (size_t)(w / 4) * (h / 4);
+            k_bc7_encode_mode6<<<blocksFor(nBlocks, 64), 64, 0, c->stream>>>(raw.p + rawOff[i], w, h, blocks.p + outOff[i] / 8);
+            c->kernelLaunches++;
+        }
+    }
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dataOut, bc7 ? (const void *)blocks.p : (const void *)raw.p, outBytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    raw.release();
+    blocks.release();
+    *formatOut = bc7 ? PRT_TEX_BC7_UNORM : PRT_TEX_RGBA8_UNORM;
+    *mipLevelCountOut = levels;
     return PRT_OK;
 }
 

@@ -66,7 +66,7 @@ ABI_SYMBOLS = (
     "prt_build_blas", "prt_build_tlas", "prt_set_draw_instances", "prt_set_instance_transforms", "prt_set_lights",
     "prt_set_camera", "prt_record", "prt_output_f32_device", "prt_read_illumination_f16", "prt_read_output_f32",
     "prt_release_preserved", "prt_trace_primary", "prt_trace_rays", "prt_export_sum_device", "prt_import_sum_device",
-    "prt_export_sum_to_device", "prt_encode_bc7", "prt_set_tone_map_lut", "prt_tone_map", "prt_tone_map_device",
+    "prt_export_sum_to_device", "prt_encode_bc7", "prt_compress_texture", "prt_set_tone_map_lut", "prt_tone_map", "prt_tone_map_device",
     "prt_get_counters", "prt_reset_counters", "prt_get_timings", "prt_get_bvh_stats", "prt_probe_texture",
     "prt_debug_read_blas", "prt_debug_read_tlas",
 )
@@ -100,6 +100,7 @@ def load_library():
             "prt_read_output_f32": [vp, vp, u64], "prt_release_preserved": [vp], "prt_trace_primary": [vp, vp, u32, u32, vp],
             "prt_trace_rays": [vp, vp, vp, vp, u32, C.c_int, vp], "prt_export_sum_device": [vp, C.POINTER(vp)],
             "prt_import_sum_device": [vp, vp], "prt_export_sum_to_device": [vp, vp],
+            "prt_compress_texture": [vp, vp, u32, u32, u32, u32, vp, u64, C.POINTER(u32), C.POINTER(u32)],
             "prt_set_tone_map_lut": [vp, vp, u32], "prt_tone_map": [vp, vp, vp, u64], "prt_tone_map_device": [vp, vp, C.POINTER(vp)],
             "prt_encode_bc7": [vp, vp, u32, u32, vp, u64], "prt_get_counters": [vp, C.POINTER(PrtCounters)], "prt_reset_counters": [vp],
             "prt_get_timings": [vp, C.POINTER(PrtTimings)], "prt_get_bvh_stats": [vp, C.POINTER(PrtBvhStats)],

@@ -1,7 +1,5 @@
 """Host helpers of the display transform: the R9G9B9E5 3D LUT that render::ToneMap loads from
 res/texture/tony_mc_mapface.dds (ToneMap.cpp:37-39) and a stand-in table for machines without the asset."""
-import struct
-
 import numpy as np
 
 DXGI_FORMAT_R9G9B9E5_SHAREDEXP = 67
@@ -42,17 +40,12 @@ def stand_in_lut(dim: int = 48) -> np.ndarray:
 
 
 def read_lut_dds(path: str) -> np.ndarray:
-    """The payload of a DX10-header volume .dds in R9G9B9E5 (res/texture/tony_mc_mapface.dds): uint32 [d*h*w]."""
-    with open(path, "rb") as f:
-        data = f.read()
-    if data[:4] != b"DDS " or data[84:88] != b"DX10":
-        raise RuntimeError("not a DX10 .dds")
-    height, width = struct.unpack_from("<II", data, 12)
-    depth = struct.unpack_from("<I", data, 24)[0]
-    if struct.unpack_from("<I", data, 128)[0] != DXGI_FORMAT_R9G9B9E5_SHAREDEXP:
-        raise RuntimeError("the LUT must be DXGI_FORMAT_R9G9B9E5_SHAREDEXP")
-    n = width * height * max(depth, 1)
-    return np.frombuffer(data, np.uint32, n, 148).copy()
+    """The payload of the volume .dds render::ToneMap loads (res/texture/tony_mc_mapface.dds): uint32 [d*h*w]."""
+    from . import dds
+    d = dds.read_dds(path)
+    if d.format != dds.FORMAT_R9G9B9E5_SHAREDEXP or not (d.width == d.height == d.depth):
+        raise RuntimeError("the LUT must be a cubic DXGI_FORMAT_R9G9B9E5_SHAREDEXP volume")
+    return d.data.view(np.uint32).copy()
 
 
 def write_ppm(path: str, rgba8: np.ndarray):

@@ -10,6 +10,10 @@ import pytest
 import oracle
 from prosper_b200 import tonemap
 
+TONY_DDS_HEADER = (
+    "444453207c0000000f1080003000000030000000c00000003000000001000000" + "00" * 44 +
+    "2000000004000000445831300000000000000000000000000000000000000000" +
+    "0810000000002000000000000000000000000000" + "4300000004000000000000000100000000000000")
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "tonemap_tony.json")
 
 
@@ -85,15 +89,8 @@ def test_stand_in_lut_is_monotone_on_greys_and_dds_reader(tmp_path):
     rgb = tonemap.unpack_rgb9e5(lut).reshape(48, 48, 48, 3)
     diag = rgb[np.arange(48), np.arange(48), np.arange(48)]
     assert (np.diff(diag[:, 0]) >= 0).all() and diag[0].max() == 0 and diag[-1].min() > 0.95
-    # a DX10 volume .dds with the header fields read_lut_dds looks at (DDS.cpp-style layout: 4 + 124 + 20 bytes)
-    import struct
-    hdr = bytearray(148)
-    hdr[0:4] = b"DDS "
-    struct.pack_into("<I", hdr, 4, 124)
-    struct.pack_into("<II", hdr, 12, 48, 48)
-    struct.pack_into("<I", hdr, 24, 48)
-    hdr[84:88] = b"DX10"
-    struct.pack_into("<I", hdr, 128, tonemap.DXGI_FORMAT_R9G9B9E5_SHAREDEXP)
+    # the 148 header bytes of the reference's res/texture/tony_mc_mapface.dds (48^3 volume, DXGI format 67)
+    hdr = bytes.fromhex(TONY_DDS_HEADER)
     path = tmp_path / "lut.dds"
     path.write_bytes(bytes(hdr) + lut.tobytes())
     assert np.array_equal(tonemap.read_lut_dds(str(path)), lut)
