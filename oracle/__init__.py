@@ -237,3 +237,31 @@ def decode_rgb9e5(texel: int) -> np.ndarray:
     out = np.zeros(3, np.float32)
     lib().orc_decode_rgb9e5(int(texel), _p(out))
     return out
+
+
+_REF_STBIR = os.path.join(_HERE, "_ref", "libstbir.so")
+
+
+def build_ref() -> str:
+    """oracle/_ref/libstbir.so from the reference's vendored stb header (only where /root/reference exists; the
+    prebuilt file travels to the GPU box). Returns the path, or "" when neither the sources nor a prebuilt file exist."""
+    if os.path.exists("/root/reference/ext/stb/stb_image_resize2.h"):
+        src_time = os.path.getmtime(os.path.join(_HERE, "ref_stbir.c"))
+        if not os.path.exists(_REF_STBIR) or os.path.getmtime(_REF_STBIR) < src_time:
+            subprocess.run(["make", "-C", _HERE, "-B", "_ref/libstbir.so"], check=True, capture_output=True)
+    return _REF_STBIR if os.path.exists(_REF_STBIR) else ""
+
+
+def ref_stbir_resize(img: np.ndarray, out_w: int, out_h: int, srgb: bool) -> np.ndarray:
+    """The reference's own mip filter (stbir_resize_uint8_srgb / _linear, Texture.cpp:193-208) on an RGBA8 image."""
+    path = build_ref()
+    if not path:
+        raise FileNotFoundError("oracle/_ref/libstbir.so is not built")
+    l = C.CDLL(path)
+    l.ref_stbir_resize.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
+    src = np.ascontiguousarray(img, np.uint8)
+    h, w, ch = src.shape
+    out = np.zeros((out_h, out_w, ch), np.uint8)
+    if not l.ref_stbir_resize(_p(src), w, h, _p(out), out_w, out_h, ch, int(srgb)):
+        raise RuntimeError("stbir_resize failed")
+    return out

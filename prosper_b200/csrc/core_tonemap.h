@@ -54,12 +54,10 @@ HD V3 decodeRgb9e5(uint32_t v)
     return V3{(float)(v & 0x1FFu) * scale, (float)((v >> 9) & 0x1FFu) * scale, (float)((v >> 18) & 0x1FFu) * scale};
 }
 
-struct alignas(16) LutTexel { float x, y, z, w; };
-
 struct ToneLut
 {
-    const LutTexel *texels; // dim^3, x fastest, decoded at upload
-    uint32_t dim;
+    const uint32_t *texels; // dim^3 R9G9B9E5 words, x fastest: kept packed (442 KB for 48^3) so the eight taps of a pixel
+    uint32_t dim;           // mostly hit L1; the decode is three conversions and exact
 };
 
 // textureLod(sampler3D, uv, 0) with a linear clamp-to-edge sampler (ToneMap.cpp:95-98): unnormalised
@@ -85,7 +83,7 @@ HD V3 sampleLutTrilinear(const ToneLut &lut, V3 uv)
     {
         const int x = (k & 1) ? i1[0] : i0[0], y = (k & 2) ? i1[1] : i0[1], z = (k & 4) ? i1[2] : i0[2];
         const float wt = ((k & 1) ? w[0] : 1.f - w[0]) * ((k & 2) ? w[1] : 1.f - w[1]) * ((k & 4) ? w[2] : 1.f - w[2]);
-        const LutTexel t = lut.texels[((size_t)z * dim + y) * dim + x];
+        const V3 t = decodeRgb9e5(lut.texels[((size_t)z * dim + y) * dim + x]);
         acc.x += wt * t.x;
         acc.y += wt * t.y;
         acc.z += wt * t.z;
@@ -115,7 +113,7 @@ HD uint32_t toneMapPixel(const ToneLut &lut, V3 color, float exposure, float con
 {
     color = V3{color.x * exposure, color.y * exposure, color.z * exposure};
     V3 hsv = rgbToHsv(color);
-    hsv.z = powf(hsv.z, contrast);
+    if (contrast != 1.f) hsv.z = powf(hsv.z, contrast); // pow(x, 1) == x exactly
     color = tonyMcMapface(lut, hsvToRgb(hsv));
     const float g = 1.f / 2.2f;
     return toUnorm8(powf(color.x, g)) | (toUnorm8(powf(color.y, g)) << 8) | (toUnorm8(powf(color.z, g)) << 16) | 0xFF000000u;

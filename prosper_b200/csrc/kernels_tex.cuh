@@ -183,15 +183,7 @@ __global__ void k_probe_sample(SceneView sv, uint32_t textureSampler, const floa
 
 
 // ---- display transform: tone_map.comp over Output::illumination -> RGBA8 unorm ----
-__global__ void k_decode_rgb9e5(const uint32_t *__restrict__ in, LutTexel *__restrict__ out, uint32_t n)
-{
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const V3 c = decodeRgb9e5(in[i]);
-    out[i] = LutTexel{c.x, c.y, c.z, 1.f};
-}
-
-// One thread per pixel: 16 B in, 4 B out, eight LUT taps that stay in L1/L2 (the 48^3 table is 1.7 MB decoded).
+// One thread per pixel: 16 B in, 4 B out, eight LUT taps that stay in L1/L2 (the 48^3 table is 442 KB packed).
 // The pass reads the fp16 illumination image in the reference (RtRef.cpp:336-377 blits to R16G16B16A16 first), so
 // the fp32 running mean goes through the same rounding here instead of through a separate blit launch.
 __global__ void k_tone_map(const float4 *__restrict__ accum, ToneLut lut, float exposure, float contrast,
@@ -205,14 +197,21 @@ __global__ void k_tone_map(const float4 *__restrict__ accum, ToneLut lut, float 
 }
 
 // ---- texture-cache build: the mip chain of generateMipLevels (Texture.cpp:165-211) ----
-// One thread per destination texel: 2x2 box over the parent level (edge-clamped for odd parents), colour averaged in
-// linear light when the texture is sRGB (stbir_resize_uint8_srgb's colour handling; alpha is always linear), back to 8
-// bits by searching the midpoint table -- table lookups and three additions in a fixed order, so the result is
-// bit-identical to the numpy restatement the tests hold. toLinear[256], midpoints[255] (midpoints[b] = the linear value
-// halfway between codes b and b+1).
-__device__ __forceinline__ uint32_t boxEncode(float v, const float *__restrict__ midpoints)
+// What stbir_resize_uint8_srgb / _linear (ext/stb/stb_image_resize2.h, the reference's call at Texture.cpp:193-208) do for
+// an exact 2:1 reduction of an RGBA image with default settings: decode (sRGB table for colour, /255 for alpha or for
+// linear textures), "fancy" alpha weighting (filter R G B A and R*A G*A B*A, divide the weighted colour by the filtered
+// alpha unless it is ~0), the default downsampling filter = Mitchell-Netravali B=C=1/3 stretched by 2, i.e. eight fixed
+// taps per axis at +-0.25, 0.75, 1.25, 1.75 (normalised), clamped edges, re-encode to 8 bits. One thread per destination
+// texel; every operation is a single rounding in a fixed order (tables, __fmul_rn/__fadd_rn/__fdiv_rn), so the result
+// is bit-identical to the numpy restatement in prosper_b200/texture_cache.py, which tests pin against the real stb code.
+// tables: decode colour [256], decode linear [256], colour midpoints [255], linear midpoints [255], taps [8].
+struct MipTables
 {
-    uint32_t lo = 0, hi = 255; // smallest b with v < midpoints[b], or 255
+    const float *colour, *linear, *colourMid, *linearMid, *taps;
+};
+__device__ __forceinline__ uint32_t mipEncode(float v, const float *__restrict__ midpoints)
+{
+    uint32_t lo = 0, hi = 255; // number of midpoints <= v
     while (lo < hi)
     {
         const uint32_t mid = (lo + hi) >> 1;
@@ -221,31 +220,50 @@ __device__ __forceinline__ uint32_t boxEncode(float v, const float *__restrict__
     }
     return lo;
 }
-__global__ void k_downsample_box(const uint32_t *__restrict__ src, uint32_t sw, uint32_t sh, uint32_t *__restrict__ dst,
-                                 uint32_t dw, uint32_t dh, const float *__restrict__ toLinear,
-                                 const float *__restrict__ midpoints, const float *__restrict__ alphaMidpoints, int srgb)
+__global__ void k_downsample_mitchell(const uint32_t *__restrict__ src, int sw, int sh, uint32_t *__restrict__ dst, int dw,
+                                      int dh, MipTables tb)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= dw * dh) return;
-    const uint32_t x = i % dw, y = i / dw;
-    const uint32_t x0 = min(2 * x, sw - 1), x1 = min(2 * x + 1, sw - 1), y0 = min(2 * y, sh - 1), y1 = min(2 * y + 1, sh - 1);
-    const uint32_t t[4] = {src[y0 * sw + x0], src[y0 * sw + x1], src[y1 * sw + x0], src[y1 * sw + x1]};
-    uint32_t out = 0;
-#pragma unroll
-    for (int ch = 0; ch < 4; ++ch)
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= dw * dh) return;
+    const int dx = idx % dw, dy = idx / dw;
+    float acc[7];
+#pragma unroll 1
+    for (int j = 0; j < 8; ++j)
     {
-        const bool lin = !srgb || ch == 3;
-        float v[4];
+        const int y = min(max(2 * dy - 3 + j, 0), sh - 1);
+        float h[7];
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
+        for (int i = 0; i < 8; ++i)
         {
-            const uint32_t b = (t[k] >> (8 * ch)) & 0xFFu;
-            v[k] = lin ? (float)b : toLinear[b];
+            const int x = min(max(2 * dx - 3 + i, 0), sw - 1);
+            const uint32_t t = src[(size_t)y * sw + x];
+            float v[7];
+            v[0] = tb.colour[t & 0xFFu];
+            v[1] = tb.colour[(t >> 8) & 0xFFu];
+            v[2] = tb.colour[(t >> 16) & 0xFFu];
+            v[3] = tb.linear[t >> 24];
+            v[4] = __fmul_rn(v[0], v[3]);
+            v[5] = __fmul_rn(v[1], v[3]);
+            v[6] = __fmul_rn(v[2], v[3]);
+            const float w = tb.taps[i];
+#pragma unroll
+            for (int c = 0; c < 7; ++c) h[c] = i == 0 ? __fmul_rn(w, v[c]) : __fadd_rn(h[c], __fmul_rn(w, v[c]));
         }
-        const float mean = __fmul_rn(__fadd_rn(__fadd_rn(v[0], v[1]), __fadd_rn(v[2], v[3])), 0.25f);
-        out |= boxEncode(mean, lin ? alphaMidpoints : midpoints) << (8 * ch);
+        const float w = tb.taps[j];
+#pragma unroll
+        for (int c = 0; c < 7; ++c) acc[c] = j == 0 ? __fmul_rn(w, h[c]) : __fadd_rn(acc[c], __fmul_rn(w, h[c]));
     }
-    dst[i] = out;
+    const float alpha = acc[3];
+    float rgb[3] = {acc[0], acc[1], acc[2]};
+    if (!(alpha < 7.52316385e-37f)) // stbir__small_float = 2^-120
+    {
+        const float ia = __fdiv_rn(1.0f, alpha);
+        rgb[0] = __fmul_rn(acc[4], ia);
+        rgb[1] = __fmul_rn(acc[5], ia);
+        rgb[2] = __fmul_rn(acc[6], ia);
+    }
+    dst[idx] = mipEncode(rgb[0], tb.colourMid) | (mipEncode(rgb[1], tb.colourMid) << 8) | (mipEncode(rgb[2], tb.colourMid) << 16) |
+               (mipEncode(alpha, tb.linearMid) << 24);
 }
 
 } // namespace prt

@@ -200,10 +200,10 @@ struct prt_ctx
     uint64_t pathCapacity = 0;
     DBuf<float4> accum, sum;
     DBuf<uint2> f16;
-    DBuf<LutTexel> toneLut; // decoded 3D LUT of the display transform (8(f)3)
+    DBuf<uint32_t> toneLut; // R9G9B9E5 3D LUT of the display transform (8(f)3)
     uint32_t toneLutDim = 0;
     DBuf<uint32_t> ldr;
-    DBuf<float> mipTables; // sRGB decode [256], sRGB midpoints [255], linear midpoints [255] (8(f)1 mip chain)
+    DBuf<float> mipTables; // decode tables, code midpoints and filter taps of the mip chain (8(f)1)
     DBuf<prt_hit> userHits;
     DBuf<float4> userO, userD;
     DBuf<uint32_t> userSeeds;
@@ -605,12 +605,18 @@ extern "C" prt_status prt_compress_texture(prt_ctx *c, const void *rgba8, uint32
     CK(cudaSetDevice(c->cfg.device));
     if (c->mipTables.cap == 0)
     {
-        // sRGB decode table and the midpoints between neighbouring codes, in double then rounded once
-        std::vector<float> t(256 + 255 + 255);
+        // decode tables, the midpoints between neighbouring codes and the eight filter taps, each computed in double and
+        // rounded once: [0,256) sRGB->linear, [256,512) b/255, [512,767) sRGB midpoints, [768,1023) linear midpoints,
+        // [1024,1032) Mitchell(B=C=1/3) at 1.75 1.25 0.75 0.25 | 0.25 ... 1.75, normalised
+        std::vector<float> t(1032, 0.f);
         auto lin = [](double s) { return s <= 0.04045 ? s / 12.92 : std::pow((s + 0.055) / 1.055, 2.4); };
-        for (int b = 0; b < 256; ++b) t[b] = (float)lin(b / 255.0);
-        for (int b = 0; b < 255; ++b) t[256 + b] = (float)lin((b + 0.5) / 255.0);
-        for (int b = 0; b < 255; ++b) t[511 + b] = (float)b + 0.5f;
+        auto mitchell = [](double x) { return x < 1.0 ? (16.0 + x * x * (21.0 * x - 36.0)) / 18.0 : (32.0 + x * (-60.0 + x * (36.0 - 7.0 * x))) / 18.0; };
+        for (int b = 0; b < 256; ++b) t[b] = (float)lin(b / 255.0), t[256 + b] = (float)(b / 255.0);
+        for (int b = 0; b < 255; ++b) t[512 + b] = (float)lin((b + 0.5) / 255.0), t[768 + b] = (float)((b + 0.5) / 255.0);
+        const double d[8] = {1.75, 1.25, 0.75, 0.25, 0.25, 0.75, 1.25, 1.75};
+        double sum = 0;
+        for (double x : d) sum += mitchell(x);
+        for (int k = 0; k < 8; ++k) t[1024 + k] = (float)(mitchell(d[k]) / sum);
         CK(c->mipTables.ensure(t.size()));
         CK(cudaMemcpyAsync(c->mipTables.p, t.data(), t.size() * 4, cudaMemcpyHostToDevice, c->stream));
         CK(cudaStreamSynchronize(c->stream));
@@ -629,9 +635,11 @@ extern "C" prt_status prt_compress_texture(prt_ctx *c, const void *rgba8, uint32
         if (i > 0)
         {
             const uint32_t pw = std::max(width >> (i - 1), 1u), ph = std::max(height >> (i - 1), 1u);
-            k_downsample_box<<<blocksFor((size_t)w * h, 256), 256, 0, c->stream>>>(
-                raw.p + rawOff[i - 1], pw, ph, raw.p + rawOff[i], w, h, c->mipTables.p, c->mipTables.p + 256,
-                c->mipTables.p + 511, colorSpace == 0);
+            const float *tp = c->mipTables.p;
+            const bool srgb = colorSpace == 0;
+            const MipTables tb{srgb ? tp : tp + 256, tp + 256, srgb ? tp + 512 : tp + 768, tp + 768, tp + 1024};
+            k_downsample_mitchell<<<blocksFor((size_t)w * h, 128), 128, 0, c->stream>>>(raw.p + rawOff[i - 1], (int)pw, (int)ph,
+                                                                                       raw.p + rawOff[i], (int)w, (int)h, tb);
             c->kernelLaunches++;
         }
         if (bc7)
@@ -1203,15 +1211,9 @@ extern "C" prt_status prt_set_tone_map_lut(prt_ctx *c, const uint32_t *rgb9e5, u
     REQUIRE(dim >= 2 && dim <= 256, "LUT edge must be in [2, 256] (the shipped table is 48)");
     CK(cudaSetDevice(c->cfg.device));
     const size_t n = (size_t)dim * dim * dim;
-    DBuf<uint32_t> raw;
-    CK(raw.ensure(n));
     CK(c->toneLut.ensure(n));
-    CK(cudaMemcpyAsync(raw.p, rgb9e5, n * 4, cudaMemcpyHostToDevice, c->stream));
-    k_decode_rgb9e5<<<blocksFor(n, 256), 256, 0, c->stream>>>(raw.p, c->toneLut.p, (uint32_t)n);
-    c->kernelLaunches++;
-    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(c->toneLut.p, rgb9e5, n * 4, cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));
-    raw.release();
     c->toneLutDim = dim;
     return PRT_OK;
 }

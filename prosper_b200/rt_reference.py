@@ -287,6 +287,13 @@ class World:
         _check(self.lib.prt_tone_map(self.handle, _p(pc), _p(out), out.nbytes))
         return out
 
+    def tone_map_device(self, exposure: float, contrast: float) -> int:
+        """Same pass, result left on the GPU: device pointer of the RGBA8 image (stream-ordered, not synchronised)."""
+        pc = np.array([exposure, contrast], np.float32)
+        out = C.c_void_p()
+        _check(self.lib.prt_tone_map_device(self.handle, _p(pc), C.byref(out)))
+        return int(out.value)
+
     def read_blas(self, model: int):
         """(nodes uint8 [n, 80], tris uint8 [t, 48]) of the BLAS of `model` (test hook)."""
         nn, nt = C.c_uint32(), C.c_uint32()

@@ -50,26 +50,56 @@ def compress_to_file(world: "rt.World", target_path: str, rgba8: np.ndarray, col
     return out
 
 
-# ---- numpy restatement of the mip filter, for the tests (same tables, same operation order as k_downsample_box) ----
+# ---- numpy restatement of the mip filter: what k_downsample_mitchell computes, operation for operation --------------
+# (stbir_resize_uint8_srgb / _linear for an exact 2:1 reduction of RGBA, default settings; ext/stb/stb_image_resize2.h:
+# default downsampling filter Mitchell, :876-877; "fancy" alpha weighting, :6784-6797, 4008-4215; edge clamp.)
 def _srgb_to_linear(s):
     s = np.asarray(s, np.float64)
     return np.where(s <= 0.04045, s / 12.92, ((s + 0.055) / 1.055) ** 2.4)
 
 
-def downsample_box(level: np.ndarray, srgb: bool) -> np.ndarray:
+def _mitchell(x):
+    return (16.0 + x * x * (21.0 * x - 36.0)) / 18.0 if x < 1.0 else (32.0 + x * (-60.0 + x * (36.0 - 7.0 * x))) / 18.0
+
+
+def mip_tables():
+    d = [1.75, 1.25, 0.75, 0.25, 0.25, 0.75, 1.25, 1.75]
+    taps = np.array([_mitchell(x) for x in d], np.float64)
+    codes = np.arange(256) / 255.0
+    mids = (np.arange(255) + 0.5) / 255.0
+    return {"colour": _srgb_to_linear(codes).astype(np.float32), "linear": codes.astype(np.float32),
+            "colourMid": _srgb_to_linear(mids).astype(np.float32), "linearMid": mids.astype(np.float32),
+            "taps": (taps / taps.sum()).astype(np.float32)}
+
+
+def downsample_mitchell(level: np.ndarray, srgb: bool) -> np.ndarray:
+    """RGBA8 [h, w, 4] -> [max(h/2,1), max(w/2,1), 4]; float32 throughout, one rounding per operation, the same order as
+    the kernel (horizontal taps left to right, then vertical taps top to bottom)."""
+    tb = mip_tables()
     h, w, _ = level.shape
     dw, dh = max(w >> 1, 1), max(h >> 1, 1)
-    xs0, xs1 = np.minimum(2 * np.arange(dw), w - 1), np.minimum(2 * np.arange(dw) + 1, w - 1)
-    ys0, ys1 = np.minimum(2 * np.arange(dh), h - 1), np.minimum(2 * np.arange(dh) + 1, h - 1)
-    to_linear = _srgb_to_linear(np.arange(256) / 255.0).astype(np.float32)
-    mid_srgb = _srgb_to_linear((np.arange(255) + 0.5) / 255.0).astype(np.float32)
-    mid_lin = (np.arange(255) + 0.5).astype(np.float32)
+    dec = tb["colour"] if srgb else tb["linear"]
+    a = tb["linear"][level[..., 3]]
+    rgb = dec[level[..., :3]]
+    v = np.concatenate([rgb, a[..., None], rgb * a[..., None]], axis=-1).astype(np.float32)  # R G B A Rpm Gpm Bpm
+    taps = tb["taps"]
+    hacc = None
+    for i in range(8):
+        xs = np.clip(2 * np.arange(dw) - 3 + i, 0, w - 1)
+        term = taps[i] * v[:, xs]
+        hacc = term if hacc is None else hacc + term
+    acc = None
+    for j in range(8):
+        ys = np.clip(2 * np.arange(dh) - 3 + j, 0, h - 1)
+        term = taps[j] * hacc[ys]
+        acc = term if acc is None else acc + term
+    alpha = acc[..., 3]
+    tiny = np.float32(2.0 ** -120)  # stbir__small_float
+    with np.errstate(divide="ignore", invalid="ignore"):
+        ia = (np.float32(1.0) / alpha).astype(np.float32)
+        colour = np.where((alpha < tiny)[..., None], acc[..., :3], acc[..., 4:7] * ia[..., None]).astype(np.float32)
     out = np.zeros((dh, dw, 4), np.uint8)
-    for ch in range(4):
-        lin = (not srgb) or ch == 3
-        c = level[..., ch]
-        taps = [c[np.ix_(ys, xs)] for ys, xs in ((ys0, xs0), (ys0, xs1), (ys1, xs0), (ys1, xs1))]
-        v = [t.astype(np.float32) if lin else to_linear[t] for t in taps]
-        mean = ((v[0] + v[1]) + (v[2] + v[3])) * np.float32(0.25)
-        out[..., ch] = np.searchsorted(mid_lin if lin else mid_srgb, mean, side="right").astype(np.uint8)
+    mid = tb["colourMid"] if srgb else tb["linearMid"]
+    out[..., :3] = np.searchsorted(mid, colour, side="right").astype(np.uint8)
+    out[..., 3] = np.searchsorted(tb["linearMid"], alpha, side="right").astype(np.uint8)
     return out
