@@ -222,7 +222,7 @@ inline Ray pinholeCameraRay(const CameraUniforms &c, vec2 uv)
     const vec3 right = {c.worldToCamera[0][0], c.worldToCamera[1][0], c.worldToCamera[2][0]};
     const vec3 up = {c.worldToCamera[0][1], c.worldToCamera[1][1], c.worldToCamera[2][1]};
     const vec3 fwd = cameraWorldFwd(c);
-    ray.d = normalize((((right * ndx) * tanHalfFovY) * aspect + ((up * ndy) * tanHalfFovY)) + fwd);
+    ray.d = normalizeExact((((right * ndx) * tanHalfFovY) * aspect + ((up * ndy) * tanHalfFovY)) + fwd);
     return ray;
 }
 

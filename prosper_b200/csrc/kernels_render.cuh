@@ -152,10 +152,109 @@ __device__ __forceinline__ int pluralityKind(int kind, bool flexible, int &live)
     return n1 > n0 ? 1 : (n0 > 0 ? 0 : 1);
 }
 
+// ---- ray reordering -------------------------------------------------------------------------------------------------
+// Secondary rays leave k_shade in path order, i.e. spatially scattered. A counting sort of the queue INDICES by
+// (direction octant, Morton cell of the origin on a 2^bits grid over the TLAS root's quantisation frame) hands each warp
+// of the persistent trace kernels 32 rays that start close together and walk the tree in the same child order, which is
+// what the per-step vote and L1 want. Results do not depend on the order (every ray writes its own slot), so hit IDs and
+// radiance are unchanged bit for bit. Three small launches per queue: bin (key + histogram), scan, scatter.
+#ifndef PRT_RAY_SORT_CELL_BITS
+#define PRT_RAY_SORT_CELL_BITS 5
+#endif
+#ifndef PRT_RAY_SORT_CELL_MAJOR
+#define PRT_RAY_SORT_CELL_MAJOR 0
+#endif
+constexpr uint32_t RAY_SORT_BINS = 8u << (3 * PRT_RAY_SORT_CELL_BITS);
+constexpr uint32_t RAY_SCAN_THREADS = 1024;
+
+__device__ __forceinline__ uint32_t spreadBits3(uint32_t v)
+{
+    v = (v | (v << 16)) & 0x030000FFu;
+    v = (v | (v << 8)) & 0x0300F00Fu;
+    v = (v | (v << 4)) & 0x030C30C3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+
+__global__ void k_ray_bin(Accel as, const float4 *__restrict__ rayO, const float4 *__restrict__ rayD,
+                          const uint32_t *__restrict__ countPtr, uint32_t *__restrict__ keys, uint32_t *__restrict__ hist)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= *countPtr) return;
+    const WideNode *root = as.tlasNodes;
+    const float4 o = rayO[i], d = rayD[i];
+    const float cells = (float)(1u << PRT_RAY_SORT_CELL_BITS);
+    // the root's quantisation frame spans origin + [0, 256) * 2^(e - 127) per axis
+    const float ix = cells / (256.f * __uint_as_float((uint32_t)root->ex << 23));
+    const float iy = cells / (256.f * __uint_as_float((uint32_t)root->ey << 23));
+    const float iz = cells / (256.f * __uint_as_float((uint32_t)root->ez << 23));
+    const float top = cells - 1.f;
+    const uint32_t cx = (uint32_t)fminf(fmaxf((o.x - root->px) * ix, 0.f), top);
+    const uint32_t cy = (uint32_t)fminf(fmaxf((o.y - root->py) * iy, 0.f), top);
+    const uint32_t cz = (uint32_t)fminf(fmaxf((o.z - root->pz) * iz, 0.f), top);
+    const uint32_t octant = (d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u);
+#if PRT_RAY_SORT_CELL_MAJOR
+    const uint32_t key = (((spreadBits3(cx) << 2) | (spreadBits3(cy) << 1) | spreadBits3(cz)) << 3) | octant;
+#else
+    const uint32_t key = (octant << (3 * PRT_RAY_SORT_CELL_BITS)) | (spreadBits3(cx) << 2) | (spreadBits3(cy) << 1) | spreadBits3(cz);
+#endif
+    keys[i] = key;
+    atomicAdd(&hist[key], 1u);
+}
+
+// exclusive scan of the histogram in place, one block
+__global__ void __launch_bounds__(RAY_SCAN_THREADS) k_ray_scan(uint32_t *__restrict__ hist)
+{
+    constexpr uint32_t PER = RAY_SORT_BINS / RAY_SCAN_THREADS;
+    __shared__ uint32_t warpSums[RAY_SCAN_THREADS / 32];
+    uint32_t *mine = hist + threadIdx.x * PER;
+    uint32_t sum = 0;
+    for (uint32_t k = 0; k < PER; k += 4)
+    {
+        const uint4 v = *reinterpret_cast<const uint4 *>(mine + k);
+        sum += v.x + v.y + v.z + v.w;
+    }
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint32_t incl = sum;
+    for (int off = 1; off < 32; off <<= 1)
+    {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, off);
+        if ((int)lane >= off) incl += t;
+    }
+    if (lane == 31) warpSums[warp] = incl;
+    __syncthreads();
+    if (warp == 0)
+    {
+        uint32_t w = warpSums[lane];
+        for (int off = 1; off < 32; off <<= 1)
+        {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, w, off);
+            if ((int)lane >= off) w += t;
+        }
+        warpSums[lane] = w;
+    }
+    __syncthreads();
+    uint32_t run = incl - sum + (warp ? warpSums[warp - 1] : 0u);
+    for (uint32_t k = 0; k < PER; ++k)
+    {
+        const uint32_t v = mine[k];
+        mine[k] = run;
+        run += v;
+    }
+}
+
+__global__ void k_ray_scatter(const uint32_t *__restrict__ countPtr, const uint32_t *__restrict__ keys, uint32_t *__restrict__ hist,
+                              uint32_t *__restrict__ perm)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= *countPtr) return;
+    perm[atomicAdd(&hist[keys[i]], 1u)] = i;
+}
+
 // traceClosest, main.rgen:62-81. Persistent warps over the closest-ray queue of `bounce`.
 template <bool COUNT>
 __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
-    k_trace_closest(Accel as, SceneView sv, PathBuffers pb, int q, uint32_t bounce, GlobalCounters *gc)
+    k_trace_closest(Accel as, SceneView sv, PathBuffers pb, int q, uint32_t bounce, GlobalCounters *gc, const uint32_t *__restrict__ perm)
 {
     const uint32_t count = pb.counts[bounce];
     uint32_t *cursor = &pb.counts[CURSOR_BASE + bounce];
@@ -178,7 +277,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
             const uint32_t next = fetchSlots(cursor, count, !active, exhausted);
             if (!active && next < count)
             {
-                slot = next;
+                slot = perm ? perm[next] : next;
                 const float4 o = pb.rayO[q][slot], d = pb.rayD[q][slot];
                 active = traceBegin(s, st, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.rayId[q][slot].y, COUNT ? &tc : nullptr);
                 if (!active) pb.hits[slot] = make_uint4(MISS_INDEX, MISS_INDEX, 0u, 0u);
@@ -235,7 +334,10 @@ __device__ __forceinline__ V4 warpTextureTap(const SceneView &sv, uint32_t textu
 }
 
 // One loop iteration of main.rgen:241-283 minus the traces.
-__global__ void __launch_bounds__(RENDER_THREADS)
+#ifndef PRT_SHADE_MIN_BLOCKS
+#define PRT_SHADE_MIN_BLOCKS 8 // 64 registers (48 B of spills): 88 instead of 98 ms per step, the kernel waits on gathers
+#endif
+__global__ void __launch_bounds__(RENDER_THREADS, PRT_SHADE_MIN_BLOCKS)
     k_shade(SceneView sv, prt_reference_pc pc, PathBuffers pb, int q, uint32_t bounce, GlobalCounters *gc, int countShaded)
 {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
@@ -328,7 +430,7 @@ __global__ void __launch_bounds__(RENDER_THREADS)
 // shadow(), main.rgen:49-60, fused with the addBounce of evaluateDirectLighting's result
 template <bool COUNT>
 __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
-    k_trace_shadow(Accel as, SceneView sv, PathBuffers pb, uint32_t bounce, GlobalCounters *gc)
+    k_trace_shadow(Accel as, SceneView sv, PathBuffers pb, uint32_t bounce, GlobalCounters *gc, const uint32_t *__restrict__ perm)
 {
     const uint32_t count = pb.counts[COUNT_SHADOW_BASE + bounce];
     uint32_t *cursor = &pb.counts[CURSOR_BASE + COUNT_SHADOW_BASE + bounce];
@@ -361,7 +463,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
             const uint32_t next = fetchSlots(cursor, count, !active, exhausted);
             if (!active && next < count)
             {
-                slot = next;
+                slot = perm ? perm[next] : next;
                 const float4 o = pb.shadowO[slot], d = pb.shadowD[slot];
                 active = traceBegin(s, st, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.shadowId[slot].y, COUNT ? &tc : nullptr);
                 if (!active) retire();

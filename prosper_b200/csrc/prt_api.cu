@@ -9,6 +9,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -200,6 +201,8 @@ struct prt_ctx
     uint64_t pathCapacity = 0;
     DBuf<float4> accum, sum;
     DBuf<uint2> f16;
+    DBuf<uint32_t> sortKeys, sortPerm, sortHist; // ray reordering (kernels_render.cuh)
+    uint32_t raySort = 0;                        // off: measured no gain. bit 0: closest queues of bounce >= 1, bit 1: shadow queues of bounce >= 1, bit 2: shadow queue of bounce 0
     DBuf<uint32_t> toneLut; // R9G9B9E5 3D LUT of the display transform (8(f)3)
     uint32_t toneLutDim = 0;
     DBuf<uint32_t> ldr;
@@ -293,6 +296,9 @@ static prt_status allocPathBuffers(prt_ctx *c, uint64_t paths)
         CK(cudaMalloc((void **)&pb.counts, COUNT_WORDS * sizeof(uint32_t)));
         CK(cudaMemset(pb.counts, 0, COUNT_WORDS * sizeof(uint32_t)));
     }
+    CK(c->sortKeys.ensure(paths));
+    CK(c->sortPerm.ensure(paths));
+    CK(c->sortHist.ensure(RAY_SORT_BINS));
     c->pathCapacity = paths;
     return PRT_OK;
 }
@@ -341,6 +347,7 @@ extern "C" prt_status prt_create(const prt_config *cfg, prt_ctx **out)
         CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->cfg.device));
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_trace_closest<false>, RENDER_THREADS, 0));
         c->traceBlocks = (uint32_t)std::max(1, sms * std::max(1, perSm));
+        if (const char *e = std::getenv("PRT_RAY_SORT")) c->raySort = (uint32_t)std::atoi(e); // experiment switch
         int coop = 0, perSmCollapse = 0;
         CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->cfg.device));
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSmCollapse, k_collapse_all_levels_grid, 128, 0));
@@ -1086,6 +1093,18 @@ static prt_status checkRenderState(prt_ctx *c, const prt_reference_pc *pc, uint3
     return PRT_OK;
 }
 
+// Counting sort of a ray queue's indices by (octant, origin cell): fills c->sortPerm. The queue length lives on the device.
+static void sortRays(prt_ctx *c, const Accel &as, const float4 *rayO, const float4 *rayD, const uint32_t *countPtr, uint32_t grid,
+                     uint32_t &launches)
+{
+    cudaStream_t st = c->stream;
+    cudaMemsetAsync(c->sortHist.p, 0, RAY_SORT_BINS * sizeof(uint32_t), st);
+    k_ray_bin<<<grid, RENDER_THREADS, 0, st>>>(as, rayO, rayD, countPtr, c->sortKeys.p, c->sortHist.p);
+    k_ray_scan<<<1, RAY_SCAN_THREADS, 0, st>>>(c->sortHist.p);
+    k_ray_scatter<<<grid, RENDER_THREADS, 0, st>>>(countPtr, c->sortKeys.p, c->sortHist.p, c->sortPerm.p);
+    launches += 3;
+}
+
 // Enqueues `samples` frames starting at pc.frameIndex as one wavefront batch.
 static prt_status renderBatch(prt_ctx *c, prt_reference_pc pc, uint32_t width, uint32_t height, uint32_t samples, bool accumulate,
                               bool timeTrace)
@@ -1107,15 +1126,27 @@ static prt_status renderBatch(prt_ctx *c, prt_reference_pc pc, uint32_t width, u
     {
         const int q = (int)(b & 1u);
         CK(c->mark(0));
-        if (count) k_trace_closest<true><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters);
-        else k_trace_closest<false><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters);
+        const uint32_t *perm = nullptr;
+        if (b >= 1 && (c->raySort & 1u))
+        {
+            sortRays(c, as, c->pb.rayO[q], c->pb.rayD[q], c->pb.counts + b, grid, launches);
+            perm = c->sortPerm.p;
+        }
+        if (count) k_trace_closest<true><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters, perm);
+        else k_trace_closest<false><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters, perm);
         CK(c->mark(1));
         k_shade<<<grid, RENDER_THREADS, 0, st>>>(sv, pc, c->pb, q, b, c->dCounters, count ? 1 : 0);
         launches += 2;
         if (debugView) break; // main.rgen:259-264: debug views stop at the first hit
         CK(c->mark(2));
-        if (count) k_trace_shadow<true><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters);
-        else k_trace_shadow<false><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters);
+        perm = nullptr;
+        if ((b >= 1 && (c->raySort & 2u)) || (b == 0 && (c->raySort & 4u)))
+        {
+            sortRays(c, as, c->pb.shadowO, c->pb.shadowD, c->pb.counts + COUNT_SHADOW_BASE + b, grid, launches);
+            perm = c->sortPerm.p;
+        }
+        if (count) k_trace_shadow<true><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters, perm);
+        else k_trace_shadow<false><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters, perm);
         launches++;
     }
     CK(c->mark(3));
@@ -1272,7 +1303,7 @@ extern "C" prt_status prt_trace_primary(prt_ctx *c, const prt_reference_pc *pcIn
     cudaStream_t st = c->stream;
     const uint32_t grid = blocksFor(pixels, RENDER_THREADS);
     k_raygen<<<grid, RENDER_THREADS, 0, st>>>(sv, *pcIn, width, height, 1, c->pb);
-    k_trace_closest<true><<<std::min(grid, c->traceBlocks), RENDER_THREADS, 0, st>>>(as, sv, c->pb, 0, 0, c->dCounters);
+    k_trace_closest<true><<<std::min(grid, c->traceBlocks), RENDER_THREADS, 0, st>>>(as, sv, c->pb, 0, 0, c->dCounters, nullptr);
     k_hits_to_records<<<blocksFor(pixels, 256), 256, 0, st>>>(c->pb.hits, c->userHits.p, (uint32_t)pixels);
     c->kernelLaunches += 3;
     CK(cudaGetLastError());

@@ -469,3 +469,22 @@ def test_sum_export_import_round_trip(test_scene):
     whole = r2.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=5).illumination_f32()
     assert np.allclose(merged[..., :3], whole[..., :3], rtol=2e-5, atol=1e-6)
     world.close()
+
+
+def test_ray_reordering_does_not_change_the_image(small_atrium_instanced, monkeypatch):
+    """The counting sort of the secondary-ray queues (octant, origin cell) only changes which warp traces which ray:
+    every ray writes its own slot, so counters and the accumulated image are identical to the unsorted run, bit for bit."""
+    w, h = 160, 96
+    images, counters = [], []
+    for mode in ("0", "7"):
+        monkeypatch.setenv("PRT_RAY_SORT", mode)
+        world = _world(small_atrium_instanced, w, h, flags=rt.CFG_COUNTERS | rt.CFG_EXACT_FILTER, spl=4)
+        r = rt.RtReference()
+        r.init(world)
+        r.drawUi(maxBounces=4)
+        images.append(r.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=4).illumination_f32())
+        c = world.counters()
+        counters.append({k: c[k] for k in ("closestRays", "shadowRays", "nodesVisited", "trisTested", "anyHitCalls", "shadedHits")})
+        world.close()
+    assert counters[0] == counters[1]
+    assert np.array_equal(images[0], images[1])
