@@ -38,6 +38,7 @@ import numpy as np  # noqa: E402
 WIDTH, HEIGHT, BOUNCES = 1920, 1080, 4
 SAMPLE_W, SAMPLE_H = 480, 270  # CPU sample: the same camera at 1/16 of the pixels
 METRIC = "Mrays/s (closest + shadow rays), 1080p Sponza-class atrium, 4 bounces"
+BUILDER_FLAGS = {"lbvh": 0, "ploc": 8, "sah": 16}  # PRT_CFG_PLOC, PRT_CFG_BINNED_SAH (include/prt.h)
 
 
 def parse_args():
@@ -51,6 +52,8 @@ def parse_args():
     ap.add_argument("--tex-size", type=int, default=1024)
     ap.add_argument("--detail", type=float, default=1.0)
     ap.add_argument("--lights", type=int, default=0, help="configs[2]: 1024 point/spot lights")
+    ap.add_argument("--builder", default="lbvh", choices=("lbvh", "ploc", "sah"),
+                    help="BLAS topology: Karras LBVH (default), PLOC or top-down binned SAH; all go through the same collapse")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--workload", default="atrium", choices=("atrium", "district"),
@@ -73,7 +76,7 @@ def workload_config(args, scene, n_gpus):
                     f"{len(scene.point_lights)}+{len(scene.spot_lights)} point/spot lights + sun + sky IBL",
         "scene": "procedural stand-in for Sponza (BASELINE.json configs[1]); no Sponza asset in the image",
         "width": WIDTH, "height": HEIGHT, "spp_per_step_per_gpu": args.spp, "max_bounces": BOUNCES,
-        "samples_per_launch": args.samples_per_launch,
+        "samples_per_launch": args.samples_per_launch, "blas_builder": args.builder,
         "partition": "by sample (frame indices), scene replicated" if n_gpus > 1 else "single GPU",
         "l2": "inputs larger than L2: path/ray/hit queues of one launch = "
               f"{args.samples_per_launch * WIDTH * HEIGHT * 232 / 1e6:.0f} MB streamed per bounce (L2 126 MB)",
@@ -398,7 +401,7 @@ def run_ours(args):
     if os.environ.get("PRT_EXPERIMENT_OPAQUE"):  # experiment only: no any-hit work at all (changes the image)
         scene.materials["alphaMode"] = 0
     world = rt.World(scene, device=local_rank, max_width=WIDTH, max_height=HEIGHT,
-                     samples_per_launch=args.samples_per_launch, flags=0)
+                     samples_per_launch=args.samples_per_launch, flags=BUILDER_FLAGS[args.builder])
     world.updateBuffers()
     world.buildAccelerationStructures()
     world.synchronize()
@@ -526,7 +529,7 @@ def run_ours(args):
     breakdown = None
     if rank == 0 and not args.no_roofline:
         cw = rt.World(scene, device=local_rank, max_width=WIDTH, max_height=HEIGHT,
-                      samples_per_launch=args.samples_per_launch, flags=rt.CFG_COUNTERS)
+                      samples_per_launch=args.samples_per_launch, flags=rt.CFG_COUNTERS | BUILDER_FLAGS[args.builder])
         cw.updateBuffers()
         cw.buildAccelerationStructures()
         cp = rt.RtReference()

@@ -12,9 +12,13 @@ namespace prt {
 
 #if defined(__CUDA_ARCH__)
 HD uint32_t atomAdd(uint32_t *p, uint32_t v) { return atomicAdd(p, v); }
+HD void atomMin(uint32_t *p, uint32_t v) { atomicMin(p, v); }
+HD void atomMax(uint32_t *p, uint32_t v) { atomicMax(p, v); }
 HD void memFence() { __threadfence(); }
 #else
 HD uint32_t atomAdd(uint32_t *p, uint32_t v) { const uint32_t o = *p; *p = o + v; return o; }
+HD void atomMin(uint32_t *p, uint32_t v) { if (v < *p) *p = v; }
+HD void atomMax(uint32_t *p, uint32_t v) { if (v > *p) *p = v; }
 HD void memFence() {}
 #endif
 
@@ -296,6 +300,228 @@ HD void plocRelabelNode(const Lbvh &t, uint32_t node, const uint32_t *newPos)
 {
     if (t.left[node] < 0) t.left[node] = ~(int32_t)newPos[~t.left[node]];
     if (t.right[node] < 0) t.right[node] = ~(int32_t)newPos[~t.right[node]];
+}
+
+// ---- binned SAH: top-down, level-synchronous (Wald 2007 binning, one level of the whole tree per pass) --------
+// BLAS alternative behind PRT_CFG_BINNED_SAH. Every level runs four per-slot passes over the primitive index array:
+// centroid bounds per active range -> SAH_BINS bins along the longest centroid axis (box + count per bin) -> the
+// range's first slot sweeps the bins for the cheapest split (area_L * n_L + area_R * n_R) and creates the two child
+// ranges -> partition into the children's sub-ranges (ping-pong arrays). A range is named by key = first >> 1
+// (ranges of a level are disjoint and hold >= 2 primitives, so keys are unique); an internal node is named by the
+// gap it splits (first + leftCount - 1, a bijection between internal nodes and the n - 1 gaps between leaves),
+// with the root's gap and 0 swapped so that the root is node 0 as the collapse expects. Neither needs an allocator,
+// so tree and numbering do not depend on atomic order. Fills the same arrays as the Karras builder, nodeBox
+// included (the union of a range's bin boxes), so no refit pass follows. Ranges whose centroids coincide, and every
+// range from level SAH_MEDIAN_LEVEL on, are halved by position, which bounds the depth.
+constexpr uint32_t SAH_BINS = 16;
+constexpr uint32_t SAH_FINAL = 0xFFFFFFFFu;   // slot key: the slot is a finished leaf
+constexpr uint32_t SAH_MEDIAN = 0xFFFFFFFFu;  // SahSplit::axisBin: halve by position
+constexpr uint32_t SAH_MEDIAN_LEVEL = 48;
+constexpr uint32_t SAH_MAX_LEVELS = 96;
+
+// monotone float <-> uint map, so that bounds are plain atomicMin / atomicMax
+HD uint32_t ordF(float f) { const uint32_t u = f2u(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+HD float unordF(uint32_t o) { return u2f((o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o); }
+
+struct SahBin // 32 B; planes in ordF form; empty: lo = 0xFFFFFFFF, hi = 0, count = 0
+{
+    uint32_t lo[3], hi[3], count, pad;
+};
+struct SahRange
+{
+    uint32_t first, count;
+    int32_t parent;   // internal node above, -1 for the root range
+    uint32_t isRight;
+};
+struct SahSplit // what the partition pass needs of a range, written by its first slot
+{
+    uint32_t first, count, leftCount, axisBin; // axisBin = axis << 8 | first bin of the right side, or SAH_MEDIAN
+    float cmin, scale;
+    uint32_t cursorL, cursorR;
+};
+struct Sah
+{
+    Lbvh t; // outputs; t.order is set by the caller to the final index array
+    const uint32_t *idxIn;
+    uint32_t *idxOut;
+    const uint32_t *keyIn; // slot -> key of the active range holding it, or SAH_FINAL
+    uint32_t *keyOut;
+    const SahRange *rangeIn;
+    SahRange *rangeOut;
+    SahSplit *split;  // [keys]
+    SahBin *bins;     // [keys][SAH_BINS]
+    uint32_t *cent;   // [keys][6] centroid bounds in ordF form
+    uint32_t *active; // [SAH_MAX_LEVELS + 1] ranges created by each level
+    uint32_t *rootGap;
+    uint32_t level;
+};
+
+HD float sahCentroid(const Box &b, uint32_t axis) { return (b.lo[axis] + b.hi[axis]) * 0.5f; }
+HD void sahAxis(const uint32_t *cent, uint32_t &axis, float &cmin, float &scale)
+{
+    float best = -1.0f;
+    axis = 0; cmin = 0.0f;
+    for (uint32_t a = 0; a < 3; ++a)
+    {
+        const float lo = unordF(cent[a]), hi = unordF(cent[3 + a]);
+        const float e = hi - lo;
+        if (e > best) { best = e; axis = a; cmin = lo; }
+    }
+    scale = best > 0.0f ? (float)SAH_BINS / best : 0.0f;
+    if (!(scale < 3.0e38f)) scale = 0.0f; // denormal extent: treat as coincident
+}
+HD uint32_t sahBinOf(float c, float cmin, float scale)
+{
+    const float f = (c - cmin) * scale;
+    const int b = f > 0.0f ? (int)fminf_(f, (float)(SAH_BINS - 1)) : 0;
+    return (uint32_t)b;
+}
+HD void sahBinAdd(SahBin *dst, const Box &b)
+{
+    for (int a = 0; a < 3; ++a) { atomMin(&dst->lo[a], ordF(b.lo[a])); atomMax(&dst->hi[a], ordF(b.hi[a])); }
+    atomAdd(&dst->count, 1u);
+}
+HD void sahBinMerge(SahBin *dst, const SahBin &src)
+{
+    for (int a = 0; a < 3; ++a) { atomMin(&dst->lo[a], src.lo[a]); atomMax(&dst->hi[a], src.hi[a]); }
+    atomAdd(&dst->count, src.count);
+}
+HD void sahBinClear(SahBin *b)
+{
+    for (int a = 0; a < 3; ++a) { b->lo[a] = 0xFFFFFFFFu; b->hi[a] = 0u; }
+    b->count = 0; b->pad = 0;
+}
+HD void sahCentClear(uint32_t *cent) { for (int a = 0; a < 3; ++a) { cent[a] = 0xFFFFFFFFu; cent[3 + a] = 0u; } }
+
+// pass 1, per slot
+HD void sahCentroidPass(const Sah &s, uint32_t slot)
+{
+    const uint32_t key = s.keyIn[slot];
+    if (key == SAH_FINAL) return;
+    const Box b = s.t.primBox[s.idxIn[slot]];
+    for (uint32_t a = 0; a < 3; ++a)
+    {
+        const uint32_t o = ordF(sahCentroid(b, a));
+        atomMin(&s.cent[key * 6u + a], o);
+        atomMax(&s.cent[key * 6u + 3u + a], o);
+    }
+}
+// pass 2, per slot: bin index of the slot's primitive (false: the slot is final)
+HD bool sahSlotBin(const Sah &s, uint32_t slot, uint32_t &key, uint32_t &bin, Box &b)
+{
+    key = s.keyIn[slot];
+    if (key == SAH_FINAL) return false;
+    uint32_t axis; float cmin, scale;
+    sahAxis(&s.cent[key * 6u], axis, cmin, scale);
+    b = s.t.primBox[s.idxIn[slot]];
+    bin = sahBinOf(sahCentroid(b, axis), cmin, scale);
+    return true;
+}
+HD void sahBinPass(const Sah &s, uint32_t slot)
+{
+    uint32_t key, bin; Box b;
+    if (sahSlotBin(s, slot, key, bin, b)) sahBinAdd(&s.bins[key * SAH_BINS + bin], b);
+}
+HD uint32_t sahNodeOfGap(uint32_t gap, uint32_t rootGap) { return gap == rootGap ? 0u : (gap == 0u ? rootGap : gap); }
+HD float sahOrdHalfArea(const uint32_t *lo, const uint32_t *hi)
+{
+    const float ex = unordF(hi[0]) - unordF(lo[0]), ey = unordF(hi[1]) - unordF(lo[1]), ez = unordF(hi[2]) - unordF(lo[2]);
+    return ex * ey + ey * ez + ez * ex;
+}
+// pass 3, per slot; only the first slot of an active range works
+HD void sahSplitPass(const Sah &s, uint32_t slot)
+{
+    const uint32_t key = s.keyIn[slot];
+    if (key == SAH_FINAL) return;
+    const SahRange r = s.rangeIn[key];
+    if (slot != r.first) return;
+    uint32_t axis; float cmin, scale;
+    sahAxis(&s.cent[key * 6u], axis, cmin, scale);
+    sahCentClear(&s.cent[key * 6u]);
+    SahBin *bins = &s.bins[key * SAH_BINS];
+    // suffix sweep: area and count of bins [i, SAH_BINS)
+    float areaR[SAH_BINS];
+    uint32_t countR[SAH_BINS];
+    uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u}, cnt = 0;
+    for (int i = (int)SAH_BINS - 1; i >= 0; --i)
+    {
+        const SahBin b = bins[i];
+        if (b.count)
+        {
+            for (int a = 0; a < 3; ++a) { lo[a] = b.lo[a] < lo[a] ? b.lo[a] : lo[a]; hi[a] = b.hi[a] > hi[a] ? b.hi[a] : hi[a]; }
+            cnt += b.count;
+        }
+        areaR[i] = cnt ? sahOrdHalfArea(lo, hi) : 0.0f;
+        countR[i] = cnt;
+    }
+    Box nodeBox;
+    for (int a = 0; a < 3; ++a) { nodeBox.lo[a] = unordF(lo[a]); nodeBox.hi[a] = unordF(hi[a]); }
+    // prefix sweep + choice
+    float bestCost = 3.4e38f;
+    uint32_t bestBin = 0, bestLeft = 0;
+    uint32_t llo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, lhi[3] = {0u, 0u, 0u}, lcnt = 0;
+    for (uint32_t i = 1; i < SAH_BINS; ++i)
+    {
+        const SahBin b = bins[i - 1];
+        if (b.count)
+        {
+            for (int a = 0; a < 3; ++a) { llo[a] = b.lo[a] < llo[a] ? b.lo[a] : llo[a]; lhi[a] = b.hi[a] > lhi[a] ? b.hi[a] : lhi[a]; }
+            lcnt += b.count;
+        }
+        if (lcnt == 0 || countR[i] == 0) continue;
+        const float cost = sahOrdHalfArea(llo, lhi) * (float)lcnt + areaR[i] * (float)countR[i];
+        if (cost < bestCost) { bestCost = cost; bestBin = i; bestLeft = lcnt; }
+    }
+    for (uint32_t i = 0; i < SAH_BINS; ++i) sahBinClear(&bins[i]);
+    SahSplit sp;
+    sp.first = r.first; sp.count = r.count; sp.cmin = cmin; sp.scale = scale; sp.cursorL = 0; sp.cursorR = 0;
+    if (bestLeft == 0 || s.level >= SAH_MEDIAN_LEVEL) { sp.leftCount = r.count / 2u; sp.axisBin = SAH_MEDIAN; }
+    else { sp.leftCount = bestLeft; sp.axisBin = (axis << 8) | bestBin; }
+    s.split[key] = sp;
+
+    const uint32_t gap = r.first + sp.leftCount - 1u;
+    if (r.parent < 0) *s.rootGap = gap;
+    const uint32_t node = r.parent < 0 ? 0u : sahNodeOfGap(gap, *s.rootGap);
+    const Lbvh &t = s.t;
+    t.first[node] = r.first;
+    t.last[node] = r.first + r.count - 1u;
+    t.nodeBox[node] = nodeBox;
+    t.parentOfInternal[node] = r.parent;
+    if (r.parent >= 0) { if (r.isRight) t.right[r.parent] = (int32_t)node; else t.left[r.parent] = (int32_t)node; }
+    uint32_t made = 0;
+    if (sp.leftCount == 1u) { t.left[node] = ~(int32_t)r.first; t.parentOfLeaf[r.first] = (int32_t)node; }
+    else { s.rangeOut[r.first >> 1] = SahRange{r.first, sp.leftCount, (int32_t)node, 0u}; made++; }
+    const uint32_t rf = r.first + sp.leftCount, rc = r.count - sp.leftCount;
+    if (rc == 1u) { t.right[node] = ~(int32_t)rf; t.parentOfLeaf[rf] = (int32_t)node; }
+    else { s.rangeOut[rf >> 1] = SahRange{rf, rc, (int32_t)node, 1u}; made++; }
+    if (made) atomAdd(&s.active[s.level + 1u], made);
+}
+// pass 4, per slot: side of the slot's primitive (0 left, 1 right); false: the slot is final / halved by position
+HD bool sahSlotSide(const Sah &s, uint32_t slot, uint32_t prim, const SahSplit &sp, uint32_t &side)
+{
+    if (sp.axisBin == SAH_MEDIAN) { side = (slot - sp.first) >= sp.leftCount ? 1u : 0u; return false; }
+    const Box b = s.t.primBox[prim];
+    side = sahBinOf(sahCentroid(b, sp.axisBin >> 8), sp.cmin, sp.scale) >= (sp.axisBin & 0xFFu) ? 1u : 0u;
+    return true;
+}
+HD void sahPlace(const Sah &s, uint32_t pos, uint32_t prim, const SahSplit &sp, uint32_t side)
+{
+    const uint32_t childFirst = side ? sp.first + sp.leftCount : sp.first;
+    const uint32_t childCount = side ? sp.count - sp.leftCount : sp.leftCount;
+    s.idxOut[pos] = prim;
+    s.keyOut[pos] = childCount >= 2u ? (childFirst >> 1) : SAH_FINAL;
+}
+HD void sahPartitionPass(const Sah &s, uint32_t slot)
+{
+    const uint32_t key = s.keyIn[slot];
+    const uint32_t prim = s.idxIn[slot];
+    if (key == SAH_FINAL) { s.idxOut[slot] = prim; s.keyOut[slot] = SAH_FINAL; return; }
+    SahSplit *spp = &s.split[key];
+    const SahSplit sp = *spp;
+    uint32_t side, pos = slot;
+    if (sahSlotSide(s, slot, prim, sp, side))
+        pos = side ? sp.first + sp.leftCount + atomAdd(&spp->cursorR, 1u) : sp.first + atomAdd(&spp->cursorL, 1u);
+    sahPlace(s, pos, prim, sp, side);
 }
 
 // ---- collapse to 8-wide + quantise -----------------------------------------------------------------

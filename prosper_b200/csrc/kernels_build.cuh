@@ -216,6 +216,119 @@ __global__ void k_ploc_finish_nodes(Lbvh t, const uint32_t *newPos)
     plocRelabelNode(t, i, newPos);
 }
 
+// ---- binned SAH (core_bvh.h): per level centroid bounds -> bins -> split -> partition, one thread per slot.
+// Near the root most blocks lie inside one range: those reduce in the warp / bin in shared memory first, so the
+// range's global counters see one update per warp or block instead of one per primitive.
+constexpr int SAH_THREADS = 256;
+
+__global__ void k_sah_init(Sah s, uint32_t keys, uint32_t *idx0, uint32_t *key0, SahRange *range0)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < s.t.count) { idx0[i] = i; key0[i] = 0u; }
+    if (i < keys)
+    {
+        sahCentClear(&s.cent[i * 6u]);
+        for (uint32_t b = 0; b < SAH_BINS; ++b) sahBinClear(&s.bins[i * SAH_BINS + b]);
+    }
+    if (i <= SAH_MAX_LEVELS) s.active[i] = i == 0 ? 1u : 0u;
+    if (i == 0) { range0[0] = SahRange{0u, s.t.count, -1, 0u}; *s.rootGap = 0u; }
+}
+
+// true when every slot of this block belongs to the same active range (ranges are contiguous)
+__device__ __forceinline__ bool sahBlockUniform(const Sah &s, uint32_t &key)
+{
+    const uint32_t base = blockIdx.x * blockDim.x;
+    const uint32_t lastSlot = min(base + blockDim.x, s.t.count) - 1u;
+    key = s.keyIn[base];
+    return key != SAH_FINAL && key == s.keyIn[lastSlot];
+}
+
+__global__ void __launch_bounds__(SAH_THREADS) k_sah_centroid(Sah s)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t key;
+    if (!sahBlockUniform(s, key))
+    {
+        if (slot < s.t.count) sahCentroidPass(s, slot);
+        return;
+    }
+    uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u};
+    if (slot < s.t.count)
+    {
+        const Box b = s.t.primBox[s.idxIn[slot]];
+        for (uint32_t a = 0; a < 3; ++a) lo[a] = hi[a] = ordF(sahCentroid(b, a));
+    }
+    for (uint32_t a = 0; a < 3; ++a)
+    {
+        lo[a] = __reduce_min_sync(0xFFFFFFFFu, lo[a]);
+        hi[a] = __reduce_max_sync(0xFFFFFFFFu, hi[a]);
+    }
+    if ((threadIdx.x & 31u) == 0u)
+        for (uint32_t a = 0; a < 3; ++a) { atomicMin(&s.cent[key * 6u + a], lo[a]); atomicMax(&s.cent[key * 6u + 3u + a], hi[a]); }
+}
+
+__global__ void __launch_bounds__(SAH_THREADS) k_sah_bin(Sah s)
+{
+    __shared__ SahBin sb[SAH_BINS];
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t key;
+    if (!sahBlockUniform(s, key))
+    {
+        if (slot < s.t.count) sahBinPass(s, slot);
+        return;
+    }
+    if (threadIdx.x < SAH_BINS) sahBinClear(&sb[threadIdx.x]);
+    __syncthreads();
+    if (slot < s.t.count)
+    {
+        uint32_t k, bin; Box b;
+        if (sahSlotBin(s, slot, k, bin, b)) sahBinAdd(&sb[bin], b);
+    }
+    __syncthreads();
+    if (threadIdx.x < SAH_BINS && sb[threadIdx.x].count) sahBinMerge(&s.bins[key * SAH_BINS + threadIdx.x], sb[threadIdx.x]);
+}
+
+__global__ void k_sah_split(Sah s)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot < s.t.count) sahSplitPass(s, slot);
+}
+
+__global__ void __launch_bounds__(SAH_THREADS) k_sah_partition(Sah s)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = slot < s.t.count;
+    const uint32_t key = valid ? s.keyIn[slot] : SAH_FINAL;
+    const uint32_t key0 = __shfl_sync(0xFFFFFFFFu, key, 0);
+    const bool warpUniform = __all_sync(0xFFFFFFFFu, valid && key == key0 && key != SAH_FINAL);
+    if (!warpUniform)
+    {
+        if (valid) sahPartitionPass(s, slot);
+        return;
+    }
+    // whole warp inside one range: one cursor update per side per warp
+    SahSplit *spp = &s.split[key];
+    const SahSplit sp = *spp;
+    const uint32_t prim = s.idxIn[slot];
+    uint32_t side, pos = slot;
+    if (sahSlotSide(s, slot, prim, sp, side)) // uniform across the warp: axisBin belongs to the range
+    {
+        const uint32_t lane = threadIdx.x & 31u;
+        const uint32_t right = __ballot_sync(0xFFFFFFFFu, side != 0u), left = ~right;
+        uint32_t baseL = 0, baseR = 0;
+        if (lane == 0)
+        {
+            if (left) baseL = atomicAdd(&spp->cursorL, (uint32_t)__popc(left));
+            if (right) baseR = atomicAdd(&spp->cursorR, (uint32_t)__popc(right));
+        }
+        baseL = __shfl_sync(0xFFFFFFFFu, baseL, 0);
+        baseR = __shfl_sync(0xFFFFFFFFu, baseR, 0);
+        const uint32_t below = (1u << lane) - 1u;
+        pos = side ? sp.first + sp.leftCount + baseR + __popc(right & below) : sp.first + baseL + __popc(left & below);
+    }
+    sahPlace(s, pos, prim, sp, side);
+}
+
 // One collapse level: items [0, *countIn) of queueIn. Launched with enough threads for the worst
 // case; the live count is read from device memory so the host never waits between levels.
 __global__ void k_collapse_level(Collapse c, const uint32_t *__restrict__ countIn)

@@ -193,6 +193,11 @@ struct prt_ctx
     DBuf<int32_t> bPlocRef[2], bPlocMergedRef;
     DBuf<Box> bPlocBox[2], bPlocMergedBox;
     DBuf<uint32_t> bPlocNearest, bPlocBlocks, bNewPos;
+    // binned-SAH scratch (BLAS builds)
+    DBuf<uint32_t> bSahKey[2], bSahCent;
+    DBuf<SahRange> bSahRange[2];
+    DBuf<SahSplit> bSahSplit;
+    DBuf<SahBin> bSahBins;
     DBuf<WideNode> bNodes;
     DBuf<BuildBounds> bBounds;
 
@@ -333,7 +338,7 @@ extern "C" prt_status prt_create(const prt_config *cfg, prt_ctx **out)
     CK(c->dPoints.ensure(PRT_MAX_POINT_LIGHTS));
     CK(c->dSpots.ensure(PRT_MAX_SPOT_LIGHTS));
     CK(c->bBounds.ensure(1));
-    CK(c->bScalars.ensure(256));
+    CK(c->bScalars.ensure(512)); // [256 ..] the binned-SAH per-level counts
     const uint64_t pixels = (uint64_t)cfg->maxWidth * cfg->maxHeight;
     if (pixels)
     {
@@ -393,6 +398,8 @@ extern "C" void prt_destroy(prt_ctx *c)
     for (int i = 0; i < 2; ++i) { c->bKeys[i].release(); c->bOrder[i].release(); c->bQueue[i].release(); }
     for (int i = 0; i < 2; ++i) { c->bPlocRef[i].release(); c->bPlocBox[i].release(); }
     c->bPlocMergedRef.release(); c->bPlocMergedBox.release(); c->bPlocNearest.release(); c->bPlocBlocks.release(); c->bNewPos.release();
+    for (int i = 0; i < 2; ++i) { c->bSahKey[i].release(); c->bSahRange[i].release(); }
+    c->bSahCent.release(); c->bSahSplit.release(); c->bSahBins.release();
     c->bHist.release(); c->bFirst.release(); c->bLast.release(); c->bVisit.release(); c->bPrimOut.release(); c->bScalars.release();
     c->bLeft.release(); c->bRight.release(); c->bParentI.release(); c->bParentL.release(); c->bNodes.release(); c->bBounds.release();
     c->accum.release(); c->sum.release(); c->f16.release(); c->userHits.release(); c->userO.release(); c->userD.release();
@@ -795,7 +802,8 @@ static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *la
     const uint64_t keyMask = tlas ? 0xFFFFFFFF00000000ull : ~0ull;
     k_pad_and_keys<<<blocksFor(n, 256), 256, 0, st>>>(c->bBoxes.p, n, c->bBounds.p, tlas ? 0 : 1, keyMask, c->bKeys[0].p, c->bOrder[0].p);
     *launches += 1;
-    const bool flipped = radixSortPairs(c->bKeys[0].p, c->bOrder[0].p, c->bKeys[1].p, c->bOrder[1].p, n, tlas ? 32 : 0, c->bHist.p, st, launches);
+    const bool sah = n > 1 && !tlas && (c->cfg.flags & PRT_CFG_BINNED_SAH);
+    const bool flipped = sah ? false : radixSortPairs(c->bKeys[0].p, c->bOrder[0].p, c->bKeys[1].p, c->bOrder[1].p, n, tlas ? 32 : 0, c->bHist.p, st, launches);
     CK(cudaGetLastError());
 
     Lbvh t{};
@@ -807,7 +815,46 @@ static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *la
     t.parentOfInternal = c->bParentI.p; t.parentOfLeaf = c->bParentL.p;
     t.nodeBox = c->bNodeBox.p; t.visit = c->bVisit.p;
     uint32_t *scal = c->bScalars.p;
-    if (n > 1 && !tlas && (c->cfg.flags & PRT_CFG_PLOC))
+    if (sah)
+    {
+        // BLAS: top-down binned SAH, four passes per tree level; the count of ranges a level created is read back
+        // every eighth level. Scalars: [243] the root's gap, [256 .. 256 + SAH_MAX_LEVELS] ranges per level.
+        const uint32_t keys = n / 2u + 1u;
+        for (int i = 0; i < 2; ++i) { CK(c->bSahKey[i].ensure(n)); CK(c->bSahRange[i].ensure(keys)); }
+        CK(c->bSahCent.ensure(6u * keys)); CK(c->bSahSplit.ensure(keys)); CK(c->bSahBins.ensure((size_t)SAH_BINS * keys));
+        Sah s{};
+        s.t = t;
+        s.split = c->bSahSplit.p; s.bins = c->bSahBins.p; s.cent = c->bSahCent.p;
+        s.active = scal + 256; s.rootGap = scal + 243;
+        const uint32_t grid = blocksFor(n, SAH_THREADS);
+        k_sah_init<<<blocksFor(std::max(n, SAH_MAX_LEVELS + 1u), 256), 256, 0, st>>>(s, keys, c->bOrder[0].p, c->bSahKey[0].p, c->bSahRange[0].p);
+        *launches += 1;
+        bool done = false;
+        uint32_t level = 0;
+        for (; level < SAH_MAX_LEVELS && !done; ++level)
+        {
+            const int a = (int)(level & 1u), b = a ^ 1;
+            s.level = level;
+            s.idxIn = c->bOrder[a].p; s.idxOut = c->bOrder[b].p;
+            s.keyIn = c->bSahKey[a].p; s.keyOut = c->bSahKey[b].p;
+            s.rangeIn = c->bSahRange[a].p; s.rangeOut = c->bSahRange[b].p;
+            k_sah_centroid<<<grid, SAH_THREADS, 0, st>>>(s);
+            k_sah_bin<<<grid, SAH_THREADS, 0, st>>>(s);
+            k_sah_split<<<grid, SAH_THREADS, 0, st>>>(s);
+            k_sah_partition<<<grid, SAH_THREADS, 0, st>>>(s);
+            *launches += 4;
+            if ((level & 7u) == 7u)
+            {
+                uint32_t made = 0;
+                CK(cudaMemcpyAsync(&made, s.active + level + 1, 4, cudaMemcpyDeviceToHost, st));
+                CK(cudaStreamSynchronize(st));
+                done = made == 0;
+            }
+        }
+        REQUIRE(done, "binned SAH did not finish within its level budget");
+        t.order = c->bOrder[level & 1u].p;
+    }
+    else if (n > 1 && !tlas && (c->cfg.flags & PRT_CFG_PLOC))
     {
         // BLAS: PLOC (surface-area-driven topology). Scalars: [240], [241] live cluster counts (ping-pong), [242] nodes made.
         for (int i = 0; i < 2; ++i) { CK(c->bPlocRef[i].ensure(n)); CK(c->bPlocBox[i].ensure(n)); }

@@ -27,7 +27,7 @@ struct HostBvh
     uint32_t levels = 0;
 };
 
-HostBvh buildHierarchyHost(std::vector<Box> &boxes, V3 lo, V3 hi, bool tlas, bool ploc = false)
+HostBvh buildHierarchyHost(std::vector<Box> &boxes, V3 lo, V3 hi, bool tlas, bool ploc = false, bool sah = false)
 {
     const uint32_t n = (uint32_t)boxes.size();
     HostBvh out;
@@ -51,7 +51,43 @@ HostBvh buildHierarchyHost(std::vector<Box> &boxes, V3 lo, V3 hi, bool tlas, boo
     t.left = left.data(); t.right = right.data(); t.first = first.data(); t.last = last.data();
     t.parentOfInternal = parentI.data(); t.parentOfLeaf = parentL.data(); t.nodeBox = nodeBox.data(); t.visit = visit.data();
     std::vector<uint32_t> orderOut(n), newPos(n);
-    if (n > 1 && !tlas && ploc)
+    if (n > 1 && !tlas && sah)
+    {
+        // binned SAH, the k_sah_* sequence of buildHierarchy (prt_api.cu): four per-slot passes per level
+        const uint32_t keys = n / 2u + 1u;
+        std::vector<uint32_t> idx[2] = {std::vector<uint32_t>(n), std::vector<uint32_t>(n)};
+        std::vector<uint32_t> key[2] = {std::vector<uint32_t>(n, 0u), std::vector<uint32_t>(n)};
+        std::vector<SahRange> range[2] = {std::vector<SahRange>(keys), std::vector<SahRange>(keys)};
+        std::vector<SahSplit> split(keys);
+        std::vector<SahBin> bins((size_t)SAH_BINS * keys);
+        std::vector<uint32_t> cent(6u * keys), active(SAH_MAX_LEVELS + 2u, 0u);
+        uint32_t rootGap = 0;
+        for (uint32_t i = 0; i < n; ++i) idx[0][i] = i;
+        for (uint32_t k = 0; k < keys; ++k)
+        {
+            sahCentClear(&cent[k * 6u]);
+            for (uint32_t b = 0; b < SAH_BINS; ++b) sahBinClear(&bins[k * SAH_BINS + b]);
+        }
+        range[0][0] = SahRange{0u, n, -1, 0u};
+        active[0] = 1;
+        Sah s{};
+        s.t = t; s.split = split.data(); s.bins = bins.data(); s.cent = cent.data(); s.active = active.data(); s.rootGap = &rootGap;
+        uint32_t level = 0;
+        for (; level < SAH_MAX_LEVELS && active[level] > 0; ++level)
+        {
+            const int a = (int)(level & 1u), b = a ^ 1;
+            s.level = level;
+            s.idxIn = idx[a].data(); s.idxOut = idx[b].data(); s.keyIn = key[a].data(); s.keyOut = key[b].data();
+            s.rangeIn = range[a].data(); s.rangeOut = range[b].data();
+            for (uint32_t i = 0; i < n; ++i) sahCentroidPass(s, i);
+            for (uint32_t i = 0; i < n; ++i) sahBinPass(s, i);
+            for (uint32_t i = 0; i < n; ++i) sahSplitPass(s, i);
+            for (uint32_t i = 0; i < n; ++i) sahPartitionPass(s, i);
+        }
+        orderOut = idx[level & 1u];
+        t.order = orderOut.data();
+    }
+    else if (n > 1 && !tlas && ploc)
     {
         // PLOC, the k_ploc_* sequence of buildHierarchy (prt_api.cu) with the compaction done serially
         std::vector<int32_t> ref[2] = {std::vector<int32_t>(n), std::vector<int32_t>(n)}, mergedRef(n);
@@ -221,11 +257,13 @@ static void buildTlasHost(hs_ctx *c)
 
 extern "C" {
 
-// flags: bit 0 = software filter for material taps (PRT_CFG_EXACT_FILTER), bit 1 = PLOC builder (PRT_CFG_PLOC)
+// flags: bit 0 = software filter for material taps (PRT_CFG_EXACT_FILTER), bit 1 = PLOC builder (PRT_CFG_PLOC),
+// bit 2 = binned-SAH builder (PRT_CFG_BINNED_SAH)
 hs_ctx *hs_create(const orc_scene *scene, int flags)
 {
     const int exactMaterialFilter = flags & 1;
     const bool ploc = (flags & 2) != 0;
+    const bool sah = (flags & 4) != 0;
     hs_ctx *c = new hs_ctx;
     c->s = *scene;
     const orc_scene &s = c->s;
@@ -313,7 +351,7 @@ hs_ctx *hs_create(const orc_scene *scene, int flags)
             }
         }
         if (tris.empty()) continue;
-        HostBvh h = buildHierarchyHost(boxes, lo, hi, false, ploc);
+        HostBvh h = buildHierarchyHost(boxes, lo, hi, false, ploc, sah);
         if (h.primOut.size() != tris.size()) { c->buildError = 1; continue; }
         c->blasLevels = std::max(c->blasLevels, h.levels);
         c->blas[m].nodes = std::move(h.nodes);

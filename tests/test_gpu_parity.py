@@ -121,6 +121,35 @@ def test_primary_ids_ploc_builder(small_atrium_instanced):
     world.close()
 
 
+def test_primary_ids_and_radiance_binned_sah_builder(small_atrium_instanced, test_scene):
+    # PRT_CFG_BINNED_SAH: top-down binned-SAH BLAS topology (k_sah_*), the same hit records and the same image
+    for scene, (w, h) in ((small_atrium_instanced, (160, 90)), (test_scene, (96, 64))):
+        world = rt.World(scene, max_width=w, max_height=h, flags=rt.CFG_COUNTERS | rt.CFG_BINNED_SAH)
+        world.updateBuffers()
+        world.buildAccelerationStructures()
+        orc = oracle.Oracle(scene)
+        pc = sd.reference_pc(frame_index=2)
+        ho, margin = orc.trace_primary(pc, w, h)
+        hg = world.trace_primary(pc, w, h)
+        assert (_id_mismatch(ho, hg) & ~(margin < ALPHA_TIE_MARGIN)).sum() == 0
+        assert world.counters()["stackOverflows"] == 0
+        # the wavefront image must not depend on the tree: compare with the default builder bit for bit
+        r = rt.RtReference()
+        r.init(world)
+        r.drawUi(maxBounces=4)
+        a = r.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=2).illumination_f32()
+        world.close()
+        ref_world = rt.World(scene, max_width=w, max_height=h, flags=rt.CFG_COUNTERS)
+        ref_world.updateBuffers()
+        ref_world.buildAccelerationStructures()
+        r2 = rt.RtReference()
+        r2.init(ref_world)
+        r2.drawUi(maxBounces=4)
+        b = r2.record(ref_world, (0, 0, w, h), rt.Options(ibl=True), frames=2).illumination_f32()
+        ref_world.close()
+        assert np.array_equal(a, b)
+
+
 def test_dof_primary(test_scene):
     w, h = 96, 64
     world = _world(test_scene, w, h)

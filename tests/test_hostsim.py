@@ -41,6 +41,18 @@ def test_ploc_builder_bit_exact(small_atrium_instanced, small_helmet):
         assert hs.trace_counters()["overflow"] == 0
 
 
+def test_binned_sah_builder_bit_exact(small_atrium_instanced, small_helmet, test_scene):
+    # PRT_CFG_BINNED_SAH: the top-down binned-SAH topology through the same collapse; hit records unchanged
+    for scene, (w, h) in ((small_atrium_instanced, (160, 90)), (small_helmet, (128, 128)), (test_scene, (96, 64))):
+        orc, hs = oracle.Oracle(scene), hostsim.HostSim(scene, binned_sah=True)
+        st = hs.stats()
+        assert st["buildError"] == 0 and st["blasTris"] == scene.triangle_count
+        pc = sd.reference_pc(frame_index=3)
+        ho, _ = orc.trace_primary(pc, w, h)
+        assert np.array_equal(ho, hs.trace_primary(pc, w, h)), "a different tree must not change a single hit record"
+        assert hs.trace_counters()["overflow"] == 0
+
+
 def test_wavefront_stages_reproduce_the_oracle_image(test_scene, small_atrium_instanced):
     for scene, (w, h) in ((test_scene, (96, 64)), (small_atrium_instanced, (80, 45))):
         orc, hs = oracle.Oracle(scene), hostsim.HostSim(scene)
