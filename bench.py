@@ -38,7 +38,7 @@ import numpy as np  # noqa: E402
 WIDTH, HEIGHT, BOUNCES = 1920, 1080, 4
 SAMPLE_W, SAMPLE_H = 480, 270  # CPU sample: the same camera at 1/16 of the pixels
 METRIC = "Mrays/s (closest + shadow rays), 1080p Sponza-class atrium, 4 bounces"
-BUILDER_FLAGS = {"lbvh": 0, "ploc": 8, "sah": 16}  # PRT_CFG_PLOC, PRT_CFG_BINNED_SAH (include/prt.h)
+BUILDER_FLAGS = {"sah": 0, "ploc": 8, "lbvh": 16}  # PRT_CFG_PLOC, PRT_CFG_LBVH_BLAS (include/prt.h)
 
 
 def parse_args():
@@ -52,8 +52,8 @@ def parse_args():
     ap.add_argument("--tex-size", type=int, default=1024)
     ap.add_argument("--detail", type=float, default=1.0)
     ap.add_argument("--lights", type=int, default=0, help="configs[2]: 1024 point/spot lights")
-    ap.add_argument("--builder", default="lbvh", choices=("lbvh", "ploc", "sah"),
-                    help="BLAS topology: Karras LBVH (default), PLOC or top-down binned SAH; all go through the same collapse")
+    ap.add_argument("--builder", default="sah", choices=("sah", "lbvh", "ploc"),
+                    help="BLAS topology: top-down binned SAH (default), Karras LBVH or PLOC; all go through the same collapse")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--workload", default="atrium", choices=("atrium", "district"),

@@ -43,9 +43,10 @@ enum {
     PRT_CFG_DECODE_BC7 = 1u << 2,   /* expand BC7 payloads to RGBA8 arrays at upload (a CUDA kernel)
                                        instead of sampling block-compressed CUDA arrays */
     PRT_CFG_PLOC = 1u << 3,         /* BLAS topology by PLOC (agglomerative, surface-area driven) instead of the
-                                       Karras Morton hierarchy; same collapse, same results, different tree */
-    PRT_CFG_BINNED_SAH = 1u << 4    /* BLAS topology by a top-down binned-SAH build (16 bins along the longest
-                                       centroid axis, one tree level per pass); same collapse, same results */
+                                       default; same collapse, same results, different tree */
+    PRT_CFG_LBVH_BLAS = 1u << 4     /* BLAS topology by the Karras Morton hierarchy (what every TLAS build uses)
+                                       instead of the default top-down binned-SAH build (PRT_SAH_BINS bins per
+                                       axis, one tree level per pass); same collapse, same results */
 };
 
 /* ---- lifetime: RtReference::init / ~RtReference (RtRef.cpp:90-120) ------------------------ */

@@ -303,8 +303,8 @@ HD void plocRelabelNode(const Lbvh &t, uint32_t node, const uint32_t *newPos)
 }
 
 // ---- binned SAH: top-down, level-synchronous (Wald 2007 binning, one level of the whole tree per pass) --------
-// BLAS alternative behind PRT_CFG_BINNED_SAH. Every level runs four per-slot passes over the primitive index array:
-// centroid bounds per active range -> SAH_BINS bins along the longest centroid axis (box + count per bin) -> the
+// The default BLAS builder (PRT_CFG_LBVH_BLAS and PRT_CFG_PLOC select the others). Every level runs four per-slot passes over the primitive index array:
+// centroid bounds per active range -> SAH_BINS bins along each axis (box + count per bin) -> the
 // range's first slot sweeps the bins for the cheapest split (area_L * n_L + area_R * n_R) and creates the two child
 // ranges -> partition into the children's sub-ranges (ping-pong arrays). A range is named by key = first >> 1
 // (ranges of a level are disjoint and hold >= 2 primitives, so keys are unique); an internal node is named by the
@@ -312,10 +312,20 @@ HD void plocRelabelNode(const Lbvh &t, uint32_t node, const uint32_t *newPos)
 // with the root's gap and 0 swapped so that the root is node 0 as the collapse expects. Neither needs an allocator,
 // so tree and numbering do not depend on atomic order. Fills the same arrays as the Karras builder, nodeBox
 // included (the union of a range's bin boxes), so no refit pass follows. Ranges whose centroids coincide, and every
-// range from level SAH_MEDIAN_LEVEL on, are halved by position, which bounds the depth.
-constexpr uint32_t SAH_BINS = 16;
+// range from level SAH_MEDIAN_LEVEL on, are binned by primitive index and split at the most balanced border.
+#ifndef PRT_SAH_BINS
+#define PRT_SAH_BINS 16
+#endif
+#ifndef PRT_SAH_AXES
+#define PRT_SAH_AXES 1 // 1: bin along the longest centroid axis; 3: along every axis, cheapest split of all (measured: no faster to trace)
+#endif
+constexpr uint32_t SAH_BINS = PRT_SAH_BINS;
+constexpr uint32_t SAH_AXES = PRT_SAH_AXES;
+constexpr uint32_t SAH_RANGE_BINS = SAH_BINS * SAH_AXES; // bins of one range: [axis slot][bin]
 constexpr uint32_t SAH_FINAL = 0xFFFFFFFFu;   // slot key: the slot is a finished leaf
-constexpr uint32_t SAH_MEDIAN = 0xFFFFFFFFu;  // SahSplit::axisBin: halve by position
+constexpr uint32_t SAH_MEDIAN = 0xFFFFFFFFu;  // SahSplit::axisBin: halve by position (safety net, see sahSplitPass)
+constexpr uint32_t SAH_INDEX_AXIS = 3u;       // axis code: the primitive index (coincident centroids, depth bound)
+constexpr uint32_t SAH_CENT = 8u;             // words of centroid bounds per range: lo xyz, hi xyz, min / max primitive index
 constexpr uint32_t SAH_MEDIAN_LEVEL = 48;
 constexpr uint32_t SAH_MAX_LEVELS = 96;
 
@@ -349,26 +359,50 @@ struct Sah
     const SahRange *rangeIn;
     SahRange *rangeOut;
     SahSplit *split;  // [keys]
-    SahBin *bins;     // [keys][SAH_BINS]
-    uint32_t *cent;   // [keys][6] centroid bounds in ordF form
+    SahBin *bins;     // [keys][SAH_RANGE_BINS]
+    uint32_t *cent;   // [keys][SAH_CENT] centroid bounds in ordF form + primitive index bounds
     uint32_t *active; // [SAH_MAX_LEVELS + 1] ranges created by each level
     uint32_t *rootGap;
     uint32_t level;
 };
 
-HD float sahCentroid(const Box &b, uint32_t axis) { return (b.lo[axis] + b.hi[axis]) * 0.5f; }
-HD void sahAxis(const uint32_t *cent, uint32_t &axis, float &cmin, float &scale)
+// the binned axes of a range: axis slot k bins along axis[k] with (c - cmin[k]) * scale[k]; scale 0 = no extent
+// byIndex: the range is binned by primitive index instead (its centroids coincide, or the level is past
+// SAH_MEDIAN_LEVEL) and split at the most balanced bin border -- an order-free rule, so the tree stays deterministic
+struct SahAxes
 {
-    float best = -1.0f;
-    axis = 0; cmin = 0.0f;
+    uint32_t axis[SAH_AXES];
+    float cmin[SAH_AXES], scale[SAH_AXES];
+    bool byIndex;
+    uint32_t idxMin, idxSpan;
+};
+HD float sahCentroid(const Box &b, uint32_t axis) { return (b.lo[axis] + b.hi[axis]) * 0.5f; }
+HD SahAxes sahAxes(const uint32_t *cent, uint32_t level)
+{
+    float lo[3], ext[3];
+    uint32_t longest = 0;
     for (uint32_t a = 0; a < 3; ++a)
     {
-        const float lo = unordF(cent[a]), hi = unordF(cent[3 + a]);
-        const float e = hi - lo;
-        if (e > best) { best = e; axis = a; cmin = lo; }
+        lo[a] = unordF(cent[a]);
+        ext[a] = unordF(cent[3 + a]) - lo[a];
+        if (ext[a] > ext[longest]) longest = a;
     }
-    scale = best > 0.0f ? (float)SAH_BINS / best : 0.0f;
-    if (!(scale < 3.0e38f)) scale = 0.0f; // denormal extent: treat as coincident
+    SahAxes r;
+    for (uint32_t k = 0; k < SAH_AXES; ++k)
+    {
+        const uint32_t a = SAH_AXES == 3 ? k : longest;
+        float scale = ext[a] > 0.0f ? (float)SAH_BINS / ext[a] : 0.0f;
+        if (!(scale < 3.0e38f)) scale = 0.0f; // denormal extent: treat as coincident
+        r.axis[k] = a; r.cmin[k] = lo[a]; r.scale[k] = scale;
+    }
+    r.byIndex = level >= SAH_MEDIAN_LEVEL || !(ext[longest] > 0.0f) || !((float)SAH_BINS / ext[longest] < 3.0e38f);
+    r.idxMin = cent[6];
+    r.idxSpan = cent[7] - cent[6] + 1u;
+    return r;
+}
+HD uint32_t sahIndexBinOf(uint32_t prim, uint32_t idxMin, uint32_t idxSpan)
+{
+    return (uint32_t)(((uint64_t)(prim - idxMin) * SAH_BINS) / idxSpan);
 }
 HD uint32_t sahBinOf(float c, float cmin, float scale)
 {
@@ -391,36 +425,38 @@ HD void sahBinClear(SahBin *b)
     for (int a = 0; a < 3; ++a) { b->lo[a] = 0xFFFFFFFFu; b->hi[a] = 0u; }
     b->count = 0; b->pad = 0;
 }
-HD void sahCentClear(uint32_t *cent) { for (int a = 0; a < 3; ++a) { cent[a] = 0xFFFFFFFFu; cent[3 + a] = 0u; } }
+HD void sahCentClear(uint32_t *cent) { for (int a = 0; a < 3; ++a) { cent[a] = 0xFFFFFFFFu; cent[3 + a] = 0u; } cent[6] = 0xFFFFFFFFu; cent[7] = 0u; }
 
 // pass 1, per slot
 HD void sahCentroidPass(const Sah &s, uint32_t slot)
 {
     const uint32_t key = s.keyIn[slot];
     if (key == SAH_FINAL) return;
-    const Box b = s.t.primBox[s.idxIn[slot]];
+    const uint32_t prim = s.idxIn[slot];
+    const Box b = s.t.primBox[prim];
     for (uint32_t a = 0; a < 3; ++a)
     {
         const uint32_t o = ordF(sahCentroid(b, a));
-        atomMin(&s.cent[key * 6u + a], o);
-        atomMax(&s.cent[key * 6u + 3u + a], o);
+        atomMin(&s.cent[key * SAH_CENT + a], o);
+        atomMax(&s.cent[key * SAH_CENT + 3u + a], o);
     }
+    atomMin(&s.cent[key * SAH_CENT + 6u], prim);
+    atomMax(&s.cent[key * SAH_CENT + 7u], prim);
 }
-// pass 2, per slot: bin index of the slot's primitive (false: the slot is final)
-HD bool sahSlotBin(const Sah &s, uint32_t slot, uint32_t &key, uint32_t &bin, Box &b)
+// pass 2, per slot: adds the slot's primitive to one bin per axis slot of `dst` (the range's bins or a block's copy)
+HD void sahBinInto(const Sah &s, uint32_t slot, uint32_t key, SahBin *dst)
 {
-    key = s.keyIn[slot];
-    if (key == SAH_FINAL) return false;
-    uint32_t axis; float cmin, scale;
-    sahAxis(&s.cent[key * 6u], axis, cmin, scale);
-    b = s.t.primBox[s.idxIn[slot]];
-    bin = sahBinOf(sahCentroid(b, axis), cmin, scale);
-    return true;
+    const SahAxes ax = sahAxes(&s.cent[key * SAH_CENT], s.level);
+    const uint32_t prim = s.idxIn[slot];
+    const Box b = s.t.primBox[prim];
+    if (ax.byIndex) { sahBinAdd(&dst[sahIndexBinOf(prim, ax.idxMin, ax.idxSpan)], b); return; }
+    for (uint32_t k = 0; k < SAH_AXES; ++k)
+        sahBinAdd(&dst[k * SAH_BINS + sahBinOf(sahCentroid(b, ax.axis[k]), ax.cmin[k], ax.scale[k])], b);
 }
 HD void sahBinPass(const Sah &s, uint32_t slot)
 {
-    uint32_t key, bin; Box b;
-    if (sahSlotBin(s, slot, key, bin, b)) sahBinAdd(&s.bins[key * SAH_BINS + bin], b);
+    const uint32_t key = s.keyIn[slot];
+    if (key != SAH_FINAL) sahBinInto(s, slot, key, &s.bins[key * SAH_RANGE_BINS]);
 }
 HD uint32_t sahNodeOfGap(uint32_t gap, uint32_t rootGap) { return gap == rootGap ? 0u : (gap == 0u ? rootGap : gap); }
 HD float sahOrdHalfArea(const uint32_t *lo, const uint32_t *hi)
@@ -435,48 +471,56 @@ HD void sahSplitPass(const Sah &s, uint32_t slot)
     if (key == SAH_FINAL) return;
     const SahRange r = s.rangeIn[key];
     if (slot != r.first) return;
-    uint32_t axis; float cmin, scale;
-    sahAxis(&s.cent[key * 6u], axis, cmin, scale);
-    sahCentClear(&s.cent[key * 6u]);
-    SahBin *bins = &s.bins[key * SAH_BINS];
-    // suffix sweep: area and count of bins [i, SAH_BINS)
-    float areaR[SAH_BINS];
-    uint32_t countR[SAH_BINS];
-    uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u}, cnt = 0;
-    for (int i = (int)SAH_BINS - 1; i >= 0; --i)
-    {
-        const SahBin b = bins[i];
-        if (b.count)
-        {
-            for (int a = 0; a < 3; ++a) { lo[a] = b.lo[a] < lo[a] ? b.lo[a] : lo[a]; hi[a] = b.hi[a] > hi[a] ? b.hi[a] : hi[a]; }
-            cnt += b.count;
-        }
-        areaR[i] = cnt ? sahOrdHalfArea(lo, hi) : 0.0f;
-        countR[i] = cnt;
-    }
-    Box nodeBox;
-    for (int a = 0; a < 3; ++a) { nodeBox.lo[a] = unordF(lo[a]); nodeBox.hi[a] = unordF(hi[a]); }
-    // prefix sweep + choice
+    const SahAxes ax = sahAxes(&s.cent[key * SAH_CENT], s.level);
+    sahCentClear(&s.cent[key * SAH_CENT]);
     float bestCost = 3.4e38f;
-    uint32_t bestBin = 0, bestLeft = 0;
-    uint32_t llo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, lhi[3] = {0u, 0u, 0u}, lcnt = 0;
-    for (uint32_t i = 1; i < SAH_BINS; ++i)
+    uint32_t bestBin = 0, bestLeft = 0, bestSlot = 0;
+    Box nodeBox{};
+    for (uint32_t k = 0; k < (ax.byIndex ? 1u : SAH_AXES); ++k)
     {
-        const SahBin b = bins[i - 1];
-        if (b.count)
+        SahBin *bins = &s.bins[key * SAH_RANGE_BINS + k * SAH_BINS];
+        // suffix sweep: area and count of bins [i, SAH_BINS)
+        float areaR[SAH_BINS];
+        uint32_t countR[SAH_BINS];
+        uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u}, cnt = 0;
+        for (int i = (int)SAH_BINS - 1; i >= 0; --i)
         {
-            for (int a = 0; a < 3; ++a) { llo[a] = b.lo[a] < llo[a] ? b.lo[a] : llo[a]; lhi[a] = b.hi[a] > lhi[a] ? b.hi[a] : lhi[a]; }
-            lcnt += b.count;
+            const SahBin b = bins[i];
+            if (b.count)
+            {
+                for (int a = 0; a < 3; ++a) { lo[a] = b.lo[a] < lo[a] ? b.lo[a] : lo[a]; hi[a] = b.hi[a] > hi[a] ? b.hi[a] : hi[a]; }
+                cnt += b.count;
+            }
+            areaR[i] = cnt ? sahOrdHalfArea(lo, hi) : 0.0f;
+            countR[i] = cnt;
         }
-        if (lcnt == 0 || countR[i] == 0) continue;
-        const float cost = sahOrdHalfArea(llo, lhi) * (float)lcnt + areaR[i] * (float)countR[i];
-        if (cost < bestCost) { bestCost = cost; bestBin = i; bestLeft = lcnt; }
+        if (k == 0) // every axis slot holds all primitives of the range
+            for (int a = 0; a < 3; ++a) { nodeBox.lo[a] = unordF(lo[a]); nodeBox.hi[a] = unordF(hi[a]); }
+        // prefix sweep + choice (ties keep the earlier axis and bin)
+        uint32_t llo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, lhi[3] = {0u, 0u, 0u}, lcnt = 0;
+        for (uint32_t i = 1; i < SAH_BINS; ++i)
+        {
+            const SahBin b = bins[i - 1];
+            if (b.count)
+            {
+                for (int a = 0; a < 3; ++a) { llo[a] = b.lo[a] < llo[a] ? b.lo[a] : llo[a]; lhi[a] = b.hi[a] > lhi[a] ? b.hi[a] : lhi[a]; }
+                lcnt += b.count;
+            }
+            if (lcnt == 0 || countR[i] == 0) continue;
+            const float cost = ax.byIndex ? (float)(lcnt > countR[i] ? lcnt - countR[i] : countR[i] - lcnt)
+                                          : sahOrdHalfArea(llo, lhi) * (float)lcnt + areaR[i] * (float)countR[i];
+            if (cost < bestCost) { bestCost = cost; bestBin = i; bestLeft = lcnt; bestSlot = k; }
+        }
+        for (uint32_t i = 0; i < SAH_BINS; ++i) sahBinClear(&bins[i]);
     }
-    for (uint32_t i = 0; i < SAH_BINS; ++i) sahBinClear(&bins[i]);
     SahSplit sp;
-    sp.first = r.first; sp.count = r.count; sp.cmin = cmin; sp.scale = scale; sp.cursorL = 0; sp.cursorR = 0;
-    if (bestLeft == 0 || s.level >= SAH_MEDIAN_LEVEL) { sp.leftCount = r.count / 2u; sp.axisBin = SAH_MEDIAN; }
-    else { sp.leftCount = bestLeft; sp.axisBin = (axis << 8) | bestBin; }
+    sp.first = r.first; sp.count = r.count; sp.cursorL = 0; sp.cursorR = 0;
+    sp.cmin = ax.byIndex ? u2f(ax.idxMin) : ax.cmin[bestSlot];
+    sp.scale = ax.byIndex ? u2f(ax.idxSpan) : ax.scale[bestSlot];
+    // distinct primitive indices always leave two non-empty bins, so a range of >= 2 primitives always finds a split;
+    // halving by position is kept as the safety net only (it would depend on the order the partition left behind)
+    if (bestLeft == 0) { sp.leftCount = r.count / 2u; sp.axisBin = SAH_MEDIAN; }
+    else { sp.leftCount = bestLeft; sp.axisBin = ((ax.byIndex ? SAH_INDEX_AXIS : ax.axis[bestSlot]) << 8) | bestBin; }
     s.split[key] = sp;
 
     const uint32_t gap = r.first + sp.leftCount - 1u;
@@ -500,6 +544,11 @@ HD void sahSplitPass(const Sah &s, uint32_t slot)
 HD bool sahSlotSide(const Sah &s, uint32_t slot, uint32_t prim, const SahSplit &sp, uint32_t &side)
 {
     if (sp.axisBin == SAH_MEDIAN) { side = (slot - sp.first) >= sp.leftCount ? 1u : 0u; return false; }
+    if ((sp.axisBin >> 8) == SAH_INDEX_AXIS)
+    {
+        side = sahIndexBinOf(prim, f2u(sp.cmin), f2u(sp.scale)) >= (sp.axisBin & 0xFFu) ? 1u : 0u;
+        return true;
+    }
     const Box b = s.t.primBox[prim];
     side = sahBinOf(sahCentroid(b, sp.axisBin >> 8), sp.cmin, sp.scale) >= (sp.axisBin & 0xFFu) ? 1u : 0u;
     return true;

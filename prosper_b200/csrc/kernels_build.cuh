@@ -220,6 +220,7 @@ __global__ void k_ploc_finish_nodes(Lbvh t, const uint32_t *newPos)
 // Near the root most blocks lie inside one range: those reduce in the warp / bin in shared memory first, so the
 // range's global counters see one update per warp or block instead of one per primitive.
 constexpr int SAH_THREADS = 256;
+static_assert(SAH_RANGE_BINS <= SAH_THREADS, "one thread per bin clears and flushes the block's bins");
 
 __global__ void k_sah_init(Sah s, uint32_t keys, uint32_t *idx0, uint32_t *key0, SahRange *range0)
 {
@@ -227,8 +228,8 @@ __global__ void k_sah_init(Sah s, uint32_t keys, uint32_t *idx0, uint32_t *key0,
     if (i < s.t.count) { idx0[i] = i; key0[i] = 0u; }
     if (i < keys)
     {
-        sahCentClear(&s.cent[i * 6u]);
-        for (uint32_t b = 0; b < SAH_BINS; ++b) sahBinClear(&s.bins[i * SAH_BINS + b]);
+        sahCentClear(&s.cent[i * SAH_CENT]);
+        for (uint32_t b = 0; b < SAH_RANGE_BINS; ++b) sahBinClear(&s.bins[i * SAH_RANGE_BINS + b]);
     }
     if (i <= SAH_MAX_LEVELS) s.active[i] = i == 0 ? 1u : 0u;
     if (i == 0) { range0[0] = SahRange{0u, s.t.count, -1, 0u}; *s.rootGap = 0u; }
@@ -252,24 +253,31 @@ __global__ void __launch_bounds__(SAH_THREADS) k_sah_centroid(Sah s)
         if (slot < s.t.count) sahCentroidPass(s, slot);
         return;
     }
-    uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u};
+    uint32_t lo[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[4] = {0u, 0u, 0u, 0u}; // xyz + primitive index
     if (slot < s.t.count)
     {
-        const Box b = s.t.primBox[s.idxIn[slot]];
+        const uint32_t prim = s.idxIn[slot];
+        const Box b = s.t.primBox[prim];
         for (uint32_t a = 0; a < 3; ++a) lo[a] = hi[a] = ordF(sahCentroid(b, a));
+        lo[3] = hi[3] = prim;
     }
-    for (uint32_t a = 0; a < 3; ++a)
+    for (uint32_t a = 0; a < 4; ++a)
     {
         lo[a] = __reduce_min_sync(0xFFFFFFFFu, lo[a]);
         hi[a] = __reduce_max_sync(0xFFFFFFFFu, hi[a]);
     }
     if ((threadIdx.x & 31u) == 0u)
-        for (uint32_t a = 0; a < 3; ++a) { atomicMin(&s.cent[key * 6u + a], lo[a]); atomicMax(&s.cent[key * 6u + 3u + a], hi[a]); }
+    {
+        uint32_t *cent = &s.cent[key * SAH_CENT];
+        for (uint32_t a = 0; a < 3; ++a) { atomicMin(&cent[a], lo[a]); atomicMax(&cent[3u + a], hi[a]); }
+        atomicMin(&cent[6], lo[3]);
+        atomicMax(&cent[7], hi[3]);
+    }
 }
 
 __global__ void __launch_bounds__(SAH_THREADS) k_sah_bin(Sah s)
 {
-    __shared__ SahBin sb[SAH_BINS];
+    __shared__ SahBin sb[SAH_RANGE_BINS];
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t key;
     if (!sahBlockUniform(s, key))
@@ -277,15 +285,11 @@ __global__ void __launch_bounds__(SAH_THREADS) k_sah_bin(Sah s)
         if (slot < s.t.count) sahBinPass(s, slot);
         return;
     }
-    if (threadIdx.x < SAH_BINS) sahBinClear(&sb[threadIdx.x]);
+    if (threadIdx.x < SAH_RANGE_BINS) sahBinClear(&sb[threadIdx.x]);
     __syncthreads();
-    if (slot < s.t.count)
-    {
-        uint32_t k, bin; Box b;
-        if (sahSlotBin(s, slot, k, bin, b)) sahBinAdd(&sb[bin], b);
-    }
+    if (slot < s.t.count) sahBinInto(s, slot, key, sb);
     __syncthreads();
-    if (threadIdx.x < SAH_BINS && sb[threadIdx.x].count) sahBinMerge(&s.bins[key * SAH_BINS + threadIdx.x], sb[threadIdx.x]);
+    if (threadIdx.x < SAH_RANGE_BINS && sb[threadIdx.x].count) sahBinMerge(&s.bins[key * SAH_RANGE_BINS + threadIdx.x], sb[threadIdx.x]);
 }
 
 __global__ void k_sah_split(Sah s)

@@ -802,7 +802,7 @@ static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *la
     const uint64_t keyMask = tlas ? 0xFFFFFFFF00000000ull : ~0ull;
     k_pad_and_keys<<<blocksFor(n, 256), 256, 0, st>>>(c->bBoxes.p, n, c->bBounds.p, tlas ? 0 : 1, keyMask, c->bKeys[0].p, c->bOrder[0].p);
     *launches += 1;
-    const bool sah = n > 1 && !tlas && (c->cfg.flags & PRT_CFG_BINNED_SAH);
+    const bool sah = n > 1 && !tlas && !(c->cfg.flags & (PRT_CFG_PLOC | PRT_CFG_LBVH_BLAS));
     const bool flipped = sah ? false : radixSortPairs(c->bKeys[0].p, c->bOrder[0].p, c->bKeys[1].p, c->bOrder[1].p, n, tlas ? 32 : 0, c->bHist.p, st, launches);
     CK(cudaGetLastError());
 
@@ -817,11 +817,11 @@ static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *la
     uint32_t *scal = c->bScalars.p;
     if (sah)
     {
-        // BLAS: top-down binned SAH, four passes per tree level; the count of ranges a level created is read back
+        // BLAS (default): top-down binned SAH, four passes per tree level; the count of ranges a level created is read back
         // every eighth level. Scalars: [243] the root's gap, [256 .. 256 + SAH_MAX_LEVELS] ranges per level.
         const uint32_t keys = n / 2u + 1u;
         for (int i = 0; i < 2; ++i) { CK(c->bSahKey[i].ensure(n)); CK(c->bSahRange[i].ensure(keys)); }
-        CK(c->bSahCent.ensure(6u * keys)); CK(c->bSahSplit.ensure(keys)); CK(c->bSahBins.ensure((size_t)SAH_BINS * keys));
+        CK(c->bSahCent.ensure((size_t)SAH_CENT * keys)); CK(c->bSahSplit.ensure(keys)); CK(c->bSahBins.ensure((size_t)SAH_RANGE_BINS * keys));
         Sah s{};
         s.t = t;
         s.split = c->bSahSplit.p; s.bins = c->bSahBins.p; s.cent = c->bSahCent.p;

@@ -26,7 +26,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # PRT_LIB: an alternative build of the same library (kernel experiments); there is still no fallback
 LIB_PATH = os.environ.get("PRT_LIB") or os.path.join(_HERE, "libprt_b200.so")
 
-CFG_COUNTERS, CFG_EXACT_FILTER, CFG_DECODE_BC7, CFG_PLOC, CFG_BINNED_SAH = 1, 2, 4, 8, 16
+CFG_COUNTERS, CFG_EXACT_FILTER, CFG_DECODE_BC7, CFG_PLOC, CFG_LBVH_BLAS = 1, 2, 4, 8, 16
 
 
 class PrtConfig(C.Structure):

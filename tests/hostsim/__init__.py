@@ -56,10 +56,10 @@ def _p(a):
 
 
 class HostSim:
-    def __init__(self, scene, exact_material_filter: bool = True, ploc: bool = False, binned_sah: bool = False):
+    def __init__(self, scene, exact_material_filter: bool = True, ploc: bool = False, lbvh_blas: bool = False):
         self.scene = scene
         self._s, self._keep = oracle.pack_scene(scene)
-        self._ctx = lib().hs_create(C.byref(self._s), (1 if exact_material_filter else 0) | (2 if ploc else 0) | (4 if binned_sah else 0))
+        self._ctx = lib().hs_create(C.byref(self._s), (1 if exact_material_filter else 0) | (2 if ploc else 0) | (4 if lbvh_blas else 0))
 
     def close(self):
         if self._ctx:

@@ -59,14 +59,14 @@ HostBvh buildHierarchyHost(std::vector<Box> &boxes, V3 lo, V3 hi, bool tlas, boo
         std::vector<uint32_t> key[2] = {std::vector<uint32_t>(n, 0u), std::vector<uint32_t>(n)};
         std::vector<SahRange> range[2] = {std::vector<SahRange>(keys), std::vector<SahRange>(keys)};
         std::vector<SahSplit> split(keys);
-        std::vector<SahBin> bins((size_t)SAH_BINS * keys);
-        std::vector<uint32_t> cent(6u * keys), active(SAH_MAX_LEVELS + 2u, 0u);
+        std::vector<SahBin> bins((size_t)SAH_RANGE_BINS * keys);
+        std::vector<uint32_t> cent((size_t)SAH_CENT * keys), active(SAH_MAX_LEVELS + 2u, 0u);
         uint32_t rootGap = 0;
         for (uint32_t i = 0; i < n; ++i) idx[0][i] = i;
         for (uint32_t k = 0; k < keys; ++k)
         {
-            sahCentClear(&cent[k * 6u]);
-            for (uint32_t b = 0; b < SAH_BINS; ++b) sahBinClear(&bins[k * SAH_BINS + b]);
+            sahCentClear(&cent[k * SAH_CENT]);
+            for (uint32_t b = 0; b < SAH_RANGE_BINS; ++b) sahBinClear(&bins[k * SAH_RANGE_BINS + b]);
         }
         range[0][0] = SahRange{0u, n, -1, 0u};
         active[0] = 1;
@@ -258,12 +258,12 @@ static void buildTlasHost(hs_ctx *c)
 extern "C" {
 
 // flags: bit 0 = software filter for material taps (PRT_CFG_EXACT_FILTER), bit 1 = PLOC builder (PRT_CFG_PLOC),
-// bit 2 = binned-SAH builder (PRT_CFG_BINNED_SAH)
+// bit 2 = Karras BLAS builder (PRT_CFG_LBVH_BLAS) instead of the default binned SAH
 hs_ctx *hs_create(const orc_scene *scene, int flags)
 {
     const int exactMaterialFilter = flags & 1;
     const bool ploc = (flags & 2) != 0;
-    const bool sah = (flags & 4) != 0;
+    const bool sah = (flags & (2 | 4)) == 0;
     hs_ctx *c = new hs_ctx;
     c->s = *scene;
     const orc_scene &s = c->s;

@@ -121,10 +121,10 @@ def test_primary_ids_ploc_builder(small_atrium_instanced):
     world.close()
 
 
-def test_primary_ids_and_radiance_binned_sah_builder(small_atrium_instanced, test_scene):
-    # PRT_CFG_BINNED_SAH: top-down binned-SAH BLAS topology (k_sah_*), the same hit records and the same image
+def test_primary_ids_and_radiance_karras_blas_builder(small_atrium_instanced, test_scene):
+    # PRT_CFG_LBVH_BLAS: Karras BLAS topology instead of the default binned SAH (k_sah_*): the same hit records, the same image
     for scene, (w, h) in ((small_atrium_instanced, (160, 90)), (test_scene, (96, 64))):
-        world = rt.World(scene, max_width=w, max_height=h, flags=rt.CFG_COUNTERS | rt.CFG_BINNED_SAH)
+        world = rt.World(scene, max_width=w, max_height=h, flags=rt.CFG_COUNTERS | rt.CFG_LBVH_BLAS)
         world.updateBuffers()
         world.buildAccelerationStructures()
         orc = oracle.Oracle(scene)

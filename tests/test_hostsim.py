@@ -41,10 +41,10 @@ def test_ploc_builder_bit_exact(small_atrium_instanced, small_helmet):
         assert hs.trace_counters()["overflow"] == 0
 
 
-def test_binned_sah_builder_bit_exact(small_atrium_instanced, small_helmet, test_scene):
-    # PRT_CFG_BINNED_SAH: the top-down binned-SAH topology through the same collapse; hit records unchanged
+def test_karras_blas_builder_bit_exact(small_atrium_instanced, small_helmet, test_scene):
+    # PRT_CFG_LBVH_BLAS: the Karras topology instead of the default binned SAH, through the same collapse; hit records unchanged
     for scene, (w, h) in ((small_atrium_instanced, (160, 90)), (small_helmet, (128, 128)), (test_scene, (96, 64))):
-        orc, hs = oracle.Oracle(scene), hostsim.HostSim(scene, binned_sah=True)
+        orc, hs = oracle.Oracle(scene), hostsim.HostSim(scene, lbvh_blas=True)
         st = hs.stats()
         assert st["buildError"] == 0 and st["blasTris"] == scene.triangle_count
         pc = sd.reference_pc(frame_index=3)
