@@ -314,14 +314,15 @@ HD void plocRelabelNode(const Lbvh &t, uint32_t node, const uint32_t *newPos)
 // included (the union of a range's bin boxes), so no refit pass follows. Ranges whose centroids coincide, and every
 // range from level SAH_MEDIAN_LEVEL on, are binned by primitive index and split at the most balanced border.
 #ifndef PRT_SAH_BINS
-#define PRT_SAH_BINS 16
+#define PRT_SAH_BINS 64 // measured on the atrium: 8 / 16 / 32 / 64 bins trace at 884 / 867 / 890 / 896 Mrays/s
 #endif
 #ifndef PRT_SAH_AXES
 #define PRT_SAH_AXES 1 // 1: bin along the longest centroid axis; 3: along every axis, cheapest split of all (measured: no faster to trace)
 #endif
 constexpr uint32_t SAH_BINS = PRT_SAH_BINS;
 constexpr uint32_t SAH_AXES = PRT_SAH_AXES;
-constexpr uint32_t SAH_RANGE_BINS = SAH_BINS * SAH_AXES; // bins of one range: [axis slot][bin]
+constexpr uint32_t SAH_RANGE_BINS = SAH_BINS * SAH_AXES; // most bins one range uses: [axis slot][sahBinsFor(count)]
+constexpr uint32_t SAH_SLOT_BINS = 2u * SAH_AXES;        // bins reserved per slot: a range owns [first, first + count) * SAH_SLOT_BINS
 constexpr uint32_t SAH_FINAL = 0xFFFFFFFFu;   // slot key: the slot is a finished leaf
 constexpr uint32_t SAH_MEDIAN = 0xFFFFFFFFu;  // SahSplit::axisBin: halve by position (safety net, see sahSplitPass)
 constexpr uint32_t SAH_INDEX_AXIS = 3u;       // axis code: the primitive index (coincident centroids, depth bound)
@@ -359,7 +360,7 @@ struct Sah
     const SahRange *rangeIn;
     SahRange *rangeOut;
     SahSplit *split;  // [keys]
-    SahBin *bins;     // [keys][SAH_RANGE_BINS]
+    SahBin *bins;     // [count * SAH_SLOT_BINS]; a range's bins start at first * SAH_SLOT_BINS (sahBinsFor(count) <= 2 * count)
     uint32_t *cent;   // [keys][SAH_CENT] centroid bounds in ordF form + primitive index bounds
     uint32_t *active; // [SAH_MAX_LEVELS + 1] ranges created by each level
     uint32_t *rootGap;
@@ -376,8 +377,10 @@ struct SahAxes
     bool byIndex;
     uint32_t idxMin, idxSpan;
 };
+// Bins a range of `count` primitives uses: small ranges (most ranges of the deep levels) sweep and clear only a few.
+HD uint32_t sahBinsFor(uint32_t count) { return count >= SAH_BINS / 2u ? SAH_BINS : (count < 2u ? 4u : count * 2u); }
 HD float sahCentroid(const Box &b, uint32_t axis) { return (b.lo[axis] + b.hi[axis]) * 0.5f; }
-HD SahAxes sahAxes(const uint32_t *cent, uint32_t level)
+HD SahAxes sahAxes(const uint32_t *cent, uint32_t level, uint32_t nb)
 {
     float lo[3], ext[3];
     uint32_t longest = 0;
@@ -391,23 +394,23 @@ HD SahAxes sahAxes(const uint32_t *cent, uint32_t level)
     for (uint32_t k = 0; k < SAH_AXES; ++k)
     {
         const uint32_t a = SAH_AXES == 3 ? k : longest;
-        float scale = ext[a] > 0.0f ? (float)SAH_BINS / ext[a] : 0.0f;
+        float scale = ext[a] > 0.0f ? (float)nb / ext[a] : 0.0f;
         if (!(scale < 3.0e38f)) scale = 0.0f; // denormal extent: treat as coincident
         r.axis[k] = a; r.cmin[k] = lo[a]; r.scale[k] = scale;
     }
-    r.byIndex = level >= SAH_MEDIAN_LEVEL || !(ext[longest] > 0.0f) || !((float)SAH_BINS / ext[longest] < 3.0e38f);
+    r.byIndex = level >= SAH_MEDIAN_LEVEL || !(ext[longest] > 0.0f) || !((float)nb / ext[longest] < 3.0e38f);
     r.idxMin = cent[6];
     r.idxSpan = cent[7] - cent[6] + 1u;
     return r;
 }
-HD uint32_t sahIndexBinOf(uint32_t prim, uint32_t idxMin, uint32_t idxSpan)
+HD uint32_t sahIndexBinOf(uint32_t prim, uint32_t idxMin, uint32_t idxSpan, uint32_t nb)
 {
-    return (uint32_t)(((uint64_t)(prim - idxMin) * SAH_BINS) / idxSpan);
+    return (uint32_t)(((uint64_t)(prim - idxMin) * nb) / idxSpan);
 }
-HD uint32_t sahBinOf(float c, float cmin, float scale)
+HD uint32_t sahBinOf(float c, float cmin, float scale, uint32_t nb)
 {
     const float f = (c - cmin) * scale;
-    const int b = f > 0.0f ? (int)fminf_(f, (float)(SAH_BINS - 1)) : 0;
+    const int b = f > 0.0f ? (int)fminf_(f, (float)(nb - 1u)) : 0;
     return (uint32_t)b;
 }
 HD void sahBinAdd(SahBin *dst, const Box &b)
@@ -444,19 +447,22 @@ HD void sahCentroidPass(const Sah &s, uint32_t slot)
     atomMax(&s.cent[key * SAH_CENT + 7u], prim);
 }
 // pass 2, per slot: adds the slot's primitive to one bin per axis slot of `dst` (the range's bins or a block's copy)
-HD void sahBinInto(const Sah &s, uint32_t slot, uint32_t key, SahBin *dst)
+HD void sahBinInto(const Sah &s, uint32_t slot, uint32_t key, uint32_t count, SahBin *dst)
 {
-    const SahAxes ax = sahAxes(&s.cent[key * SAH_CENT], s.level);
+    const uint32_t nb = sahBinsFor(count);
+    const SahAxes ax = sahAxes(&s.cent[key * SAH_CENT], s.level, nb);
     const uint32_t prim = s.idxIn[slot];
     const Box b = s.t.primBox[prim];
-    if (ax.byIndex) { sahBinAdd(&dst[sahIndexBinOf(prim, ax.idxMin, ax.idxSpan)], b); return; }
+    if (ax.byIndex) { sahBinAdd(&dst[sahIndexBinOf(prim, ax.idxMin, ax.idxSpan, nb)], b); return; }
     for (uint32_t k = 0; k < SAH_AXES; ++k)
-        sahBinAdd(&dst[k * SAH_BINS + sahBinOf(sahCentroid(b, ax.axis[k]), ax.cmin[k], ax.scale[k])], b);
+        sahBinAdd(&dst[k * nb + sahBinOf(sahCentroid(b, ax.axis[k]), ax.cmin[k], ax.scale[k], nb)], b);
 }
 HD void sahBinPass(const Sah &s, uint32_t slot)
 {
     const uint32_t key = s.keyIn[slot];
-    if (key != SAH_FINAL) sahBinInto(s, slot, key, &s.bins[key * SAH_RANGE_BINS]);
+    if (key == SAH_FINAL) return;
+    const SahRange r = s.rangeIn[key];
+    sahBinInto(s, slot, key, r.count, &s.bins[(size_t)r.first * SAH_SLOT_BINS]);
 }
 HD uint32_t sahNodeOfGap(uint32_t gap, uint32_t rootGap) { return gap == rootGap ? 0u : (gap == 0u ? rootGap : gap); }
 HD float sahOrdHalfArea(const uint32_t *lo, const uint32_t *hi)
@@ -471,19 +477,20 @@ HD void sahSplitPass(const Sah &s, uint32_t slot)
     if (key == SAH_FINAL) return;
     const SahRange r = s.rangeIn[key];
     if (slot != r.first) return;
-    const SahAxes ax = sahAxes(&s.cent[key * SAH_CENT], s.level);
+    const uint32_t nb = sahBinsFor(r.count);
+    const SahAxes ax = sahAxes(&s.cent[key * SAH_CENT], s.level, nb);
     sahCentClear(&s.cent[key * SAH_CENT]);
     float bestCost = 3.4e38f;
     uint32_t bestBin = 0, bestLeft = 0, bestSlot = 0;
     Box nodeBox{};
     for (uint32_t k = 0; k < (ax.byIndex ? 1u : SAH_AXES); ++k)
     {
-        SahBin *bins = &s.bins[key * SAH_RANGE_BINS + k * SAH_BINS];
-        // suffix sweep: area and count of bins [i, SAH_BINS)
+        SahBin *bins = &s.bins[(size_t)r.first * SAH_SLOT_BINS + k * nb];
+        // suffix sweep: area and count of bins [i, nb)
         float areaR[SAH_BINS];
         uint32_t countR[SAH_BINS];
         uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u}, cnt = 0;
-        for (int i = (int)SAH_BINS - 1; i >= 0; --i)
+        for (int i = (int)nb - 1; i >= 0; --i)
         {
             const SahBin b = bins[i];
             if (b.count)
@@ -498,7 +505,7 @@ HD void sahSplitPass(const Sah &s, uint32_t slot)
             for (int a = 0; a < 3; ++a) { nodeBox.lo[a] = unordF(lo[a]); nodeBox.hi[a] = unordF(hi[a]); }
         // prefix sweep + choice (ties keep the earlier axis and bin)
         uint32_t llo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, lhi[3] = {0u, 0u, 0u}, lcnt = 0;
-        for (uint32_t i = 1; i < SAH_BINS; ++i)
+        for (uint32_t i = 1; i < nb; ++i)
         {
             const SahBin b = bins[i - 1];
             if (b.count)
@@ -511,7 +518,7 @@ HD void sahSplitPass(const Sah &s, uint32_t slot)
                                           : sahOrdHalfArea(llo, lhi) * (float)lcnt + areaR[i] * (float)countR[i];
             if (cost < bestCost) { bestCost = cost; bestBin = i; bestLeft = lcnt; bestSlot = k; }
         }
-        for (uint32_t i = 0; i < SAH_BINS; ++i) sahBinClear(&bins[i]);
+        for (uint32_t i = 0; i < nb; ++i) sahBinClear(&bins[i]);
     }
     SahSplit sp;
     sp.first = r.first; sp.count = r.count; sp.cursorL = 0; sp.cursorR = 0;
@@ -546,11 +553,11 @@ HD bool sahSlotSide(const Sah &s, uint32_t slot, uint32_t prim, const SahSplit &
     if (sp.axisBin == SAH_MEDIAN) { side = (slot - sp.first) >= sp.leftCount ? 1u : 0u; return false; }
     if ((sp.axisBin >> 8) == SAH_INDEX_AXIS)
     {
-        side = sahIndexBinOf(prim, f2u(sp.cmin), f2u(sp.scale)) >= (sp.axisBin & 0xFFu) ? 1u : 0u;
+        side = sahIndexBinOf(prim, f2u(sp.cmin), f2u(sp.scale), sahBinsFor(sp.count)) >= (sp.axisBin & 0xFFu) ? 1u : 0u;
         return true;
     }
     const Box b = s.t.primBox[prim];
-    side = sahBinOf(sahCentroid(b, sp.axisBin >> 8), sp.cmin, sp.scale) >= (sp.axisBin & 0xFFu) ? 1u : 0u;
+    side = sahBinOf(sahCentroid(b, sp.axisBin >> 8), sp.cmin, sp.scale, sahBinsFor(sp.count)) >= (sp.axisBin & 0xFFu) ? 1u : 0u;
     return true;
 }
 HD void sahPlace(const Sah &s, uint32_t pos, uint32_t prim, const SahSplit &sp, uint32_t side)

@@ -226,11 +226,9 @@ __global__ void k_sah_init(Sah s, uint32_t keys, uint32_t *idx0, uint32_t *key0,
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < s.t.count) { idx0[i] = i; key0[i] = 0u; }
-    if (i < keys)
-    {
-        sahCentClear(&s.cent[i * SAH_CENT]);
-        for (uint32_t b = 0; b < SAH_RANGE_BINS; ++b) sahBinClear(&s.bins[i * SAH_RANGE_BINS + b]);
-    }
+    if (i < s.t.count)
+        for (uint32_t b = 0; b < SAH_SLOT_BINS; ++b) sahBinClear(&s.bins[(size_t)i * SAH_SLOT_BINS + b]);
+    if (i < keys) sahCentClear(&s.cent[i * SAH_CENT]);
     if (i <= SAH_MAX_LEVELS) s.active[i] = i == 0 ? 1u : 0u;
     if (i == 0) { range0[0] = SahRange{0u, s.t.count, -1, 0u}; *s.rootGap = 0u; }
 }
@@ -285,11 +283,13 @@ __global__ void __launch_bounds__(SAH_THREADS) k_sah_bin(Sah s)
         if (slot < s.t.count) sahBinPass(s, slot);
         return;
     }
-    if (threadIdx.x < SAH_RANGE_BINS) sahBinClear(&sb[threadIdx.x]);
+    const SahRange r = s.rangeIn[key];
+    const uint32_t used = sahBinsFor(r.count) * SAH_AXES; // same [axis slot][bin] layout as the range's own bins
+    if (threadIdx.x < used) sahBinClear(&sb[threadIdx.x]);
     __syncthreads();
-    if (slot < s.t.count) sahBinInto(s, slot, key, sb);
+    if (slot < s.t.count) sahBinInto(s, slot, key, r.count, sb);
     __syncthreads();
-    if (threadIdx.x < SAH_RANGE_BINS && sb[threadIdx.x].count) sahBinMerge(&s.bins[key * SAH_RANGE_BINS + threadIdx.x], sb[threadIdx.x]);
+    if (threadIdx.x < used && sb[threadIdx.x].count) sahBinMerge(&s.bins[(size_t)r.first * SAH_SLOT_BINS + threadIdx.x], sb[threadIdx.x]);
 }
 
 __global__ void k_sah_split(Sah s)

@@ -821,7 +821,7 @@ static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *la
         // every eighth level. Scalars: [243] the root's gap, [256 .. 256 + SAH_MAX_LEVELS] ranges per level.
         const uint32_t keys = n / 2u + 1u;
         for (int i = 0; i < 2; ++i) { CK(c->bSahKey[i].ensure(n)); CK(c->bSahRange[i].ensure(keys)); }
-        CK(c->bSahCent.ensure((size_t)SAH_CENT * keys)); CK(c->bSahSplit.ensure(keys)); CK(c->bSahBins.ensure((size_t)SAH_RANGE_BINS * keys));
+        CK(c->bSahCent.ensure((size_t)SAH_CENT * keys)); CK(c->bSahSplit.ensure(keys)); CK(c->bSahBins.ensure((size_t)SAH_SLOT_BINS * n));
         Sah s{};
         s.t = t;
         s.split = c->bSahSplit.p; s.bins = c->bSahBins.p; s.cent = c->bSahCent.p;

@@ -59,15 +59,12 @@ HostBvh buildHierarchyHost(std::vector<Box> &boxes, V3 lo, V3 hi, bool tlas, boo
         std::vector<uint32_t> key[2] = {std::vector<uint32_t>(n, 0u), std::vector<uint32_t>(n)};
         std::vector<SahRange> range[2] = {std::vector<SahRange>(keys), std::vector<SahRange>(keys)};
         std::vector<SahSplit> split(keys);
-        std::vector<SahBin> bins((size_t)SAH_RANGE_BINS * keys);
+        std::vector<SahBin> bins((size_t)SAH_SLOT_BINS * n);
         std::vector<uint32_t> cent((size_t)SAH_CENT * keys), active(SAH_MAX_LEVELS + 2u, 0u);
         uint32_t rootGap = 0;
         for (uint32_t i = 0; i < n; ++i) idx[0][i] = i;
-        for (uint32_t k = 0; k < keys; ++k)
-        {
-            sahCentClear(&cent[k * SAH_CENT]);
-            for (uint32_t b = 0; b < SAH_RANGE_BINS; ++b) sahBinClear(&bins[k * SAH_RANGE_BINS + b]);
-        }
+        for (uint32_t k = 0; k < keys; ++k) sahCentClear(&cent[k * SAH_CENT]);
+        for (SahBin &b : bins) sahBinClear(&b);
         range[0][0] = SahRange{0u, n, -1, 0u};
         active[0] = 1;
         Sah s{};
