@@ -2,9 +2,9 @@
 //
 // Replaces what the Vulkan driver does behind vkCmdBuildAccelerationStructuresKHR for prosper
 // (BLAS: src/scene/World.cpp:585-747; TLAS, rebuilt every frame: World.cpp:749-802, 878-961).
-// Pipeline (kernels.cu wires these bodies to launches): primitive boxes -> 63-bit Morton keys ->
-// radix sort -> Karras hierarchy -> bottom-up refit -> surface-area-driven collapse into 8-wide
-// nodes -> quantised 80-byte nodes + primitive records in node order.
+// Pipeline (kernels_build.cuh wires these bodies to launches): primitive boxes -> a binary hierarchy (BLAS: top-down
+// binned SAH; TLAS: 63-bit Morton keys -> radix sort -> Karras hierarchy -> bottom-up refit) -> surface-area-driven
+// collapse into 8-wide nodes -> quantised 80-byte nodes + primitive records in node order.
 #pragma once
 #include "hd.h"
 
@@ -440,17 +440,17 @@ HD void sahCentroidPass(const Sah &s, uint32_t slot)
     for (uint32_t a = 0; a < 3; ++a)
     {
         const uint32_t o = ordF(sahCentroid(b, a));
-        atomMin(&s.cent[key * SAH_CENT + a], o);
-        atomMax(&s.cent[key * SAH_CENT + 3u + a], o);
+        atomMin(&s.cent[(size_t)key * SAH_CENT + a], o);
+        atomMax(&s.cent[(size_t)key * SAH_CENT + 3u + a], o);
     }
-    atomMin(&s.cent[key * SAH_CENT + 6u], prim);
-    atomMax(&s.cent[key * SAH_CENT + 7u], prim);
+    atomMin(&s.cent[(size_t)key * SAH_CENT + 6u], prim);
+    atomMax(&s.cent[(size_t)key * SAH_CENT + 7u], prim);
 }
 // pass 2, per slot: adds the slot's primitive to one bin per axis slot of `dst` (the range's bins or a block's copy)
 HD void sahBinInto(const Sah &s, uint32_t slot, uint32_t key, uint32_t count, SahBin *dst)
 {
     const uint32_t nb = sahBinsFor(count);
-    const SahAxes ax = sahAxes(&s.cent[key * SAH_CENT], s.level, nb);
+    const SahAxes ax = sahAxes(&s.cent[(size_t)key * SAH_CENT], s.level, nb);
     const uint32_t prim = s.idxIn[slot];
     const Box b = s.t.primBox[prim];
     if (ax.byIndex) { sahBinAdd(&dst[sahIndexBinOf(prim, ax.idxMin, ax.idxSpan, nb)], b); return; }
@@ -478,8 +478,8 @@ HD void sahSplitPass(const Sah &s, uint32_t slot)
     const SahRange r = s.rangeIn[key];
     if (slot != r.first) return;
     const uint32_t nb = sahBinsFor(r.count);
-    const SahAxes ax = sahAxes(&s.cent[key * SAH_CENT], s.level, nb);
-    sahCentClear(&s.cent[key * SAH_CENT]);
+    const SahAxes ax = sahAxes(&s.cent[(size_t)key * SAH_CENT], s.level, nb);
+    sahCentClear(&s.cent[(size_t)key * SAH_CENT]);
     float bestCost = 3.4e38f;
     uint32_t bestBin = 0, bestLeft = 0, bestSlot = 0;
     Box nodeBox{};

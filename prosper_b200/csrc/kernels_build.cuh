@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(SAH_THREADS) k_sah_centroid(Sah s)
     }
     if ((threadIdx.x & 31u) == 0u)
     {
-        uint32_t *cent = &s.cent[key * SAH_CENT];
+        uint32_t *cent = &s.cent[(size_t)key * SAH_CENT];
         for (uint32_t a = 0; a < 3; ++a) { atomicMin(&cent[a], lo[a]); atomicMax(&cent[3u + a], hi[a]); }
         atomicMin(&cent[6], lo[3]);
         atomicMax(&cent[7], hi[3]);
