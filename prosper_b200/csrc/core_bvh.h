@@ -319,6 +319,10 @@ HD void plocRelabelNode(const Lbvh &t, uint32_t node, const uint32_t *newPos)
 #ifndef PRT_SAH_AXES
 #define PRT_SAH_AXES 1 // 1: bin along the longest centroid axis; 3: along every axis, cheapest split of all (measured: no faster to trace)
 #endif
+#ifndef PRT_SAH_GRANULE
+#define PRT_SAH_GRANULE 1 // primitives per unit of leaf cost in the SAH sum (experiment: 3 = one leaf slot of the wide node)
+#endif
+constexpr uint32_t SAH_GRANULE = PRT_SAH_GRANULE;
 constexpr uint32_t SAH_BINS = PRT_SAH_BINS;
 constexpr uint32_t SAH_AXES = PRT_SAH_AXES;
 constexpr uint32_t SAH_RANGE_BINS = SAH_BINS * SAH_AXES; // most bins one range uses: [axis slot][sahBinsFor(count)]
@@ -515,7 +519,8 @@ HD void sahSplitPass(const Sah &s, uint32_t slot)
             }
             if (lcnt == 0 || countR[i] == 0) continue;
             const float cost = ax.byIndex ? (float)(lcnt > countR[i] ? lcnt - countR[i] : countR[i] - lcnt)
-                                          : sahOrdHalfArea(llo, lhi) * (float)lcnt + areaR[i] * (float)countR[i];
+                                          : sahOrdHalfArea(llo, lhi) * (float)((lcnt + SAH_GRANULE - 1u) / SAH_GRANULE) +
+                                                areaR[i] * (float)((countR[i] + SAH_GRANULE - 1u) / SAH_GRANULE);
             if (cost < bestCost) { bestCost = cost; bestBin = i; bestLeft = lcnt; bestSlot = k; }
         }
         for (uint32_t i = 0; i < nb; ++i) sahBinClear(&bins[i]);
