@@ -517,3 +517,34 @@ def test_ray_reordering_does_not_change_the_image(small_atrium_instanced, monkey
         world.close()
     assert counters[0] == counters[1]
     assert np.array_equal(images[0], images[1])
+
+
+def test_scene_loaded_from_prosper_mesh_cache_files(tmp_path, test_scene):
+    """Row a26 / f1: every mesh written as a .prosper_mesh file, read back and uploaded in reverse order through
+    uploadGeometryData's offset arithmetic (prosper_b200/mesh_cache.py); the GPU's hit records and image through the C ABI
+    equal the oracle's on the ORIGINAL scene."""
+    import dataclasses
+    from prosper_b200 import mesh_cache as mc
+    scene, (w, h) = test_scene, (96, 64)
+    n = len(scene.mesh_infos)
+    cache = mc.GeometryCache()
+    for m in range(n):
+        hd, blob = mc.extract_mesh(scene.geometry_buffers[int(scene.metadatas[m]["bufferIndex"])], scene.metadatas[m], scene.mesh_infos[m])
+        mc.write_cache(str(tmp_path), 7, m, hd, blob)
+    for m in reversed(range(n)):
+        hd, blob = mc.read_cache(mc.cache_path(str(tmp_path), m))
+        cache.upload(hd, blob, int(scene.mesh_infos[m]["materialIndex"]))
+    bufs, mds, infos = cache.finish()
+    sub, draws = scene.sub_models.copy(), scene.draw_instances.copy()
+    sub["meshIndex"] = n - 1 - sub["meshIndex"]
+    draws["meshIndex"] = n - 1 - draws["meshIndex"]
+    rebuilt = dataclasses.replace(scene, geometry_buffers=bufs, metadatas=mds, mesh_infos=infos, sub_models=sub, draw_instances=draws)
+    world = _world(rebuilt, w, h)
+    orc = oracle.Oracle(scene)
+    pc = sd.reference_pc(frame_index=1)
+    ho, margin = orc.trace_primary(pc, w, h)
+    hg = world.trace_primary(pc, w, h)
+    assert (_id_mismatch(ho, hg) & ~(margin < ALPHA_TIE_MARGIN)).sum() == 0
+    same = ~_id_mismatch(ho, hg)
+    assert np.array_equal(ho["bary"][same], hg["bary"][same])
+    world.close()
