@@ -46,6 +46,8 @@ def lib():
         l.hs_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_int]
         l.hs_render.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_int, C.c_void_p]
         l.hs_bc7_decode_block.restype = C.c_int
+        l.hs_build_check.restype = C.c_uint32
+        l.hs_build_check.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
         l.hs_replace_blas.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
         _lib = l
     return _lib
@@ -109,3 +111,13 @@ class HostSim:
         pc = np.ascontiguousarray(pc.reshape(1))
         lib().hs_render(self._ctx, _p(pc), width, height, samples, _p(rgba), threads, _p(counters))
         return rgba, counters
+
+
+def build_check(boxes, builder: str = "sah"):
+    """Builds the BLAS hierarchy over bare boxes [n, 6] (lo xyz, hi xyz) and validates the wide tree.
+    Returns dict(nodes, levels, depth, errors)."""
+    import numpy as np
+    b = np.ascontiguousarray(boxes, dtype=np.float32).reshape(-1, 6)
+    out = (C.c_uint32 * 4)()
+    lib().hs_build_check(b.ctypes.data_as(C.c_void_p), len(b), {"sah": 0, "lbvh": 1, "ploc": 2}[builder], out)
+    return dict(nodes=out[0], levels=out[1], depth=out[2], errors=out[3])

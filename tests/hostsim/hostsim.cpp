@@ -506,4 +506,63 @@ int hs_bc7_decode_block(const uint8_t block[16], uint8_t out[64])
     return bc7DecodeBlock(lo, hi, (uint32_t *)out) ? 0 : -1;
 }
 
+// Builder check on bare boxes (n x {lo xyz, hi xyz}): builds the BLAS hierarchy with builder 0 = binned SAH, 1 = Karras,
+// 2 = PLOC and walks the wide tree. out: [0] wide nodes, [1] collapse levels, [2] depth of the wide tree, [3] errors
+// (a primitive missing or repeated in the node-order permutation, or a primitive box sticking out of a slot box on its
+// path). Returns [3].
+struct CheckWalk
+{
+    const HostBvh &h;
+    const std::vector<Box> &boxes;
+    std::vector<uint32_t> seen;
+    uint32_t errors = 0, depth = 0;
+    void walk(uint32_t nodeIndex, uint32_t level, const Box *bounds, uint32_t nBounds)
+    {
+        depth = std::max(depth, level);
+        const WideNode &n = h.nodes[nodeIndex];
+        const float sx = u2f((uint32_t)n.ex << 23), sy = u2f((uint32_t)n.ey << 23), sz = u2f((uint32_t)n.ez << 23);
+        std::vector<Box> path(bounds, bounds + nBounds);
+        path.push_back(Box{});
+        uint32_t child = n.childBase;
+        for (int s = 0; s < 8; ++s)
+        {
+            if (n.meta[s] == 0) continue;
+            path.back() = Box{{n.px + n.qlo[0][s] * sx, n.py + n.qlo[1][s] * sy, n.pz + n.qlo[2][s] * sz},
+                              {n.px + n.qhi[0][s] * sx, n.py + n.qhi[1][s] * sy, n.pz + n.qhi[2][s] * sz}};
+            if (n.imask & (1u << s)) { walk(child++, level + 1, path.data(), (uint32_t)path.size()); continue; }
+            const uint32_t count = (uint32_t)popc((uint32_t)n.meta[s] >> 5), offset = n.meta[s] & 31u;
+            for (uint32_t j = 0; j < count; ++j)
+            {
+                const uint32_t slot = n.primBase + offset + j;
+                if (slot >= h.primOut.size()) { errors++; continue; }
+                const uint32_t prim = h.primOut[slot];
+                if (prim >= boxes.size()) { errors++; continue; }
+                seen[prim]++;
+                for (const Box &b : path)
+                    for (int a = 0; a < 3; ++a)
+                        if (boxes[prim].lo[a] < b.lo[a] || boxes[prim].hi[a] > b.hi[a]) { errors++; break; }
+            }
+        }
+    }
+};
+
+uint32_t hs_build_check(const float *boxesIn, uint32_t n, int builder, uint32_t out[4])
+{
+    std::vector<Box> boxes(n);
+    V3 lo = {3.4e38f, 3.4e38f, 3.4e38f}, hi = {-3.4e38f, -3.4e38f, -3.4e38f};
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        for (int a = 0; a < 3; ++a) { boxes[i].lo[a] = boxesIn[i * 6 + a]; boxes[i].hi[a] = boxesIn[i * 6 + 3 + a]; }
+        lo = vmin(lo, boxLo(boxes[i]));
+        hi = vmax(hi, boxHi(boxes[i]));
+    }
+    const HostBvh h = buildHierarchyHost(boxes, lo, hi, false, builder == 2, builder == 0); // pads the boxes in place
+    CheckWalk w{h, boxes, std::vector<uint32_t>(n, 0u)};
+    if (h.primOut.size() != n) w.errors++;
+    else if (n > 0) w.walk(0, 1, nullptr, 0);
+    for (uint32_t i = 0; i < n; ++i) if (w.seen[i] != 1u) w.errors++;
+    out[0] = (uint32_t)h.nodes.size(); out[1] = h.levels; out[2] = w.depth; out[3] = w.errors;
+    return w.errors;
+}
+
 } // extern "C"
