@@ -6,6 +6,7 @@
 // binned SAH; TLAS: 63-bit Morton keys -> radix sort -> Karras hierarchy -> bottom-up refit) -> surface-area-driven
 // collapse into 8-wide nodes -> quantised 80-byte nodes + primitive records in node order.
 #pragma once
+#include <cstddef>
 #include "hd.h"
 
 namespace prt {
@@ -47,12 +48,16 @@ HD float boxHalfArea(const Box &b)
     return ex * ey + ey * ez + ez * ex;
 }
 
-// Compressed 8-wide node, 80 bytes = five 128-bit loads (Ylitie/Karras/Laine 2017 layout).
+// Compressed 8-wide node, 80 bytes (Ylitie/Karras/Laine 2017 layout) stored at a 128-byte stride: a node never straddles
+// an L1 line and is fetched with two 256-bit loads and one 128-bit load (three L1 wavefronts per lane instead of the
+// five to seven of five 128-bit loads at a 16-byte alignment -- the L1 wavefront queue is a co-bottleneck of the trace
+// kernels).
 // Child boxes are quantised to 8 bits per plane on a per-node grid: plane = p + q * 2^(e-127).
 // meta[i]: 0 = empty slot; internal child: (1 << 5) | (24 + i); leaf: (unary count << 5) | first
 // primitive offset relative to primBase (offset + count <= 24). imask bit i = slot i is internal;
 // internal children are stored consecutively from childBase in slot order.
-struct alignas(16) WideNode
+constexpr int WIDE_NODE_BYTES = 80; // payload; sizeof(WideNode) is the 128-byte stride
+struct alignas(128) WideNode
 {
     float px, py, pz;
     uint8_t ex, ey, ez, imask;
@@ -62,11 +67,12 @@ struct alignas(16) WideNode
     uint8_t qlo[3][8];
     uint8_t qhi[3][8];
 };
-static_assert(sizeof(WideNode) == 80, "WideNode is five 16-byte words");
+static_assert(sizeof(WideNode) == 128 && offsetof(WideNode, qhi) + 24 == WIDE_NODE_BYTES, "WideNode: 80 bytes of payload at a 128-byte stride");
 
-// Triangle record in node order, 48 bytes = three 128-bit loads. e1 = v1 - v0 and e2 = v2 - v0 are
+// Triangle record in node order, 48 bytes at a 64-byte stride = one 256-bit and one 128-bit load inside one L1 line. e1 = v1 - v0 and e2 = v2 - v0 are
 // the same single-rounding subtractions the exact ray/triangle test would do, hoisted to build time.
-struct alignas(16) TriRec
+constexpr int TRI_REC_BYTES = 48; // payload; sizeof(TriRec) is the 64-byte stride
+struct alignas(64) TriRec
 {
     float v0[3];
     uint32_t primitive; // gl_PrimitiveID
@@ -75,7 +81,7 @@ struct alignas(16) TriRec
     float e2[3];
     uint32_t pad;
 };
-static_assert(sizeof(TriRec) == 48, "TriRec");
+static_assert(sizeof(TriRec) == 64, "TriRec: 48 bytes of payload at a 64-byte stride");
 
 // Any-hit record of one triangle, parallel to the TriRec array (same index): the three texture coordinates the
 // any-hit stage would otherwise fetch through the draw instance, the mesh metadata and the index buffer

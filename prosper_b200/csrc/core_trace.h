@@ -13,7 +13,7 @@
 #include "core_scene.h"
 
 #ifndef PRT_TRACE_PREFETCH
-#define PRT_TRACE_PREFETCH 0 // measured: 3 % slower on the atrium
+#define PRT_TRACE_PREFETCH 0 // measured twice (r01: -3 %, r02 pooled kernel: -14 %): prefetch.global.L1 of the next item costs more L1 than it hides
 #endif
 
 namespace prt {
@@ -41,7 +41,10 @@ struct Accel
     const WideNode *tlasNodes; // nullptr = empty scene
     const InstRec *instances;  // TLAS node order
     uint32_t instanceCount;    // 1: rays start inside the only instance (its BLAS root culls what the TLAS root would)
+    uint32_t planeBias;        // 0x47000000 (the float 32768): handed in as data so that the node test's PRMTs keep it in a
+                               // register and take their byte selectors as immediates (intersectNode)
 };
+constexpr uint32_t PLANE_BIAS = 0x47000000u;
 
 struct NodeRay
 {
@@ -176,330 +179,455 @@ HD AlphaUv loadAlphaUv(const AlphaUv *p)
 #endif
 }
 
+// __byte_perm (PRMT): result byte k = byte (sel >> 4k) & 7 of the eight bytes b:a.
+HD uint32_t bytePerm(uint32_t a, uint32_t b, uint32_t sel)
+{
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(a, b, sel);
+#else
+    const uint64_t v = ((uint64_t)b << 32) | a;
+    uint32_t r = 0;
+    for (int k = 0; k < 4; ++k) r |= (uint32_t)((v >> (8 * ((sel >> (4 * k)) & 7u))) & 255u) << (8 * k);
+    return r;
+#endif
+}
+HD float fmaf_(float a, float b, float c) { return fmaf(a, b, c); }
+
+// The 80-byte node as the five 128-bit words it is fetched in.
+struct NodeWords
+{
+    uint4 w0; // px, py, pz, ex | ey << 8 | ez << 16 | imask << 24
+    uint4 w1; // childBase, primBase, meta[0..3], meta[4..7]
+    uint4 w2; // qlo[x][0..3], qlo[x][4..7], qlo[y][0..3], qlo[y][4..7]
+    uint4 w3; // qlo[z][0..3], qlo[z][4..7], qhi[x][0..3], qhi[x][4..7]
+    uint4 w4; // qhi[y][0..3], qhi[y][4..7], qhi[z][0..3], qhi[z][4..7]
+};
+static_assert(sizeof(NodeWords) == WIDE_NODE_BYTES, "NodeWords mirrors the payload of WideNode");
+
+#if defined(__CUDA_ARCH__)
+// One 256-bit read-only load (LDG.E.256, sm_100): `p` must be 32-byte aligned.
+__device__ __forceinline__ void ldg256(const void *p, uint4 &a, uint4 &b)
+{
+    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+        : "l"(p));
+}
+#endif
+
+HD void loadNodeWords(const WideNode *p, NodeWords &n)
+{
+#if defined(__CUDA_ARCH__)
+    const char *s = reinterpret_cast<const char *>(p);
+    ldg256(s, n.w0, n.w1);
+    ldg256(s + 32, n.w2, n.w3);
+    n.w4 = __ldg(reinterpret_cast<const uint4 *>(s + 64));
+#else
+    memcpy(&n, p, sizeof(NodeWords));
+#endif
+}
+
 // Intersects the ray with the eight quantised child boxes. Returns the hit mask: internal children
 // in bits 24..31 at position 24 + (slot ^ octinv) (nearer octant = higher bit), leaf primitives in
 // bits 0..23.
-HD uint32_t intersectNode(const WideNode &n, const NodeRay &r, float tMin, float tMax)
+//
+// A plane sits at p + q * 2^(e-127), q in 0..255, so its ray parameter is q * s + op with s = 2^(e-127) / d and
+// op = (p - o) / d, per axis. The byte q goes straight from the packed word into the mantissa of the float
+// 32768 + q (one PRMT; no integer-to-float conversion, which is a quarter-rate XU instruction and was half of that
+// pipe's load), and the bias moves into the constant: t = (32768 + q) * s + (op - 32768 * s), one FMA per plane.
+//
+// CONSERVATIVE by construction: every rounding on the way is bounded by operand magnitude and
+// the bound is folded into the constants -- near planes use b - err, far planes b + err, with
+//   err = |1/d| * 2^-22 * (|p| + |o| + 256 * 2^(e-127))      plane position (builder rounding) and p - o
+//       + 2^-21 * (|op| + 33023 * |s|)                        the products, the bias fold and the final FMA,
+// so a point inside a child's real box always passes its slab test whatever the tree shape, including on-grid flat
+// boxes and origins next to a plane of a large node. 32768 * |s| is 128 node extents, so the widening is about
+// 1e-4 of the node's extent along the ray: no measurable loss of culling.
+HD uint32_t intersectNode(const NodeWords &n, V3 o, V3 idir, uint32_t octinv, float tMin, float tMax, uint32_t bias)
 {
-    const float sx = u2f((uint32_t)n.ex << 23) * r.ix, sy = u2f((uint32_t)n.ey << 23) * r.iy, sz = u2f((uint32_t)n.ez << 23) * r.iz;
-    const float ox = (n.px - r.o.x) * r.ix, oy = (n.py - r.o.y) * r.iy, oz = (n.pz - r.o.z) * r.iz;
+    const float kBias = 32768.f, kRel = 4.76837158e-7f /* 2^-21 */, kPos = 2.38418579e-7f /* 2^-22 */;
+    const float cx = u2f((n.w0.w & 0xFFu) << 23), cy = u2f((n.w0.w & 0xFF00u) << 15), cz = u2f((n.w0.w & 0xFF0000u) << 7);
+    const float px = u2f(n.w0.x), py = u2f(n.w0.y), pz = u2f(n.w0.z);
+    const float sx = cx * idir.x, sy = cy * idir.y, sz = cz * idir.z;
+    const float opx = (px - o.x) * idir.x, opy = (py - o.y) * idir.y, opz = (pz - o.z) * idir.z;
+    const float bx = fmaf_(-kBias, sx, opx), by = fmaf_(-kBias, sy, opy), bz = fmaf_(-kBias, sz, opz);
+    const float ex = fmaf_(fabsf(idir.x) * kPos, fmaf_(256.f, cx, fabsf(px) + fabsf(o.x)), fmaf_(fabsf(sx), 33023.f * kRel, fabsf(opx) * kRel));
+    const float ey = fmaf_(fabsf(idir.y) * kPos, fmaf_(256.f, cy, fabsf(py) + fabsf(o.y)), fmaf_(fabsf(sy), 33023.f * kRel, fabsf(opy) * kRel));
+    const float ez = fmaf_(fabsf(idir.z) * kPos, fmaf_(256.f, cz, fabsf(pz) + fabsf(o.z)), fmaf_(fabsf(sz), 33023.f * kRel, fabsf(opz) * kRel));
+    const float bnx = bx - ex, bfx = bx + ex, bny = by - ey, bfy = by + ey, bnz = bz - ez, bfz = bz + ez;
     // Entry/exit planes by ray octant instead of min/max per axis: with a non-negative direction the scaled
-    // step is non-negative and lo * s + o <= hi * s + o, so the near plane is `lo` (and vice versa) -- the same
-    // values min(x0, x1) / max(x0, x1) would pick. Branch-free so that the eight slots stay converged; an empty
-    // slot (meta == 0) contributes no bits whatever its planes say.
-    // (selected a 32-bit word at a time so that the node stays in registers)
-    uint32_t lo[6], hi[6];
-    memcpy(lo, n.qlo, 24);
-    memcpy(hi, n.qhi, 24);
-    const bool px = (r.octinv & 1u) != 0, py = (r.octinv & 2u) != 0, pz = (r.octinv & 4u) != 0;
-    const uint32_t nw[6] = {px ? lo[0] : hi[0], px ? lo[1] : hi[1], py ? lo[2] : hi[2], py ? lo[3] : hi[3], pz ? lo[4] : hi[4], pz ? lo[5] : hi[5]};
-    const uint32_t fw[6] = {px ? hi[0] : lo[0], px ? hi[1] : lo[1], py ? hi[2] : lo[2], py ? hi[3] : lo[3], pz ? hi[4] : lo[4], pz ? hi[5] : lo[5]};
+    // step is non-negative, so the near plane is `lo` (and vice versa). Selected a packed word at a time.
+    const bool dx = (octinv & 1u) != 0, dy = (octinv & 2u) != 0, dz = (octinv & 4u) != 0;
+    const uint32_t nx[2] = {dx ? n.w2.x : n.w3.z, dx ? n.w2.y : n.w3.w}, fx[2] = {dx ? n.w3.z : n.w2.x, dx ? n.w3.w : n.w2.y};
+    const uint32_t ny[2] = {dy ? n.w2.z : n.w4.x, dy ? n.w2.w : n.w4.y}, fy[2] = {dy ? n.w4.x : n.w2.z, dy ? n.w4.y : n.w2.w};
+    const uint32_t nz[2] = {dz ? n.w3.x : n.w4.z, dz ? n.w3.y : n.w4.w}, fz[2] = {dz ? n.w4.z : n.w3.x, dz ? n.w4.w : n.w3.y};
+    // meta bytes four at a time: a slot's bits are childBits << bitIndex with bitIndex = low5 (^ octinv for an internal
+    // child, whose low5 is 24 + slot) and childBits = meta >> 5 (1 for an internal child, the unary primitive count
+    // of a leaf, 0 for an empty slot, which therefore never contributes)
+    const uint32_t oct4 = octinv * 0x01010101u;
     uint32_t mask = 0;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-    for (int s = 0; s < 8; ++s)
+    for (int h = 0; h < 2; ++h)
     {
-        const uint32_t meta = n.meta[s];
-        const int w = s >> 2, sh = (s & 3) * 8;
-        const float x0 = (float)((nw[0 + w] >> sh) & 255u) * sx + ox, x1 = (float)((fw[0 + w] >> sh) & 255u) * sx + ox;
-        const float y0 = (float)((nw[2 + w] >> sh) & 255u) * sy + oy, y1 = (float)((fw[2 + w] >> sh) & 255u) * sy + oy;
-        const float z0 = (float)((nw[4 + w] >> sh) & 255u) * sz + oz, z1 = (float)((fw[4 + w] >> sh) & 255u) * sz + oz;
-        float tn = fmaxf_(fmaxf_(x0, y0), fmaxf_(z0, tMin));
-        float tf = fminf_(fminf_(x1, y1), fminf_(z1, tMax));
-        tn = tn - fabsf(tn) * 4e-7f;
-        tf = tf + fabsf(tf) * 4e-7f;
-        const uint32_t low5 = meta & 31u;
-        const uint32_t bits = ((meta & 0x18u) == 0x18u) ? (1u << (low5 ^ r.octinv)) : ((meta >> 5) << low5);
-        mask |= (tn <= tf) ? bits : 0u;
+        const uint32_t meta4 = h ? n.w1.w : n.w1.z;
+        const uint32_t inner4 = ((meta4 & (meta4 << 1)) & 0x10101010u) >> 4; // 1 per internal byte
+        const uint32_t index4 = (meta4 ^ (oct4 & (inner4 * 7u))) & 0x1F1F1F1Fu;
+        const uint32_t bits4 = (meta4 >> 5) & 0x07070707u;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int k = 0; k < 4; ++k)
+        {
+            const uint32_t sel = 0x7404u | ((uint32_t)k << 4); // bytes: 0x47, 0x00, q, 0x00 = the float 32768 + q
+            const float x0 = fmaf_(u2f(bytePerm(nx[h], bias, sel)), sx, bnx), x1 = fmaf_(u2f(bytePerm(fx[h], bias, sel)), sx, bfx);
+            const float y0 = fmaf_(u2f(bytePerm(ny[h], bias, sel)), sy, bny), y1 = fmaf_(u2f(bytePerm(fy[h], bias, sel)), sy, bfy);
+            const float z0 = fmaf_(u2f(bytePerm(nz[h], bias, sel)), sz, bnz), z1 = fmaf_(u2f(bytePerm(fz[h], bias, sel)), sz, bfz);
+            const float tn = fmaxf_(fmaxf_(x0, y0), fmaxf_(z0, tMin));
+            const float tf = fminf_(fminf_(x1, y1), fminf_(z1, tMax));
+            const uint32_t bits = ((bits4 >> (8 * k)) & 0xFFu) << ((index4 >> (8 * k)) & 0xFFu);
+            mask |= (tn <= tf) ? bits : 0u;
+        }
     }
     return mask;
 }
 
-// Traversal state of one ray, resumable one step at a time so that the persistent trace kernels can
-// retire and refill lanes between steps (kernels_render.cuh); traceRay below runs it to completion.
-struct TraceState
+// ---- pooled traversal state --------------------------------------------------------------------------------------
+// A ray in flight is six 128-bit rows plus a stack. The rows live wherever the caller puts them (`rows[i * stride]`):
+// shared memory, [row][ray][thread], in the persistent trace kernels -- every thread owns PRT_POOL_RAYS rays and advances, each round, whichever of them wants
+// the item kind the warp voted for (kernels_render.cuh) -- and plain arrays in traceRay below (the CPU simulator,
+// prt_trace_rays). Every item reads the rows it needs and writes back only what it changed, so nothing but a kind per
+// ray stays in registers between items. All row accesses are whole 128-bit rows: [thread]-contiguous uint4 columns are
+// conflict-free, while a 32-bit access at a 16-byte lane stride is a 4-way bank conflict (measured: 30 % of the
+// shared-memory wavefronts of the first pooled kernel were conflicts, with the L1 data pipe 80 % busy).
+//
+// The committed hit itself is not traversal state: a commit writes the 16-byte record straight to the caller's hit
+// queue (plus the two tie-break keys beside it), the rows keep only its t (`curT`) and a flag.
+enum : int { ROW_O = 0, ROW_D = 1, ROW_I = 2, ROW_G = 3, ROW_M = 4, ROW_P = 5, POOL_ROWS = 6 };
+//  ROW_O  origin.xyz (current space: world in the TLAS, object in a BLAS), curT = committed hit ? its t : tMax
+//  ROW_D  direction.xyz (current space), unused
+//  ROW_I  reciprocal direction.xyz (zero components nudged), octinv | TRACE_HAS_HIT
+//  ROW_G  node group (base index, hit bits | imask), primitive group (base index | TRACE_PENDING, hit bits)
+//  ROW_M  sp | (stack depth at BLAS entry + 1) << 16 (0 while in the TLAS), tMin, queue slot, instance position
+//  ROW_P  node array, triangle array of the current level (two pointers)
+enum : int { KIND_NODE = 0, KIND_TRI = 1, KIND_ANYHIT = 2, KIND_INSTANCE = 3, KIND_COUNT = 4, KIND_IDLE = 7 };
+constexpr uint32_t TRACE_PENDING = 0x80000000u; // ROW_G.z: a candidate waits for its any-hit test (parked in RayCtx::pend)
+constexpr uint32_t TRACE_HAS_HIT = 0x100u;      // ROW_I.w
+// The stack is per-thread local memory (L1). Measured alternative: the first 8 entries in shared memory next to the rows
+// and the level pointers fetched through the instance record -- 942 instead of 990 Mrays/s, because the larger carve-out
+// leaves 28 KB of L1 for nodes and triangles (hit rate 16 % instead of 31-45 %) and the two-tier entry access costs 10 %
+// more instructions.
+struct RayCtx
 {
-    float tMin, tMax;
-    NodeRay ray;     // ray in the current space (world in the TLAS, object in a BLAS)
-    const WideNode *nodes;
-    const TriRec *tris;
-    uint32_t instIndex;
-    uint32_t gx, gy; // node group: base index, hit bits | imask
-    uint32_t px, py; // primitive group: base index, hit bits
-    int sp;
-    int blasSp;      // stack depth at BLAS entry; -1 while in the TLAS
-    HitRec best;
-};
-// Rarely read part of the traversal state (instance entry/exit, any-hit): lives next to the stack in local
-// memory so that it does not hold registers across the hot node / triangle loop.
-struct TraceCold
-{
-    V3 o, d;            // world-space ray
-    uint32_t seed;      // payload.randomSeed (scene.rahit:35)
-    uint32_t instCustom;
-    const AlphaUv *uvs; // any-hit records of the current BLAS (may be nullptr)
-    float pendT, pendU, pendV; // candidate waiting for its any-hit test (TRACE_PENDING set in TraceState::px)
-    uint32_t pendTri;          // its index in the BLAS triangle array
-};
-constexpr uint32_t TRACE_PENDING = 0x80000000u;
-
-// kept apart from TraceState so that the scalar state stays in registers (a dynamically indexed member
-// would drag the whole struct into local memory)
-struct TraceStack
-{
-    uint32_t x[TRACE_STACK], y[TRACE_STACK];
-    TraceCold cold;
-    HD void put(int i, uint32_t a, uint32_t b) { x[i] = a; y[i] = b; }
-    HD void get(int i, uint32_t &a, uint32_t &b) const { a = x[i]; b = y[i]; }
+    uint4 *rows;      // row i at rows[i * stride]
+    uint32_t stride;
+    uint2 *stack;     // TRACE_STACK entries
+    uint4 *pend;      // parked any-hit candidate: t, u, v bits and the triangle index
+    HD uint4 &row(int i) const { return rows[(uint32_t)i * stride]; }
+    HD uint2 &entry(uint32_t i) const { return stack[i]; }
 };
 
-#if defined(__CUDACC__)
-// The first TRACE_SMEM_STACK entries of every thread's stack live in shared memory ([entry][thread], 8-byte
-// columns: conflict-free), deeper ones in a per-thread local array that is almost never touched.
-constexpr int TRACE_SMEM_STACK = 12;
-struct SharedTraceStack
+// Where a ray comes from and where its result goes, by queue slot.
+struct TraceIO
 {
-    uint2 *column; // &smem[0][threadIdx.x]
-    uint32_t stride; // threads per block
-    uint32_t ox[TRACE_STACK - TRACE_SMEM_STACK], oy[TRACE_STACK - TRACE_SMEM_STACK];
-    TraceCold cold;
-    __device__ __forceinline__ void put(int i, uint32_t a, uint32_t b)
-    {
-        if (i < TRACE_SMEM_STACK) column[(uint32_t)i * stride] = make_uint2(a, b);
-        else { ox[i - TRACE_SMEM_STACK] = a; oy[i - TRACE_SMEM_STACK] = b; }
-    }
-    __device__ __forceinline__ void get(int i, uint32_t &a, uint32_t &b) const
-    {
-        if (i < TRACE_SMEM_STACK) { const uint2 v = column[(uint32_t)i * stride]; a = v.x; b = v.y; }
-        else { a = ox[i - TRACE_SMEM_STACK]; b = oy[i - TRACE_SMEM_STACK]; }
-    }
+    const float4 *rayO; // world-space origin.xyz, tMin
+    const float4 *rayD; // world-space direction.xyz, tMax
+    const uint2 *ids;   // .y = payload.randomSeed (scene.rahit:35)
+    uint4 *hits;        // closest: drawInstanceIndex, primitiveID, barycentric bits (written at every commit)
+    uint2 *tie;         // closest: (instance index, geometry index) of the committed hit -- the tie-break keys
+    unsigned long long *overflow; // sticky count of dropped stack entries (never silent, in every build)
 };
+
+HD void stackPush(const RayCtx &c, uint32_t &sp, uint32_t a, uint32_t b, const TraceIO &io)
+{
+    if (sp < (uint32_t)TRACE_STACK) { c.entry(sp) = make_uint2(a, b); sp++; }
+    else if (io.overflow)
+    {
+#if defined(__CUDA_ARCH__)
+        atomicAdd(io.overflow, 1ull); // global memory
+#else
+        (*io.overflow)++;
 #endif
+    }
+}
 
-// Returns false when there is nothing to traverse (the ray is a miss).
-template <class Stack>
-HD bool traceBegin(TraceState &s, Stack &st, const Accel &as, V3 o, V3 d, float tMin, float tMax, uint32_t seed,
-                   TraceCounters *cnt = nullptr)
+HD void storeRaySpace(const RayCtx &c, V3 o, V3 d, float curT, uint32_t flags)
 {
-    s.best.drawInstanceIndex = MISS_INDEX;
-    s.best.primitiveID = MISS_INDEX;
-    s.best.u = 0.f; s.best.v = 0.f; s.best.t = tMax; s.best.instance = MISS_INDEX; s.best.geometry = 0;
-    st.cold.o = o; st.cold.d = d; st.cold.seed = seed; st.cold.instCustom = 0; st.cold.uvs = nullptr;
-    s.tMin = tMin; s.tMax = tMax;
-    s.sp = 0;
-    s.blasSp = -1;
-    setupNodeRay(s.ray, o, d);
-    s.nodes = as.tlasNodes;
-    s.tris = nullptr;
-    s.instIndex = 0;
-    s.gx = 0; s.gy = 0x80000000u;
-    s.px = 0; s.py = 0;
-    if (as.tlasNodes == nullptr) return false;
+    NodeRay r;
+    setupNodeRay(r, o, d);
+    c.row(ROW_O) = make_uint4(f2u(o.x), f2u(o.y), f2u(o.z), f2u(curT));
+    c.row(ROW_D) = make_uint4(f2u(d.x), f2u(d.y), f2u(d.z), 0u);
+    c.row(ROW_I) = make_uint4(f2u(r.ix), f2u(r.iy), f2u(r.iz), r.octinv | flags);
+}
+
+// Node and triangle arrays of the level the ray is in.
+HD void storePointers(const RayCtx &c, const WideNode *nodes, const TriRec *tris)
+{
+    const uint64_t a = (uint64_t)(uintptr_t)nodes, b = (uint64_t)(uintptr_t)tris;
+    c.row(ROW_P) = make_uint4((uint32_t)a, (uint32_t)(a >> 32), (uint32_t)b, (uint32_t)(b >> 32));
+}
+HD const WideNode *levelNodes(const uint4 &P) { return reinterpret_cast<const WideNode *>((uintptr_t)(((uint64_t)P.y << 32) | P.x)); }
+HD const TriRec *levelTris(const uint4 &P) { return reinterpret_cast<const TriRec *>((uintptr_t)(((uint64_t)P.w << 32) | P.z)); }
+// The stack's top entry, loaded at the START of an item so that a pop at its end does not wait for local memory (the
+// pop runs at ~6 of 32 lanes and its load was 19 % of the kernel's stall samples).
+HD uint2 stackTop(const RayCtx &c, uint32_t sp) { return c.entry(sp ? sp - 1u : 0u); }
+
+HD int kindOf(const uint4 &g, uint32_t blasP1)
+{
+    return (g.z & TRACE_PENDING) ? KIND_ANYHIT : (g.w != 0 ? (blasP1 ? KIND_TRI : KIND_INSTANCE) : KIND_NODE);
+}
+
+// Starts a ray in `c`. Returns its first item kind, KIND_IDLE when there is nothing to traverse (a miss).
+HD int traceBegin(const RayCtx &c, const Accel &as, const TraceIO &io, uint32_t qslot, TraceCounters *cnt)
+{
+    if (as.tlasNodes == nullptr) return KIND_IDLE;
+    const float4 wo = io.rayO[qslot], wd = io.rayD[qslot];
+    const V3 o = {wo.x, wo.y, wo.z}, d = {wd.x, wd.y, wd.z};
+    c.row(ROW_G) = make_uint4(0u, 0x80000000u, 0u, 0u);
     if (as.instanceCount == 1u)
     {
         // single-instance scene (a baked glTF such as Sponza): skip the one-node TLAS
         const InstRec &inst = as.instances[0];
         if (cnt) cnt->instances++;
-        if ((inst.mask & 0xFFu) == 0) return false;
-        s.blasSp = 0;
-        setupNodeRay(s.ray, xformPoint(inst.w2o, o), xformVector(inst.w2o, d));
-        s.nodes = inst.nodes;
-        s.tris = inst.tris;
-        st.cold.uvs = inst.uvs;
-        st.cold.instCustom = inst.customIndex;
-        s.instIndex = inst.index;
+        if ((inst.mask & 0xFFu) == 0) return KIND_IDLE;
+        storeRaySpace(c, xformPoint(inst.w2o, o), xformVector(inst.w2o, d), wd.w, 0u);
+        storePointers(c, inst.nodes, inst.tris);
+        c.row(ROW_M) = make_uint4(0u | (1u << 16), f2u(wo.w), qslot, 0u);
+        return KIND_NODE;
     }
-    return true;
+    storeRaySpace(c, o, d, wd.w, 0u);
+    storePointers(c, as.tlasNodes, nullptr);
+    c.row(ROW_M) = make_uint4(0u, f2u(wo.w), qslot, 0u);
+    return KIND_NODE;
 }
 
-// One step of traceRayEXT = ONE item of work, so that the lanes of a warp stay in lock step on items of
-// similar cost: the any-hit test of a parked candidate, or one pending primitive of the current primitive group
-// (a triangle test, or entering an instance), or one node (take the nearest pending child of the current node
-// group, intersect its eight boxes). Pops when both groups are exhausted. traceItemKind tells which it will be.
-// SHADOW = gl_RayFlagsTerminateOnFirstHitEXT (main.rgen:52). Returns true when the ray is finished.
-HD int traceItemKind(const TraceState &s) { return (s.px & TRACE_PENDING) ? 2 : (s.py != 0 ? 1 : 0); }
-// A lane with pending primitives AND pending nodes may serve either kind: postponing its primitive group (it goes
-// on the stack) is legal because the result does not depend on traversal order.
-HD bool traceCanPostpone(const TraceState &s) { return !(s.px & TRACE_PENDING) && s.py != 0 && (s.gy & 0xFF000000u) != 0; }
-
-// preferNode: take a node item even though primitives are pending (only meaningful when traceCanPostpone(s)).
-// kind: the caller's knowledge of traceItemKind(s) (-1: look it up). The trace kernels pass the warp-uniform kind
-// their vote selected, which turns the three-way choice below into a uniform branch.
-template <bool SHADOW, bool COUNT, class Stack>
-HD bool traceStep(TraceState &s, Stack &st, const Accel &as, const SceneView &sv, TraceCounters *cnt, bool preferNode = false,
-                  int kind = -1)
+// End of every item: when both groups are exhausted pop the next one (leaving the BLAS when its entries are used up);
+// an empty stack finishes the ray. Stores the group row and the state row, returns the next item kind.
+HD int traceFinishItem(const RayCtx &c, const Accel &as, const TraceIO &io, uint4 g, uint4 m, uint32_t sp, uint32_t blasP1, uint2 top)
 {
-    if (preferNode && traceCanPostpone(s))
+    if (g.w == 0 && (g.y & 0xFF000000u) == 0 && !(g.z & TRACE_PENDING))
     {
-        if (s.sp < TRACE_STACK) { st.put(s.sp, s.px, s.py); s.sp++; s.py = 0; }
-        // (a full stack keeps the primitives first: nothing is lost, only the order stays as it was)
-        kind = 0;
-    }
-    if (kind < 0) kind = traceItemKind(s);
-    if (kind == 2)
-    {
-        // scene.rahit for the candidate parked by the triangle item below (its own item kind, so that the lanes of
-        // a warp run the alpha test together instead of one or two at a time inside the triangle item)
-        s.px &= ~TRACE_PENDING;
-        const uint32_t tri = st.cold.pendTri;
-        const float t = st.cold.pendT, u = st.cold.pendU, v = st.cold.pendV;
-        const TriRec &tr = s.tris[tri];
-        const uint32_t geom = tr.geometry & 0x7FFFFFFFu;
-        const uint32_t drawInstanceIndex = st.cold.instCustom + geom;
-        if (COUNT) cnt->anyHits++;
-        const AlphaUv *uvs = st.cold.uvs;
-        const uint32_t seed = st.cold.seed;
-        bool accept = true;
-        bool fast = uvs != nullptr && sv.alphaMats != nullptr;
-        if (fast)
-        {
-            const AlphaMat am = loadAlphaMat(sv.alphaMats + drawInstanceIndex);
-            fast = (am.bits & ALPHAMAT_USABLE) != 0;
-            if (fast) accept = anyHitAcceptFast(am, loadAlphaUv(uvs + tri), u, v, seed);
-        }
-        if (!fast) accept = anyHitAccept(sv, drawInstanceIndex, tr.primitive, u, v, seed);
-        if (accept)
-        {
-            s.best.drawInstanceIndex = drawInstanceIndex;
-            s.best.primitiveID = tr.primitive;
-            s.best.u = u; s.best.v = v; s.best.t = t;
-            s.best.instance = s.instIndex;
-            s.best.geometry = geom;
-            if (SHADOW) return true;
-        }
-    }
-    else if (kind == 1)
-    {
-        const int pbit = bfind(s.py);
-        s.py &= ~(1u << pbit);
-        if (s.blasSp < 0)
-        {
-            // TLAS leaf: enter the instance (traversal state of the TLAS goes on the stack)
-            const InstRec &inst = as.instances[s.px + (uint32_t)pbit];
-            if (COUNT) cnt->instances++;
-            if ((inst.mask & 0xFFu) != 0)
-            {
-                if (s.gy & 0xFF000000u)
-                {
-                    if (s.sp < TRACE_STACK) { st.put(s.sp, s.gx, s.gy); s.sp++; }
-                    else if (COUNT) cnt->overflow++;
-                }
-                if (s.py != 0)
-                {
-                    if (s.sp < TRACE_STACK) { st.put(s.sp, s.px, s.py); s.sp++; }
-                    else if (COUNT) cnt->overflow++;
-                }
-                s.blasSp = s.sp;
-                setupNodeRay(s.ray, xformPoint(inst.w2o, st.cold.o), xformVector(inst.w2o, st.cold.d));
-                s.nodes = inst.nodes;
-                s.tris = inst.tris;
-                st.cold.uvs = inst.uvs;
-                st.cold.instCustom = inst.customIndex;
-                s.instIndex = inst.index;
-                s.gx = 0; s.gy = 0x80000000u;
-                s.py = 0;
-                return false;
-            }
-        }
-        else
-        {
-            const TriRec &tr = s.tris[s.px + (uint32_t)pbit];
-            if (COUNT) cnt->tris++;
-            float t, u, v;
-            if (intersectTriangleExact(s.ray.o, s.ray.d, s.tMin, s.tMax, V3{tr.v0[0], tr.v0[1], tr.v0[2]}, V3{tr.e1[0], tr.e1[1], tr.e1[2]},
-                                       V3{tr.e2[0], tr.e2[1], tr.e2[2]}, t, u, v))
-            {
-                const uint32_t geom = tr.geometry & 0x7FFFFFFFu;
-                if (betterHit(t, s.instIndex, geom, tr.primitive, s.best))
-                {
-                    if (!(tr.geometry >> 31))
-                    {
-                        // non-opaque geometry: park the candidate, its any-hit test is the lane's next item
-                        st.cold.pendT = t; st.cold.pendU = u; st.cold.pendV = v;
-                        st.cold.pendTri = s.px + (uint32_t)pbit;
-                        s.px |= TRACE_PENDING;
-                        return false;
-                    }
-                    s.best.drawInstanceIndex = st.cold.instCustom + geom;
-                    s.best.primitiveID = tr.primitive;
-                    s.best.u = u; s.best.v = v; s.best.t = t;
-                    s.best.instance = s.instIndex;
-                    s.best.geometry = geom;
-                    if (SHADOW) return true;
-                }
-            }
-        }
-    }
-    else if (s.gy & 0xFF000000u)
-    {
-        const int bit = bfind(s.gy);
-        const uint32_t imask = s.gy;
-        s.gy &= ~(1u << bit);
-        if (s.gy & 0xFF000000u)
-        {
-            if (s.sp < TRACE_STACK) { st.put(s.sp, s.gx, s.gy); s.sp++; }
-            else if (COUNT) cnt->overflow++;
-        }
-        const uint32_t slot = ((uint32_t)bit - 24u) ^ s.ray.octinv;
-        const uint32_t rel = (uint32_t)popc(imask & 0xFFu & ((1u << slot) - 1u));
-        WideNode n;
-        loadNode(s.nodes + s.gx + rel, n);
-        if (COUNT) cnt->nodes++;
-        const float tFar = s.best.drawInstanceIndex == MISS_INDEX ? s.tMax : fminf_(s.tMax, s.best.t);
-        const uint32_t hits = intersectNode(n, s.ray, s.tMin, tFar);
-        s.gx = n.childBase;
-        s.gy = (hits & 0xFF000000u) | n.imask;
-        s.px = n.primBase;
-        s.py = hits & 0x00FFFFFFu;
-#if PRT_TRACE_PREFETCH
-        if (s.py != 0)
-        {
-            if (s.blasSp >= 0) prefetchL1(s.tris + s.px + (uint32_t)bfind(s.py));
-        }
-        else if (s.gy & 0xFF000000u)
-        {
-            const uint32_t nslot = ((uint32_t)bfind(s.gy) - 24u) ^ s.ray.octinv;
-            const WideNode *next = s.nodes + s.gx + (uint32_t)popc(s.gy & 0xFFu & ((1u << nslot) - 1u));
-            prefetchL1(next);
-            prefetchL1(reinterpret_cast<const char *>(next) + 64);
-        }
-#endif
-    }
-
-    if (s.py == 0 && (s.gy & 0xFF000000u) == 0)
-    {
-        if (s.sp == 0) return true;
-        if (s.sp == s.blasSp)
+        if (sp == 0) return KIND_IDLE;
+        if (sp + 1u == blasP1)
         {
             // BLAS exhausted: back to world space
-            s.blasSp = -1;
-            setupNodeRay(s.ray, st.cold.o, st.cold.d);
-            s.nodes = as.tlasNodes;
+            blasP1 = 0;
+            const float4 wo = io.rayO[m.z], wd = io.rayD[m.z];
+            storeRaySpace(c, V3{wo.x, wo.y, wo.z}, V3{wd.x, wd.y, wd.z}, u2f(c.row(ROW_O).w), c.row(ROW_I).w & TRACE_HAS_HIT);
+            storePointers(c, as.tlasNodes, nullptr);
         }
-        s.sp--;
-        st.get(s.sp, s.gx, s.gy);
-        if ((s.gy & 0xFF000000u) == 0)
-        {
-            // a postponed primitive group (pushed when an instance was entered)
-            s.px = s.gx; s.py = s.gy;
-            s.gx = 0; s.gy = 0;
-        }
+        sp--;
+        const uint2 e = top;
+        if (e.y & 0xFF000000u) { g.x = e.x; g.y = e.y; g.z = 0; g.w = 0; }
+        else { g.x = 0; g.y = 0; g.z = e.x; g.w = e.y; } // a postponed primitive group (pushed when an instance was entered)
     }
+    c.row(ROW_G) = g;
+    m.x = sp | (blasP1 << 16);
+    c.row(ROW_M) = m;
+    return kindOf(g, blasP1);
+}
+
+// gl_RayFlagsTerminateOnFirstHitEXT (SHADOW, main.rgen:52): the first accepted hit ends the ray. Otherwise the record
+// goes to the hit queue and curT shrinks. `O` is the caller's copy of ROW_O. Returns true when the ray is finished.
+template <bool SHADOW>
+HD bool commitHit(const RayCtx &c, const Accel &as, const TraceIO &io, uint4 O, uint32_t qslot, uint32_t instPos, uint32_t geom, uint32_t prim,
+                  float t, float u, float v)
+{
+    uint4 I = c.row(ROW_I);
+    I.w |= TRACE_HAS_HIT;
+    c.row(ROW_I) = I;
+    if (SHADOW) return true;
+    const InstRec &inst = as.instances[instPos];
+    io.hits[qslot] = make_uint4(inst.customIndex + geom, prim, f2u(u), f2u(v));
+    io.tie[qslot] = make_uint2(inst.index, geom);
+    O.w = f2u(t);
+    c.row(ROW_O) = O;
     return false;
 }
 
-// traceRayEXT to completion. Returns true on a hit.
+// KIND_NODE: take the nearest pending child of the node group, intersect its eight boxes.
+template <bool COUNT>
+HD int traceNodeItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceCounters *cnt)
+{
+    uint4 g = c.row(ROW_G);
+    const uint4 m = c.row(ROW_M);
+    uint32_t sp = m.x & 0xFFFFu;
+    const uint32_t blasP1 = m.x >> 16;
+    uint2 top = stackTop(c, sp);
+    const WideNode *nodes = levelNodes(c.row(ROW_P));
+    const uint4 I = c.row(ROW_I);
+    const uint32_t octinv = I.w & 7u;
+    const int bit = bfind(g.y);
+    const uint32_t imask = g.y;
+    g.y &= ~(1u << bit);
+    if (g.y & 0xFF000000u)
+    {
+        if (sp < (uint32_t)TRACE_STACK) top = make_uint2(g.x, g.y);
+        stackPush(c, sp, g.x, g.y, io);
+    }
+    const uint32_t slot = ((uint32_t)bit - 24u) ^ octinv;
+    const uint32_t rel = (uint32_t)popc(imask & 0xFFu & ((1u << slot) - 1u));
+    NodeWords n;
+    loadNodeWords(nodes + g.x + rel, n);
+    if (COUNT) cnt->nodes++;
+    const uint4 O = c.row(ROW_O);
+    const uint32_t hits = intersectNode(n, V3{u2f(O.x), u2f(O.y), u2f(O.z)}, V3{u2f(I.x), u2f(I.y), u2f(I.z)}, octinv, u2f(m.y), u2f(O.w), as.planeBias);
+    g.x = n.w1.x;
+    g.y = (hits & 0xFF000000u) | (n.w0.w >> 24);
+    g.z = n.w1.y;
+    g.w = hits & 0x00FFFFFFu;
+    return traceFinishItem(c, as, io, g, m, sp, blasP1, top);
+}
+
+// KIND_TRI: one pending primitive of the primitive group inside a BLAS = one exact ray/triangle test.
+template <bool SHADOW, bool COUNT>
+HD int traceTriItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceCounters *cnt)
+{
+    uint4 g = c.row(ROW_G);
+    const uint4 m = c.row(ROW_M);
+    const TriRec *tris = levelTris(c.row(ROW_P));
+    // this item ends in a pop exactly when it tests the group's last primitive with no node child pending
+    const bool willPop = (g.w & (g.w - 1u)) == 0 && (g.y & 0xFF000000u) == 0;
+    const uint2 top = willPop ? stackTop(c, m.x & 0xFFFFu) : make_uint2(0u, 0u);
+    const int pbit = bfind(g.w);
+    g.w &= ~(1u << pbit);
+    const uint32_t triIndex = g.z + (uint32_t)pbit;
+#if defined(__CUDA_ARCH__)
+    uint4 a, b;
+    ldg256(tris + triIndex, a, b);
+    const uint4 e = __ldg(reinterpret_cast<const uint4 *>(tris + triIndex) + 2);
+#else
+    uint4 a, b, e;
+    memcpy(&a, &tris[triIndex], 16); memcpy(&b, (const char *)&tris[triIndex] + 16, 16); memcpy(&e, (const char *)&tris[triIndex] + 32, 16);
+#endif
+    if (COUNT) cnt->tris++;
+    const uint4 O = c.row(ROW_O), D = c.row(ROW_D);
+    const float curT = u2f(O.w);
+    float t, u, v;
+    // the open interval (tMin, tMax) and "closer than the committed hit" in one comparison against curT (the committed
+    // t is below tMax); an exact tie goes to the smallest (instance, geometry, primitive) -- betterHit's order
+    const bool inside = intersectTriangleExact(V3{u2f(O.x), u2f(O.y), u2f(O.z)}, V3{u2f(D.x), u2f(D.y), u2f(D.z)}, u2f(m.y), 3.402823466e38f,
+                                               V3{u2f(a.x), u2f(a.y), u2f(a.z)}, V3{u2f(b.x), u2f(b.y), u2f(b.z)}, V3{u2f(e.x), u2f(e.y), u2f(e.z)},
+                                               t, u, v);
+    bool candidate = inside & (t < curT);
+    const uint32_t geom = b.w & 0x7FFFFFFFu;
+    if (inside && t == curT && !SHADOW)
+    {
+        const uint32_t flags = c.row(ROW_I).w;
+        if (flags & TRACE_HAS_HIT)
+        {
+            const uint2 key = io.tie[m.z];
+            const uint32_t bestPrim = io.hits[m.z].y;
+            const uint32_t inst = as.instances[m.w].index;
+            candidate = inst != key.x ? inst < key.x : (geom != key.y ? geom < key.y : a.w < bestPrim);
+        }
+    }
+    if (candidate)
+    {
+        if (!(b.w >> 31))
+        {
+            // non-opaque geometry: park the candidate, its any-hit test is the ray's next item
+            *c.pend = make_uint4(f2u(t), f2u(u), f2u(v), triIndex);
+            g.z |= TRACE_PENDING;
+        }
+        else if (commitHit<SHADOW>(c, as, io, O, m.z, m.w, geom, a.w, t, u, v))
+            return KIND_IDLE;
+    }
+    return traceFinishItem(c, as, io, g, m, m.x & 0xFFFFu, m.x >> 16, top);
+}
+
+// KIND_ANYHIT: scene.rahit for the candidate parked by the triangle item (its own kind, so that the rays of a warp
+// run the alpha test together instead of one or two at a time inside the triangle item).
+template <bool SHADOW, bool COUNT>
+HD int traceAnyHitItem(const RayCtx &c, const Accel &as, const SceneView &sv, const TraceIO &io, TraceCounters *cnt)
+{
+    uint4 g = c.row(ROW_G);
+    const uint4 m = c.row(ROW_M);
+    g.z &= ~TRACE_PENDING;
+    const uint4 pd = *c.pend;
+    const float t = u2f(pd.x), u = u2f(pd.y), v = u2f(pd.z);
+    const uint32_t tri = pd.w;
+    const InstRec &inst = as.instances[m.w];
+    const TriRec *tris = inst.tris;
+    const uint32_t geom = tris[tri].geometry & 0x7FFFFFFFu, prim = tris[tri].primitive;
+    const uint32_t drawInstanceIndex = inst.customIndex + geom;
+    const uint32_t seed = io.ids[m.z].y;
+    if (COUNT) cnt->anyHits++;
+    const AlphaUv *uvs = inst.uvs;
+    bool accept = true;
+    bool fast = uvs != nullptr && sv.alphaMats != nullptr;
+    if (fast)
+    {
+        const AlphaMat am = loadAlphaMat(sv.alphaMats + drawInstanceIndex);
+        fast = (am.bits & ALPHAMAT_USABLE) != 0;
+        if (fast) accept = anyHitAcceptFast(am, loadAlphaUv(uvs + tri), u, v, seed);
+    }
+    if (!fast) accept = anyHitAccept(sv, drawInstanceIndex, prim, u, v, seed);
+    if (accept && commitHit<SHADOW>(c, as, io, c.row(ROW_O), m.z, m.w, geom, prim, t, u, v)) return KIND_IDLE;
+    return traceFinishItem(c, as, io, g, m, m.x & 0xFFFFu, m.x >> 16, stackTop(c, m.x & 0xFFFFu));
+}
+
+// KIND_INSTANCE: one pending primitive of a TLAS leaf = enter that instance (the TLAS groups go on the stack).
+template <bool COUNT>
+HD int traceInstanceItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceCounters *cnt)
+{
+    uint4 g = c.row(ROW_G);
+    uint4 m = c.row(ROW_M);
+    uint32_t sp = m.x & 0xFFFFu;
+    const int pbit = bfind(g.w);
+    g.w &= ~(1u << pbit);
+    const uint32_t instPos = g.z + (uint32_t)pbit;
+    const InstRec &inst = as.instances[instPos];
+    if (COUNT) cnt->instances++;
+    if ((inst.mask & 0xFFu) == 0) return traceFinishItem(c, as, io, g, m, sp, 0u, stackTop(c, sp));
+    if (g.y & 0xFF000000u) stackPush(c, sp, g.x, g.y, io);
+    if (g.w != 0) stackPush(c, sp, g.z, g.w, io);
+    const float4 wo = io.rayO[m.z], wd = io.rayD[m.z];
+    storeRaySpace(c, xformPoint(inst.w2o, V3{wo.x, wo.y, wo.z}), xformVector(inst.w2o, V3{wd.x, wd.y, wd.z}), u2f(c.row(ROW_O).w),
+                  c.row(ROW_I).w & TRACE_HAS_HIT);
+    storePointers(c, inst.nodes, inst.tris);
+    c.row(ROW_G) = make_uint4(0u, 0x80000000u, 0u, 0u);
+    c.row(ROW_M) = make_uint4(sp | ((sp + 1u) << 16), m.y, m.z, instPos);
+    return KIND_NODE;
+}
+
+template <bool SHADOW, bool COUNT>
+HD int traceItem(int kind, const RayCtx &c, const Accel &as, const SceneView &sv, const TraceIO &io, TraceCounters *cnt)
+{
+    switch (kind)
+    {
+    case KIND_NODE: return traceNodeItem<COUNT>(c, as, io, cnt);
+    case KIND_TRI: return traceTriItem<SHADOW, COUNT>(c, as, io, cnt);
+    case KIND_ANYHIT: return traceAnyHitItem<SHADOW, COUNT>(c, as, sv, io, cnt);
+    default: return traceInstanceItem<COUNT>(c, as, io, cnt);
+    }
+}
+
+// traceRayEXT to completion for one ray (CPU simulator, prt_trace_rays). Returns true on a hit.
 template <bool SHADOW, bool COUNT>
 HDNI bool traceRay(const Accel &as, const SceneView &sv, V3 o, V3 d, float tMin, float tMax, uint32_t seed, HitRec &best,
-                   TraceCounters *cnt)
+                   TraceCounters *cnt, unsigned long long *overflow)
 {
-    TraceState s;
-    TraceStack st;
-    if (traceBegin(s, st, as, o, d, tMin, tMax, seed, COUNT ? cnt : nullptr))
-        while (!traceStep<SHADOW, COUNT>(s, st, as, sv, cnt)) {}
-    best = s.best;
-    return best.drawInstanceIndex != MISS_INDEX;
+    uint4 rows[POOL_ROWS];
+    uint2 stack[TRACE_STACK];
+    uint4 pend;
+    const RayCtx c = {rows, 1u, stack, &pend};
+    const float4 wo = make_float4(o.x, o.y, o.z, tMin), wd = make_float4(d.x, d.y, d.z, tMax);
+    const uint2 id = make_uint2(0u, seed);
+    uint4 hit = make_uint4(MISS_INDEX, MISS_INDEX, 0u, 0u);
+    uint2 tie = make_uint2(MISS_INDEX, 0u);
+    const TraceIO io = {&wo, &wd, &id, &hit, &tie, overflow};
+    rows[ROW_I] = make_uint4(0u, 0u, 0u, 0u);
+    rows[ROW_O] = make_uint4(0u, 0u, 0u, f2u(tMax));
+    int kind = traceBegin(c, as, io, 0u, COUNT ? cnt : nullptr);
+    while (kind != KIND_IDLE) kind = traceItem<SHADOW, COUNT>(kind, c, as, sv, io, cnt);
+    const bool found = (rows[ROW_I].w & TRACE_HAS_HIT) != 0;
+    best.drawInstanceIndex = SHADOW ? (found ? 0u : MISS_INDEX) : hit.x;
+    best.primitiveID = hit.y;
+    best.u = u2f(hit.z); best.v = u2f(hit.w);
+    best.t = u2f(rows[ROW_O].w);
+    best.instance = tie.x; best.geometry = tie.y;
+    return found;
 }
 
 } // namespace prt

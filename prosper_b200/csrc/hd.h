@@ -15,6 +15,16 @@
 #define HDNI inline
 #endif
 
+#ifndef __CUDACC__
+// the CUDA vector types the per-thread bodies use, for the host (simulator) build
+struct uint2 { uint32_t x, y; };
+struct alignas(16) uint4 { uint32_t x, y, z, w; };
+struct alignas(16) float4 { float x, y, z, w; };
+inline uint2 make_uint2(uint32_t x, uint32_t y) { return uint2{x, y}; }
+inline uint4 make_uint4(uint32_t x, uint32_t y, uint32_t z, uint32_t w) { return uint4{x, y, z, w}; }
+inline float4 make_float4(float x, float y, float z, float w) { return float4{x, y, z, w}; }
+#endif
+
 namespace prt {
 
 // ---- exact IEEE binary32 operations (never contracted into FMA) ---------------------------------

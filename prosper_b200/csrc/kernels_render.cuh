@@ -16,21 +16,19 @@ constexpr int RENDER_THREADS = 128;
 constexpr uint32_t COUNT_SHADOW_BASE = 8; // counts[b] = closest rays of bounce b, counts[8 + b] = shadow rays
 constexpr uint32_t CURSOR_BASE = 16;      // counts[16 + i] = fetch cursor of the persistent trace kernel over queue i
 constexpr uint32_t COUNT_WORDS = 32;
-// Persistent trace kernels: a warp refills its retired lanes from the queue once fewer than this many
-// lanes are still traversing (Aila & Laine's dynamic fetch); below it, finished lanes idle until the refill.
-#ifndef PRT_TRACE_REFILL_BELOW
-#define PRT_TRACE_REFILL_BELOW 26
+// Persistent trace kernels (k_trace below): every thread owns PRT_POOL_RAYS rays.
+#ifndef PRT_POOL_RAYS
+#define PRT_POOL_RAYS 2
 #endif
-#ifndef PRT_TRACE_SMEM_STACK
-#define PRT_TRACE_SMEM_STACK 0
+#ifndef PRT_POOL_REFILL
+#define PRT_POOL_REFILL (8 * PRT_POOL_RAYS) // idle ray slots per warp (of 32 * PRT_POOL_RAYS) that trigger a refill
 #endif
-#ifndef PRT_TRACE_POSTPONE
-#define PRT_TRACE_POSTPONE 0 // measured: postponing primitive groups costs pruning, 586 vs 687 Mrays/s
+#ifndef PRT_TRACE_SINGLE_KIND
+#define PRT_TRACE_SINGLE_KIND 0 // 1: only the most wanted kind runs per census
 #endif
 #ifndef PRT_TRACE_MIN_BLOCKS
-#define PRT_TRACE_MIN_BLOCKS 8
+#define PRT_TRACE_MIN_BLOCKS 6
 #endif
-constexpr int TRACE_REFILL_BELOW = PRT_TRACE_REFILL_BELOW;
 
 struct PathBuffers
 {
@@ -41,6 +39,7 @@ struct PathBuffers
     float4 *rayD[2];     // direction.xyz, tMax
     uint2 *rayId[2];     // path index, payload.randomSeed
     uint4 *hits;         // per closest-ray slot: drawInstanceIndex, primitiveID, bary bits
+    uint2 *tie;          // per closest-ray slot: (instance index, geometry index) of the committed hit (tie-break keys)
     float4 *shadowO;     // shadow queue
     float4 *shadowD;
     uint2 *shadowId;
@@ -112,44 +111,6 @@ __global__ void __launch_bounds__(RENDER_THREADS)
     pb.rayO[0][p] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.tMin);
     pb.rayD[0][p] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.tMax);
     pb.rayId[0][p] = make_uint2(p, pcg(rng.state.x ^ rng.state.z)); // main.rgen:71
-}
-
-// Hands the idle lanes of a warp their next queue slots: one atomic per warp per refill. Returns the slot of this
-// lane (>= count: nothing left); `exhausted` is warp-uniform and tells that the queue has no more work to hand out.
-__device__ __forceinline__ uint32_t fetchSlots(uint32_t *cursor, uint32_t count, bool idle, bool &exhausted)
-{
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t need = __ballot_sync(0xFFFFFFFFu, idle);
-    if (need == 0) return 0xFFFFFFFFu;
-    const int leader = __ffs(need) - 1;
-    uint32_t base = 0;
-    if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)__popc(need));
-    base = __shfl_sync(0xFFFFFFFFu, base, leader);
-    exhausted = base + (uint32_t)__popc(need) >= count;
-    return idle ? base + (uint32_t)__popc(need & ((1u << lane) - 1u)) : 0xFFFFFFFFu;
-}
-
-// The item kind (0 node, 1 primitive, 2 any-hit; -1 idle) most lanes of the warp want next; `live` = lanes with a ray.
-// Ties go to the later stage, which frees lanes for the earlier ones. `flexible` lanes (kind 1 that could also take
-// a node item, traceCanPostpone; only with PRT_TRACE_POSTPONE) do not vote: they join whichever of node /
-// primitive wins.
-__device__ __forceinline__ int pluralityKind(int kind, bool flexible, int &live)
-{
-#if PRT_TRACE_POSTPONE
-    const int n0 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 0));
-    const int n2 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 2));
-    const int n1 = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1 && !flexible));
-    const int nf = __popc(__ballot_sync(0xFFFFFFFFu, kind == 1 && flexible));
-#else
-    // the three counts in one warp reduction: lane contributes 1 << (10 * kind)
-    const uint32_t sum = __reduce_add_sync(0xFFFFFFFFu, kind < 0 ? 0u : 1u << (10 * kind));
-    const int n0 = (int)(sum & 1023u), n1 = (int)((sum >> 10) & 1023u), n2 = (int)(sum >> 20);
-    const int nf = 0;
-    (void)flexible;
-#endif
-    live = n0 + n1 + n2 + nf;
-    if (n2 > 0 && n2 >= n1 + nf && n2 >= n0 + nf) return 2;
-    return n1 > n0 ? 1 : (n0 > 0 ? 0 : 1);
 }
 
 // ---- ray reordering -------------------------------------------------------------------------------------------------
@@ -251,57 +212,114 @@ __global__ void k_ray_scatter(const uint32_t *__restrict__ countPtr, const uint3
     perm[atomicAdd(&hist[keys[i]], 1u)] = i;
 }
 
-// traceClosest, main.rgen:62-81. Persistent warps over the closest-ray queue of `bounce`.
-template <bool COUNT>
+// traceClosest (main.rgen:62-81) and shadow() (main.rgen:49-60, fused with the addBounce of evaluateDirectLighting's
+// result): persistent warps over the closest-ray queue of `bounce`, or over its shadow queue (SHADOW).
+//
+// Every thread owns R rays whose state sits in shared memory ([row][ray][thread]: conflict-free 128-bit rows, core_trace.h)
+// and whose stacks sit in its local memory. One round = ONE item (a node, a triangle, an any-hit test or an instance
+// entry) for at most one ray per thread: a census of the kinds the warp's rays are waiting for (one REDUX), the most
+// wanted kind runs, and a thread advances whichever of its rays wants it. With one ray per thread 14.5 of 32 lanes
+// took part in an item (the r01 kernel: the lanes whose kind lost the vote idled); with R rays a lane idles only when
+// none of its R rays wants the winning kind. Finished rays retire in place; when `refillAt` slots of the warp are
+// idle they are refilled from the queue with one atomic (Aila & Laine's dynamic fetch).
+template <int R, bool SHADOW, bool COUNT>
 __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
-    k_trace_closest(Accel as, SceneView sv, PathBuffers pb, int q, uint32_t bounce, GlobalCounters *gc, const uint32_t *__restrict__ perm)
+    k_trace(Accel as, SceneView sv, PathBuffers pb, int q, uint32_t bounce, GlobalCounters *gc, const uint32_t *__restrict__ perm,
+            uint32_t refillAt)
 {
-    const uint32_t count = pb.counts[bounce];
-    uint32_t *cursor = &pb.counts[CURSOR_BASE + bounce];
+    __shared__ uint4 rowMem[POOL_ROWS * R * RENDER_THREADS];
+    uint2 stack[R][TRACE_STACK]; // per-thread local memory, L1-resident
+    uint4 pend[R];
+    const uint32_t lane = threadIdx.x & 31u, ltMask = (1u << lane) - 1u;
+    const uint32_t count = pb.counts[(SHADOW ? COUNT_SHADOW_BASE : 0u) + bounce];
+    uint32_t *cursor = &pb.counts[CURSOR_BASE + (SHADOW ? COUNT_SHADOW_BASE : 0u) + bounce];
+    const TraceIO io = {SHADOW ? pb.shadowO : pb.rayO[q], SHADOW ? pb.shadowD : pb.rayD[q], SHADOW ? pb.shadowId : pb.rayId[q],
+                        SHADOW ? nullptr : pb.hits, SHADOW ? nullptr : pb.tie, &gc->stackOverflows};
     TraceCounters tc = {0, 0, 0, 0, 0};
-    TraceState s;
-#if PRT_TRACE_SMEM_STACK
-    __shared__ uint2 stackMem[TRACE_SMEM_STACK * RENDER_THREADS];
-    SharedTraceStack st;
-    st.column = stackMem + threadIdx.x;
-    st.stride = RENDER_THREADS;
-#else
-    TraceStack st; // per-thread local memory, L1-resident: measured faster than the shared-memory variant
-#endif
-    bool active = false, exhausted = false;
-    uint32_t slot = 0;
+    auto ctx = [&](int r) { return RayCtx{rowMem + r * RENDER_THREADS + threadIdx.x, (uint32_t)(R * RENDER_THREADS), stack[r], &pend[r]}; };
+    auto retire = [&](uint32_t slot, bool hit) {
+        if (SHADOW)
+        {
+            if (!hit) // unoccluded
+            {
+                const float4 c = pb.shadowC[slot];
+                const uint32_t path = pb.shadowId[slot].x;
+                float4 col = pb.color[path];
+                col.x += c.x; col.y += c.y; col.z += c.z;
+                pb.color[path] = col;
+            }
+        }
+        else if (!hit) pb.hits[slot] = make_uint4(MISS_INDEX, MISS_INDEX, 0u, 0u);
+    };
+    int kind[R]; // the item each owned ray waits for (registers: every index below is a compile-time constant)
+#pragma unroll
+    for (int r = 0; r < R; ++r) kind[r] = KIND_IDLE;
+    bool exhausted = false;
     for (;;)
     {
-        if (!exhausted)
+        // census: lanes that hold a ray of each kind (6 bits per kind), idle slots (from bit 24)
+        uint32_t mine = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) mine = kind[r] == KIND_IDLE ? mine + (1u << 24) : mine | (1u << (6 * kind[r]));
+        const uint32_t census = __reduce_add_sync(0xFFFFFFFFu, mine);
+        const uint32_t idle = census >> 24;
+        if (!exhausted && idle >= refillAt)
         {
-            const uint32_t next = fetchSlots(cursor, count, !active, exhausted);
-            if (!active && next < count)
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(cursor, idle);
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            exhausted = base + idle >= count;
+#pragma unroll
+            for (int r = 0; r < R; ++r)
             {
-                slot = perm ? perm[next] : next;
-                const float4 o = pb.rayO[q][slot], d = pb.rayD[q][slot];
-                active = traceBegin(s, st, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.rayId[q][slot].y, COUNT ? &tc : nullptr);
-                if (!active) pb.hits[slot] = make_uint4(MISS_INDEX, MISS_INDEX, 0u, 0u);
+                const bool want = kind[r] == KIND_IDLE;
+                const uint32_t m = __ballot_sync(0xFFFFFFFFu, want);
+                const uint32_t next = base + (uint32_t)__popc(m & ltMask);
+                base += (uint32_t)__popc(m);
+                if (want && next < count)
+                {
+                    const uint32_t slot = perm ? perm[next] : next;
+                    kind[r] = traceBegin(ctx(r), as, io, slot, COUNT ? &tc : nullptr);
+                    if (kind[r] == KIND_IDLE) retire(slot, false);
+                }
             }
+            continue;
         }
-        if (!__any_sync(0xFFFFFFFFu, active)) break;
-        for (;;)
-        {
-            // Plurality vote: a step is one any-hit test, one primitive item or one node item (traceStep); only the
-            // kind most live lanes are waiting for runs this iteration and the others wait for their turn, so an
-            // issued instruction serves a large share of the live lanes instead of three kinds running mostly empty.
-            const int kind = active ? traceItemKind(s) : -1;
-            const bool flexible = PRT_TRACE_POSTPONE && active && traceCanPostpone(s);
-            int live;
-            const int run = pluralityKind(kind, flexible, live);
-            if (live == 0 || (!exhausted && live < TRACE_REFILL_BELOW)) break; // refill (or finish) before the next item
-            if ((kind == run || (flexible && run == 0)) && traceStep<false, COUNT>(s, st, as, sv, &tc, PRT_TRACE_POSTPONE && run == 0, PRT_TRACE_POSTPONE ? -1 : run))
+        if ((census & 0xFFFFFFu) == 0) break; // nothing in flight and nothing left to fetch
+        // One census serves a whole round: every kind that at least half as many lanes want as the most wanted one runs,
+        // nodes first, and a lane may advance one ray per kind (after its node item a ray often wants a triangle item,
+        // which it then gets in the same round). The any-hit test is long and rare: it waits for a quarter of the warp.
+        const uint32_t n0 = census & 63u, n1 = (census >> 6) & 63u, n2 = (census >> 12) & 63u, n3 = (census >> 18) & 63u;
+        const uint32_t most = max(max(n0, n1), max(n2, n3));
+        const uint32_t bar = (most + 1u) >> 1;
+        auto runKind = [&](const int run) {
+            int r = -1;
+#pragma unroll
+            for (int i = R - 1; i >= 0; --i)
+                if (kind[i] == run) r = i;
+            if (r >= 0)
             {
-                pb.hits[slot] = make_uint4(s.best.drawInstanceIndex, s.best.primitiveID, __float_as_uint(s.best.u), __float_as_uint(s.best.v));
-                active = false;
+                const RayCtx c = ctx(r);
+                const int k = traceItem<SHADOW, COUNT>(run, c, as, sv, io, &tc);
+                if (k == KIND_IDLE) retire(c.row(ROW_M).z, (c.row(ROW_I).w & TRACE_HAS_HIT) != 0);
+#pragma unroll
+                for (int i = 0; i < R; ++i)
+                    if (i == r) kind[i] = k;
             }
-        }
+        };
+#if PRT_TRACE_SINGLE_KIND
+        if (n2 == most) runKind(KIND_ANYHIT);
+        else if (n1 == most) runKind(KIND_TRI);
+        else if (n3 == most) runKind(KIND_INSTANCE);
+        else runKind(KIND_NODE);
+#else
+        if (n0 >= bar) runKind(KIND_NODE);
+        if (n3 >= bar) runKind(KIND_INSTANCE);
+        if (n1 >= bar) runKind(KIND_TRI);
+        if (n2 == most || n2 >= 8u) runKind(KIND_ANYHIT);
+#endif
     }
-    if (COUNT) flushTraceCounters(gc, tc);
+    if (COUNT) flushTraceCounters(gc, tc, SHADOW);
 }
 
 // texture() through the texture units for one tap of every lane of the warp. All 32 lanes must call
@@ -427,66 +445,6 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_SHADE_MIN_BLOCKS)
     }
 }
 
-// shadow(), main.rgen:49-60, fused with the addBounce of evaluateDirectLighting's result
-template <bool COUNT>
-__global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
-    k_trace_shadow(Accel as, SceneView sv, PathBuffers pb, uint32_t bounce, GlobalCounters *gc, const uint32_t *__restrict__ perm)
-{
-    const uint32_t count = pb.counts[COUNT_SHADOW_BASE + bounce];
-    uint32_t *cursor = &pb.counts[CURSOR_BASE + COUNT_SHADOW_BASE + bounce];
-    TraceCounters tc = {0, 0, 0, 0, 0};
-    TraceState s;
-#if PRT_TRACE_SMEM_STACK
-    __shared__ uint2 stackMem[TRACE_SMEM_STACK * RENDER_THREADS];
-    SharedTraceStack st;
-    st.column = stackMem + threadIdx.x;
-    st.stride = RENDER_THREADS;
-#else
-    TraceStack st; // per-thread local memory, L1-resident: measured faster than the shared-memory variant
-#endif
-    bool active = false, exhausted = false;
-    uint32_t slot = 0;
-    auto retire = [&]() {
-        if (s.best.drawInstanceIndex == MISS_INDEX) // unoccluded
-        {
-            const float4 c = pb.shadowC[slot];
-            const uint32_t path = pb.shadowId[slot].x;
-            float4 col = pb.color[path];
-            col.x += c.x; col.y += c.y; col.z += c.z;
-            pb.color[path] = col;
-        }
-    };
-    for (;;)
-    {
-        if (!exhausted)
-        {
-            const uint32_t next = fetchSlots(cursor, count, !active, exhausted);
-            if (!active && next < count)
-            {
-                slot = perm ? perm[next] : next;
-                const float4 o = pb.shadowO[slot], d = pb.shadowD[slot];
-                active = traceBegin(s, st, as, V3{o.x, o.y, o.z}, V3{d.x, d.y, d.z}, o.w, d.w, pb.shadowId[slot].y, COUNT ? &tc : nullptr);
-                if (!active) retire();
-            }
-        }
-        if (!__any_sync(0xFFFFFFFFu, active)) break;
-        for (;;)
-        {
-            const int kind = active ? traceItemKind(s) : -1; // plurality vote, see k_trace_closest
-            const bool flexible = PRT_TRACE_POSTPONE && active && traceCanPostpone(s);
-            int live;
-            const int run = pluralityKind(kind, flexible, live);
-            if (live == 0 || (!exhausted && live < TRACE_REFILL_BELOW)) break;
-            if ((kind == run || (flexible && run == 0)) && traceStep<true, COUNT>(s, st, as, sv, &tc, PRT_TRACE_POSTPONE && run == 0, PRT_TRACE_POSTPONE ? -1 : run))
-            {
-                retire();
-                active = false;
-            }
-        }
-    }
-    if (COUNT) flushTraceCounters(gc, tc, true);
-}
-
 // Adds the per-bounce live counts of the finished batch to the 64-bit totals.
 __global__ void k_tally(PathBuffers pb, GlobalCounters *gc, uint32_t pixelSamples)
 {
@@ -569,7 +527,7 @@ __global__ void __launch_bounds__(RENDER_THREADS)
     {
         const float4 oo = o[i], dd = d[i];
         HitRec hit;
-        traceRay<SHADOW, true>(as, sv, V3{oo.x, oo.y, oo.z}, V3{dd.x, dd.y, dd.z}, oo.w, dd.w, seeds ? seeds[i] : 0u, hit, &tc);
+        traceRay<SHADOW, true>(as, sv, V3{oo.x, oo.y, oo.z}, V3{dd.x, dd.y, dd.z}, oo.w, dd.w, seeds ? seeds[i] : 0u, hit, &tc, &gc->stackOverflows);
         prt_hit h;
         h.drawInstanceIndex = hit.drawInstanceIndex;
         h.primitiveID = hit.primitiveID;

@@ -220,6 +220,8 @@ struct prt_ctx
     GlobalCounters *dCounters = nullptr;
     uint64_t kernelLaunches = 0;
     uint32_t traceBlocks = 148; // grid of the persistent trace kernels
+    uint32_t poolRays = PRT_POOL_RAYS;   // rays per thread of the persistent trace kernels (kernels_render.cuh)
+    uint32_t refillAt = PRT_POOL_REFILL; // idle ray slots per warp that trigger a refill
     uint32_t coopBlocks = 0;    // co-resident blocks of k_collapse_all_levels_grid (0: cooperative launch unsupported)
 
     // timing
@@ -275,11 +277,60 @@ struct prt_ctx
         a.tlasNodes = tlasInstances ? tlasNodes.p : nullptr;
         a.instances = tlasInst.p;
         a.instanceCount = tlasInstances;
+        a.planeBias = PLANE_BIAS;
         return a;
     }
 };
 
 extern "C" const char *prt_last_error(void) { return g_lastError.c_str(); }
+
+// The persistent trace kernels are instantiated for 1 and 2 rays per thread (3 measured slower: its rows squeeze L1); PRT_POOL_RAYS (build default) or the
+// environment (experiment switch) picks one per context.
+template <int R, bool SHADOW>
+static void launchTraceR(prt_ctx *c, bool count, uint32_t grid, const Accel &as, const SceneView &sv, int q, uint32_t b, const uint32_t *perm)
+{
+    if (count) k_trace<R, SHADOW, true><<<grid, RENDER_THREADS, 0, c->stream>>>(as, sv, c->pb, q, b, c->dCounters, perm, c->refillAt);
+    else k_trace<R, SHADOW, false><<<grid, RENDER_THREADS, 0, c->stream>>>(as, sv, c->pb, q, b, c->dCounters, perm, c->refillAt);
+}
+template <bool SHADOW>
+static void launchTrace(prt_ctx *c, bool count, uint32_t grid, const Accel &as, const SceneView &sv, int q, uint32_t b, const uint32_t *perm)
+{
+    switch (c->poolRays)
+    {
+    case 1: launchTraceR<1, SHADOW>(c, count, grid, as, sv, q, b, perm); break;
+    default: launchTraceR<2, SHADOW>(c, count, grid, as, sv, q, b, perm); break;
+    }
+}
+template <int R>
+static cudaError_t configureTrace(prt_ctx *c, int sms)
+{
+    // Blocks per SM from the launch bounds (registers) and the ray rows (shared memory), then a shared-memory carve-out
+    // that is just large enough for them: what is left of the 256 KB is L1, which serves the nodes, the triangles and
+    // the per-thread stacks (with the maximum carve-out the L1 hit rate fell from 70 % to 32 %).
+    int perSm = 0, dev = 0;
+    cudaError_t err = cudaSuccess;
+    cudaFuncAttributes fa;
+    if ((err = cudaFuncGetAttributes(&fa, k_trace<R, false, false>)) != cudaSuccess) return err;
+    if ((err = cudaGetDevice(&dev)) != cudaSuccess) return err;
+    cudaDeviceProp prop;
+    if ((err = cudaGetDeviceProperties(&prop, dev)) != cudaSuccess) return err;
+    const size_t perBlock = fa.sharedSizeBytes + prop.reservedSharedMemPerBlock;
+    const int byRegs = (int)(prop.regsPerMultiprocessor / std::max(1, fa.numRegs * RENDER_THREADS));
+    const int bySmem = (int)(prop.sharedMemPerMultiprocessor / perBlock);
+    perSm = std::max(1, std::min(std::min(byRegs, bySmem), PRT_TRACE_MIN_BLOCKS));
+    if (const char *e = std::getenv("PRT_TRACE_BLOCKS_PER_SM")) perSm = std::min(perSm, std::max(1, std::atoi(e))); // experiment switch
+    int carve = (int)std::min<size_t>(100, (perSm * perBlock * 100 + prop.sharedMemPerMultiprocessor - 1) / prop.sharedMemPerMultiprocessor);
+    if (const char *e = std::getenv("PRT_TRACE_CARVEOUT")) carve = std::atoi(e); // experiment switch
+    if ((err = cudaFuncSetAttribute(k_trace<R, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve)) != cudaSuccess) return err;
+    if ((err = cudaFuncSetAttribute(k_trace<R, true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve)) != cudaSuccess) return err;
+    if ((err = cudaFuncSetAttribute(k_trace<R, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve)) != cudaSuccess) return err;
+    if ((err = cudaFuncSetAttribute(k_trace<R, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve)) != cudaSuccess) return err;
+    int occ = 0;
+    if ((err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_trace<R, false, false>, RENDER_THREADS, 0)) != cudaSuccess) return err;
+    perSm = std::max(1, std::min(perSm, occ));
+    c->traceBlocks = (uint32_t)std::max(1, sms * std::max(1, perSm));
+    return cudaSuccess;
+}
 
 // ---- lifetime: RtReference::init / ~RtReference (RtRef.cpp:90-120) ------------------------------------
 static prt_status allocPathBuffers(prt_ctx *c, uint64_t paths)
@@ -288,8 +339,8 @@ static prt_status allocPathBuffers(prt_ctx *c, uint64_t paths)
     PathBuffers &pb = c->pb;
     void **ptrs[] = {(void **)&pb.rng,      (void **)&pb.throughput, (void **)&pb.color,   (void **)&pb.rayO[0], (void **)&pb.rayO[1],
                      (void **)&pb.rayD[0],  (void **)&pb.rayD[1],    (void **)&pb.rayId[0], (void **)&pb.rayId[1], (void **)&pb.hits,
-                     (void **)&pb.shadowO,  (void **)&pb.shadowD,    (void **)&pb.shadowId, (void **)&pb.shadowC};
-    const size_t elem[] = {16, 16, 16, 16, 16, 16, 16, 8, 8, 16, 16, 16, 8, 16};
+                     (void **)&pb.shadowO,  (void **)&pb.shadowD,    (void **)&pb.shadowId, (void **)&pb.shadowC, (void **)&pb.tie};
+    const size_t elem[] = {16, 16, 16, 16, 16, 16, 16, 8, 8, 16, 16, 16, 8, 16, 8};
     for (size_t i = 0; i < sizeof(elem) / sizeof(elem[0]); ++i)
     {
         if (*ptrs[i]) CK(cudaFree(*ptrs[i]));
@@ -350,8 +401,10 @@ extern "C" prt_status prt_create(const prt_config *cfg, prt_ctx **out)
         // persistent trace kernels: one resident wave of blocks (SM count x blocks per SM)
         int sms = 0, perSm = 0;
         CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->cfg.device));
-        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_trace_closest<false>, RENDER_THREADS, 0));
-        c->traceBlocks = (uint32_t)std::max(1, sms * std::max(1, perSm));
+        if (const char *e = std::getenv("PRT_POOL_RAYS")) c->poolRays = (uint32_t)std::min(2, std::max(1, std::atoi(e))); // experiment switch
+        c->refillAt = 8u * c->poolRays;
+        CK(c->poolRays == 1 ? configureTrace<1>(c, sms) : configureTrace<2>(c, sms));
+        if (const char *e = std::getenv("PRT_POOL_REFILL")) c->refillAt = (uint32_t)std::max(1, std::atoi(e)); // experiment switch
         if (const char *e = std::getenv("PRT_RAY_SORT")) c->raySort = (uint32_t)std::atoi(e); // experiment switch
         int coop = 0, perSmCollapse = 0;
         CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->cfg.device));
@@ -388,7 +441,7 @@ extern "C" void prt_destroy(prt_ctx *c)
     }
     PathBuffers &pb = c->pb;
     void *ptrs[] = {pb.rng,      pb.throughput, pb.color,   pb.rayO[0], pb.rayO[1], pb.rayD[0],  pb.rayD[1], pb.rayId[0],
-                    pb.rayId[1], pb.hits,       pb.shadowO, pb.shadowD, pb.shadowId, pb.shadowC, pb.counts,  c->dCounters};
+                    pb.rayId[1], pb.hits,       pb.shadowO, pb.shadowD, pb.shadowId, pb.shadowC, pb.counts,  c->dCounters, pb.tie};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     c->geomTable.release(); c->dMeta.release(); c->dMat.release(); c->dSlots.release(); c->dSky.release();
@@ -404,6 +457,7 @@ extern "C" void prt_destroy(prt_ctx *c)
     c->bLeft.release(); c->bRight.release(); c->bParentI.release(); c->bParentL.release(); c->bNodes.release(); c->bBounds.release();
     c->accum.release(); c->sum.release(); c->f16.release(); c->userHits.release(); c->userO.release(); c->userD.release();
     c->userSeeds.release();
+    c->toneLut.release(); c->ldr.release(); c->mipTables.release(); c->sortKeys.release(); c->sortPerm.release(); c->sortHist.release();
     for (int i = 0; i < 2; ++i)
     {
         if (c->evRecord[i]) cudaEventDestroy(c->evRecord[i]);
@@ -1179,8 +1233,7 @@ static prt_status renderBatch(prt_ctx *c, prt_reference_pc pc, uint32_t width, u
             sortRays(c, as, c->pb.rayO[q], c->pb.rayD[q], c->pb.counts + b, grid, launches);
             perm = c->sortPerm.p;
         }
-        if (count) k_trace_closest<true><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters, perm);
-        else k_trace_closest<false><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, q, b, c->dCounters, perm);
+        launchTrace<false>(c, count, tgrid, as, sv, q, b, perm);
         CK(c->mark(1));
         k_shade<<<grid, RENDER_THREADS, 0, st>>>(sv, pc, c->pb, q, b, c->dCounters, count ? 1 : 0);
         launches += 2;
@@ -1192,8 +1245,7 @@ static prt_status renderBatch(prt_ctx *c, prt_reference_pc pc, uint32_t width, u
             sortRays(c, as, c->pb.shadowO, c->pb.shadowD, c->pb.counts + COUNT_SHADOW_BASE + b, grid, launches);
             perm = c->sortPerm.p;
         }
-        if (count) k_trace_shadow<true><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters, perm);
-        else k_trace_shadow<false><<<tgrid, RENDER_THREADS, 0, st>>>(as, sv, c->pb, b, c->dCounters, perm);
+        launchTrace<true>(c, count, tgrid, as, sv, q, b, perm);
         launches++;
     }
     CK(c->mark(3));
@@ -1350,7 +1402,7 @@ extern "C" prt_status prt_trace_primary(prt_ctx *c, const prt_reference_pc *pcIn
     cudaStream_t st = c->stream;
     const uint32_t grid = blocksFor(pixels, RENDER_THREADS);
     k_raygen<<<grid, RENDER_THREADS, 0, st>>>(sv, *pcIn, width, height, 1, c->pb);
-    k_trace_closest<true><<<std::min(grid, c->traceBlocks), RENDER_THREADS, 0, st>>>(as, sv, c->pb, 0, 0, c->dCounters, nullptr);
+    launchTrace<false>(c, true, std::min(grid, c->traceBlocks), as, sv, 0, 0, nullptr);
     k_hits_to_records<<<blocksFor(pixels, 256), 256, 0, st>>>(c->pb.hits, c->userHits.p, (uint32_t)pixels);
     c->kernelLaunches += 3;
     CK(cudaGetLastError());
@@ -1554,13 +1606,13 @@ extern "C" prt_status prt_debug_read_blas(prt_ctx *c, uint32_t modelIndex, void 
     CK(cudaSetDevice(c->cfg.device));
     if (nodesOut)
     {
-        REQUIRE(nodesBytes >= (uint64_t)b.nodeCount * sizeof(WideNode), "node buffer too small");
-        CK(cudaMemcpyAsync(nodesOut, b.nodes, (size_t)b.nodeCount * sizeof(WideNode), cudaMemcpyDeviceToHost, c->stream));
+        REQUIRE(nodesBytes >= (uint64_t)b.nodeCount * WIDE_NODE_BYTES, "node buffer too small");
+        CK(cudaMemcpy2DAsync(nodesOut, WIDE_NODE_BYTES, b.nodes, sizeof(WideNode), WIDE_NODE_BYTES, b.nodeCount, cudaMemcpyDeviceToHost, c->stream));
     }
     if (trisOut)
     {
-        REQUIRE(trisBytes >= (uint64_t)b.triCount * sizeof(TriRec), "triangle buffer too small");
-        CK(cudaMemcpyAsync(trisOut, b.tris, (size_t)b.triCount * sizeof(TriRec), cudaMemcpyDeviceToHost, c->stream));
+        REQUIRE(trisBytes >= (uint64_t)b.triCount * TRI_REC_BYTES, "triangle buffer too small");
+        CK(cudaMemcpy2DAsync(trisOut, TRI_REC_BYTES, b.tris, sizeof(TriRec), TRI_REC_BYTES, b.triCount, cudaMemcpyDeviceToHost, c->stream));
     }
     CK(cudaStreamSynchronize(c->stream));
     return PRT_OK;
@@ -1575,8 +1627,8 @@ extern "C" prt_status prt_debug_read_tlas(prt_ctx *c, void *nodesOut, uint64_t n
     CK(cudaSetDevice(c->cfg.device));
     if (nodesOut && n)
     {
-        REQUIRE(nodesBytes >= (uint64_t)n * sizeof(WideNode), "node buffer too small (instanceCount nodes)");
-        CK(cudaMemcpyAsync(nodesOut, c->tlasNodes.p, (size_t)n * sizeof(WideNode), cudaMemcpyDeviceToHost, c->stream));
+        REQUIRE(nodesBytes >= (uint64_t)n * WIDE_NODE_BYTES, "node buffer too small (instanceCount nodes)");
+        CK(cudaMemcpy2DAsync(nodesOut, WIDE_NODE_BYTES, c->tlasNodes.p, sizeof(WideNode), WIDE_NODE_BYTES, n, cudaMemcpyDeviceToHost, c->stream));
     }
     if (instOut && n)
     {

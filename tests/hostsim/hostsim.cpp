@@ -248,6 +248,7 @@ static void buildTlasHost(hs_ctx *c)
             c->as.tlasNodes = c->tlasNodes.data();
             c->as.instances = c->tlasInst.data();
             c->as.instanceCount = (uint32_t)c->tlasInst.size();
+            c->as.planeBias = PLANE_BIAS;
         }
     }
 }
@@ -393,14 +394,16 @@ void hs_trace_primary(hs_ctx *c, const void *pcIn, uint32_t width, uint32_t heig
     const prt_reference_pc pc = *(const prt_reference_pc *)pcIn;
     parallelFor(height, threads, [&](uint32_t y) {
         TraceCounters tc = {0, 0, 0, 0, 0};
+        unsigned long long ovf = 0;
         for (uint32_t x = 0; x < width; ++x)
         {
             Rng rng;
             const Ray ray = generatePrimaryRay(c->sv, pc, pc.frameIndex, x, y, width, height, rng);
             HitRec h;
-            traceRay<false, true>(c->as, c->sv, ray.o, ray.d, ray.tMin, ray.tMax, pcg(rng.state.x ^ rng.state.z), h, &tc);
+            traceRay<false, true>(c->as, c->sv, ray.o, ray.d, ray.tMin, ray.tMax, pcg(rng.state.x ^ rng.state.z), h, &tc, &ovf);
             hits[(size_t)y * width + x] = prt_hit{h.drawInstanceIndex, h.primitiveID, {h.u, h.v}};
         }
+        tc.overflow += (uint32_t)ovf;
         flush(c, tc);
     });
 }
@@ -411,15 +414,17 @@ void hs_trace_rays(hs_ctx *c, const float *originTmin, const float *dirTmax, con
     const uint32_t chunk = 1024;
     parallelFor((count + chunk - 1) / chunk, threads, [&](uint32_t r) {
         TraceCounters tc = {0, 0, 0, 0, 0};
+        unsigned long long ovf = 0;
         for (uint32_t i = r * chunk; i < std::min(count, (r + 1) * chunk); ++i)
         {
             const V3 o = {originTmin[i * 4], originTmin[i * 4 + 1], originTmin[i * 4 + 2]};
             const V3 d = {dirTmax[i * 4], dirTmax[i * 4 + 1], dirTmax[i * 4 + 2]};
             HitRec h;
-            if (shadow) traceRay<true, true>(c->as, c->sv, o, d, originTmin[i * 4 + 3], dirTmax[i * 4 + 3], seeds ? seeds[i] : 0u, h, &tc);
-            else traceRay<false, true>(c->as, c->sv, o, d, originTmin[i * 4 + 3], dirTmax[i * 4 + 3], seeds ? seeds[i] : 0u, h, &tc);
+            if (shadow) traceRay<true, true>(c->as, c->sv, o, d, originTmin[i * 4 + 3], dirTmax[i * 4 + 3], seeds ? seeds[i] : 0u, h, &tc, &ovf);
+            else traceRay<false, true>(c->as, c->sv, o, d, originTmin[i * 4 + 3], dirTmax[i * 4 + 3], seeds ? seeds[i] : 0u, h, &tc, &ovf);
             hits[i] = prt_hit{h.drawInstanceIndex, h.primitiveID, {h.u, h.v}};
         }
+        tc.overflow += (uint32_t)ovf;
         flush(c, tc);
     });
 }
@@ -433,6 +438,7 @@ void hs_render(hs_ctx *c, const void *pcIn, uint32_t width, uint32_t height, uin
     std::atomic<uint64_t> closest{0}, shadowRays{0}, shaded{0};
     parallelFor(height, threads, [&](uint32_t y) {
         TraceCounters tc = {0, 0, 0, 0, 0};
+        unsigned long long ovf = 0;
         uint64_t nc = 0, nsr = 0, nsh = 0;
         for (uint32_t x = 0; x < width; ++x)
         {
@@ -450,7 +456,7 @@ void hs_render(hs_ctx *c, const void *pcIn, uint32_t width, uint32_t height, uin
                 for (uint32_t bounce = 0; bounce < bounces; ++bounce)
                 {
                     HitRec h;
-                    traceRay<false, true>(c->as, c->sv, ray.o, ray.d, ray.tMin, ray.tMax, seed, h, &tc);
+                    traceRay<false, true>(c->as, c->sv, ray.o, ray.d, ray.tMin, ray.tMax, seed, h, &tc, &ovf);
                     nc++;
                     ShadeResult r;
                     SurfaceGeom geom;
@@ -466,7 +472,7 @@ void hs_render(hs_ctx *c, const void *pcIn, uint32_t width, uint32_t height, uin
                     {
                         HitRec sh;
                         nsr++;
-                        if (!traceRay<true, true>(c->as, c->sv, r.shadowO, r.shadowD, 0.1f, r.shadowTMax, r.shadowSeed, sh, &tc))
+                        if (!traceRay<true, true>(c->as, c->sv, r.shadowO, r.shadowD, 0.1f, r.shadowTMax, r.shadowSeed, sh, &tc, &ovf))
                             color = color + r.shadowContribution;
                     }
                     if (!r.alive) break;
@@ -487,6 +493,7 @@ void hs_render(hs_ctx *c, const void *pcIn, uint32_t width, uint32_t height, uin
                 }
             }
         }
+        tc.overflow += (uint32_t)ovf;
         flush(c, tc);
         closest += nc; shadowRays += nsr; shaded += nsh;
     });

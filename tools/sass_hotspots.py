@@ -28,5 +28,7 @@ for (src, ex, tex, sm), (l, txt) in zip(inst, loc):
 tot = sum(a[0] for a in agg.values()); tt = sum(a[1] for a in agg.values())
 print(f"total warp-inst {tot/1e9:.2f} G, thread-inst {tt/1e9:.2f} G, avg lanes {tt/max(tot,1):.2f}")
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
-for l, a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+key = 2 if len(sys.argv) > 4 and sys.argv[4] == "samples" else 0
+print("total samples", sum(a[2] for a in agg.values()))
+for l, a in sorted(agg.items(), key=lambda kv: -kv[1][key])[:top]:
     print(f"{l[0]:28s}:{l[1]:4d}  sass {a[3]:4d}  warp-inst {a[0]/tot*100:5.1f}%  lanes {a[1]/max(a[0],1):5.1f}  samples {a[2]}")
