@@ -29,9 +29,10 @@ inline vec3 operator-(vec3 a) { return {-a.x, -a.y, -a.z}; }
 inline vec3 operator*(vec3 a, vec3 b) { return {a.x * b.x, a.y * b.y, a.z * b.z}; }
 inline vec3 operator*(vec3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
 inline vec3 operator*(float s, vec3 a) { return {a.x * s, a.y * s, a.z * s}; }
-// vector / scalar: one reciprocal, three multiplies (the lowering GLSL implementations use; precision of OpFDiv on
-// vectors and of normalize() is implementation-defined) -- the CUDA kernels do the same, operation for operation
-inline vec3 operator/(vec3 a, float s) { const float r = 1.0f / s; return {a.x * r, a.y * r, a.z * r}; }
+// vector / scalar as the GLSL text says it (sampling.glsl:32, lighting.glsl:29, main.rgen:293): a division per component.
+// The oracle never changes for performance: the CUDA kernels lower this to one reciprocal and three multiplies
+// (prosper_b200/csrc/hd.h) and have to pass the parity tests WITHIN THEIR STATED TOLERANCE against this, not bit for bit.
+inline vec3 operator/(vec3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
 inline vec3 operator/(vec3 a, vec3 b) { return {a.x / b.x, a.y / b.y, a.z / b.z}; }
 inline vec3 &operator+=(vec3 &a, vec3 b) { a = a + b; return a; }
 inline vec3 &operator*=(vec3 &a, vec3 b) { a = a * b; return a; }
@@ -47,10 +48,10 @@ inline vec3 cross(vec3 a, vec3 b)
     return {(a.y * b.z) - (a.z * b.y), (a.z * b.x) - (a.x * b.z), (a.x * b.y) - (a.y * b.x)};
 }
 inline float length(vec3 a) { return std::sqrt(dot(a, a)); }
-// exact contract (pinhole primary ray): three true divisions by sqrt(dot(v,v)), the device's xnormalize
-inline vec3 normalizeExact(vec3 a) { const float l = std::sqrt(dot(a, a)); return {a.x / l, a.y / l, a.z / l}; }
-// shading: v * (1 / sqrt(dot(v,v))), see operator/ above
+// normalize = v / sqrt(dot(v,v)) (division, not rsqrt). The primary-ray direction is part of the exact contract (the
+// device's xnormalize does the same three divisions); shading normals are compared within tolerance.
 inline vec3 normalize(vec3 a) { return a / std::sqrt(dot(a, a)); }
+inline vec3 normalizeExact(vec3 a) { return normalize(a); }
 // math.glsl:5. GLSL clamp() of a NaN is undefined; contract: NaN -> 0 (fmaxf drops the NaN), which is
 // what __saturatef does on the device.
 inline float saturate(float x) { return std::fmin(std::fmax(x, 0.0f), 1.0f); }

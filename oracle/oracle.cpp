@@ -836,8 +836,7 @@ void orc_render(orc_ctx *ctx, const void *pcIn, uint32_t width, uint32_t height,
                 {
                     const vec3 historyColor = {out[0], out[1], out[2]};
                     const float historyCount = out[3] + 1;
-                    const vec3 delta = color - historyColor; // main.rgen:293: a true division per channel, as k_accumulate does
-                    const vec3 newColor = historyColor + vec3{delta.x / historyCount, delta.y / historyCount, delta.z / historyCount};
+                    const vec3 newColor = historyColor + (color - historyColor) / historyCount; // main.rgen:293
                     out[0] = newColor.x; out[1] = newColor.y; out[2] = newColor.z; out[3] = historyCount;
                 }
             }

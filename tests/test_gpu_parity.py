@@ -150,17 +150,33 @@ def test_primary_ids_and_radiance_karras_blas_builder(small_atrium_instanced, te
         assert np.array_equal(a, b)
 
 
-def test_dof_primary(test_scene):
-    w, h = 96, 64
-    world = _world(test_scene, w, h)
-    orc = oracle.Oracle(test_scene)
+def test_dof_primary(test_scene, small_atrium):
+    """Thin-lens primary rays (ray.glsl:46-78). Their cos / sin / sqrt and the vector normalisation are outside the exact
+    contract (device libm and FMA contraction against glibc), so an ID may flip on a silhouette: the bound is north_star's
+    exclusion target, < 0.1 % of the pixels -- in fact 10x tighter, < 0.01 % (measured on B200: 0 and 1 of 98,304)."""
+    w, h = 384, 256
     flags = sd.FLAG_ACCUMULATE | sd.FLAG_CLAMP_INDIRECT | sd.FLAG_IBL | sd.FLAG_SKIP_HISTORY | sd.FLAG_DOF
-    pc = sd.reference_pc(frame_index=3, flags=flags, aperture=0.05, focus_distance=3.0, focal_len=0.035)
-    ho, margin = orc.trace_primary(pc, w, h)
-    hg = world.trace_primary(pc, w, h)
-    # thin-lens rays use cos/sin (not in the exact contract): IDs agree except on silhouettes
-    assert _id_mismatch(ho, hg).mean() < 0.01
-    world.close()
+    for scene in (test_scene, small_atrium):
+        world = _world(scene, w, h)
+        orc = oracle.Oracle(scene)
+        for f in (3, 17):
+            pc = sd.reference_pc(frame_index=f, flags=flags, aperture=0.05, focus_distance=3.0, focal_len=0.035)
+            ho, margin = orc.trace_primary(pc, w, h)
+            hg = world.trace_primary(pc, w, h)
+            assert _id_mismatch(ho, hg).mean() < 1e-4, f"{scene.name} frame {f}: {_id_mismatch(ho, hg).sum()} of {w * h} IDs differ"
+        world.close()
+
+
+def test_single_instance_shortcut_with_a_moved_instance(small_atrium):
+    """A one-instance scene skips the one-node TLAS (core_trace.h traceBegin): the shortcut must honour the instance's
+    transform, so rotate / translate / scale the only instance and compare IDs and barycentrics bit for bit."""
+    import copy
+    scene = copy.deepcopy(small_atrium)
+    assert len(scene.tlas_instances) == 1
+    t = sd.instance_transforms(sd.trs((0.3, -0.2, 0.5), (0.2, 1.0, 0.1), 0.35, (1.1, 0.9, 1.05)))
+    scene.transforms[0] = t
+    scene.tlas_instances[0]["transform"] = t["modelToWorld"]
+    _check_primary(scene, 160, 90, frames=(1, 2))
 
 
 def test_random_rays_closest_and_shadow(test_scene, small_atrium_instanced):
@@ -445,14 +461,15 @@ def test_degenerate_inputs_on_gpu(small_stress):
 
 def test_radiance_atrium_with_lights_and_foliage(small_atrium_instanced):
     """Converged-radiance gate on the atrium stand-in: 47 instances, alpha-MASK foliage, sun + 32 point/spot lights +
-    sky, 4 bounces, 16 spp at equal frame indices. This scene is firefly-heavy (two oracle runs with different frame
-    indices differ by relRMSE ~4.3 at 16 spp, tools/filter_tolerance.py), so a handful of paths that take another
-    branch dominate the per-pixel metric. Tolerance (stated): relRMSE on luminance < 2 % with the software filter
-    (measured 0.5 %), < 12 % with the texture units' 8-bit-weight filter (measured 7.6 %, i.e. < 3 % of the Monte
-    Carlo noise at equal spp); mean image bias < 0.1 % (measured 0.006 %); ray counts within 0.5 %."""
-    scene, (w, h, spp) = small_atrium_instanced, (160, 90, 16)
+    sky, 4 bounces, 64 spp at equal frame indices ("relRMSE <= 2 % at 64 spp, bias <= 0.5 %"). This scene is
+    firefly-heavy (two oracle runs with different frame indices differ by relRMSE ~4.3 at 16 spp,
+    tools/filter_tolerance.py), so a handful of paths that take another branch dominate the per-pixel metric.
+    Tolerance (stated): relRMSE on luminance < 2 % with the software filter, < 6 % with the texture units'
+    8-bit-weight filter on these 64^2 textures (every tap is a magnification); mean image bias < 0.1 %; ray counts
+    within 0.5 %."""
+    scene, (w, h, spp) = small_atrium_instanced, (160, 90, 64)
     ref, counters = oracle.Oracle(scene).render(sd.reference_pc(max_bounces=4), w, h, spp)
-    for flags, tol in ((rt.CFG_COUNTERS | rt.CFG_EXACT_FILTER, 0.02), (rt.CFG_COUNTERS, 0.12)):
+    for flags, tol in ((rt.CFG_COUNTERS | rt.CFG_EXACT_FILTER, 0.02), (rt.CFG_COUNTERS, 0.06)):
         world = _world(scene, w, h, flags=flags, spl=4)
         r = rt.RtReference()
         r.init(world)
@@ -548,3 +565,45 @@ def test_scene_loaded_from_prosper_mesh_cache_files(tmp_path, test_scene):
     same = ~_id_mismatch(ho, hg)
     assert np.array_equal(ho["bary"][same], hg["bary"][same])
     world.close()
+
+
+def _radiance_against_oracle(scene, w, h, spp, cases):
+    """cases: (world flags, relRMSE tolerance, relative bias tolerance). Returns nothing; asserts with the measured values."""
+    ref, counters = oracle.Oracle(scene).render(sd.reference_pc(max_bounces=4), w, h, spp)
+    for flags, tol, bias_tol in cases:
+        world = _world(scene, w, h, flags=flags, spl=4)
+        r = rt.RtReference()
+        r.init(world)
+        r.drawUi(maxBounces=4)
+        out = r.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=spp).illumination_f32()
+        c = world.counters()
+        world.close()
+        rel = _rel_rmse(out, ref)
+        bias = (out[..., :3].mean() - ref[..., :3].mean()) / ref[..., :3].mean()
+        assert np.all(out[..., 3] == spp)
+        assert rel < tol, f"{scene.name} flags {flags}: relRMSE {rel:.4f} (tolerance {tol})"
+        assert abs(bias) < bias_tol, f"{scene.name} flags {flags}: bias {bias:.2e}"
+        assert abs(c["closestRays"] - int(counters[0])) <= 0.002 * int(counters[0])
+        assert abs(c["shadowRays"] - int(counters[1])) <= 0.005 * int(counters[1])
+        assert c["stackOverflows"] == 0
+
+
+def test_radiance_on_the_bench_scene_64spp():
+    """The radiance gate where the headline number is quoted: bench.py's scene (atrium(seed=1), 1024^2 BC7 textures), its
+    camera, the hardware-filter path the bench runs, 4 bounces, 64 spp -- at 480x270 so that the oracle finishes in
+    ~20 s. Stated tolerance: luminance relRMSE (1e-2 floor) < 3 % through the texture units (measured on B200: 2.3 %;
+    SURVEY 8d proposed 2 %, which the software filter meets: < 1.5 %, measured 0.9 %), mean image bias < 0.05 %
+    (measured 0.003 %). For scale: two oracle runs over different frame indices differ by relRMSE 32 %."""
+    from prosper_b200 import scene_zoo
+    scene = scene_zoo.atrium(480, 270, seed=1, tex_size=1024)
+    _radiance_against_oracle(scene, 480, 270, 64, ((rt.CFG_COUNTERS, 0.03, 5e-4), (rt.CFG_COUNTERS | rt.CFG_EXACT_FILTER, 0.015, 5e-4)))
+
+
+def test_radiance_with_1024_lights():
+    """BASELINE.json configs[2]: 1024 point / spot lights by the reference's recipe (WorldData.cpp:1324-1353), uniform light
+    sampling over 1 + 1024 lights (lighting.glsl:70-89). 160x90, 16 spp. Tolerance: software filter relRMSE < 0.5 %
+    (measured 0.06 %), texture units < 8 % on these 64^2 textures (measured 4.6 %); bias < 0.05 %."""
+    from prosper_b200 import scene_zoo
+    scene = scene_zoo.atrium(160, 90, tex_size=64, detail=0.08, lights=1024)
+    assert len(scene.point_lights) + len(scene.spot_lights) == 1024
+    _radiance_against_oracle(scene, 160, 90, 16, ((rt.CFG_COUNTERS | rt.CFG_EXACT_FILTER, 0.005, 5e-4), (rt.CFG_COUNTERS, 0.08, 5e-4)))

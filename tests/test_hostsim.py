@@ -59,8 +59,15 @@ def test_wavefront_stages_reproduce_the_oracle_image(test_scene, small_atrium_in
         pc = sd.reference_pc(max_bounces=4)
         a, ca = orc.render(pc, w, h, 3)
         b, cb = hs.render(pc, w, h, 3)
-        assert np.array_equal(ca, cb)
-        assert np.array_equal(a, b), "same compiler, same roundings: the images must be identical"
+        # The oracle divides where the GLSL divides (sampling.glsl:32, lighting.glsl:29, main.rgen:293); the product
+        # lowers vector / scalar to one reciprocal and three multiplies (csrc/hd.h). Same compiler otherwise, so the
+        # tolerance is tight: ray counts within 0.1 % (a roulette / alpha decision flips now and then), luminance
+        # relRMSE (1e-2 floor) below 1e-3 and mean bias below 1e-4 (measured: 5e-6 .. 6e-5 and 2e-7 .. 1.5e-6).
+        assert np.all(np.abs(ca.astype(np.int64) - cb.astype(np.int64)) <= np.maximum(1, ca // 1000))
+        lum = np.array([0.2126, 0.7152, 0.0722], np.float32)
+        la, lb = a[..., :3] @ lum, b[..., :3] @ lum
+        assert np.sqrt(np.mean(((la - lb) / (np.abs(la) + 1e-2)) ** 2)) < 1e-3
+        assert abs(float(lb.mean() - la.mean())) < 1e-4 * float(la.mean())
 
 
 def test_random_rays_all_octants(test_scene, small_atrium_instanced):
