@@ -48,7 +48,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
     ap.add_argument("--spp", type=int, default=64, help="frames per step (configs[1]: 64)")
-    ap.add_argument("--samples-per-launch", type=int, default=4)
+    ap.add_argument("--samples-per-launch", type=int, default=8)
     ap.add_argument("--tex-size", type=int, default=1024)
     ap.add_argument("--detail", type=float, default=1.0)
     ap.add_argument("--lights", type=int, default=0, help="configs[2]: 1024 point/spot lights")
@@ -56,9 +56,11 @@ def parse_args():
                     help="BLAS topology: top-down binned SAH (default), Karras LBVH or PLOC; all go through the same collapse")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
-    ap.add_argument("--workload", default="atrium", choices=("atrium", "district"),
+    ap.add_argument("--workload", default="atrium", choices=("atrium", "district", "helmet"),
                     help="district: BASELINE configs[3] (3.4 M triangles, 1024 animated instances, TLAS rebuilt per frame, "
-                         "3840x2160, 16 spp per frame) as an extra measurement; the driver's line is the default atrium")
+                         "3840x2160, 16 spp per frame); helmet: configs[0] (FlightHelmet glTF, 512x512, 16 spp) with the oracle "
+                         "timed on the SAME config; both are extra measurements, the driver's line is the default atrium")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling block (configs[2]: 1024 lights, one 64 spp image split over the ranks)")
     ap.add_argument("--no-stress", action="store_true", help="skip the 10k-instance TLAS rebuild measurement")
     ap.add_argument("--stress-instances", type=int, default=10000)
     return ap.parse_args()
@@ -337,6 +339,79 @@ def run_district(args):
 
 
 
+def run_helmet(args):
+    """BASELINE configs[0]: a real glTF (the reference's res/glTF/FlightHelmet, ingested by the scene host; DamagedHelmet is
+    not in the image), sky + one directional light, 512x512, 16 spp, 4 bounces -- and the CPU oracle timed on the SAME
+    config in the same run. Single GPU."""
+    import oracle
+    from prosper_b200 import gltf_scene, rt_reference as rt, scene_data as sd
+    w = h = 512
+    spp = 16
+    full = os.path.join(ROOT, "tests", "golden", "_flight_helmet_full")
+    scene = gltf_scene.flight_helmet(w, h, cache_dir=full if os.path.exists(os.path.join(full, "scene.npz")) else None)
+    world = rt.World(scene, device=0, max_width=w, max_height=h, samples_per_launch=spp, flags=0)
+    world.updateBuffers()
+    world.buildAccelerationStructures()
+    world.synchronize()
+    p = rt.RtReference()
+    p.init(world)
+    p.drawUi(maxBounces=BOUNCES)
+    opts = rt.Options(ibl=True)
+
+    def step(e2e):
+        if e2e:
+            world.updateBuffers()
+            world.buildTlas(scene.tlas_instances)
+        p.m_frameIndex = 0
+        p.m_accumulationDirty = True
+        out = p.record(world, (0, 0, w, h), opts, frames=spp)
+        if e2e:
+            out.illumination()
+        world.synchronize()
+        return out
+
+    for _ in range(max(3, args.warmup)):
+        step(False)
+    world.reset_counters()
+    clocks = ClockSampler(0)
+    clocks.start()
+    dev_ms = []
+    for _ in range(args.steps):
+        step(False)
+        dev_ms.append(world.timings()["lastRecordMs"])
+    c = world.counters()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step(True)
+    e2e_s = time.perf_counter() - t0
+    clk = clocks.stop()
+    rays = (c["closestRays"] + c["shadowRays"]) / args.steps
+    world.close()
+    orc = oracle.Oracle(scene)
+    cores = os.cpu_count() or 1
+    t0 = time.perf_counter()
+    _, cnt = orc.render(sd.reference_pc(max_bounces=BOUNCES), w, h, spp, threads=0)
+    cpu_s = time.perf_counter() - t0
+    orc.close()
+    h2d = sum(int(a.nbytes) for a in (scene.draw_instances, scene.transforms, scene.directional_light, scene.camera, scene.tlas_instances))
+    _emit({
+        "metric": "Mrays/s (closest + shadow rays), 512x512 FlightHelmet glTF, 16 spp, 4 bounces", "value": rays / (sum(dev_ms) / args.steps) / 1e3,
+        "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sum(dev_ms) / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "the reference's FlightHelmet asset",
+        "config": {"workload": f"FlightHelmet glTF ({scene.triangle_count} triangles in {len(scene.tlas_instances)} instances, 4 opaque + 1 BLEND "
+                               f"material, {sum(t is not None for t in scene.textures)} of 15 textures present at "
+                               f"{max(t.width for t in scene.textures if t is not None)}^2 BC7), sky + default directional light, {w}x{h}, {spp} spp, "
+                               f"{BOUNCES} bounces", "config_index": 0,
+                   "l2": "one launch holds all 16 spp: 4.2 M paths x 232 B = 973 MB of queues (L2 126 MB)"},
+        "spp_per_s": spp / (sum(dev_ms) / args.steps * 1e-3),
+        "e2e": {"value": rays * args.steps / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": w * h * 8,
+                "ms_per_step": e2e_s / args.steps * 1e3, "path": "World.updateBuffers + World.buildTlas + RtReference.record + fp16 read-back"},
+        "cpu_baseline": {"value": float(cnt[0] + cnt[1]) / cpu_s / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "port", "seconds": cpu_s,
+                         "sample": f"the whole config: {w}x{h} x {spp} spp, {BOUNCES} bounces, {int(cnt[0] + cnt[1])} rays, std::thread over {cores} threads"},
+        "gpu_launches": int(c["kernelLaunches"]), "clocks": clk,
+    })
+
+
 def next_rows(world, pixels, peak_gbs):
     """SURVEY 8(f) rows built so far, measured beside the headline: the display transform over the image `world` has just
     rendered (device-resident, CUDA-event-free wall clock around a synchronised batch of launches) and the texture-cache
@@ -423,18 +498,26 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def render_step():
+    def reduce_to_rank0():
+        """The path's one collective, stream-ordered on the library stream end to end: k_mean_to_sum into the torch
+        buffer, ncclReduce(sum) enqueued behind it (the process group's stream waits on the current stream = the
+        library's, and work.wait() makes the library stream wait for the collective), k_sum_to_mean on rank 0.
+        No host synchronisation anywhere."""
+        world.export_sum_to(reduced.data_ptr())
+        with torch.cuda.stream(stream):
+            work = dist.reduce(reduced, dst=0, op=dist.ReduceOp.SUM, async_op=True)
+            work.wait()
+        if rank == 0:
+            world.import_sum(reduced.data_ptr())
+
+    def render_step(first=None, frames=None, reduce=True):
         """rank g renders frame indices g*spp+1 .. (g+1)*spp into a fresh accumulation (RNG seed = (px, frameIndex),
         main.rgen:229); N>1: one reduce of the (sum, count) image to rank 0."""
-        pass_.m_frameIndex = first_frame - 1  # record() pre-increments (RtRef.cpp:170)
+        pass_.m_frameIndex = (first_frame if first is None else first) - 1  # record() pre-increments (RtRef.cpp:170)
         pass_.m_accumulationDirty = True
-        out = pass_.record(world, area, opts, frames=args.spp)
-        if world_size > 1:
-            world.export_sum_to(reduced.data_ptr())
-            partition.reduce_sum_image(reduced, dst=0)
-            torch.cuda.current_stream().synchronize()
-            if rank == 0:
-                world.import_sum(reduced.data_ptr())
+        out = pass_.record(world, area, opts, frames=args.spp if frames is None else frames)
+        if world_size > 1 and reduce:
+            reduce_to_rank0()
         return out
 
     def e2e_step():
@@ -514,6 +597,51 @@ def run_ours(args):
            "ms_per_step": e2e_s / args.steps * 1e3,
            "path": "World.updateBuffers + World.buildTlas (host instance records) + RtReference.record + "
                    "Output.illumination() fp16 read-back to host"}
+
+    # ---- strong scaling: BASELINE configs[2] -- ONE 1080p x 64 spp image with 1024 point / spot lights, its frame
+    # indices split over the ranks, the reduce inside the timed region; the 1-rank time of the same image is measured
+    # in the same process (rank 0 alone, the others wait at the barrier) so the speed-up needs no second run
+    strong = None
+    if not args.no_strong:
+        import copy
+        from prosper_b200 import scene_zoo
+        lit = copy.copy(scene)
+        lo, hi = (-13.0, 0.5, -5.0), (13.0, 10.0, 5.0)  # the box scene_zoo.atrium(lights=1024) scatters its lights in
+        lit.point_lights, lit.spot_lights = scene_zoo.make_lights(1024, lo, hi, seed=3)
+        world.updateBuffers(lit)
+        total_spp = 64
+        per_rank = max(1, total_spp // world_size)
+
+        def timed(fn, reps):
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(reps):
+                fn()
+            e1.record(stream)
+            barrier()
+            return max_over_ranks(e0.elapsed_time(e1) / reps)
+
+        reps = max(2, min(args.steps, 5))
+        split = lambda: render_step(first=rank * per_rank + 1, frames=per_rank, reduce=True)
+        split(); split()
+        world.reset_counters()
+        t_split = timed(split, reps)
+        strong_rays = sum_over_ranks(world.counters()["closestRays"] + world.counters()["shadowRays"]) / reps
+        t_reduce = 0.0
+        if world_size > 1:
+            t_reduce = timed(reduce_to_rank0, reps)
+        alone = lambda: render_step(first=1, frames=per_rank * world_size, reduce=False) if rank == 0 else None
+        alone()
+        t_alone = timed(alone, 2) if world_size > 1 else t_split
+        strong = {"workload": f"atrium + 1024 point/spot lights (configs[2]), ONE {WIDTH}x{HEIGHT} x {per_rank * world_size} spp image, "
+                              f"{per_rank} frame indices per rank, ncclReduce(sum) to rank 0 inside the timed region",
+                  "ms_per_image": t_split, "ms_per_image_1gpu_same_process": t_alone, "speedup_vs_1": t_alone / t_split,
+                  "reduce_ms": t_reduce, "reduce_share": t_reduce / t_split if t_split > 0 else 0.0,
+                  "mrays_s": strong_rays / t_split / 1e3, "n_gpus": world_size,
+                  "lights": "512 point + 512 spot, the reference's recipe (WorldData.cpp:1324-1353), seed 3",
+                  "timing": "CUDA events on the library stream, max over ranks, barrier + synchronize on both sides"}
+        world.updateBuffers(scene)
 
     # ---- TLAS rebuild metric ("ms per TLAS rebuild", App.cpp:575 BuildTLAS scope) ---------------------------------
     tlas_ms = []
@@ -620,6 +748,8 @@ def run_ours(args):
         "rays_per_step": rays_all / args.steps, "wall_ms_per_step": wall_ms / args.steps,
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clk, "tlas": tlas,
     }
+    if strong is not None:
+        line["strong"] = strong
     if roofline is not None:
         line["roofline"] = roofline
         line["breakdown"] = breakdown
@@ -651,6 +781,8 @@ def main():
         run_reference(args)
     elif args.workload == "district":
         run_district(args)
+    elif args.workload == "helmet":
+        run_helmet(args)
     else:
         run_ours(args)
 

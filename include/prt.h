@@ -159,9 +159,12 @@ prt_status prt_debug_read_tlas(prt_ctx *ctx, void *nodesOut, uint64_t nodesBytes
 /* Device pointer to the fp32 RGBA *sum* image (rgb = sum of samples, a = count) suitable for
  * ncclReduce(sum); prt_resolve_sum turns a reduced sum back into the running-mean image. */
 prt_status prt_export_sum_device(prt_ctx *ctx, float **outSum);
+/* STREAM-ORDERED on prt_stream(ctx), no host synchronisation: `sumDevice` must be complete in that stream's order (make
+ * prt_stream() the collective's stream, or have it wait on the collective's event) before this is called. */
 prt_status prt_import_sum_device(prt_ctx *ctx, const float *sumDevice);
 /* Same as prt_export_sum_device but writes the sum image into caller-owned DEVICE memory (width*height*16 B,
- * e.g. a buffer registered with the caller's communicator) and returns once it is complete. */
+ * e.g. a buffer registered with the caller's communicator). STREAM-ORDERED on prt_stream(ctx): the copy is enqueued,
+ * not awaited, so a collective enqueued behind prt_stream() overlaps nothing on the host. */
 prt_status prt_export_sum_to_device(prt_ctx *ctx, float *dstDevice);
 
 /* ---- metrics (the reference's "RtReference"/"BuildTLAS" profiler scopes, App.cpp:575) ------ */

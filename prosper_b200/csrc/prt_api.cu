@@ -1458,10 +1458,10 @@ extern "C" prt_status prt_export_sum_to_device(prt_ctx *c, float *dstDevice)
     REQUIRE(c->historyValid, "nothing recorded yet");
     CK(cudaSetDevice(c->cfg.device));
     const uint32_t pixels = c->accumWidth * c->accumHeight;
+    // stream-ordered on prt_stream(): the caller's collective is enqueued behind it (no host synchronisation)
     k_mean_to_sum<<<blocksFor(pixels, 256), 256, 0, c->stream>>>(c->accum.p, reinterpret_cast<float4 *>(dstDevice), pixels);
     c->kernelLaunches++;
     CK(cudaGetLastError());
-    CK(cudaStreamSynchronize(c->stream));
     return PRT_OK;
 }
 
@@ -1471,10 +1471,11 @@ extern "C" prt_status prt_import_sum_device(prt_ctx *c, const float *sumDevice)
     REQUIRE(c->accumWidth && c->accumHeight, "no render area yet");
     CK(cudaSetDevice(c->cfg.device));
     const uint32_t pixels = c->accumWidth * c->accumHeight;
+    // stream-ordered on prt_stream(): `sumDevice` must be complete in that stream's order (e.g. the collective's work.wait()
+    // with prt_stream() current); no host synchronisation
     k_sum_to_mean<<<blocksFor(pixels, 256), 256, 0, c->stream>>>(reinterpret_cast<const float4 *>(sumDevice), c->accum.p, pixels);
     c->kernelLaunches++;
     CK(cudaGetLastError());
-    CK(cudaStreamSynchronize(c->stream));
     c->historyValid = true;
     return PRT_OK;
 }

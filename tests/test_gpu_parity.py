@@ -497,12 +497,14 @@ def test_sum_export_import_round_trip(test_scene):
     a = r.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=3).illumination_f32()
     buf_a = torch.empty(w * h * 4, dtype=torch.float32, device="cuda")
     world.export_sum_to(buf_a.data_ptr())
+    world.synchronize()  # the export is stream-ordered on the library stream, torch reads on its own
     assert np.allclose(buf_a.cpu().numpy().reshape(h, w, 4)[..., :3], a[..., :3] * 3, rtol=1e-6)
     # "rank 1": frames 4..5 into a fresh accumulation
     r.m_accumulationDirty = True
     b = r.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=2).illumination_f32()
     buf_b = torch.empty_like(buf_a)
     world.export_sum_to(buf_b.data_ptr())
+    world.synchronize()
     total = buf_a + buf_b
     torch.cuda.synchronize()
     world.import_sum(total.data_ptr())
