@@ -6,7 +6,7 @@
  * name says `_device`; the library copies them to HBM on the context's stream. One context per
  * GPU; calls on a context are single-threaded and stream-ordered. Every function returns
  * PRT_OK or a negative prt_status; prt_last_error() gives the message (the C++ wrapper
- * host/RtReference.hpp re-throws it as std::runtime_error like the reference does,
+ * include/prt_rt_reference.hpp re-throws it as std::runtime_error like the reference does,
  * RtRef.cpp:112-113). There is no CPU fallback: without a CUDA device prt_create fails.
  */
 #ifndef PRT_H
@@ -77,7 +77,8 @@ prt_status prt_encode_bc7(prt_ctx *ctx, const void *rgba8, uint32_t width, uint3
                           uint64_t blocksBytes);
 
 /* Texture-cache build, the whole chain of `compress` (Texture.cpp:213-296) on the GPU: RGBA8 level 0 (HOST) -> mip
- * levels (generateMipLevels, 165-211; 2x2 box, colour in linear light when colorSpace == 0 = sRGB, 1 = linear) ->
+ * levels (generateMipLevels, 165-211: stb's default 2:1 reduction = Mitchell-Netravali, 8 taps per axis, alpha-weighted,
+ * colour filtered in linear light when colorSpace == 0 = sRGB, as is when 1 = linear) ->
  * BC7 blocks per level, or plain RGBA8 levels when a kept level is not whole 4x4 blocks (229-237). Levels are the
  * full chain minus the last two (217-225). dataOut (HOST) receives the levels back to back exactly as utils::Dds::data
  * holds them (Dds.cpp:95-133), so writeDds / prosper_b200.dds.write_dds can store it unchanged. */
@@ -173,7 +174,7 @@ typedef struct prt_counters {
     uint64_t shadowRays;    /* main.rgen:57 */
     uint64_t nodesVisited;  /* 80-byte wide nodes fetched (TLAS + BLAS) */
     uint64_t trisTested;    /* 48-byte triangle records fetched */
-    uint64_t instancesEntered; /* 64-byte instance records fetched */
+    uint64_t instancesEntered; /* 96-byte instance records fetched */
     uint64_t anyHitCalls;   /* scene.rahit invocations */
     uint64_t shadedHits;    /* evaluateSurface calls */
     uint64_t textureTaps;   /* bilinear material/alpha fetches */
@@ -198,7 +199,7 @@ typedef struct prt_timings {
     uint32_t lastShadeLaunches;
     float lastTraceShadowMs;
     uint32_t lastTraceShadowLaunches;
-    uint32_t pad;
+    uint32_t ringWraps;       /* laps of the pinned upload ring so far (gfx::RingBuffer wraps to 0, RingBuffer.cpp:56-133) */
 } prt_timings;
 prt_status prt_get_timings(prt_ctx *ctx, prt_timings *out);
 

@@ -80,6 +80,7 @@ struct UploadRing
 {
     uint8_t *base = nullptr;
     size_t capacity = 0, head = 0;
+    uint32_t wraps = 0; // laps completed (prt_timings::ringWraps; the wrap path has its own test)
     cudaEvent_t lap = nullptr;
     static constexpr size_t kAlignment = 256; // RingBuffer.hpp:18 sAlignment
 
@@ -110,6 +111,7 @@ struct UploadRing
             e = cudaEventSynchronize(lap);
             if (e != cudaSuccess) return e;
             start = 0;
+            wraps++;
         }
         memcpy(base + start, src, bytes);
         head = start + bytes;
@@ -359,9 +361,25 @@ static prt_status allocPathBuffers(prt_ctx *c, uint64_t paths)
     return PRT_OK;
 }
 
+static prt_status createContext(const prt_config *cfg, prt_ctx **out);
 extern "C" prt_status prt_create(const prt_config *cfg, prt_ctx **out)
 {
     if (!cfg || !out) return fail(PRT_ERR_INVALID, "prt_create: null argument");
+    *out = nullptr;
+    const prt_status st = createContext(cfg, out);
+    if (st != PRT_OK && *out)
+    {
+        // a half-initialised context never reaches the caller
+        const std::string why = g_lastError;
+        prt_destroy(*out);
+        *out = nullptr;
+        g_lastError = why;
+    }
+    return st;
+}
+
+static prt_status createContext(const prt_config *cfg, prt_ctx **out)
+{
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
         return fail(PRT_ERR_NO_DEVICE, "prt_create: no CUDA device (this library has no CPU fallback)");
@@ -375,7 +393,11 @@ extern "C" prt_status prt_create(const prt_config *cfg, prt_ctx **out)
     if (c->cfg.samplesPerLaunch == 0) c->cfg.samplesPerLaunch = 1;
     *out = c;
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    CK(c->ring.init(32u << 20));
+    {
+        size_t ringBytes = 32u << 20;
+        if (const char *e = std::getenv("PRT_RING_BYTES")) ringBytes = std::max<size_t>(4096, (size_t)std::atoll(e)); // test switch: forces wraps
+        CK(c->ring.init(ringBytes));
+    }
     CK(cudaMalloc((void **)&c->dCounters, sizeof(GlobalCounters)));
     CK(cudaMemset(c->dCounters, 0, sizeof(GlobalCounters)));
     for (int i = 0; i < 2; ++i)
@@ -536,6 +558,13 @@ extern "C" prt_status prt_set_texture(prt_ctx *c, uint32_t index, const prt_text
     REQUIRE(c && desc && desc->data, "prt_set_texture");
     REQUIRE(index >= 1 && index < (1u << 24), "texture index 0 is the reserved 'no texture' slot (WorldData.cpp:727-741)");
     REQUIRE(desc->width > 0 && desc->height > 0, "empty texture");
+    REQUIRE(desc->format == PRT_TEX_RGBA8_UNORM || desc->format == PRT_TEX_BC7_UNORM, "unknown texture format");
+    {
+        // validate the payload before anything is released or allocated
+        const uint64_t need = desc->format == PRT_TEX_BC7_UNORM ? (uint64_t)((desc->width + 3) / 4) * ((desc->height + 3) / 4) * 16
+                                                                 : (uint64_t)desc->width * desc->height * 4;
+        REQUIRE(desc->dataBytes >= need, desc->format == PRT_TEX_BC7_UNORM ? "BC7 payload shorter than level 0" : "RGBA8 payload shorter than level 0");
+    }
     CK(cudaSetDevice(c->cfg.device));
     if (c->textures.size() <= index) c->textures.resize(index + 1);
     TexRes &t = c->textures[index];
@@ -1034,8 +1063,11 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
     }
     REQUIRE(total < (1ull << 31), "model too large");
     if (outReference) *outReference = (uint64_t)modelIndex + 1;
-    b.built = true;
-    if (total == 0) return PRT_OK;
+    if (total == 0)
+    {
+        b.built = true;
+        return PRT_OK;
+    }
     const uint32_t n = (uint32_t)total;
     CK(cudaEventRecord(c->evBlas[0], st));
     uint32_t launches = 0;
@@ -1076,6 +1108,7 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
     CK(cudaEventRecord(c->evBlas[1], st));
     c->blasTimed = true;
     c->kernelLaunches += launches;
+    b.built = true; // only a build that got this far is referable from prt_build_tlas
     return PRT_OK;
 }
 
@@ -1212,6 +1245,7 @@ static prt_status renderBatch(prt_ctx *c, prt_reference_pc pc, uint32_t width, u
 {
     cudaStream_t st = c->stream;
     const uint64_t total = (uint64_t)width * height * samples;
+    REQUIRE(total < (1ull << 32), "width x height x samplesPerLaunch must stay below 2^32 paths (32-bit path indices)");
     CKS(allocPathBuffers(c, total));
     const SceneView sv = c->view();
     const Accel as = c->accel();
@@ -1535,6 +1569,7 @@ extern "C" prt_status prt_get_timings(prt_ctx *c, prt_timings *out)
     }
     out->lastRecordLaunches = c->lastRecordLaunches;
     out->lastTlasLaunches = c->lastTlasLaunches;
+    out->ringWraps = c->ring.wraps;
     return PRT_OK;
 }
 

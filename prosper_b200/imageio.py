@@ -8,7 +8,7 @@ import numpy as np
 
 
 def tonemap(rgb: np.ndarray) -> np.ndarray:
-    """Simple Reinhard + gamma for previews (the reference's Tony McMapface LUT pass is out of scope)."""
+    """Simple Reinhard + gamma for quick previews; the reference's display transform (Tony McMapface LUT) is prt_tone_map / prosper_b200.tonemap."""
     c = np.nan_to_num(np.maximum(rgb, 0.0))
     return np.clip(c / (1.0 + c), 0, 1) ** (1 / 2.2)
 

@@ -609,3 +609,39 @@ def test_radiance_with_1024_lights():
     scene = scene_zoo.atrium(160, 90, tex_size=64, detail=0.08, lights=1024)
     assert len(scene.point_lights) + len(scene.spot_lights) == 1024
     _radiance_against_oracle(scene, 160, 90, 16, ((rt.CFG_COUNTERS | rt.CFG_EXACT_FILTER, 0.005, 5e-4), (rt.CFG_COUNTERS, 0.08, 5e-4)))
+
+
+def test_upload_ring_wraps_without_corrupting_uploads(small_stress, monkeypatch):
+    """gfx::RingBuffer wraps to 0 and must not stomp in-flight data (RingBuffer.cpp:56-133); the CUDA ring waits for the
+    previous lap's copies instead of asserting. A 64 KB ring (PRT_RING_BYTES, test switch) under 150 instances wraps every
+    couple of frames: after ten frames of moving instances the traced IDs still match the oracle on the last pose, and an
+    upload larger than half the ring takes the unstaged path."""
+    import copy
+    monkeypatch.setenv("PRT_RING_BYTES", str(64 * 1024))
+    scene = copy.deepcopy(small_stress)
+    w, h = 160, 90
+    world = _world(scene, w, h)
+    base = scene.transforms["modelToWorld"].copy()
+    for frame in range(1, 11):
+        for i in range(len(scene.tlas_instances) - 1):
+            m = np.eye(4)
+            m[:3, :4] = base[i]
+            m[:3, 3] += 0.05 * frame * np.array([np.sin(i), 0.3 * np.cos(2 * i), np.cos(i)])
+            t = sd.instance_transforms(m)
+            scene.transforms[i] = t
+            scene.tlas_instances[i]["transform"] = t["modelToWorld"]
+        world.updateBuffers(scene)
+        world.buildTlas(scene.tlas_instances)
+    assert world.timings()["ringWraps"] >= 3
+    pc = sd.reference_pc(frame_index=2)
+    ho, margin = oracle.Oracle(scene).trace_primary(pc, w, h)
+    hg = world.trace_primary(pc, w, h)
+    assert (_id_mismatch(ho, hg) & ~(margin < ALPHA_TIE_MARGIN)).sum() == 0
+    # radiance uses the uploaded transforms (normalToWorld) and lights too
+    r = rt.RtReference()
+    r.init(world)
+    r.drawUi(maxBounces=2)
+    out = r.record(world, (0, 0, w, h), rt.Options(ibl=True), frames=2).illumination_f32()
+    ref, _ = oracle.Oracle(scene).render(sd.reference_pc(max_bounces=2), w, h, 2)
+    assert _rel_rmse(out, ref) < 0.02
+    world.close()
