@@ -132,6 +132,34 @@ prt_status prt_read_output_f32(prt_ctx *ctx, float *dstHost, uint64_t dstBytes);
 /* RtReference::releasePreserved (RtRef.cpp:385-391): drops the accumulation history */
 prt_status prt_release_preserved(prt_ctx *ctx);
 
+/* ---- ReSTIR DI trace pass: render::rtdi::Trace (src/render/rtdi/Trace.hpp:19-56, Trace.cpp:176-362;
+ * res/shader/rt/direct_illumination/main.rgen) and the pass that feeds it, rtdi::InitialReservoirs
+ * (restir_di/initial_reservoirs.comp). Trace::Input = {G-buffer, reservoirs}: the G-buffer in the formats of
+ * GBufferRenderer.cpp:31-32 -- albedo+roughness R8G8B8A8_UNORM, encoded normal+metallic A2B10G10R10_UNORM_PACK32, non-linear
+ * reverse-Z depth D32 (0 = nothing drawn) -- and one R32G32 reservoir per pixel (light index bits, unbiased contribution
+ * weight; restir_di/reservoir.glsl). The pass keeps its own running-mean history like RtReference does. -------------- */
+typedef struct prt_rtdi_trace_pc { /* shader_structs/push_constants/restir_di/trace.h */
+    uint32_t drawType;
+    uint32_t frameIndex;
+    uint32_t flags; /* PRT_FLAG_SKIP_HISTORY | PRT_FLAG_ACCUMULATE (Trace.cpp:255-263) */
+} prt_rtdi_trace_pc;
+/* the caller's (raster) G-buffer; HOST pointers, width*height texels each; fixes the pass's resolution */
+prt_status prt_rtdi_set_gbuffer(prt_ctx *ctx, uint32_t width, uint32_t height, const uint32_t *albedoRoughness,
+                                const uint32_t *normalMetallic, const float *nonLinearDepth);
+/* or: the G-buffer a raster pass would have produced, from the tracer's own primary hits through the pixel centres
+ * (gbuffer.frag:57-110; the raster G-buffer pass itself is out of scope) */
+prt_status prt_rtdi_gbuffer_from_primary(prt_ctx *ctx, uint32_t width, uint32_t height, uint32_t frameIndex);
+prt_status prt_rtdi_read_gbuffer(prt_ctx *ctx, uint32_t *albedoRoughness, uint32_t *normalMetallic, float *nonLinearDepth);
+/* reservoirs: the caller's (2 floats per pixel; HOST), or restir_di/initial_reservoirs.comp on the device */
+prt_status prt_rtdi_set_reservoirs(prt_ctx *ctx, const float *packed);
+prt_status prt_rtdi_initial_reservoirs(prt_ctx *ctx, uint32_t frameIndex);
+prt_status prt_rtdi_read_reservoirs(prt_ctx *ctx, float *packedOut);
+/* Trace::record: one frame = one shadow ray per lit pixel through the TLAS of prt_build_tlas, running mean as main.rgen:150-164 */
+prt_status prt_rtdi_trace(prt_ctx *ctx, const prt_rtdi_trace_pc *pc);
+prt_status prt_rtdi_read_output_f32(prt_ctx *ctx, float *dstHost, uint64_t dstBytes);      /* RGBA fp32, count in .a */
+prt_status prt_rtdi_read_illumination_f16(prt_ctx *ctx, void *dstHost, uint64_t dstBytes);  /* Trace::Output::illumination */
+prt_status prt_rtdi_release_preserved(prt_ctx *ctx);                                        /* Trace::releasePreserved */
+
 /* Primary-ray hit records (traceClosest payload, main.rgen:62-81) for frame pc->frameIndex:
  * what the reference can only show through its DrawType debug views (main.rgen:181-193). */
 prt_status prt_trace_primary(prt_ctx *ctx, const prt_reference_pc *pc, uint32_t width,

@@ -67,6 +67,9 @@ def lib():
                                         C.c_int]
         l.orc_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int,
                                      C.c_void_p, C.c_void_p, C.c_int]
+        l.orc_rtdi_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32] + [C.c_void_p] * 5 + [C.c_int, C.c_void_p]
+        l.orc_rtdi_initial_reservoirs.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32] + [C.c_void_p] * 4 + [C.c_int]
+        l.orc_rtdi_gbuffer.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32] + [C.c_void_p] * 3 + [C.c_int]
         l.orc_pcg.restype = C.c_uint32
         l.orc_pcg.argtypes = [C.c_uint32]
         l.orc_rng_to_01.restype = C.c_float
@@ -209,6 +212,33 @@ class Oracle:
         margin = np.zeros(n, np.float32)
         lib().orc_trace_rays(self._ctx, _p(o), _p(d), _p(sd), n, 1 if shadow else 0, _p(hits), _p(margin), threads)
         return hits, margin
+
+    # ---- ReSTIR DI trace pass ----
+    def rtdi_gbuffer(self, frame_index, width, height, threads=0):
+        """(albedoRoughness u32 [h, w], normalMetallic u32 [h, w], nonLinearDepth f32 [h, w]) from the primary hits."""
+        ar, nm = np.zeros((height, width), np.uint32), np.zeros((height, width), np.uint32)
+        z = np.zeros((height, width), np.float32)
+        lib().orc_rtdi_gbuffer(self._ctx, C.c_uint32(frame_index), C.c_uint32(width), C.c_uint32(height), _p(ar), _p(nm), _p(z), C.c_int(threads))
+        return ar, nm, z
+
+    def rtdi_initial_reservoirs(self, frame_index, gbuffer, threads=0):
+        ar, nm, z = (np.ascontiguousarray(a) for a in gbuffer)
+        h, w = ar.shape
+        out = np.zeros((h, w, 2), np.float32)
+        lib().orc_rtdi_initial_reservoirs(self._ctx, C.c_uint32(frame_index), C.c_uint32(w), C.c_uint32(h), _p(ar), _p(nm), _p(z), _p(out), C.c_int(threads))
+        return out
+
+    def rtdi_trace(self, draw_type, frame_index, flags, gbuffer, reservoirs, rgba=None, threads=0):
+        """One frame of rt/direct_illumination/main.rgen. Returns (rgba [h, w, 4], shadow rays traced)."""
+        ar, nm, z = (np.ascontiguousarray(a) for a in gbuffer)
+        h, w = ar.shape
+        res = np.ascontiguousarray(reservoirs, np.float32)
+        if rgba is None:
+            rgba = np.zeros((h, w, 4), np.float32)
+        pc = np.array([draw_type, frame_index, flags], np.uint32)
+        rays = np.zeros(1, np.uint64)
+        lib().orc_rtdi_trace(self._ctx, _p(pc), C.c_uint32(w), C.c_uint32(h), _p(ar), _p(nm), _p(z), _p(res), _p(rgba), C.c_int(threads), _p(rays))
+        return rgba, int(rays[0])
 
     def sample_texture(self, tex, smp, u, v):
         out = np.zeros(4, np.float32)

@@ -700,6 +700,226 @@ template <typename F> static void parallelRows(uint32_t rows, int threads, F &&f
     for (auto &t : pool) t.join();
 }
 
+// ---- ReSTIR DI trace pass: rt/direct_illumination/main.rgen (+ restir_di/*.glsl, initial_reservoirs.comp) ---------------------
+struct GBuffer
+{
+    const uint32_t *albedoRoughness; // R8G8B8A8_UNORM (GBufferRenderer.cpp:31)
+    const uint32_t *normalMetallic;  // A2B10G10R10_UNORM_PACK32 (GBufferRenderer.cpp:32)
+    const float *nonLinearDepth;
+    uint32_t width, height;
+};
+static vec4 unpackUnorm8x4(uint32_t p)
+{
+    return {(float)(p & 255u) / 255.f, (float)((p >> 8) & 255u) / 255.f, (float)((p >> 16) & 255u) / 255.f, (float)(p >> 24) / 255.f};
+}
+static vec4 unpackA2B10G10R10(uint32_t p)
+{
+    return {(float)(p & 1023u) / 1023.f, (float)((p >> 10) & 1023u) / 1023.f, (float)((p >> 20) & 1023u) / 1023.f, (float)(p >> 30) / 3.f};
+}
+static uint32_t unormCode(float v, float top) { return (uint32_t)(std::fmin(std::fmax(v, 0.f), 1.f) * top + 0.5f); }
+
+static vec3 signedOctDecode(vec3 n) // scene/material.glsl:20-31
+{
+    vec3 OutN;
+    OutN.x = (n.x - n.y);
+    OutN.y = (n.x + n.y) - 1.0f;
+    OutN.z = n.z * 2.0f - 1.0f;
+    OutN.z = OutN.z * (1.0f - std::fabs(OutN.x) - std::fabs(OutN.y));
+    return normalize(OutN);
+}
+static vec3 signedOctEncode(vec3 n) // gbuffer.frag:41-55
+{
+    vec3 OutN;
+    n = n / (std::fabs(n.x) + std::fabs(n.y) + std::fabs(n.z));
+    OutN.y = n.y * 0.5f + 0.5f;
+    OutN.x = n.x * 0.5f + OutN.y;
+    OutN.y = n.x * -0.5f + OutN.y;
+    const float fltMax = 3.40282e+38f;
+    OutN.z = saturate(n.z * fltMax);
+    return OutN;
+}
+static Material loadFromGbuffer(const GBuffer &gb, uint32_t px, uint32_t py) // scene/material.glsl:33-48
+{
+    const size_t i = (size_t)py * gb.width + px;
+    const vec4 albedoRoughness = unpackUnorm8x4(gb.albedoRoughness[i]);
+    const vec4 normalMetallic = unpackA2B10G10R10(gb.normalMetallic[i]);
+    Material m;
+    m.albedo = {albedoRoughness.x, albedoRoughness.y, albedoRoughness.z};
+    m.roughness = albedoRoughness.w;
+    m.normal = signedOctDecode(vec3{normalMetallic.x, normalMetallic.y, normalMetallic.w});
+    m.metallic = normalMetallic.z;
+    m.alpha = -1.0f;
+    return m;
+}
+static vec4 mulMat4(const float m[4][4], vec4 v)
+{
+    return {m[0][0] * v.x + m[1][0] * v.y + m[2][0] * v.z + m[3][0] * v.w, m[0][1] * v.x + m[1][1] * v.y + m[2][1] * v.z + m[3][1] * v.w,
+            m[0][2] * v.x + m[1][2] * v.y + m[2][2] * v.z + m[3][2] * v.w, m[0][3] * v.x + m[1][3] * v.y + m[2][3] * v.z + m[3][3] * v.w};
+}
+static vec3 worldPos(const CameraUniforms &c, vec2 uv, float nonLinearDepth) // scene/camera.glsl:24-30
+{
+    const vec4 surfaceVS = mulMat4(c.clipToWorld, vec4{uv.x * 2 - 1, uv.y * 2 - 1, nonLinearDepth, 1});
+    return vec3{surfaceVS.x, surfaceVS.y, surfaceVS.z} / surfaceVS.w;
+}
+static float linearizeDepth(const CameraUniforms &c, float nonLinearDepth) // scene/camera.glsl:11-22
+{
+    return -c.cameraToClip[3][2] / (nonLinearDepth + c.cameraToClip[2][2]);
+}
+static VisibleSurface gbufferSurface(const Scene &sc, const GBuffer &gb, uint32_t px, uint32_t py) // main.rgen:117-131
+{
+    const CameraUniforms &camera = *(const CameraUniforms *)sc.s.camera;
+    const vec2 uv = {(float)px / (float)gb.width, (float)py / (float)gb.height};
+    const float nonLinearDepth = gb.nonLinearDepth[(size_t)py * gb.width + px];
+    VisibleSurface surface{};
+    surface.positionWS = worldPos(camera, uv, nonLinearDepth);
+    surface.invViewRayWS = normalize(vec3{camera.eye[0], camera.eye[1], camera.eye[2]} - surface.positionWS);
+    surface.material = loadFromGbuffer(gb, px, py);
+    surface.normalWS = surface.material.normal;
+    surface.uv = {0, 0};
+    surface.NoV = saturate(dot(surface.normalWS, surface.invViewRayWS));
+    surface.linearDepth = linearizeDepth(camera, nonLinearDepth);
+    return surface;
+}
+
+struct LightReservoir // restir_di/reservoir.glsl:4-9
+{
+    int32_t lightIndex;
+    float unbiasedContributionWeight;
+};
+static float luminance(vec3 c) { return dot(vec3{0.299f, 0.587f, 0.114f}, c); } // common/math.glsl:15
+static float pHatLight(const Scene &sc, const VisibleSurface &surface, uint32_t lightIndex) // resampling_phat.glsl:4-19
+{
+    vec3 l;
+    float d;
+    vec3 irradiance;
+    sampleLight(sc, surface, lightIndex, l, d, irradiance);
+    const vec3 brdf = evalBRDFTimesNoL(l, surface);
+    return luminance(irradiance * brdf);
+}
+static LightReservoir initialLightCandidate(const Scene &sc, const VisibleSurface &surface, Rng &rng) // initial_reservoirs.comp:31-60
+{
+    const int lightCount = 1 + (int)(sc.s.pointLightCount + sc.s.spotLightCount);
+    LightReservoir reservoir = {-1, 0.f};
+    float sumResamplingWeights = 0;
+    const uint32_t sampleCount = 5;
+    for (uint32_t i = 0; i < sampleCount; ++i)
+    {
+        const int lightIndex = std::min((int)(rng.rnd01() * (float)lightCount), lightCount - 1);
+        const float misWeight = 1.f / sampleCount;
+        const float unbiasedContributionWeight = (float)lightCount;
+        const float resamplingWeight = misWeight * pHatLight(sc, surface, (uint32_t)lightIndex) * unbiasedContributionWeight;
+        sumResamplingWeights += resamplingWeight;
+        if (rng.rnd01() < resamplingWeight / sumResamplingWeights) reservoir.lightIndex = lightIndex;
+    }
+    if (reservoir.lightIndex >= 0)
+        reservoir.unbiasedContributionWeight = sumResamplingWeights / pHatLight(sc, surface, (uint32_t)reservoir.lightIndex);
+    return reservoir;
+}
+static vec3 evaluateDirectLightingReSTIR(PathCtx &pc, const VisibleSurface &surface, LightReservoir reservoir) // main.rgen:89-110
+{
+    if (surface.material.alpha == 0 || reservoir.lightIndex < 0) return {0, 0, 0};
+    vec3 l;
+    float d;
+    vec3 irradiance;
+    sampleLight(pc.ctx.scene, surface, (uint32_t)reservoir.lightIndex, l, d, irradiance);
+    if (dot(l, surface.normalWS) <= 0) return {0, 0, 0};
+    irradiance = irradiance * shadow(pc, surface.positionWS, l, 0.1f, d);
+    return irradiance * evalBRDFTimesNoL(l, surface) * reservoir.unbiasedContributionWeight;
+}
+
+extern "C" {
+void orc_rtdi_trace(orc_ctx *ctx, const uint32_t tracePC[3], uint32_t width, uint32_t height, const uint32_t *albedoRoughness,
+                    const uint32_t *normalMetallic, const float *nonLinearDepth, const float *reservoirs, float *rgba, int threads,
+                    uint64_t *shadowRays)
+{ // rt/direct_illumination/main.rgen:112-164
+    const uint32_t drawType = tracePC[0], frameIndex = tracePC[1], flags = tracePC[2];
+    const GBuffer gb{albedoRoughness, normalMetallic, nonLinearDepth, width, height};
+    const int nThreads = threads > 0 ? threads : (int)std::thread::hardware_concurrency();
+    std::vector<uint64_t> perThread((size_t)std::max(nThreads, 1), 0);
+    ReferencePC dummy{};
+    parallelRows(height, nThreads, [&](uint32_t y, int tid) {
+        for (uint32_t x = 0; x < width; ++x)
+        {
+            PathCtx pc{*ctx, dummy, Rng{{x, y, frameIndex}}};
+            const VisibleSurface surface = gbufferSurface(ctx->scene, gb, x, y);
+            float *out = rgba + ((size_t)y * width + x) * 4;
+            if (drawType != 0) // DrawType_Default
+            {
+                const vec3 c = drawType == 5 /* DrawType_Position */ ? surface.positionWS : surface.material.albedo;
+                out[0] = c.x; out[1] = c.y; out[2] = c.z; out[3] = 1.f;
+                continue;
+            }
+            const size_t i = (size_t)y * width + x;
+            LightReservoir reservoir;
+            std::memcpy(&reservoir.lightIndex, &reservoirs[i * 2], 4); // floatBitsToInt
+            reservoir.unbiasedContributionWeight = reservoirs[i * 2 + 1];
+            const vec3 color = evaluateDirectLightingReSTIR(pc, surface, reservoir);
+            perThread[(size_t)tid] += pc.shadowRays;
+            if ((flags & 1u) || !((flags >> 1) & 1u))
+            {
+                out[0] = color.x; out[1] = color.y; out[2] = color.z; out[3] = 1.f;
+            }
+            else
+            {
+                const vec3 historyColor = {out[0], out[1], out[2]};
+                const float historyCount = out[3] + 1;
+                const vec3 newColor = historyColor + (color - historyColor) / historyCount;
+                out[0] = newColor.x; out[1] = newColor.y; out[2] = newColor.z; out[3] = historyCount;
+            }
+        }
+    });
+    if (shadowRays)
+        for (uint64_t v : perThread) *shadowRays += v;
+}
+
+void orc_rtdi_initial_reservoirs(orc_ctx *ctx, uint32_t frameIndex, uint32_t width, uint32_t height, const uint32_t *albedoRoughness,
+                                 const uint32_t *normalMetallic, const float *nonLinearDepth, float *reservoirsOut, int threads)
+{ // restir_di/initial_reservoirs.comp:62-89
+    const GBuffer gb{albedoRoughness, normalMetallic, nonLinearDepth, width, height};
+    parallelRows(height, threads, [&](uint32_t y, int) {
+        for (uint32_t x = 0; x < width; ++x)
+        {
+            Rng rng{{x, y, frameIndex}};
+            const VisibleSurface surface = gbufferSurface(ctx->scene, gb, x, y);
+            const LightReservoir r = initialLightCandidate(ctx->scene, surface, rng);
+            const size_t i = (size_t)y * width + x;
+            std::memcpy(&reservoirsOut[i * 2], &r.lightIndex, 4); // intBitsToFloat
+            reservoirsOut[i * 2 + 1] = r.unbiasedContributionWeight;
+        }
+    });
+}
+
+// The G-buffer texel gbuffer.frag:57-110 writes, for the primary hit through each pixel CENTRE (the raster sample point).
+void orc_rtdi_gbuffer(orc_ctx *ctx, uint32_t frameIndex, uint32_t width, uint32_t height, uint32_t *albedoRoughness, uint32_t *normalMetallic,
+                      float *nonLinearDepth, int threads)
+{
+    const CameraUniforms &camera = *(const CameraUniforms *)ctx->scene.s.camera;
+    ReferencePC dummy{};
+    parallelRows(height, threads, [&](uint32_t y, int) {
+        for (uint32_t x = 0; x < width; ++x)
+        {
+            const size_t i = (size_t)y * width + x;
+            albedoRoughness[i] = 0; normalMetallic[i] = 0; nonLinearDepth[i] = 0.f;
+            PathCtx pc{*ctx, dummy, Rng{{x, y, frameIndex}}};
+            const Ray ray = pinholeCameraRay(camera, vec2{((float)x + 0.5f) / (float)width, ((float)y + 0.5f) / (float)height});
+            TraceArgs a{ray.o, ray.d, ray.tMin, ray.tMax, pcg(x ^ frameIndex), false, nullptr};
+            const Hit hit = trace(*ctx, a);
+            if (hit.drawInstanceIndex == MISS_INDEX) continue;
+            const VisibleSurface surface = evaluateSurface(pc, ray, hit);
+            if (surface.material.alpha == 0) continue; // gbuffer.frag:62-63
+            const Material &m = surface.material;
+            albedoRoughness[i] = unormCode(m.albedo.x, 255.f) | (unormCode(m.albedo.y, 255.f) << 8) | (unormCode(m.albedo.z, 255.f) << 16) |
+                                 (unormCode(m.roughness, 255.f) << 24);
+            const vec3 e = signedOctEncode(surface.normalWS);
+            normalMetallic[i] = unormCode(e.x, 1023.f) | (unormCode(e.y, 1023.f) << 10) | (unormCode(m.metallic, 1023.f) << 20) | (unormCode(e.z, 3.f) << 30);
+            const vec4 view = mulMat4(camera.worldToCamera, vec4{surface.positionWS.x, surface.positionWS.y, surface.positionWS.z, 1.f});
+            const vec4 clip = mulMat4(camera.cameraToClip, view);
+            nonLinearDepth[i] = clip.z / clip.w;
+        }
+    });
+}
+} // extern "C"
+
 static void buildStructures(orc_ctx &ctx)
 {
     const auto t0 = std::chrono::steady_clock::now();

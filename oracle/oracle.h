@@ -85,6 +85,19 @@ void orc_trace_rays(orc_ctx *ctx, const float *originTmin, const float *dirTmax,
                     const uint32_t *seeds, uint32_t count, int shadow, void *hits,
                     float *alphaMargin, int threads);
 
+/* ReSTIR DI trace pass: res/shader/rt/direct_illumination/main.rgen for one frame over a G-buffer in the formats
+ * of GBufferRenderer.cpp:31-32 (RGBA8 albedo+roughness, A2B10G10R10 encoded normal+metallic, non-linear depth) and one
+ * R32G32 reservoir per pixel; tracePC = {drawType, frameIndex, flags}. rgba in/out (running mean, main.rgen:150-164). */
+void orc_rtdi_trace(orc_ctx *ctx, const uint32_t tracePC[3], uint32_t width, uint32_t height, const uint32_t *albedoRoughness,
+                    const uint32_t *normalMetallic, const float *nonLinearDepth, const float *reservoirs, float *rgba, int threads,
+                    uint64_t *shadowRays);
+/* restir_di/initial_reservoirs.comp: 5-candidate RIS over uniformly picked lights, no visibility */
+void orc_rtdi_initial_reservoirs(orc_ctx *ctx, uint32_t frameIndex, uint32_t width, uint32_t height, const uint32_t *albedoRoughness,
+                                 const uint32_t *normalMetallic, const float *nonLinearDepth, float *reservoirsOut, int threads);
+/* the G-buffer texels gbuffer.frag:57-110 writes, from the primary hit through every pixel centre */
+void orc_rtdi_gbuffer(orc_ctx *ctx, uint32_t frameIndex, uint32_t width, uint32_t height, uint32_t *albedoRoughness, uint32_t *normalMetallic,
+                      float *nonLinearDepth, int threads);
+
 /* ---- unit entry points for the known-answer / analytic tests ---- */
 uint32_t orc_pcg(uint32_t v);                        /* random.glsl:7-12 */
 void orc_pcg3d(const uint32_t in[3], uint32_t out[3]); /* random.glsl:17-28 */

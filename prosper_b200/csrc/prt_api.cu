@@ -17,6 +17,7 @@
 #include "kernels_build.cuh"
 #include "kernels_render.cuh"
 #include "kernels_tex.cuh"
+#include "kernels_rtdi.cuh"
 
 using namespace prt;
 
@@ -210,6 +211,13 @@ struct prt_ctx
     DBuf<uint2> f16;
     DBuf<uint32_t> sortKeys, sortPerm, sortHist; // ray reordering (kernels_render.cuh)
     uint32_t raySort = 0;                        // off: measured no gain. bit 0: closest queues of bounce >= 1, bit 1: shadow queues of bounce >= 1, bit 2: shadow queue of bounce 0
+    // ReSTIR DI trace pass (8(f)2): G-buffer, reservoirs and its own accumulation image
+    DBuf<uint32_t> gbAlbedoRoughness, gbNormalMetallic;
+    DBuf<float> gbDepth;
+    DBuf<float2> rtdiReservoirs;
+    DBuf<float4> rtdiAccum;
+    uint32_t rtdiWidth = 0, rtdiHeight = 0;
+    bool rtdiGbufferValid = false, rtdiReservoirsValid = false, rtdiHistoryValid = false;
     DBuf<uint32_t> toneLut; // R9G9B9E5 3D LUT of the display transform (8(f)3)
     uint32_t toneLutDim = 0;
     DBuf<uint32_t> ldr;
@@ -479,6 +487,7 @@ extern "C" void prt_destroy(prt_ctx *c)
     c->bLeft.release(); c->bRight.release(); c->bParentI.release(); c->bParentL.release(); c->bNodes.release(); c->bBounds.release();
     c->accum.release(); c->sum.release(); c->f16.release(); c->userHits.release(); c->userO.release(); c->userD.release();
     c->userSeeds.release();
+    c->gbAlbedoRoughness.release(); c->gbNormalMetallic.release(); c->gbDepth.release(); c->rtdiReservoirs.release(); c->rtdiAccum.release();
     c->toneLut.release(); c->ldr.release(); c->mipTables.release(); c->sortKeys.release(); c->sortPerm.release(); c->sortHist.release();
     for (int i = 0; i < 2; ++i)
     {
@@ -1413,6 +1422,185 @@ extern "C" prt_status prt_tone_map_device(prt_ctx *c, const prt_tone_map_pc *pc,
     uint32_t pixels = 0;
     CKS(toneMapLaunch(c, pc, pixels));
     *out = c->ldr.p;
+    return PRT_OK;
+}
+
+// ---- ReSTIR DI trace pass: render::rtdi::Trace (src/render/rtdi/Trace.cpp:176-362) -------------------------------------------
+static prt_status rtdiSize(prt_ctx *c, uint32_t width, uint32_t height)
+{
+    REQUIRE(width > 0 && height > 0, "empty render area");
+    const uint64_t pixels = (uint64_t)width * height;
+    if (c->cfg.maxWidth && c->cfg.maxHeight) REQUIRE(pixels <= (uint64_t)c->cfg.maxWidth * c->cfg.maxHeight, "render area larger than prt_config");
+    if (c->rtdiWidth != width || c->rtdiHeight != height)
+    {
+        c->rtdiGbufferValid = c->rtdiReservoirsValid = c->rtdiHistoryValid = false;
+        c->rtdiWidth = width;
+        c->rtdiHeight = height;
+    }
+    CK(c->gbAlbedoRoughness.ensure(pixels)); CK(c->gbNormalMetallic.ensure(pixels)); CK(c->gbDepth.ensure(pixels));
+    CK(c->rtdiReservoirs.ensure(pixels)); CK(c->rtdiAccum.ensure(pixels));
+    CKS(allocPathBuffers(c, pixels));
+    return PRT_OK;
+}
+static GBufferView gbufferView(const prt_ctx *c)
+{
+    return GBufferView{c->gbAlbedoRoughness.p, c->gbNormalMetallic.p, c->gbDepth.p, c->rtdiWidth, c->rtdiHeight};
+}
+
+extern "C" prt_status prt_rtdi_set_gbuffer(prt_ctx *c, uint32_t width, uint32_t height, const uint32_t *albedoRoughness,
+                                           const uint32_t *normalMetallic, const float *nonLinearDepth)
+{
+    REQUIRE(c && albedoRoughness && normalMetallic && nonLinearDepth, "prt_rtdi_set_gbuffer");
+    CK(cudaSetDevice(c->cfg.device));
+    CKS(rtdiSize(c, width, height));
+    const size_t pixels = (size_t)width * height;
+    CK(cudaMemcpyAsync(c->gbAlbedoRoughness.p, albedoRoughness, pixels * 4, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->gbNormalMetallic.p, normalMetallic, pixels * 4, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->gbDepth.p, nonLinearDepth, pixels * 4, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->rtdiGbufferValid = true;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_rtdi_gbuffer_from_primary(prt_ctx *c, uint32_t width, uint32_t height, uint32_t frameIndex)
+{
+    REQUIRE(c, "prt_rtdi_gbuffer_from_primary");
+    CK(cudaSetDevice(c->cfg.device));
+    prt_reference_pc pc{};
+    pc.maxBounces = 1;
+    CKS(checkRenderState(c, &pc, width, height));
+    CKS(rtdiSize(c, width, height));
+    const uint32_t pixels = width * height;
+    const SceneView sv = c->view();
+    const Accel as = c->accel();
+    const uint32_t grid = blocksFor(pixels, RENDER_THREADS);
+    k_rtdi_primary_rays<<<grid, RENDER_THREADS, 0, c->stream>>>(sv, width, height, frameIndex, c->pb);
+    launchTrace<false>(c, (c->cfg.flags & PRT_CFG_COUNTERS) != 0, std::min(grid, c->traceBlocks), as, sv, 0, 0, nullptr);
+    k_rtdi_gbuffer<<<grid, RENDER_THREADS, 0, c->stream>>>(sv, c->pb, width, height, c->gbAlbedoRoughness.p, c->gbNormalMetallic.p, c->gbDepth.p);
+    c->kernelLaunches += 3;
+    CK(cudaGetLastError());
+    c->rtdiGbufferValid = true;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_rtdi_read_gbuffer(prt_ctx *c, uint32_t *albedoRoughness, uint32_t *normalMetallic, float *nonLinearDepth)
+{
+    REQUIRE(c && albedoRoughness && normalMetallic && nonLinearDepth, "prt_rtdi_read_gbuffer");
+    REQUIRE(c->rtdiGbufferValid, "no G-buffer yet (prt_rtdi_set_gbuffer / prt_rtdi_gbuffer_from_primary)");
+    CK(cudaSetDevice(c->cfg.device));
+    const size_t pixels = (size_t)c->rtdiWidth * c->rtdiHeight;
+    CK(cudaMemcpyAsync(albedoRoughness, c->gbAlbedoRoughness.p, pixels * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(normalMetallic, c->gbNormalMetallic.p, pixels * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(nonLinearDepth, c->gbDepth.p, pixels * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_rtdi_set_reservoirs(prt_ctx *c, const float *packed)
+{
+    REQUIRE(c && packed, "prt_rtdi_set_reservoirs");
+    REQUIRE(c->rtdiGbufferValid, "set the G-buffer first: it fixes the resolution");
+    CK(cudaSetDevice(c->cfg.device));
+    const size_t pixels = (size_t)c->rtdiWidth * c->rtdiHeight;
+    CK(cudaMemcpyAsync(c->rtdiReservoirs.p, packed, pixels * 8, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->rtdiReservoirsValid = true;
+    return PRT_OK;
+}
+
+// rtdi::InitialReservoirs::record (src/render/rtdi/InitialReservoirs.cpp; restir_di/initial_reservoirs.comp)
+extern "C" prt_status prt_rtdi_initial_reservoirs(prt_ctx *c, uint32_t frameIndex)
+{
+    REQUIRE(c, "prt_rtdi_initial_reservoirs");
+    REQUIRE(c->rtdiGbufferValid, "no G-buffer yet (prt_rtdi_set_gbuffer / prt_rtdi_gbuffer_from_primary)");
+    REQUIRE(c->haveCamera && c->haveLights, "prt_set_camera / prt_set_lights have not been called");
+    CK(cudaSetDevice(c->cfg.device));
+    const uint32_t pixels = c->rtdiWidth * c->rtdiHeight;
+    k_rtdi_initial_reservoirs<<<blocksFor(pixels, RENDER_THREADS), RENDER_THREADS, 0, c->stream>>>(c->view(), gbufferView(c), frameIndex,
+                                                                                                     c->rtdiReservoirs.p);
+    c->kernelLaunches++;
+    CK(cudaGetLastError());
+    c->rtdiReservoirsValid = true;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_rtdi_read_reservoirs(prt_ctx *c, float *packedOut)
+{
+    REQUIRE(c && packedOut, "prt_rtdi_read_reservoirs");
+    REQUIRE(c->rtdiReservoirsValid, "no reservoirs yet");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(packedOut, c->rtdiReservoirs.p, (size_t)c->rtdiWidth * c->rtdiHeight * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+// rtdi::Trace::record (Trace.cpp:176-362): one frame. The history is recreated on resize, which resets it (Trace.cpp:185-219).
+extern "C" prt_status prt_rtdi_trace(prt_ctx *c, const prt_rtdi_trace_pc *pcIn)
+{
+    REQUIRE(c && pcIn, "prt_rtdi_trace");
+    REQUIRE(c->rtdiGbufferValid, "no G-buffer yet (Trace::Input::gbuffer)");
+    REQUIRE(pcIn->drawType < PRT_DRAW_COUNT, "unknown draw type");
+    REQUIRE(c->rtdiReservoirsValid || pcIn->drawType != PRT_DRAW_DEFAULT, "no reservoirs yet (Trace::Input::reservoirs)");
+    CK(cudaSetDevice(c->cfg.device));
+    prt_reference_pc rp{};
+    rp.maxBounces = 1;
+    CKS(checkRenderState(c, &rp, c->rtdiWidth, c->rtdiHeight));
+    RtdiTracePC pc{pcIn->drawType, pcIn->frameIndex, pcIn->flags};
+    if (!c->rtdiHistoryValid) pc.flags |= 1u;
+    const uint32_t pixels = c->rtdiWidth * c->rtdiHeight;
+    const SceneView sv = c->view();
+    const Accel as = c->accel();
+    const uint32_t grid = blocksFor(pixels, RENDER_THREADS);
+    const bool count = (c->cfg.flags & PRT_CFG_COUNTERS) != 0;
+    CK(cudaMemsetAsync(c->pb.counts, 0, COUNT_WORDS * sizeof(uint32_t), c->stream));
+    k_rtdi_shade<<<grid, RENDER_THREADS, 0, c->stream>>>(sv, gbufferView(c), pc, c->rtdiReservoirs.p, c->pb);
+    uint32_t launches = 2;
+    if (pc.drawType == PRT_DRAW_DEFAULT)
+    {
+        launchTrace<true>(c, count, std::min(grid, c->traceBlocks), as, sv, 0, 0, nullptr);
+        k_tally<<<1, 32, 0, c->stream>>>(c->pb, c->dCounters, pixels);
+        launches += 2;
+    }
+    k_rtdi_accumulate<<<blocksFor(pixels, 256), 256, 0, c->stream>>>(c->pb, c->rtdiAccum.p, pixels, pc.flags, pc.drawType != PRT_DRAW_DEFAULT ? 1u : 0u);
+    c->kernelLaunches += launches;
+    CK(cudaGetLastError());
+    c->rtdiHistoryValid = true;
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_rtdi_read_output_f32(prt_ctx *c, float *dstHost, uint64_t dstBytes)
+{
+    REQUIRE(c && dstHost, "prt_rtdi_read_output_f32");
+    REQUIRE(c->rtdiHistoryValid, "nothing traced yet");
+    const uint64_t bytes = (uint64_t)c->rtdiWidth * c->rtdiHeight * 16;
+    REQUIRE(dstBytes >= bytes, "destination too small");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(dstHost, c->rtdiAccum.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+// The fp16 image later passes expect (Trace.cpp:300-345)
+extern "C" prt_status prt_rtdi_read_illumination_f16(prt_ctx *c, void *dstHost, uint64_t dstBytes)
+{
+    REQUIRE(c && dstHost, "prt_rtdi_read_illumination_f16");
+    REQUIRE(c->rtdiHistoryValid, "nothing traced yet");
+    const uint32_t pixels = c->rtdiWidth * c->rtdiHeight;
+    REQUIRE(dstBytes >= (uint64_t)pixels * 8, "destination too small");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(c->f16.ensure(pixels));
+    k_blit_f16<<<blocksFor(pixels, 256), 256, 0, c->stream>>>(c->rtdiAccum.p, c->f16.p, pixels);
+    c->kernelLaunches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dstHost, c->f16.p, (size_t)pixels * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_rtdi_release_preserved(prt_ctx *c)
+{
+    REQUIRE(c, "prt_rtdi_release_preserved");
+    c->rtdiHistoryValid = false; // Trace::releasePreserved
     return PRT_OK;
 }
 

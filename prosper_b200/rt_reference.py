@@ -69,6 +69,8 @@ ABI_SYMBOLS = (
     "prt_export_sum_to_device", "prt_encode_bc7", "prt_compress_texture", "prt_set_tone_map_lut", "prt_tone_map", "prt_tone_map_device",
     "prt_get_counters", "prt_reset_counters", "prt_get_timings", "prt_get_bvh_stats", "prt_probe_texture",
     "prt_debug_read_blas", "prt_debug_read_tlas",
+    "prt_rtdi_set_gbuffer", "prt_rtdi_gbuffer_from_primary", "prt_rtdi_read_gbuffer", "prt_rtdi_set_reservoirs", "prt_rtdi_initial_reservoirs",
+    "prt_rtdi_read_reservoirs", "prt_rtdi_trace", "prt_rtdi_read_output_f32", "prt_rtdi_read_illumination_f16", "prt_rtdi_release_preserved",
 )
 
 _lib = None
@@ -107,6 +109,10 @@ def load_library():
             "prt_probe_texture": [vp, u32, vp, vp, u32, C.c_int, vp],
             "prt_debug_read_blas": [vp, u32, vp, u64, vp, u64, C.POINTER(u32), C.POINTER(u32)],
             "prt_debug_read_tlas": [vp, vp, u64, vp, u64, C.POINTER(u32)],
+            "prt_rtdi_set_gbuffer": [vp, u32, u32, vp, vp, vp], "prt_rtdi_gbuffer_from_primary": [vp, u32, u32, u32],
+            "prt_rtdi_read_gbuffer": [vp, vp, vp, vp], "prt_rtdi_set_reservoirs": [vp, vp], "prt_rtdi_initial_reservoirs": [vp, u32],
+            "prt_rtdi_read_reservoirs": [vp, vp], "prt_rtdi_trace": [vp, vp], "prt_rtdi_read_output_f32": [vp, vp, u64],
+            "prt_rtdi_read_illumination_f16": [vp, vp, u64], "prt_rtdi_release_preserved": [vp],
         }
         for name, args in sigs.items():
             fn = getattr(l, name)
