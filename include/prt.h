@@ -86,6 +86,20 @@ prt_status prt_compress_texture(prt_ctx *ctx, const void *rgba8, uint32_t width,
                                 uint32_t generateMipMaps, void *dataOut, uint64_t dataBytes, uint32_t *formatOut,
                                 uint32_t *mipLevelCountOut);
 
+/* prt_compress_texture without any device allocation. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it). Same arguments, same kernels and bit-identical output as prt_compress_texture, but the intermediate mip
+ * levels, the block staging and the filter tables live in one file-scope `static __device__` array of
+ * PRT_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit; the call makes no cudaMalloc / cudaFree.
+ * Limit: level 0 of at most PRT_STATIC_MAX_TEXELS texels (1024 x 1024 or any other shape of that area); more is refused
+ * with PRT_ERR_INVALID and a message naming the limit. All calls (all contexts on one GPU) share the array and it keeps
+ * the last call's contents: calls that overlap on the GPU race, so serialise them. rgba8 / dataOut are HOST memory. */
+#define PRT_STATIC_MAX_TEXELS (1024u * 1024u)
+#define PRT_STATIC_SCRATCH_BYTES (12u * 1024u * 1024u) /* tables 4352 B + chain < 2 x 4 B/texel + blocks < 2 x 1 B/texel */
+prt_status prt_compress_texture_static(prt_ctx *ctx, const void *rgba8, uint32_t width, uint32_t height, uint32_t colorSpace,
+                                       uint32_t generateMipMaps, void *dataOut, uint64_t dataBytes, uint32_t *formatOut,
+                                       uint32_t *mipLevelCountOut);
+
 /* Display transform (render::ToneMap, src/render/ToneMap.cpp + res/shader/tone_map.comp).
  * prt_set_tone_map_lut = ToneMap::init (ToneMap.cpp:31-42): the dim^3 3D table in DXGI R9G9B9E5_SHAREDEXP texels, x
  * fastest -- the payload of res/texture/tony_mc_mapface.dds (dim 48) as it lies in the file; HOST memory.

@@ -10,7 +10,9 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cmath>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -760,6 +762,110 @@ extern "C" prt_status prt_compress_texture(prt_ctx *c, const void *rgba8, uint32
     CK(cudaStreamSynchronize(c->stream));
     raw.release();
     blocks.release();
+    *formatOut = bc7 ? PRT_TEX_BC7_UNORM : PRT_TEX_RGBA8_UNORM;
+    *mipLevelCountOut = levels;
+    return PRT_OK;
+}
+
+// ---- prt_compress_texture_static: the same level chain with NO device allocation ------------------------------------
+// Added (no counterpart in the reference): callers that cannot reach cudaMalloc
+// (graph capture, serving loops, harnesses that forbid it) get the mip + BC7 chain with its intermediate levels, its block
+// staging and the filter tables in ONE file-scope device array. Every GPU that loads the library holds
+// PRT_STATIC_SCRATCH_BYTES of it until exit. All calls share it (it keeps the last call's contents): calls that overlap on
+// one GPU race. Nothing in it has to start at zero -- every byte a kernel reads was written earlier in the same call (level
+// 0 by the upload, level i by the downsample of level i-1, the blocks by the encoder), and the tables are written once.
+static __device__ __align__(256) unsigned char g_staticScratch[PRT_STATIC_SCRATCH_BYTES];
+static const size_t STATIC_TABLE_BYTES = 4352; // 1032 floats, rounded up to 256 B
+static const int STATIC_MAX_DEVICES = 64;
+static unsigned char *g_staticScratchPtr[STATIC_MAX_DEVICES]; // DEVICE addresses of g_staticScratch, one per GPU set up
+static std::mutex g_staticScratchMutex;
+
+// Once per device, with that device current: the device address of the array (its name is only a host-side stand-in
+// here) and the filter tables of prt_compress_texture, written into its first STATIC_TABLE_BYTES.
+static prt_status staticScratchFor(int device, unsigned char **out)
+{
+    if (device < 0 || device >= STATIC_MAX_DEVICES) return fail(PRT_ERR_INVALID, "prt_compress_texture_static: device index beyond 63");
+    std::lock_guard<std::mutex> lock(g_staticScratchMutex);
+    if (!g_staticScratchPtr[device])
+    {
+        CK(cudaSetDevice(device));
+        unsigned char *ptr = nullptr;
+        CK(cudaGetSymbolAddress((void **)&ptr, g_staticScratch));
+        if (!ptr) return fail(PRT_ERR_CUDA, "cudaGetSymbolAddress(g_staticScratch) returned a null address");
+        float t[1032] = {}; // same tables, same arithmetic as prt_compress_texture
+        auto lin = [](double s) { return s <= 0.04045 ? s / 12.92 : std::pow((s + 0.055) / 1.055, 2.4); };
+        auto mitchell = [](double x) { return x < 1.0 ? (16.0 + x * x * (21.0 * x - 36.0)) / 18.0 : (32.0 + x * (-60.0 + x * (36.0 - 7.0 * x))) / 18.0; };
+        for (int b = 0; b < 256; ++b) t[b] = (float)lin(b / 255.0), t[256 + b] = (float)(b / 255.0);
+        for (int b = 0; b < 255; ++b) t[512 + b] = (float)lin((b + 0.5) / 255.0), t[768 + b] = (float)((b + 0.5) / 255.0);
+        const double d[8] = {1.75, 1.25, 0.75, 0.25, 0.25, 0.75, 1.25, 1.75};
+        double sum = 0;
+        for (double x : d) sum += mitchell(x);
+        for (int k = 0; k < 8; ++k) t[1024 + k] = (float)(mitchell(d[k]) / sum);
+        CK(cudaMemcpy(ptr, t, sizeof(t), cudaMemcpyHostToDevice));
+        g_staticScratchPtr[device] = ptr;
+    }
+    *out = g_staticScratchPtr[device];
+    return PRT_OK;
+}
+
+extern "C" prt_status prt_compress_texture_static(prt_ctx *c, const void *rgba8, uint32_t width, uint32_t height, uint32_t colorSpace,
+                                                  uint32_t generateMipMaps, void *dataOut, uint64_t dataBytes, uint32_t *formatOut,
+                                                  uint32_t *mipLevelCountOut)
+{
+    REQUIRE(c && rgba8 && dataOut && formatOut && mipLevelCountOut, "prt_compress_texture_static");
+    REQUIRE(width > 0 && height > 0 && width <= 16384 && height <= 16384, "texture extent out of range");
+    REQUIRE((uint64_t)width * height <= PRT_STATIC_MAX_TEXELS,
+            "prt_compress_texture_static takes at most PRT_STATIC_MAX_TEXELS (1024 x 1024) texels in level 0; larger images go "
+            "through prt_compress_texture");
+    REQUIRE(colorSpace <= 1, "colorSpace is 0 (sRGB) or 1 (linear), TextureColorSpace in Texture.hpp");
+    const uint32_t full = generateMipMaps ? mipCountFor(std::max(width, height)) : 1u;
+    const uint32_t levels = full > 2 ? full - 2 : 1u;
+    bool bc7 = true;
+    for (uint32_t i = 0; i < levels; ++i)
+        if ((std::max(width >> i, 1u) % 4) != 0 || (std::max(height >> i, 1u) % 4) != 0) bc7 = false;
+    uint64_t rawOff[16], outOff[16]; // 16384 has 15 levels, 13 kept
+    uint64_t rawTexels = 0, outBytes = 0;
+    for (uint32_t i = 0; i < levels; ++i)
+    {
+        const uint64_t w = std::max(width >> i, 1u), h = std::max(height >> i, 1u);
+        rawOff[i] = rawTexels;
+        outOff[i] = outBytes;
+        rawTexels += w * h;
+        outBytes += bc7 ? (w / 4) * (h / 4) * 16 : w * h * 4;
+    }
+    REQUIRE(dataBytes >= outBytes, "destination too small for the level chain");
+    const uint64_t rawBytes = (rawTexels * 4 + 255) & ~(uint64_t)255;
+    REQUIRE(STATIC_TABLE_BYTES + rawBytes + (bc7 ? outBytes : 0) <= PRT_STATIC_SCRATCH_BYTES,
+            "level chain larger than the static scratch array (PRT_STATIC_SCRATCH_BYTES)");
+    CK(cudaSetDevice(c->cfg.device));
+    unsigned char *scratch = nullptr;
+    CKS(staticScratchFor(c->cfg.device, &scratch));
+    const float *tp = (const float *)scratch;
+    uint32_t *raw = (uint32_t *)(scratch + STATIC_TABLE_BYTES);
+    uint2 *blocks = (uint2 *)(scratch + STATIC_TABLE_BYTES + rawBytes);
+    CK(cudaMemcpyAsync(raw, rgba8, (size_t)width * height * 4, cudaMemcpyHostToDevice, c->stream));
+    for (uint32_t i = 0; i < levels; ++i)
+    {
+        const uint32_t w = std::max(width >> i, 1u), h = std::max(height >> i, 1u);
+        if (i > 0)
+        {
+            const uint32_t pw = std::max(width >> (i - 1), 1u), ph = std::max(height >> (i - 1), 1u);
+            const bool srgb = colorSpace == 0;
+            const MipTables tb{srgb ? tp : tp + 256, tp + 256, srgb ? tp + 512 : tp + 768, tp + 768, tp + 1024};
+            k_downsample_mitchell<<<blocksFor((size_t)w * h, 128), 128, 0, c->stream>>>(raw + rawOff[i - 1], (int)pw, (int)ph, raw + rawOff[i],
+                                                                                       (int)w, (int)h, tb);
+            c->kernelLaunches++;
+        }
+        if (bc7)
+        {
+            const size_t nBlocks = (size_t)(w / 4) * (h / 4);
+            k_bc7_encode_mode6<<<blocksFor(nBlocks, 64), 64, 0, c->stream>>>(raw + rawOff[i], w, h, blocks + outOff[i] / 8);
+            c->kernelLaunches++;
+        }
+    }
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dataOut, bc7 ? (const void *)blocks : (const void *)raw, outBytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
     *formatOut = bc7 ? PRT_TEX_BC7_UNORM : PRT_TEX_RGBA8_UNORM;
     *mipLevelCountOut = levels;
     return PRT_OK;

@@ -71,6 +71,7 @@ ABI_SYMBOLS = (
     "prt_debug_read_blas", "prt_debug_read_tlas",
     "prt_rtdi_set_gbuffer", "prt_rtdi_gbuffer_from_primary", "prt_rtdi_read_gbuffer", "prt_rtdi_set_reservoirs", "prt_rtdi_initial_reservoirs",
     "prt_rtdi_read_reservoirs", "prt_rtdi_trace", "prt_rtdi_read_output_f32", "prt_rtdi_read_illumination_f16", "prt_rtdi_release_preserved",
+    "prt_compress_texture_static",
 )
 
 _lib = None
@@ -103,6 +104,7 @@ def load_library():
             "prt_trace_rays": [vp, vp, vp, vp, u32, C.c_int, vp], "prt_export_sum_device": [vp, C.POINTER(vp)],
             "prt_import_sum_device": [vp, vp], "prt_export_sum_to_device": [vp, vp],
             "prt_compress_texture": [vp, vp, u32, u32, u32, u32, vp, u64, C.POINTER(u32), C.POINTER(u32)],
+            "prt_compress_texture_static": [vp, vp, u32, u32, u32, u32, vp, u64, C.POINTER(u32), C.POINTER(u32)],
             "prt_set_tone_map_lut": [vp, vp, u32], "prt_tone_map": [vp, vp, vp, u64], "prt_tone_map_device": [vp, vp, C.POINTER(vp)],
             "prt_encode_bc7": [vp, vp, u32, u32, vp, u64], "prt_get_counters": [vp, C.POINTER(PrtCounters)], "prt_reset_counters": [vp],
             "prt_get_timings": [vp, C.POINTER(PrtTimings)], "prt_get_bvh_stats": [vp, C.POINTER(PrtBvhStats)],
