@@ -480,6 +480,39 @@ HD float sahOrdHalfArea(const uint32_t *lo, const uint32_t *hi)
     const float ex = unordF(hi[0]) - unordF(lo[0]), ey = unordF(hi[1]) - unordF(lo[1]), ez = unordF(hi[2]) - unordF(lo[2]);
     return ex * ey + ey * ez + ez * ex;
 }
+// The result of a range's split: its SahSplit record, its internal node (named by the gap it splits), its two children
+// (leaves or ranges of the next level). Returns the position of the first of the `made` child ranges in the next level's
+// count; `childKeys` receives their keys (the cooperative builder queues them, k_sah_all_levels).
+HD uint32_t sahSplitEmit(const Sah &s, uint32_t key, const SahRange &r, const SahAxes &ax, uint32_t bestBin, uint32_t bestLeft, uint32_t bestSlot,
+                         const Box &nodeBox, uint32_t childKeys[2], uint32_t &made)
+{
+    SahSplit sp;
+    sp.first = r.first; sp.count = r.count; sp.cursorL = 0; sp.cursorR = 0;
+    sp.cmin = ax.byIndex ? u2f(ax.idxMin) : ax.cmin[bestSlot];
+    sp.scale = ax.byIndex ? u2f(ax.idxSpan) : ax.scale[bestSlot];
+    // distinct primitive indices always leave two non-empty bins, so a range of >= 2 primitives always finds a split;
+    // halving by position is kept as the safety net only (it would depend on the order the partition left behind)
+    if (bestLeft == 0) { sp.leftCount = r.count / 2u; sp.axisBin = SAH_MEDIAN; }
+    else { sp.leftCount = bestLeft; sp.axisBin = ((ax.byIndex ? SAH_INDEX_AXIS : ax.axis[bestSlot]) << 8) | bestBin; }
+    s.split[key] = sp;
+
+    const uint32_t gap = r.first + sp.leftCount - 1u;
+    if (r.parent < 0) *s.rootGap = gap;
+    const uint32_t node = r.parent < 0 ? 0u : sahNodeOfGap(gap, *s.rootGap);
+    const Lbvh &t = s.t;
+    t.first[node] = r.first;
+    t.last[node] = r.first + r.count - 1u;
+    t.nodeBox[node] = nodeBox;
+    t.parentOfInternal[node] = r.parent;
+    if (r.parent >= 0) { if (r.isRight) t.right[r.parent] = (int32_t)node; else t.left[r.parent] = (int32_t)node; }
+    made = 0;
+    if (sp.leftCount == 1u) { t.left[node] = ~(int32_t)r.first; t.parentOfLeaf[r.first] = (int32_t)node; }
+    else { s.rangeOut[r.first >> 1] = SahRange{r.first, sp.leftCount, (int32_t)node, 0u}; childKeys[made++] = r.first >> 1; }
+    const uint32_t rf = r.first + sp.leftCount, rc = r.count - sp.leftCount;
+    if (rc == 1u) { t.right[node] = ~(int32_t)rf; t.parentOfLeaf[rf] = (int32_t)node; }
+    else { s.rangeOut[rf >> 1] = SahRange{rf, rc, (int32_t)node, 1u}; childKeys[made++] = rf >> 1; }
+    return made ? atomAdd(&s.active[s.level + 1u], made) : 0u;
+}
 // pass 3, per slot; only the first slot of an active range works
 HD void sahSplitPass(const Sah &s, uint32_t slot)
 {
@@ -531,32 +564,8 @@ HD void sahSplitPass(const Sah &s, uint32_t slot)
         }
         for (uint32_t i = 0; i < nb; ++i) sahBinClear(&bins[i]);
     }
-    SahSplit sp;
-    sp.first = r.first; sp.count = r.count; sp.cursorL = 0; sp.cursorR = 0;
-    sp.cmin = ax.byIndex ? u2f(ax.idxMin) : ax.cmin[bestSlot];
-    sp.scale = ax.byIndex ? u2f(ax.idxSpan) : ax.scale[bestSlot];
-    // distinct primitive indices always leave two non-empty bins, so a range of >= 2 primitives always finds a split;
-    // halving by position is kept as the safety net only (it would depend on the order the partition left behind)
-    if (bestLeft == 0) { sp.leftCount = r.count / 2u; sp.axisBin = SAH_MEDIAN; }
-    else { sp.leftCount = bestLeft; sp.axisBin = ((ax.byIndex ? SAH_INDEX_AXIS : ax.axis[bestSlot]) << 8) | bestBin; }
-    s.split[key] = sp;
-
-    const uint32_t gap = r.first + sp.leftCount - 1u;
-    if (r.parent < 0) *s.rootGap = gap;
-    const uint32_t node = r.parent < 0 ? 0u : sahNodeOfGap(gap, *s.rootGap);
-    const Lbvh &t = s.t;
-    t.first[node] = r.first;
-    t.last[node] = r.first + r.count - 1u;
-    t.nodeBox[node] = nodeBox;
-    t.parentOfInternal[node] = r.parent;
-    if (r.parent >= 0) { if (r.isRight) t.right[r.parent] = (int32_t)node; else t.left[r.parent] = (int32_t)node; }
-    uint32_t made = 0;
-    if (sp.leftCount == 1u) { t.left[node] = ~(int32_t)r.first; t.parentOfLeaf[r.first] = (int32_t)node; }
-    else { s.rangeOut[r.first >> 1] = SahRange{r.first, sp.leftCount, (int32_t)node, 0u}; made++; }
-    const uint32_t rf = r.first + sp.leftCount, rc = r.count - sp.leftCount;
-    if (rc == 1u) { t.right[node] = ~(int32_t)rf; t.parentOfLeaf[rf] = (int32_t)node; }
-    else { s.rangeOut[rf >> 1] = SahRange{rf, rc, (int32_t)node, 1u}; made++; }
-    if (made) atomAdd(&s.active[s.level + 1u], made);
+    uint32_t childKeys[2], made;
+    sahSplitEmit(s, key, r, ax, bestBin, bestLeft, bestSlot, nodeBox, childKeys, made);
 }
 // pass 4, per slot: side of the slot's primitive (0 left, 1 right); false: the slot is final / halved by position
 HD bool sahSlotSide(const Sah &s, uint32_t slot, uint32_t prim, const SahSplit &sp, uint32_t &side)

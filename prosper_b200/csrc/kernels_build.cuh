@@ -216,37 +216,37 @@ __global__ void k_ploc_finish_nodes(Lbvh t, const uint32_t *newPos)
     plocRelabelNode(t, i, newPos);
 }
 
-// ---- binned SAH (core_bvh.h): per level centroid bounds -> bins -> split -> partition, one thread per slot.
-// Near the root most blocks lie inside one range: those reduce in the warp / bin in shared memory first, so the
-// range's global counters see one update per warp or block instead of one per primitive.
+// ---- binned SAH (core_bvh.h): ONE cooperative launch builds every level --------------------------------------------
+// Per level: bins (per slot) -> split (one warp per active range, from the level's queue) -> partition (per slot; it
+// also gathers the centroid bounds of the child ranges, so only level 0 has a centroid pass of its own), with a grid
+// barrier between the passes; the host neither launches per level nor reads a counter back. Near the root most tiles lie
+// inside one range: those reduce in the warp / bin in shared memory first, so the range's global counters see one update
+// per warp or block instead of one per primitive. The tree is the one the per-slot passes of core_bvh.h give (hostsim).
 constexpr int SAH_THREADS = 256;
 static_assert(SAH_RANGE_BINS <= SAH_THREADS, "one thread per bin clears and flushes the block's bins");
+static_assert(SAH_AXES == 1 && SAH_BINS <= 64, "the warp split takes two bins of one axis per lane");
 
-__global__ void k_sah_init(Sah s, uint32_t keys, uint32_t *idx0, uint32_t *key0, SahRange *range0)
+struct SahGrid
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < s.t.count) { idx0[i] = i; key0[i] = 0u; }
-    if (i < s.t.count)
-        for (uint32_t b = 0; b < SAH_SLOT_BINS; ++b) sahBinClear(&s.bins[(size_t)i * SAH_SLOT_BINS + b]);
-    if (i < keys) sahCentClear(&s.cent[i * SAH_CENT]);
-    if (i <= SAH_MAX_LEVELS) s.active[i] = i == 0 ? 1u : 0u;
-    if (i == 0) { range0[0] = SahRange{0u, s.t.count, -1, 0u}; *s.rootGap = 0u; }
-}
+    uint32_t *idx[2], *key[2], *queue[2]; // ping-pong: slot -> primitive, slot -> range key, active range keys of a level
+    SahRange *range[2];
+    uint32_t keys;                        // count / 2 + 1
+    uint32_t *levelsOut;                  // levels run; SAH_MAX_LEVELS + 1 when the budget ran out
+};
 
-// true when every slot of this block belongs to the same active range (ranges are contiguous)
-__device__ __forceinline__ bool sahBlockUniform(const Sah &s, uint32_t &key)
+// true when every slot of tile [base, base + SAH_THREADS) belongs to the same active range (ranges are contiguous)
+__device__ __forceinline__ bool sahTileUniform(const Sah &s, uint32_t base, uint32_t &key)
 {
-    const uint32_t base = blockIdx.x * blockDim.x;
-    const uint32_t lastSlot = min(base + blockDim.x, s.t.count) - 1u;
+    const uint32_t lastSlot = min(base + (uint32_t)SAH_THREADS, s.t.count) - 1u;
     key = s.keyIn[base];
     return key != SAH_FINAL && key == s.keyIn[lastSlot];
 }
 
-__global__ void __launch_bounds__(SAH_THREADS) k_sah_centroid(Sah s)
+__device__ __forceinline__ void sahCentroidTile(const Sah &s, uint32_t base)
 {
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t slot = base + threadIdx.x;
     uint32_t key;
-    if (!sahBlockUniform(s, key))
+    if (!sahTileUniform(s, base, key))
     {
         if (slot < s.t.count) sahCentroidPass(s, slot);
         return;
@@ -273,12 +273,11 @@ __global__ void __launch_bounds__(SAH_THREADS) k_sah_centroid(Sah s)
     }
 }
 
-__global__ void __launch_bounds__(SAH_THREADS) k_sah_bin(Sah s)
+__device__ __forceinline__ void sahBinTile(const Sah &s, uint32_t base, SahBin *sb)
 {
-    __shared__ SahBin sb[SAH_RANGE_BINS];
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t slot = base + threadIdx.x;
     uint32_t key;
-    if (!sahBlockUniform(s, key))
+    if (!sahTileUniform(s, base, key)) // block-uniform branch
     {
         if (slot < s.t.count) sahBinPass(s, slot);
         return;
@@ -290,47 +289,211 @@ __global__ void __launch_bounds__(SAH_THREADS) k_sah_bin(Sah s)
     if (slot < s.t.count) sahBinInto(s, slot, key, r.count, sb);
     __syncthreads();
     if (threadIdx.x < used && sb[threadIdx.x].count) sahBinMerge(&s.bins[(size_t)r.first * SAH_SLOT_BINS + threadIdx.x], sb[threadIdx.x]);
+    __syncthreads(); // the next tile of this block clears sb again
 }
 
-__global__ void k_sah_split(Sah s)
+// running union of bins: planes in ordF form + primitive count (the identity is an empty bin)
+struct SahAcc
 {
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot < s.t.count) sahSplitPass(s, slot);
+    uint32_t lo[3], hi[3], cnt;
+};
+__device__ __forceinline__ SahAcc sahAccEmpty() { return SahAcc{{0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, {0u, 0u, 0u}, 0u}; }
+__device__ __forceinline__ SahAcc sahAccUnion(const SahAcc &x, const SahAcc &y)
+{
+    SahAcc r;
+    for (int a = 0; a < 3; ++a) { r.lo[a] = min(x.lo[a], y.lo[a]); r.hi[a] = max(x.hi[a], y.hi[a]); }
+    r.cnt = x.cnt + y.cnt;
+    return r;
+}
+template <bool UP> __device__ __forceinline__ SahAcc sahAccShift(const SahAcc &x, uint32_t d)
+{
+    SahAcc r;
+    for (int a = 0; a < 3; ++a)
+    {
+        r.lo[a] = UP ? __shfl_up_sync(0xFFFFFFFFu, x.lo[a], d) : __shfl_down_sync(0xFFFFFFFFu, x.lo[a], d);
+        r.hi[a] = UP ? __shfl_up_sync(0xFFFFFFFFu, x.hi[a], d) : __shfl_down_sync(0xFFFFFFFFu, x.hi[a], d);
+    }
+    r.cnt = UP ? __shfl_up_sync(0xFFFFFFFFu, x.cnt, d) : __shfl_down_sync(0xFFFFFFFFu, x.cnt, d);
+    return r;
+}
+// cost of the border with `l` on its left and `r` on its right, as sahSplitPass computes it; >= 3.4e38 = no candidate
+__device__ __forceinline__ float sahBorderCost(const SahAcc &l, const SahAcc &r, bool byIndex)
+{
+    if (l.cnt == 0u || r.cnt == 0u) return 3.4e38f;
+    if (byIndex) return (float)(l.cnt > r.cnt ? l.cnt - r.cnt : r.cnt - l.cnt);
+    const float areaR = sahOrdHalfArea(r.lo, r.hi);
+    return sahOrdHalfArea(l.lo, l.hi) * (float)((l.cnt + SAH_GRANULE - 1u) / SAH_GRANULE) + areaR * (float)((r.cnt + SAH_GRANULE - 1u) / SAH_GRANULE);
 }
 
-__global__ void __launch_bounds__(SAH_THREADS) k_sah_partition(Sah s)
+// sahSplitPass by one warp: lane L holds bins 2L and 2L + 1, prefix / suffix unions come from shuffle scans, every lane
+// prices its two borders, the cheapest (ties: the lowest border, as the serial sweep keeps the first) wins.
+__device__ __forceinline__ void sahSplitWarp(const Sah &s, uint32_t key, uint32_t *queueOut)
 {
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31u;
+    const SahRange r = s.rangeIn[key];
+    const uint32_t nb = sahBinsFor(r.count);
+    uint32_t *cent = &s.cent[(size_t)key * SAH_CENT];
+    const SahAxes ax = sahAxes(cent, s.level, nb);
+    __syncwarp();
+    if (lane < SAH_CENT) cent[lane] = (lane < 3u || lane == 6u) ? 0xFFFFFFFFu : 0u; // sahCentClear: the left child reuses this key
+    SahAcc a = sahAccEmpty(), b = sahAccEmpty();
+    if (2u * lane < nb) // nb is even
+    {
+        uint4 *q = reinterpret_cast<uint4 *>(&s.bins[(size_t)r.first * SAH_SLOT_BINS + 2u * lane]);
+        const uint4 a0 = q[0], a1 = q[1], b0 = q[2], b1 = q[3];
+        a = SahAcc{{a0.x, a0.y, a0.z}, {a0.w, a1.x, a1.y}, a1.z};
+        b = SahAcc{{b0.x, b0.y, b0.z}, {b0.w, b1.x, b1.y}, b1.z};
+        const uint4 c0 = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u), c1 = make_uint4(0u, 0u, 0u, 0u); // sahBinClear
+        q[0] = c0; q[1] = c1; q[2] = c0; q[3] = c1;
+    }
+    const SahAcc u = sahAccUnion(a, b);
+    SahAcc pre = u, suf = u; // inclusive scans over the lanes
+    for (uint32_t d = 1; d < 32u; d <<= 1)
+    {
+        const SahAcc p = sahAccShift<true>(pre, d), q = sahAccShift<false>(suf, d);
+        if (lane >= d) pre = sahAccUnion(pre, p);
+        if (lane + d < 32u) suf = sahAccUnion(suf, q);
+    }
+    SahAcc pex = sahAccShift<true>(pre, 1), sex = sahAccShift<false>(suf, 1);
+    if (lane == 0u) pex = sahAccEmpty();
+    if (lane == 31u) sex = sahAccEmpty();
+    float cost = 3.4e38f;
+    uint32_t bin = 0u, left = 0u;
+    if (lane >= 1u && 2u * lane < nb) // border 2L: bins [0, 2L) | [2L, nb)
+    {
+        const float c = sahBorderCost(pex, suf, ax.byIndex);
+        if (c < cost) { cost = c; bin = 2u * lane; left = pex.cnt; }
+    }
+    if (2u * lane + 1u < nb) // border 2L + 1
+    {
+        const SahAcc l = sahAccUnion(pex, a);
+        const float c = sahBorderCost(l, sahAccUnion(b, sex), ax.byIndex);
+        if (c < cost) { cost = c; bin = 2u * lane + 1u; left = l.cnt; }
+    }
+    for (uint32_t d = 16u; d; d >>= 1)
+    {
+        const float oc = __shfl_xor_sync(0xFFFFFFFFu, cost, d);
+        const uint32_t ob = __shfl_xor_sync(0xFFFFFFFFu, bin, d), ol = __shfl_xor_sync(0xFFFFFFFFu, left, d);
+        if (oc < cost || (oc == cost && ob < bin)) { cost = oc; bin = ob; left = ol; }
+    }
+    if (lane == 0u)
+    {
+        Box nodeBox;
+        for (int k = 0; k < 3; ++k) { nodeBox.lo[k] = unordF(suf.lo[k]); nodeBox.hi[k] = unordF(suf.hi[k]); }
+        uint32_t childKeys[2], made;
+        const uint32_t at = sahSplitEmit(s, key, r, ax, bin, left, 0u, nodeBox, childKeys, made);
+        for (uint32_t k = 0; k < made; ++k) queueOut[at + k] = childKeys[k];
+    }
+}
+
+__device__ __forceinline__ void sahCentroidAdd(uint32_t *cent, const uint32_t lo[4], const uint32_t hi[4])
+{
+    for (uint32_t a = 0; a < 3; ++a) { atomicMin(&cent[a], lo[a]); atomicMax(&cent[3u + a], hi[a]); }
+    atomicMin(&cent[6], lo[3]);
+    atomicMax(&cent[7], hi[3]);
+}
+
+// sahPartitionPass + the centroid pass of the NEXT level: the slot's primitive moves into its child's sub-range and adds
+// its centroid (and index) to that child's bounds; a warp that lies inside one range does both once per side.
+__device__ __forceinline__ void sahPartitionTile(const Sah &s, uint32_t base)
+{
+    const uint32_t slot = base + threadIdx.x, lane = threadIdx.x & 31u;
     const bool valid = slot < s.t.count;
     const uint32_t key = valid ? s.keyIn[slot] : SAH_FINAL;
     const uint32_t key0 = __shfl_sync(0xFFFFFFFFu, key, 0);
     const bool warpUniform = __all_sync(0xFFFFFFFFu, valid && key == key0 && key != SAH_FINAL);
-    if (!warpUniform)
-    {
-        if (valid) sahPartitionPass(s, slot);
-        return;
-    }
-    // whole warp inside one range: one cursor update per side per warp
+    if (!valid) return;
+    const uint32_t prim = s.idxIn[slot];
+    if (key == SAH_FINAL) { s.idxOut[slot] = prim; s.keyOut[slot] = SAH_FINAL; return; }
     SahSplit *spp = &s.split[key];
     const SahSplit sp = *spp;
-    const uint32_t prim = s.idxIn[slot];
     uint32_t side, pos = slot;
-    if (sahSlotSide(s, slot, prim, sp, side)) // uniform across the warp: axisBin belongs to the range
+    const bool binned = sahSlotSide(s, slot, prim, sp, side);
+    const uint32_t childFirst = side ? sp.first + sp.leftCount : sp.first;
+    const uint32_t childCount = side ? sp.count - sp.leftCount : sp.leftCount;
+    uint32_t lo[4], hi[4];
+    if (childCount >= 2u)
     {
-        const uint32_t lane = threadIdx.x & 31u;
-        const uint32_t right = __ballot_sync(0xFFFFFFFFu, side != 0u), left = ~right;
-        uint32_t baseL = 0, baseR = 0;
-        if (lane == 0)
+        const Box b = s.t.primBox[prim];
+        for (uint32_t a = 0; a < 3; ++a) lo[a] = hi[a] = ordF(sahCentroid(b, a));
+        lo[3] = hi[3] = prim;
+    }
+    if (warpUniform)
+    {
+        const uint32_t right = __ballot_sync(0xFFFFFFFFu, side != 0u), left = ~right, mine = side ? right : left;
+        if (binned) // uniform across the warp: axisBin belongs to the range
         {
-            if (left) baseL = atomicAdd(&spp->cursorL, (uint32_t)__popc(left));
-            if (right) baseR = atomicAdd(&spp->cursorR, (uint32_t)__popc(right));
+            uint32_t baseL = 0, baseR = 0;
+            if (lane == 0)
+            {
+                if (left) baseL = atomicAdd(&spp->cursorL, (uint32_t)__popc(left));
+                if (right) baseR = atomicAdd(&spp->cursorR, (uint32_t)__popc(right));
+            }
+            baseL = __shfl_sync(0xFFFFFFFFu, baseL, 0);
+            baseR = __shfl_sync(0xFFFFFFFFu, baseR, 0);
+            const uint32_t below = (1u << lane) - 1u;
+            pos = side ? sp.first + sp.leftCount + baseR + __popc(right & below) : sp.first + baseL + __popc(left & below);
         }
-        baseL = __shfl_sync(0xFFFFFFFFu, baseL, 0);
-        baseR = __shfl_sync(0xFFFFFFFFu, baseR, 0);
-        const uint32_t below = (1u << lane) - 1u;
-        pos = side ? sp.first + sp.leftCount + baseR + __popc(right & below) : sp.first + baseL + __popc(left & below);
+        if (childCount >= 2u) // uniform across each side
+        {
+            for (uint32_t a = 0; a < 4; ++a) { lo[a] = __reduce_min_sync(mine, lo[a]); hi[a] = __reduce_max_sync(mine, hi[a]); }
+            if (lane == (uint32_t)__ffs((int)mine) - 1u) sahCentroidAdd(&s.cent[(size_t)(childFirst >> 1) * SAH_CENT], lo, hi);
+        }
+    }
+    else
+    {
+        if (binned) pos = side ? sp.first + sp.leftCount + atomicAdd(&spp->cursorR, 1u) : sp.first + atomicAdd(&spp->cursorL, 1u);
+        if (childCount >= 2u) sahCentroidAdd(&s.cent[(size_t)(childFirst >> 1) * SAH_CENT], lo, hi);
     }
     sahPlace(s, pos, prim, sp, side);
+}
+
+__global__ void __launch_bounds__(SAH_THREADS) k_sah_all_levels(Sah s, SahGrid g)
+{
+    __shared__ SahBin sb[SAH_RANGE_BINS];
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    const uint32_t n = s.t.count, stride = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t tileStride = gridDim.x * SAH_THREADS, warps = stride >> 5, warp = tid >> 5;
+    // start state: one range holding every primitive in index order
+    for (uint32_t i = tid; i < n; i += stride)
+    {
+        g.idx[0][i] = i;
+        g.key[0][i] = 0u;
+        for (uint32_t b = 0; b < SAH_SLOT_BINS; ++b) sahBinClear(&s.bins[(size_t)i * SAH_SLOT_BINS + b]);
+    }
+    for (uint32_t i = tid; i < g.keys; i += stride) sahCentClear(&s.cent[i * SAH_CENT]);
+    for (uint32_t i = tid; i <= SAH_MAX_LEVELS; i += stride) s.active[i] = i == 0 ? 1u : 0u;
+    if (tid == 0) { g.range[0][0] = SahRange{0u, n, -1, 0u}; g.queue[0][0] = 0u; *s.rootGap = 0u; }
+    __threadfence();
+    grid.sync();
+    s.idxIn = g.idx[0]; s.keyIn = g.key[0];
+    for (uint32_t base = blockIdx.x * SAH_THREADS; base < n; base += tileStride) sahCentroidTile(s, base);
+    __threadfence();
+    grid.sync();
+    uint32_t level = 0;
+    for (; level < SAH_MAX_LEVELS; ++level)
+    {
+        const uint32_t ranges = __ldcg(&s.active[level]);
+        if (ranges == 0u) break; // grid-uniform
+        const uint32_t a = level & 1u, b = a ^ 1u;
+        s.level = level;
+        s.idxIn = g.idx[a]; s.idxOut = g.idx[b];
+        s.keyIn = g.key[a]; s.keyOut = g.key[b];
+        s.rangeIn = g.range[a]; s.rangeOut = g.range[b];
+        for (uint32_t base = blockIdx.x * SAH_THREADS; base < n; base += tileStride) sahBinTile(s, base, sb);
+        __threadfence();
+        grid.sync();
+        for (uint32_t q = warp; q < ranges; q += warps) sahSplitWarp(s, __ldcg(&g.queue[a][q]), g.queue[b]);
+        __threadfence();
+        grid.sync();
+        for (uint32_t base = blockIdx.x * SAH_THREADS; base < n; base += tileStride) sahPartitionTile(s, base);
+        __threadfence();
+        grid.sync();
+    }
+    const bool finished = level < SAH_MAX_LEVELS || __ldcg(&s.active[SAH_MAX_LEVELS]) == 0u;
+    if (level & 1u) // the collapse reads the final order from idx[0]
+        for (uint32_t i = tid; i < n; i += stride) g.idx[0][i] = g.idx[1][i];
+    if (tid == 0) *g.levelsOut = finished ? level : SAH_MAX_LEVELS + 1u;
 }
 
 // One collapse level: items [0, *countIn) of queueIn. Launched with enough threads for the worst

@@ -137,6 +137,7 @@ struct BlasRes
     TriRec *tris = nullptr;
     AlphaUv *uvs = nullptr; // any-hit records, parallel to tris
     uint32_t nodeCount = 0, triCount = 0;
+    uint32_t nodeCap = 0, triCap = 0; // a rebuild reuses the buffers while they are large enough
     bool built = false;
 };
 
@@ -199,7 +200,7 @@ struct prt_ctx
     DBuf<Box> bPlocBox[2], bPlocMergedBox;
     DBuf<uint32_t> bPlocNearest, bPlocBlocks, bNewPos;
     // binned-SAH scratch (BLAS builds)
-    DBuf<uint32_t> bSahKey[2], bSahCent;
+    DBuf<uint32_t> bSahKey[2], bSahQueue[2], bSahCent;
     DBuf<SahRange> bSahRange[2];
     DBuf<SahSplit> bSahSplit;
     DBuf<SahBin> bSahBins;
@@ -234,6 +235,8 @@ struct prt_ctx
     uint32_t traceBlocks = 148; // grid of the persistent trace kernels
     uint32_t poolRays = PRT_POOL_RAYS;   // rays per thread of the persistent trace kernels (kernels_render.cuh)
     uint32_t refillAt = PRT_POOL_REFILL; // idle ray slots per warp that trigger a refill
+    bool blasCollapsePerLevel = false; // experiment switch PRT_BLAS_COLLAPSE_PER_LEVEL: one launch per collapse level, as round 1
+    uint32_t sahBlocks = 0;     // grid of k_sah_all_levels (co-resident by construction)
     uint32_t coopBlocks = 0;    // co-resident blocks of k_collapse_all_levels_grid (0: cooperative launch unsupported)
 
     // timing
@@ -431,7 +434,7 @@ static prt_status createContext(const prt_config *cfg, prt_ctx **out)
     }
     {
         // persistent trace kernels: one resident wave of blocks (SM count x blocks per SM)
-        int sms = 0, perSm = 0;
+        int sms = 0;
         CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->cfg.device));
         if (const char *e = std::getenv("PRT_POOL_RAYS")) c->poolRays = (uint32_t)std::min(2, std::max(1, std::atoi(e))); // experiment switch
         c->refillAt = 8u * c->poolRays;
@@ -442,6 +445,12 @@ static prt_status createContext(const prt_config *cfg, prt_ctx **out)
         CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->cfg.device));
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSmCollapse, k_collapse_all_levels_grid, 128, 0));
         c->coopBlocks = coop ? (uint32_t)(sms * std::max(0, perSmCollapse)) : 0u;
+        int perSmSah = 0;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSmSah, k_sah_all_levels, SAH_THREADS, 0));
+        int sahPerSm = std::min(perSmSah, 4); // more blocks only lengthen the grid barriers (3 per level)
+        if (const char *e = std::getenv("PRT_SAH_BLOCKS_PER_SM")) sahPerSm = std::min(perSmSah, std::max(1, std::atoi(e))); // experiment switch
+        c->blasCollapsePerLevel = std::getenv("PRT_BLAS_COLLAPSE_PER_LEVEL") != nullptr;
+        c->sahBlocks = coop ? (uint32_t)(sms * std::max(0, sahPerSm)) : 0u;
     }
     CK(cudaStreamSynchronize(c->stream));
     return PRT_OK;
@@ -483,7 +492,7 @@ extern "C" void prt_destroy(prt_ctx *c)
     for (int i = 0; i < 2; ++i) { c->bKeys[i].release(); c->bOrder[i].release(); c->bQueue[i].release(); }
     for (int i = 0; i < 2; ++i) { c->bPlocRef[i].release(); c->bPlocBox[i].release(); }
     c->bPlocMergedRef.release(); c->bPlocMergedBox.release(); c->bPlocNearest.release(); c->bPlocBlocks.release(); c->bNewPos.release();
-    for (int i = 0; i < 2; ++i) { c->bSahKey[i].release(); c->bSahRange[i].release(); }
+    for (int i = 0; i < 2; ++i) { c->bSahKey[i].release(); c->bSahRange[i].release(); c->bSahQueue[i].release(); }
     c->bSahCent.release(); c->bSahSplit.release(); c->bSahBins.release();
     c->bHist.release(); c->bFirst.release(); c->bLast.release(); c->bVisit.release(); c->bPrimOut.release(); c->bScalars.release();
     c->bLeft.release(); c->bRight.release(); c->bParentI.release(); c->bParentL.release(); c->bNodes.release(); c->bBounds.release();
@@ -1015,42 +1024,26 @@ static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *la
     uint32_t *scal = c->bScalars.p;
     if (sah)
     {
-        // BLAS (default): top-down binned SAH, four passes per tree level; the count of ranges a level created is read back
-        // every eighth level. Scalars: [243] the root's gap, [256 .. 256 + SAH_MAX_LEVELS] ranges per level.
+        // BLAS (default): top-down binned SAH, every level inside ONE cooperative launch (k_sah_all_levels). Scalars: [243] the
+        // root's gap, [244] levels run (SAH_MAX_LEVELS + 1: budget exhausted, checked by prt_build_blas with its own
+        // read-back), [256 .. 256 + SAH_MAX_LEVELS] ranges per level.
+        REQUIRE(c->sahBlocks > 0, "this device cannot launch the cooperative SAH builder");
         const uint32_t keys = n / 2u + 1u;
-        for (int i = 0; i < 2; ++i) { CK(c->bSahKey[i].ensure(n)); CK(c->bSahRange[i].ensure(keys)); }
+        for (int i = 0; i < 2; ++i) { CK(c->bSahKey[i].ensure(n)); CK(c->bSahRange[i].ensure(keys)); CK(c->bSahQueue[i].ensure(keys)); }
         CK(c->bSahCent.ensure((size_t)SAH_CENT * keys)); CK(c->bSahSplit.ensure(keys)); CK(c->bSahBins.ensure((size_t)SAH_SLOT_BINS * n));
         Sah s{};
         s.t = t;
         s.split = c->bSahSplit.p; s.bins = c->bSahBins.p; s.cent = c->bSahCent.p;
         s.active = scal + 256; s.rootGap = scal + 243;
-        const uint32_t grid = blocksFor(n, SAH_THREADS);
-        k_sah_init<<<blocksFor(std::max(n, SAH_MAX_LEVELS + 1u), 256), 256, 0, st>>>(s, keys, c->bOrder[0].p, c->bSahKey[0].p, c->bSahRange[0].p);
+        SahGrid g{};
+        for (int i = 0; i < 2; ++i) { g.idx[i] = c->bOrder[i].p; g.key[i] = c->bSahKey[i].p; g.queue[i] = c->bSahQueue[i].p; g.range[i] = c->bSahRange[i].p; }
+        g.keys = keys;
+        g.levelsOut = scal + 244;
+        void *args[] = {&s, &g};
+        const uint32_t blocks = std::min<uint32_t>(c->sahBlocks, blocksFor(n, SAH_THREADS));
+        CK(cudaLaunchCooperativeKernel((const void *)k_sah_all_levels, dim3(blocks), dim3(SAH_THREADS), args, 0, st));
         *launches += 1;
-        bool done = false;
-        uint32_t level = 0;
-        for (; level < SAH_MAX_LEVELS && !done; ++level)
-        {
-            const int a = (int)(level & 1u), b = a ^ 1;
-            s.level = level;
-            s.idxIn = c->bOrder[a].p; s.idxOut = c->bOrder[b].p;
-            s.keyIn = c->bSahKey[a].p; s.keyOut = c->bSahKey[b].p;
-            s.rangeIn = c->bSahRange[a].p; s.rangeOut = c->bSahRange[b].p;
-            k_sah_centroid<<<grid, SAH_THREADS, 0, st>>>(s);
-            k_sah_bin<<<grid, SAH_THREADS, 0, st>>>(s);
-            k_sah_split<<<grid, SAH_THREADS, 0, st>>>(s);
-            k_sah_partition<<<grid, SAH_THREADS, 0, st>>>(s);
-            *launches += 4;
-            if ((level & 7u) == 7u)
-            {
-                uint32_t made = 0;
-                CK(cudaMemcpyAsync(&made, s.active + level + 1, 4, cudaMemcpyDeviceToHost, st));
-                CK(cudaStreamSynchronize(st));
-                done = made == 0;
-            }
-        }
-        REQUIRE(done, "binned SAH did not finish within its level budget");
-        t.order = c->bOrder[level & 1u].p;
+        t.order = c->bOrder[0].p;
     }
     else if (n > 1 && !tlas && (c->cfg.flags & PRT_CFG_PLOC))
     {
@@ -1118,7 +1111,7 @@ static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *la
         k_collapse_all_levels<<<1, 1024, 0, st>>>(col, c->bQueue[0].p, c->bQueue[1].p, scal + 8, kMaxLevels);
         *launches += 1;
     }
-    else if (tlas && c->coopBlocks > 0)
+    else if (c->coopBlocks > 0 && (tlas || !c->blasCollapsePerLevel))
     {
         // one cooperative launch for all levels: enough blocks for the widest level, never more than are co-resident
         CollapseItem *qa = c->bQueue[0].p, *qb = c->bQueue[1].p;
@@ -1161,14 +1154,7 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
     CK(cudaSetDevice(c->cfg.device));
     cudaStream_t st = c->stream;
     BlasRes &b = c->blas[modelIndex];
-    if (b.nodes || b.tris || b.uvs)
-    {
-        CK(cudaStreamSynchronize(st));
-        if (b.nodes) CK(cudaFree(b.nodes));
-        if (b.tris) CK(cudaFree(b.tris));
-        if (b.uvs) CK(cudaFree(b.uvs));
-        b = BlasRes{};
-    }
+    b.built = false; // until this build has succeeded; the buffers of an earlier build are kept for reuse
     uint64_t total = 0;
     for (uint32_t g = c->modelOffsets[modelIndex]; g < c->modelOffsets[modelIndex + 1]; ++g)
     {
@@ -1180,6 +1166,7 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
     if (outReference) *outReference = (uint64_t)modelIndex + 1;
     if (total == 0)
     {
+        b.nodeCount = b.triCount = 0;
         b.built = true;
         return PRT_OK;
     }
@@ -1207,15 +1194,34 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
     }
     CK(cudaGetLastError());
     CKS(buildHierarchy(c, n, false, &launches));
-    uint32_t counts[2] = {0, 0};
+    uint32_t counts[2] = {0, 0}, sahLevels = 0;
     CK(cudaMemcpyAsync(counts, c->bScalars.p, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&sahLevels, c->bScalars.p + 244, 4, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    if (n > 1 && !(c->cfg.flags & (PRT_CFG_PLOC | PRT_CFG_LBVH_BLAS)))
+        REQUIRE(sahLevels <= SAH_MAX_LEVELS, "binned SAH did not finish within its level budget");
     REQUIRE(counts[1] == n, "collapse lost primitives");
     b.nodeCount = counts[0];
     b.triCount = n;
-    CK(cudaMalloc((void **)&b.nodes, (size_t)b.nodeCount * sizeof(WideNode)));
-    CK(cudaMalloc((void **)&b.tris, (size_t)n * sizeof(TriRec)));
-    CK(cudaMalloc((void **)&b.uvs, (size_t)n * sizeof(AlphaUv)));
+    if (b.nodeCap < b.nodeCount) // first build of the model, or it grew: the stream is idle after the read-back above
+    {
+        if (b.nodes) CK(cudaFree(b.nodes));
+        b.nodes = nullptr;
+        b.nodeCap = 0;
+        const uint32_t cap = b.nodeCount + b.nodeCount / 8u;
+        CK(cudaMalloc((void **)&b.nodes, (size_t)cap * sizeof(WideNode)));
+        b.nodeCap = cap;
+    }
+    if (b.triCap < n)
+    {
+        if (b.tris) CK(cudaFree(b.tris));
+        if (b.uvs) CK(cudaFree(b.uvs));
+        b.tris = nullptr; b.uvs = nullptr;
+        b.triCap = 0;
+        CK(cudaMalloc((void **)&b.tris, (size_t)n * sizeof(TriRec)));
+        CK(cudaMalloc((void **)&b.uvs, (size_t)n * sizeof(AlphaUv)));
+        b.triCap = n;
+    }
     CK(cudaMemcpyAsync(b.nodes, c->bNodes.p, (size_t)b.nodeCount * sizeof(WideNode), cudaMemcpyDeviceToDevice, st));
     k_emit_tris<<<blocksFor(n, 256), 256, 0, st>>>(c->bPrimOut.p, n, c->bTris.p, b.tris, c->bUvs.p, b.uvs);
     launches++;
