@@ -3,6 +3,7 @@
 // (World.cpp:878-928, 749-802), rebuilt from scratch every frame like the reference does.
 #pragma once
 #include <cooperative_groups.h>
+#include "../../include/prt_types.h"
 #include "core_build.h"
 #include "kernels_sort.cuh"
 
@@ -496,13 +497,183 @@ __global__ void __launch_bounds__(SAH_THREADS) k_sah_all_levels(Sah s, SahGrid g
     if (tid == 0) *g.levelsOut = finished ? level : SAH_MAX_LEVELS + 1u;
 }
 
-// One collapse level: items [0, *countIn) of queueIn. Launched with enough threads for the worst
-// case; the live count is read from device memory so the host never waits between levels.
-__global__ void k_collapse_level(Collapse c, const uint32_t *__restrict__ countIn)
+// ---- collapse to 8-wide: collapseItem (core_bvh.h) by EIGHT lanes, one per child -------------------------------------
+// The serial form walks 8-entry local arrays a few thousand instructions long per wide node; with a level-synchronous
+// collapse that latency, times the depth of the tree, is the whole TLAS rebuild. Here lane j of an 8-lane group holds
+// child j (reference, box, area, primitive count): the open-largest loop, the greedy slot assignment and the plane
+// quantisation become 8-lane arg-max / ballot steps. Same choices in the same order as the serial form (ties: lowest
+// child, then lowest slot), so the node is the same; only the allocator order differs, as it does between any two runs.
+__device__ __forceinline__ void collapseItemGroup(const Collapse &c, uint32_t itemIndex, uint32_t gm)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= *countIn) return;
-    collapseItem(c, i);
+    const uint32_t lane = threadIdx.x & 31u, j = lane & 7u, shift = lane & 24u; // gm = 0xFF << shift
+    const uint2 raw = __ldcg(reinterpret_cast<const uint2 *>(c.queueIn + itemIndex)); // written by other SMs one level earlier
+    const CollapseItem item = {(int32_t)raw.x, raw.y};
+    const Lbvh &t = c.t;
+    int32_t ref = 0;
+    Box box = Box{{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
+    float area = 0.f;
+    uint32_t cnt = 0u, n;
+    int32_t kidL = 0, kidR = 0; // the child's own children, fetched with it: opening it later costs no dependent load
+    auto fetch = [&](int32_t r) {
+        ref = r;
+        if (r >= 0) { kidL = t.left[r]; kidR = t.right[r]; }
+        box = lbvhRefBox(t, r);
+        area = boxHalfArea(box);
+        cnt = lbvhRefCount(t, r);
+    };
+    if (item.ref >= 0 && lbvhRefCount(t, item.ref) > c.maxLeaf)
+    {
+        if (j == 0u) fetch(t.left[item.ref]);
+        if (j == 1u) fetch(t.right[item.ref]);
+        n = 2u;
+    }
+    else
+    {
+        if (j == 0u) fetch(item.ref); // a tree that is a single leaf (count <= maxLeaf at the root)
+        n = 1u;
+    }
+    // phase 1: open the largest-area child that is too big for a leaf slot; phase 2: use spare slots to split
+    // multi-primitive leaves (tighter boxes, same memory)
+    for (int phase = 0; phase < 2; ++phase)
+    {
+        while (n < 8u)
+        {
+            const bool eligible = j < n && ref >= 0 && (phase == 0 ? cnt > c.maxLeaf : cnt <= c.maxLeaf);
+            float a = eligible ? area : -1.f;
+            uint32_t who = j;
+            for (uint32_t d = 4u; d; d >>= 1)
+            {
+                const float oa = __shfl_xor_sync(gm, a, d, 8);
+                const uint32_t ow = __shfl_xor_sync(gm, who, d, 8);
+                if (oa > a || (oa == a && ow < who)) { a = oa; who = ow; }
+            }
+            if (!(a > -1.f)) break; // group-uniform
+            const int32_t l2 = __shfl_sync(gm, kidL, who, 8), r2 = __shfl_sync(gm, kidR, who, 8);
+            if (j == who) fetch(l2);
+            if (j == n) fetch(r2);
+            n++;
+        }
+    }
+    const bool live = j < n;
+    // node bounds
+    float blo[3], bhi[3];
+    for (int k = 0; k < 3; ++k)
+    {
+        blo[k] = live ? box.lo[k] : 3.4e38f;
+        bhi[k] = live ? box.hi[k] : -3.4e38f;
+        for (uint32_t d = 4u; d; d >>= 1)
+        {
+            blo[k] = fminf(blo[k], __shfl_xor_sync(gm, blo[k], d, 8));
+            bhi[k] = fmaxf(bhi[k], __shfl_xor_sync(gm, bhi[k], d, 8));
+        }
+    }
+    // slot assignment (greedy on the Ylitie cost: child offset projected on the slot's octant diagonal)
+    const V3 nc = (V3{blo[0], blo[1], blo[2]} + V3{bhi[0], bhi[1], bhi[2]}) * 0.5f;
+    const V3 off = (boxLo(box) + boxHi(box)) * 0.5f - nc;
+    uint32_t freeSlots = 0xFFu, slot = 8u; // slot of this lane's child
+    for (uint32_t k = 0; k < n; ++k)
+    {
+        float bc = -3.4e38f;
+        uint32_t bs = 8u, who = j;
+        if (live && slot == 8u)
+            for (uint32_t sl = 0; sl < 8u; ++sl)
+            {
+                if (!((freeSlots >> sl) & 1u)) continue;
+                const float cost = ((sl & 1u) ? off.x : -off.x) + ((sl & 2u) ? off.y : -off.y) + ((sl & 4u) ? off.z : -off.z);
+                if (cost > bc) { bc = cost; bs = sl; }
+            }
+        for (uint32_t d = 4u; d; d >>= 1)
+        {
+            const float oc = __shfl_xor_sync(gm, bc, d, 8);
+            const uint32_t os = __shfl_xor_sync(gm, bs, d, 8), ow = __shfl_xor_sync(gm, who, d, 8);
+            // a lane without a candidate carries bs == 8 and loses every comparison
+            if (os != 8u && (bs == 8u || oc > bc || (oc == bc && ow < who))) { bc = oc; bs = os; who = ow; }
+        }
+        if (j == who) slot = bs;
+        freeSlots &= ~(1u << bs);
+    }
+    // from here lane j is SLOT j: pull the child assigned to it
+    uint32_t src = 8u;
+    for (uint32_t i = 0; i < 8u; ++i)
+        if (__shfl_sync(gm, slot, i, 8) == j) src = i;
+    const bool used = src < 8u;
+    const uint32_t from = used ? src : 0u;
+    const int32_t sref = __shfl_sync(gm, ref, from, 8);
+    const uint32_t pulled = __shfl_sync(gm, cnt, from, 8);
+    const uint32_t scnt = used ? pulled : 0u;
+    Box sbox;
+    for (int k = 0; k < 3; ++k) { sbox.lo[k] = __shfl_sync(gm, box.lo[k], from, 8); sbox.hi[k] = __shfl_sync(gm, box.hi[k], from, 8); }
+    // allocate internal children and leaf primitives (children in slot order)
+    const bool internal = used && scnt > c.maxLeaf;
+    const uint32_t imask = (__ballot_sync(gm, internal) >> shift) & 0xFFu;
+    const uint32_t leafCnt = used && !internal ? scnt : 0u;
+    uint32_t primSeen = leafCnt; // inclusive prefix over the slots
+    for (uint32_t d = 1u; d < 8u; d <<= 1)
+    {
+        const uint32_t o = __shfl_up_sync(gm, primSeen, d, 8);
+        if (j >= d) primSeen += o;
+    }
+    const uint32_t nPrims = __shfl_sync(gm, primSeen, 7, 8), nInternal = (uint32_t)__popc(imask);
+    primSeen -= leafCnt;
+    const uint32_t internalSeen = (uint32_t)__popc(imask & ((1u << j) - 1u));
+    uint32_t childBase = 0u, primBase = 0u, queueBase = 0u;
+    if (j == 0u)
+    {
+        if (nInternal) { childBase = atomicAdd(c.nodeCount, nInternal); queueBase = atomicAdd(c.queueOutCount, nInternal); }
+        if (nPrims) primBase = atomicAdd(c.primCount, nPrims);
+    }
+    childBase = __shfl_sync(gm, childBase, 0, 8);
+    primBase = __shfl_sync(gm, primBase, 0, 8);
+    queueBase = __shfl_sync(gm, queueBase, 0, 8);
+    uint32_t meta = 0u;
+    if (internal)
+    {
+        meta = (1u << 5) | (24u + j);
+        c.queueOut[queueBase + internalSeen] = CollapseItem{sref, childBase + internalSeen};
+    }
+    else if (used)
+    {
+        const uint32_t first = lbvhRefFirst(t, sref);
+        for (uint32_t k = 0; k < scnt; ++k) c.primOut[primBase + primSeen + k] = t.order[first + k];
+        meta = ((((1u << scnt) - 1u) << 5) | primSeen) & 0xFFu;
+    }
+    // quantisation grid: every slot quantises its own planes, the exponent grows until all eight fit
+    uint32_t e[3], ql[3], qh[3];
+    for (int a = 0; a < 3; ++a)
+    {
+        e[a] = gridExponent(bhi[a] - blo[a]);
+        for (;;)
+        {
+            const float scale = u2f(e[a] << 23);
+            bool ok = true;
+            ql[a] = 255u; qh[a] = 0u;
+            if (used) ok = quantisePlanes(blo[a], scale, sbox.lo[a], sbox.hi[a], ql[a], qh[a]);
+            if (__all_sync(gm, ok) || e[a] >= 254u) break;
+            e[a]++;
+        }
+    }
+    // the 80-byte record: lanes 0 and 4 of the group assemble the two words of each byte row
+    const uint32_t quad = 0xFu << (lane & 28u), bs = 8u * (j & 3u);
+    uint32_t rows[7];
+    rows[0] = __reduce_or_sync(quad, meta << bs);
+    for (int a = 0; a < 3; ++a)
+    {
+        rows[1 + a] = __reduce_or_sync(quad, (ql[a] & 0xFFu) << bs);
+        rows[4 + a] = __reduce_or_sync(quad, (qh[a] & 0xFFu) << bs);
+    }
+    uint32_t *out = reinterpret_cast<uint32_t *>(&c.nodes[item.wide]);
+    if ((j & 3u) == 0u)
+    {
+        const uint32_t w = j >> 2; // 0: slots 0-3, 1: slots 4-7
+        for (int r = 0; r < 7; ++r) out[6 + 2 * r + w] = rows[r];
+    }
+    if (j == 0u)
+    {
+        out[0] = f2u(blo[0]); out[1] = f2u(blo[1]); out[2] = f2u(blo[2]);
+        out[3] = e[0] | (e[1] << 8) | (e[2] << 16) | (imask << 24);
+        out[4] = childBase;
+        out[5] = primBase;
+    }
 }
 
 // All levels in one block (TLAS: a few thousand instances, launch latency matters more than width).
@@ -517,7 +688,7 @@ __global__ void __launch_bounds__(1024) k_collapse_all_levels(Collapse c, Collap
         c.queueIn = (level & 1u) ? queueB : queueA;
         c.queueOut = (level & 1u) ? queueA : queueB;
         c.queueOutCount = &queueCounts[level + 1];
-        for (uint32_t i = threadIdx.x; i < count; i += blockDim.x) collapseItem(c, i);
+        for (uint32_t i = threadIdx.x >> 3; i < count; i += blockDim.x >> 3) collapseItemGroup(c, i, 0xFFu << (threadIdx.x & 24u));
         __threadfence_block();
         __syncthreads();
     }
@@ -537,7 +708,7 @@ __global__ void __launch_bounds__(128) k_collapse_all_levels_grid(Collapse c, Co
         c.queueIn = (level & 1u) ? queueB : queueA;
         c.queueOut = (level & 1u) ? queueA : queueB;
         c.queueOutCount = &queueCounts[level + 1];
-        for (uint32_t i = tid; i < count; i += stride) collapseItem(c, i);
+        for (uint32_t i = tid >> 3; i < count; i += stride >> 3) collapseItemGroup(c, i, 0xFFu << (threadIdx.x & 24u));
         __threadfence();
         grid.sync();
     }
@@ -591,6 +762,40 @@ __global__ void k_tlas_instances(const TlasInput *__restrict__ in, uint32_t n, I
     InstRec r;
     V3 lo, hi;
     tlasInstanceRecord(in[i], r, lo, hi);
+    recs[i] = r;
+    boxes[i] = makeBox(lo, hi);
+    atomicBounds(bounds, lo, hi, true);
+}
+
+// The same from the caller's own 64-byte records (every instance active): the BLAS pointers come from a device table indexed
+// by blasReference - 1, so the host neither rewrites nor compacts the array -- it uploads it as it is.
+struct BlasTableEntry
+{
+    const WideNode *nodes;
+    const TriRec *tris;
+    const AlphaUv *uvs;
+};
+__global__ void k_tlas_instances_direct(const prt_tlas_instance *__restrict__ in, const BlasTableEntry *__restrict__ table, uint32_t n,
+                                        InstRec *__restrict__ recs, Box *__restrict__ boxes, BuildBounds *bounds)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+    {
+        atomicBounds(bounds, V3{0.f, 0.f, 0.f}, V3{0.f, 0.f, 0.f}, false);
+        return;
+    }
+    const uint4 *q = reinterpret_cast<const uint4 *>(in + i);
+    const uint4 a = q[0], b = q[1], c = q[2], d = q[3];
+    TlasInput ti;
+    const uint32_t m[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
+    for (int k = 0; k < 12; ++k) ti.transform[k] = __uint_as_float(m[k]);
+    ti.customIndexAndMask = d.x;
+    ti.index = i;
+    const BlasTableEntry e = table[(((uint64_t)d.w << 32) | d.z) - 1ull];
+    ti.nodes = e.nodes; ti.tris = e.tris; ti.uvs = e.uvs;
+    InstRec r;
+    V3 lo, hi;
+    tlasInstanceRecord(ti, r, lo, hi);
     recs[i] = r;
     boxes[i] = makeBox(lo, hi);
     atomicBounds(bounds, lo, hi, true);

@@ -9,12 +9,16 @@
 namespace prt {
 
 constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 8;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
+constexpr int SORT_ITEMS = 8;                        // keys per thread and block: large inputs (BLAS Morton builders)
+constexpr int SORT_ITEMS_SMALL = 2;                  // TLAS-sized inputs: four times the blocks, a quarter of the serial chunks
+constexpr uint32_t SORT_SMALL_N = 1u << 15;         // at most 64 blocks: each scatter block scans the digit table itself
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS_SMALL; // sizes the histogram table: the smaller tile gives the larger table
 
+template <int ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const uint64_t *__restrict__ keys, uint32_t n, int shift,
                                                             uint32_t *__restrict__ hist, uint32_t numBlocks)
 {
+    constexpr int SORT_ITEMS = ITEMS, SORT_TILE = SORT_THREADS * ITEMS;
     __shared__ uint32_t sh[256];
     sh[threadIdx.x] = 0;
     __syncthreads();
@@ -71,14 +75,45 @@ __global__ void __launch_bounds__(1024) k_scan_exclusive(uint32_t *__restrict__ 
     }
 }
 
+// SCAN: `hist` holds the raw per-block digit counts and every block derives its own bases from them (a few dozen blocks:
+// 256 x numBlocks reads per block cost less than the scan launch they replace); otherwise `hist` was scanned by
+// k_scan_exclusive.
+template <int ITEMS, bool SCAN>
 __global__ void __launch_bounds__(SORT_THREADS)
     k_sort_scatter(const uint64_t *__restrict__ keysIn, const uint32_t *__restrict__ valsIn, uint64_t *__restrict__ keysOut,
                    uint32_t *__restrict__ valsOut, uint32_t n, int shift, const uint32_t *__restrict__ hist, uint32_t numBlocks)
 {
+    constexpr int SORT_ITEMS = ITEMS, SORT_TILE = SORT_THREADS * ITEMS;
     __shared__ uint32_t binBase[256];
     __shared__ uint32_t warpCnt[SORT_THREADS / 32][256];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    binBase[tid] = hist[tid * numBlocks + blockIdx.x];
+    if (SCAN)
+    {
+        // base of digit d in this block = keys of smaller digits anywhere + keys of digit d in earlier blocks
+        static_assert(SORT_THREADS == 256, "one thread per digit");
+        uint32_t total = 0, before = 0;
+        for (uint32_t b = 0; b < numBlocks; ++b)
+        {
+            const uint32_t v = hist[tid * numBlocks + b];
+            total += v;
+            if (b < blockIdx.x) before += v;
+        }
+        uint32_t x = total; // inclusive scan over the 256 digits
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+            if (lane >= (uint32_t)o) x += y;
+        }
+        if (lane == 31u) warpCnt[0][warp] = x;
+        __syncthreads();
+        uint32_t offset = 0;
+        for (uint32_t w = 0; w < warp; ++w) offset += warpCnt[0][w];
+        __syncthreads(); // warpCnt is cleared below
+        binBase[tid] = offset + x - total + before;
+    }
+    else
+        binBase[tid] = hist[tid * numBlocks + blockIdx.x];
     const uint32_t tile = blockIdx.x * SORT_TILE;
     for (int c = 0; c < SORT_ITEMS; ++c)
     {
@@ -119,16 +154,27 @@ inline bool radixSortPairs(uint64_t *keys, uint32_t *vals, uint64_t *keysAlt, ui
                            uint32_t *hist, cudaStream_t stream, uint32_t *launches)
 {
     if (n == 0) return false;
-    const uint32_t numBlocks = (n + SORT_TILE - 1) / SORT_TILE;
+    const bool small = n <= SORT_SMALL_N;
+    const uint32_t tile = (uint32_t)SORT_THREADS * (small ? SORT_ITEMS_SMALL : SORT_ITEMS);
+    const uint32_t numBlocks = (n + tile - 1) / tile;
     bool flipped = false;
     for (int shift = firstBit; shift < 64; shift += 8)
     {
         uint64_t *kin = flipped ? keysAlt : keys, *kout = flipped ? keys : keysAlt;
         uint32_t *vin = flipped ? valsAlt : vals, *vout = flipped ? vals : valsAlt;
-        k_sort_hist<<<numBlocks, SORT_THREADS, 0, stream>>>(kin, n, shift, hist, numBlocks);
-        k_scan_exclusive<<<1, 1024, 0, stream>>>(hist, 256u * numBlocks);
-        k_sort_scatter<<<numBlocks, SORT_THREADS, 0, stream>>>(kin, vin, kout, vout, n, shift, hist, numBlocks);
-        if (launches) *launches += 3;
+        if (small)
+        {
+            k_sort_hist<SORT_ITEMS_SMALL><<<numBlocks, SORT_THREADS, 0, stream>>>(kin, n, shift, hist, numBlocks);
+            k_sort_scatter<SORT_ITEMS_SMALL, true><<<numBlocks, SORT_THREADS, 0, stream>>>(kin, vin, kout, vout, n, shift, hist, numBlocks);
+            if (launches) *launches += 2;
+        }
+        else
+        {
+            k_sort_hist<SORT_ITEMS><<<numBlocks, SORT_THREADS, 0, stream>>>(kin, n, shift, hist, numBlocks);
+            k_scan_exclusive<<<1, 1024, 0, stream>>>(hist, 256u * numBlocks);
+            k_sort_scatter<SORT_ITEMS, false><<<numBlocks, SORT_THREADS, 0, stream>>>(kin, vin, kout, vout, n, shift, hist, numBlocks);
+            if (launches) *launches += 3;
+        }
         flipped = !flipped;
     }
     return flipped;

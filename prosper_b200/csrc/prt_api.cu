@@ -53,6 +53,9 @@ static prt_status fail(prt_status st, const std::string &msg)
 
 static inline uint32_t blocksFor(uint64_t n, uint32_t threads) { return (uint32_t)std::max<uint64_t>(1, (n + threads - 1) / threads); }
 
+// Bumped whenever a DBuf moves: a captured TLAS graph holds raw pointers and is re-captured when this changed.
+static unsigned long long g_allocGeneration = 0;
+
 // Grow-only device array
 template <class T> struct DBuf
 {
@@ -61,6 +64,7 @@ template <class T> struct DBuf
     cudaError_t ensure(size_t n)
     {
         if (n <= cap) return cudaSuccess;
+        g_allocGeneration++;
         if (p) cudaFree(p);
         p = nullptr;
         cap = 0;
@@ -190,6 +194,8 @@ struct prt_ctx
     bool alphaMatsDirty = true;
     DBuf<InstRec> bInst;
     DBuf<TlasInput> bTlasIn;
+    DBuf<prt_tlas_instance> bTlasRaw; // the caller's records as they are (all instances active)
+    DBuf<BlasTableEntry> dBlasTable;  // model -> BLAS buffers, for k_tlas_instances_direct
     DBuf<Box> bBoxes, bNodeBox;
     DBuf<uint64_t> bKeys[2];
     DBuf<uint32_t> bOrder[2], bHist, bFirst, bLast, bVisit, bPrimOut, bScalars;
@@ -235,7 +241,12 @@ struct prt_ctx
     uint32_t traceBlocks = 148; // grid of the persistent trace kernels
     uint32_t poolRays = PRT_POOL_RAYS;   // rays per thread of the persistent trace kernels (kernels_render.cuh)
     uint32_t refillAt = PRT_POOL_REFILL; // idle ray slots per warp that trigger a refill
-    bool blasCollapsePerLevel = false; // experiment switch PRT_BLAS_COLLAPSE_PER_LEVEL: one launch per collapse level, as round 1
+    // TLAS rebuild as a CUDA graph (prt_build_tlas); PRT_TLAS_GRAPH=0 keeps the eager launches (experiment switch)
+    bool tlasGraphs = true, tlasGraphDirect = false, tlasEagerDirect = false;
+    bool blasTableDirty = true; // dBlasTable lags behind `blas`
+    cudaGraphExec_t tlasGraphExec = nullptr;
+    uint32_t tlasGraphN = 0, tlasGraphLaunches = 0, tlasEagerN = 0;
+    unsigned long long tlasGraphGeneration = 0, tlasEagerGeneration = 0;
     uint32_t sahBlocks = 0;     // grid of k_sah_all_levels (co-resident by construction)
     uint32_t coopBlocks = 0;    // co-resident blocks of k_collapse_all_levels_grid (0: cooperative launch unsupported)
 
@@ -445,11 +456,11 @@ static prt_status createContext(const prt_config *cfg, prt_ctx **out)
         CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->cfg.device));
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSmCollapse, k_collapse_all_levels_grid, 128, 0));
         c->coopBlocks = coop ? (uint32_t)(sms * std::max(0, perSmCollapse)) : 0u;
+        if (const char *e = std::getenv("PRT_TLAS_GRAPH")) c->tlasGraphs = std::atoi(e) != 0;
         int perSmSah = 0;
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSmSah, k_sah_all_levels, SAH_THREADS, 0));
         int sahPerSm = std::min(perSmSah, 4); // more blocks only lengthen the grid barriers (3 per level)
         if (const char *e = std::getenv("PRT_SAH_BLOCKS_PER_SM")) sahPerSm = std::min(perSmSah, std::max(1, std::atoi(e))); // experiment switch
-        c->blasCollapsePerLevel = std::getenv("PRT_BLAS_COLLAPSE_PER_LEVEL") != nullptr;
         c->sahBlocks = coop ? (uint32_t)(sms * std::max(0, sahPerSm)) : 0u;
     }
     CK(cudaStreamSynchronize(c->stream));
@@ -461,6 +472,7 @@ extern "C" void prt_destroy(prt_ctx *c)
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     cudaDeviceSynchronize();
+    if (c->tlasGraphExec) cudaGraphExecDestroy(c->tlasGraphExec);
     for (uint32_t *b : c->geomBufs)
         if (b) cudaFree(b);
     for (TexSlot &s : c->hSlots)
@@ -488,7 +500,7 @@ extern "C" void prt_destroy(prt_ctx *c)
     c->geomTable.release(); c->dMeta.release(); c->dMat.release(); c->dSlots.release(); c->dSky.release();
     c->dDraw.release(); c->dXf.release(); c->dDir.release(); c->dPoints.release(); c->dSpots.release(); c->dCam.release();
     c->tlasNodes.release(); c->tlasInst.release();
-    c->bTris.release(); c->bUvs.release(); c->dAlphaMats.release(); c->bInst.release(); c->bTlasIn.release(); c->bBoxes.release(); c->bNodeBox.release();
+    c->bTris.release(); c->bUvs.release(); c->dAlphaMats.release(); c->bInst.release(); c->bTlasIn.release(); c->bTlasRaw.release(); c->dBlasTable.release(); c->bBoxes.release(); c->bNodeBox.release();
     for (int i = 0; i < 2; ++i) { c->bKeys[i].release(); c->bOrder[i].release(); c->bQueue[i].release(); }
     for (int i = 0; i < 2; ++i) { c->bPlocRef[i].release(); c->bPlocBox[i].release(); }
     c->bPlocMergedRef.release(); c->bPlocMergedBox.release(); c->bPlocNearest.release(); c->bPlocBlocks.release(); c->bNewPos.release();
@@ -990,7 +1002,7 @@ static constexpr uint32_t kMaxLevels = 128;
 #define PRT_PLOC_RADIUS 16
 #endif
 
-static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *launches)
+static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, WideNode *nodesOut, uint32_t *launches)
 {
     cudaStream_t st = c->stream;
     for (int i = 0; i < 2; ++i)
@@ -1102,7 +1114,7 @@ static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *la
 #define PRT_BLAS_MAX_LEAF 3
 #endif
     col.maxLeaf = tlas ? 1u : (uint32_t)PRT_BLAS_MAX_LEAF;
-    col.nodes = c->bNodes.p;
+    col.nodes = nodesOut;
     col.primOut = c->bPrimOut.p;
     col.nodeCount = scal + 0;
     col.primCount = scal + 1;
@@ -1111,35 +1123,18 @@ static prt_status buildHierarchy(prt_ctx *c, uint32_t n, bool tlas, uint32_t *la
         k_collapse_all_levels<<<1, 1024, 0, st>>>(col, c->bQueue[0].p, c->bQueue[1].p, scal + 8, kMaxLevels);
         *launches += 1;
     }
-    else if (c->coopBlocks > 0 && (tlas || !c->blasCollapsePerLevel))
+    else
     {
-        // one cooperative launch for all levels: enough blocks for the widest level, never more than are co-resident
+        // one cooperative launch for all levels, eight lanes per wide node: enough blocks for the widest level, never more
+        // than are co-resident
+        REQUIRE(c->coopBlocks > 0, "this device cannot launch the cooperative collapse");
         CollapseItem *qa = c->bQueue[0].p, *qb = c->bQueue[1].p;
         uint32_t *counts = scal + 8;
         uint32_t maxLevels = kMaxLevels;
         void *args[] = {&col, &qa, &qb, &counts, &maxLevels};
-        const uint32_t blocks = std::min<uint32_t>(c->coopBlocks, blocksFor((n + 3) / 4, 128));
+        const uint32_t blocks = std::min<uint32_t>(c->coopBlocks, blocksFor((uint64_t)n * 2u, 128));
         CK(cudaLaunchCooperativeKernel((const void *)k_collapse_all_levels_grid, dim3(blocks), dim3(128), args, 0, st));
         *launches += 1;
-    }
-    else
-    {
-        for (uint32_t level = 0; level < kMaxLevels; ++level)
-        {
-            col.queueIn = c->bQueue[level & 1].p;
-            col.queueOut = c->bQueue[(level + 1) & 1].p;
-            col.queueOutCount = scal + 8 + level + 1;
-            k_collapse_level<<<blocksFor(n, 128), 128, 0, st>>>(col, scal + 8 + level);
-            *launches += 1;
-            if ((level & 7u) == 7u)
-            {
-                uint32_t next = 0;
-                CK(cudaMemcpyAsync(&next, scal + 8 + level + 1, 4, cudaMemcpyDeviceToHost, st));
-                CK(cudaStreamSynchronize(st));
-                if (next == 0) break;
-                REQUIRE(level + 1 < kMaxLevels, "BVH deeper than the collapse level budget");
-            }
-        }
     }
     CK(cudaGetLastError());
     return PRT_OK;
@@ -1193,7 +1188,8 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
         offset += prims;
     }
     CK(cudaGetLastError());
-    CKS(buildHierarchy(c, n, false, &launches));
+    CK(c->bNodes.ensure(n));
+    CKS(buildHierarchy(c, n, false, c->bNodes.p, &launches));
     uint32_t counts[2] = {0, 0}, sahLevels = 0;
     CK(cudaMemcpyAsync(counts, c->bScalars.p, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(&sahLevels, c->bScalars.p + 244, 4, cudaMemcpyDeviceToHost, st));
@@ -1230,6 +1226,27 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
     c->blasTimed = true;
     c->kernelLaunches += launches;
     b.built = true; // only a build that got this far is referable from prt_build_tlas
+    c->blasTableDirty = true;
+    return PRT_OK;
+}
+
+// The device side of a TLAS rebuild for the `n` records already uploaded (bTlasRaw: the caller's own records, all active;
+// bTlasIn: the compacted ones): instance records + boxes, hierarchy, emit.
+static prt_status enqueueTlasBuild(prt_ctx *c, uint32_t n, bool direct, uint32_t *launches)
+{
+    cudaStream_t st = c->stream;
+    CK(c->bInst.ensure(n));
+    CK(c->bBoxes.ensure(n));
+    CK(c->tlasNodes.ensure(n));
+    CK(c->tlasInst.ensure(n));
+    k_init_bounds<<<1, 32, 0, st>>>(c->bBounds.p, c->bScalars.p, 8);
+    if (direct) k_tlas_instances_direct<<<blocksFor(n, 128), 128, 0, st>>>(c->bTlasRaw.p, c->dBlasTable.p, n, c->bInst.p, c->bBoxes.p, c->bBounds.p);
+    else k_tlas_instances<<<blocksFor(n, 128), 128, 0, st>>>(c->bTlasIn.p, n, c->bInst.p, c->bBoxes.p, c->bBounds.p);
+    *launches += 2;
+    CKS(buildHierarchy(c, n, true, c->tlasNodes.p, launches)); // wide nodes <= n: the collapse writes them in place
+    k_emit_instances<<<blocksFor(n, 128), 128, 0, st>>>(c->bPrimOut.p, n, c->bInst.p, c->tlasInst.p);
+    *launches += 1;
+    CK(cudaGetLastError());
     return PRT_OK;
 }
 
@@ -1240,15 +1257,23 @@ extern "C" prt_status prt_build_tlas(prt_ctx *c, const prt_tlas_instance *instan
     if (c->cfg.maxInstances) REQUIRE(count <= c->cfg.maxInstances, "more instances than prt_config.maxInstances");
     CK(cudaSetDevice(c->cfg.device));
     cudaStream_t st = c->stream;
+    // Every instance active (the usual frame): the records go up as they are and k_tlas_instances_direct resolves the BLAS
+    // pointers from a device table. Otherwise (inactive instances, World.cpp:898-905, or empty models) the host compacts.
+    bool direct = count > 0;
+    for (uint32_t i = 0; i < count; ++i)
+    {
+        const uint64_t ref = instances[i].blasReference;
+        if (ref == 0) { direct = false; continue; }
+        REQUIRE(ref - 1 < c->blas.size() && c->blas[ref - 1].built, "instance references a BLAS that was not built");
+        if (c->blas[ref - 1].triCount == 0) direct = false;
+    }
     std::vector<TlasInput> &in = c->hTlasInput;
     in.clear();
-    for (uint32_t i = 0; i < count; ++i)
+    for (uint32_t i = 0; i < count && !direct; ++i)
     {
         const prt_tlas_instance &ti = instances[i];
         if (ti.blasReference == 0) continue; // inactive instance, World.cpp:898-905
-        const uint64_t model = ti.blasReference - 1;
-        REQUIRE(model < c->blas.size() && c->blas[model].built, "instance references a BLAS that was not built");
-        const BlasRes &b = c->blas[model];
+        const BlasRes &b = c->blas[ti.blasReference - 1];
         if (b.triCount == 0) continue;
         TlasInput t;
         memcpy(t.transform, ti.transform, sizeof(t.transform));
@@ -1259,27 +1284,74 @@ extern "C" prt_status prt_build_tlas(prt_ctx *c, const prt_tlas_instance *instan
         t.uvs = b.uvs;
         in.push_back(t);
     }
-    const uint32_t n = (uint32_t)in.size();
+    const uint32_t n = direct ? count : (uint32_t)in.size();
     CK(cudaEventRecord(c->evTlas[0], st));
     uint32_t launches = 0;
     c->tlasInstances = n;
     if (n)
     {
-        CK(c->bTlasIn.ensure(n));
-        CK(c->bInst.ensure(n));
-        CK(c->bBoxes.ensure(n));
-        CK(c->tlasNodes.ensure(n));
-        CK(c->tlasInst.ensure(n));
-        CK(c->ring.upload(c->bTlasIn.p, in.data(), (size_t)n * sizeof(TlasInput), st));
-        k_init_bounds<<<1, 32, 0, st>>>(c->bBounds.p, c->bScalars.p, 8);
-        k_tlas_instances<<<blocksFor(n, 128), 128, 0, st>>>(c->bTlasIn.p, n, c->bInst.p, c->bBoxes.p, c->bBounds.p);
-        launches += 2;
-        CKS(buildHierarchy(c, n, true, &launches));
-        // wide nodes <= n: copy the upper bound, the tail is never referenced
-        CK(cudaMemcpyAsync(c->tlasNodes.p, c->bNodes.p, (size_t)n * sizeof(WideNode), cudaMemcpyDeviceToDevice, st));
-        k_emit_instances<<<blocksFor(n, 128), 128, 0, st>>>(c->bPrimOut.p, n, c->bInst.p, c->tlasInst.p);
-        launches += 1;
-        CK(cudaGetLastError());
+        if (direct)
+        {
+            if (c->blasTableDirty)
+            {
+                std::vector<BlasTableEntry> table(c->blas.size());
+                for (size_t m = 0; m < table.size(); ++m) table[m] = BlasTableEntry{c->blas[m].nodes, c->blas[m].tris, c->blas[m].uvs};
+                CK(c->dBlasTable.ensure(table.size()));
+                CK(c->ring.upload(c->dBlasTable.p, table.data(), table.size() * sizeof(BlasTableEntry), st));
+                c->blasTableDirty = false;
+            }
+            CK(c->bTlasRaw.ensure(n));
+            CK(c->ring.upload(c->bTlasRaw.p, instances, (size_t)n * sizeof(prt_tlas_instance), st));
+        }
+        else
+        {
+            CK(c->bTlasIn.ensure(n));
+            CK(c->ring.upload(c->bTlasIn.p, in.data(), (size_t)n * sizeof(TlasInput), st));
+        }
+        // The rebuild is ~16 short dependent launches: from the second frame with the same instance count on, they are
+        // replayed as one CUDA graph (captured on the first repeat, re-captured when the count or any scratch buffer moved).
+        if (c->tlasGraphExec && c->tlasGraphN == n && c->tlasGraphDirect == direct && c->tlasGraphGeneration == g_allocGeneration)
+        {
+            CK(cudaGraphLaunch(c->tlasGraphExec, st));
+            launches = c->tlasGraphLaunches;
+        }
+        else if (c->tlasGraphs && c->tlasEagerN == n && c->tlasEagerDirect == direct && c->tlasEagerGeneration == g_allocGeneration)
+        {
+            if (c->tlasGraphExec) { CK(cudaGraphExecDestroy(c->tlasGraphExec)); c->tlasGraphExec = nullptr; }
+            CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            const prt_status s = enqueueTlasBuild(c, n, direct, &launches); // no allocation: the eager build of this size came first
+            cudaGraph_t graph = nullptr;
+            const cudaError_t e = cudaStreamEndCapture(st, &graph);
+            cudaError_t ei = e;
+            if (s == PRT_OK && e == cudaSuccess) ei = cudaGraphInstantiate(&c->tlasGraphExec, graph, 0);
+            if (graph) cudaGraphDestroy(graph);
+            if (s != PRT_OK || ei != cudaSuccess)
+            {
+                // a driver that cannot capture this sequence: say so once, keep the eager path from here on
+                cudaGetLastError();
+                c->tlasGraphExec = nullptr;
+                c->tlasGraphs = false;
+                fprintf(stderr, "prt: TLAS graph capture unavailable (%s); rebuilding with plain launches\n",
+                        s != PRT_OK ? g_lastError.c_str() : cudaGetErrorString(ei));
+                launches = 0;
+                CKS(enqueueTlasBuild(c, n, direct, &launches));
+            }
+            else
+            {
+                c->tlasGraphN = n;
+                c->tlasGraphDirect = direct;
+                c->tlasGraphGeneration = g_allocGeneration;
+                c->tlasGraphLaunches = launches;
+                CK(cudaGraphLaunch(c->tlasGraphExec, st));
+            }
+        }
+        else
+        {
+            CKS(enqueueTlasBuild(c, n, direct, &launches));
+            c->tlasEagerN = n;
+            c->tlasEagerDirect = direct;
+            c->tlasEagerGeneration = g_allocGeneration; // read after the build: its own allocations are included
+        }
     }
     CK(cudaEventRecord(c->evTlas[1], st));
     c->tlasTimed = true;
