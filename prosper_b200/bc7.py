@@ -1,4 +1,4 @@
-"""BC7 block encode/decode on the host (numpy), mode 6 only.
+"""BC7 on the host (numpy): a bounding-box mode-6 encoder for fixtures and a decoder for modes 4 / 5 / 6.
 
 The reference's texture cache stores BC7 UNORM blocks produced by ispc_texcomp's
 `alpha_ultrafast` profile (src/scene/Texture.cpp:257-287; only modes 4/5/6 enabled,
@@ -128,6 +128,71 @@ def decode_bc7_mode6(blocks: np.ndarray, width: int, height: int) -> np.ndarray:
     px = ((64 - w)[:, :, None] * e[:, None, :, 0] + w[:, :, None] * e[:, None, :, 1] + 32) >> 6
     px = px.astype(np.uint8).reshape(height // 4, width // 4, 4, 4, 4).transpose(0, 2, 1, 3, 4)
     return px.reshape(height, width, 4)
+
+
+_WEIGHTS = {2: (0, 21, 43, 64), 3: (0, 9, 18, 27, 37, 46, 55, 64), 4: tuple(int(v) for v in _W4)}
+
+
+def _decode_block(block: bytes):
+    """One 16-byte block -> 16 (r, g, b, a) tuples, row-major. Modes 4, 5 and 6 (what the reference's texture cache holds),
+    written from the format's field tables: LSB-first bit stream, mode = position of the first set bit.
+      mode 4: rotation 2, index selection 1, RGB endpoints 5 bits (R0 R1 G0 G1 B0 B1), alpha endpoints 6 bits,
+              16 x 2-bit indices (31 bits: the anchor texel drops its top bit), 16 x 3-bit indices (47 bits);
+      mode 5: rotation 2, RGB endpoints 7 bits, alpha endpoints 8 bits, 2-bit colour indices (31), 2-bit alpha indices (31);
+      mode 6: RGBA endpoints 7 bits (R0 R1 ... A0 A1), one p-bit per endpoint, 16 x 4-bit indices (63 bits).
+    Endpoints are widened to 8 bits by replicating their top bits; a texel is ((64 - w) * e0 + w * e1 + 32) >> 6."""
+    bits = int.from_bytes(block, "little")
+    pos = 0
+
+    def get(n):
+        nonlocal pos
+        v = (bits >> pos) & ((1 << n) - 1)
+        pos += n
+        return v
+
+    mode = 0
+    while mode < 8 and get(1) == 0:
+        mode += 1
+    lerp = lambda a, b, w: ((64 - w) * a + w * b + 32) >> 6
+    if mode == 6:
+        e = [[get(7) for _ in range(2)] for _ in range(4)]
+        p = [get(1), get(1)]
+        e = [[(e[c][k] << 1) | p[k] for k in range(2)] for c in range(4)]
+        idx = [get(3 if i == 0 else 4) for i in range(16)]
+        return [tuple(lerp(e[c][0], e[c][1], _WEIGHTS[4][idx[i]]) for c in range(4)) for i in range(16)]
+    if mode in (4, 5):
+        rot = get(2)
+        sel = get(1) if mode == 4 else 0
+        cb, ab = (5, 6) if mode == 4 else (7, 8)
+        widen = lambda v, n: v if n == 8 else ((v << (8 - n)) | (v >> (2 * n - 8)))
+        e = [[widen(get(cb), cb) for _ in range(2)] for _ in range(3)]
+        e.append([widen(get(ab), ab) for _ in range(2)])
+        first = [get(1 if i == 0 else 2) for i in range(16)]
+        nb = 3 if mode == 4 else 2
+        second = [get(nb - 1 if i == 0 else nb) for i in range(16)]
+        out = []
+        for i in range(16):
+            if mode == 4 and sel == 1:
+                cw, aw = _WEIGHTS[3][second[i]], _WEIGHTS[2][first[i]]
+            else:
+                cw, aw = _WEIGHTS[2][first[i]], _WEIGHTS[nb][second[i]]
+            ch = [lerp(e[c][0], e[c][1], cw) for c in range(3)] + [lerp(e[3][0], e[3][1], aw)]
+            if rot:
+                ch[3], ch[rot - 1] = ch[rot - 1], ch[3]
+            out.append(tuple(ch))
+        return out
+    raise ValueError(f"BC7 mode {mode}: the texture cache only holds modes 4, 5 and 6")
+
+
+def decode_bc7(blocks: np.ndarray, width: int, height: int) -> np.ndarray:
+    """BC7 blocks of modes 4 / 5 / 6 -> uint8 [H, W, 4]. Plain Python per block: for tests and small images."""
+    raw = np.ascontiguousarray(blocks, np.uint8).reshape(-1, 16)
+    out = np.zeros((height, width, 4), np.uint8)
+    bx = width // 4
+    for b in range(raw.shape[0]):
+        px = np.array(_decode_block(raw[b].tobytes()), np.uint8).reshape(4, 4, 4)
+        out[(b // bx) * 4:(b // bx) * 4 + 4, (b % bx) * 4:(b % bx) * 4 + 4] = px
+    return out
 
 
 def build_mip_chain_bc7(img: np.ndarray):

@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include "core_bc7.h"
+#include "core_bc7enc.h"
 #include "core_scene.h"
 #include "core_tonemap.h"
 
@@ -52,108 +53,26 @@ __global__ void k_alpha_plane(TexSlot slot, uint8_t *__restrict__ alpha, uint32_
 }
 
 // ---- BC7 encode (texture-cache build, Texture.cpp:213-296: the step prosper runs through ispc_texcomp) ------------
-// One thread per 4x4 block, mode 6 (one subset, 7-bit RGBA endpoints + p-bits, 4-bit indices): endpoints = the
-// block's per-channel bounding box, indices = nearest interpolation weight of each texel's projection on the
-// endpoint axis, anchor fix-up by swapping the endpoints. Bit-identical to prosper_b200/bc7.py (every intermediate
-// is an integer or one IEEE double division), which is what the tests pin it against.
-__device__ __forceinline__ void bc7QuantEndpoint(const int v[4], int e[4], int &p)
-{
-    // 7-bit endpoint + shared p-bit minimising the squared reconstruction error (p = 0 wins ties)
-    long long best = -1;
-    for (int pb = 0; pb < 2; ++pb)
-    {
-        int q[4];
-        long long err = 0;
-        for (int c = 0; c < 4; ++c)
-        {
-            int x = (int)rint((double)(v[c] - pb) / 2.0);
-            x = x < 0 ? 0 : (x > 127 ? 127 : x);
-            q[c] = x;
-            const int d = x * 2 + pb - v[c];
-            err += (long long)d * d;
-        }
-        if (best < 0 || err < best)
-        {
-            best = err;
-            p = pb;
-            for (int c = 0; c < 4; ++c) e[c] = q[c];
-        }
-    }
-}
-
-__global__ void k_bc7_encode_mode6(const uint32_t *__restrict__ rgba, uint32_t width, uint32_t height, uint2 *__restrict__ blocks64)
+// One thread per 4x4 block through bc7EncodeBlock (core_bc7enc.h): the reference's `alpha_ultrafast` profile -- modes 4
+// (both index layouts), 5 and 6, principal-axis endpoints, least-squares refinement, cheapest candidate. The host build
+// of the same header (tests/hostsim) emits the same bits; quality is gated against the decoders, which are pinned on
+// hand-assembled blocks and on the texture units (tests/test_bc7.py).
+__global__ void __launch_bounds__(64) k_bc7_encode(const uint32_t *__restrict__ rgba, uint32_t width, uint32_t height, uint2 *__restrict__ blocks64)
 {
     const uint32_t bx = width >> 2, by = height >> 2;
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= bx * by) return;
     const uint32_t x0 = (b % bx) * 4, y0 = (b / bx) * 4;
-    int px[16][4];
-    int lo[4] = {255, 255, 255, 255}, hi[4] = {0, 0, 0, 0};
-    for (int i = 0; i < 16; ++i)
+    uint32_t texels[16];
+    for (int row = 0; row < 4; ++row)
     {
-        const uint32_t t = __ldg(rgba + (size_t)(y0 + (i >> 2)) * width + x0 + (i & 3));
-        for (int c = 0; c < 4; ++c)
-        {
-            const int v = (int)((t >> (8 * c)) & 255u);
-            px[i][c] = v;
-            lo[c] = min(lo[c], v);
-            hi[c] = max(hi[c], v);
-        }
+        const uint4 t = __ldg(reinterpret_cast<const uint4 *>(rgba + (size_t)(y0 + row) * width + x0)); // width % 4 == 0: aligned
+        texels[4 * row + 0] = t.x; texels[4 * row + 1] = t.y; texels[4 * row + 2] = t.z; texels[4 * row + 3] = t.w;
     }
-    int e0[4], e1[4], p0, p1;
-    bc7QuantEndpoint(lo, e0, p0);
-    bc7QuantEndpoint(hi, e1, p1);
-    int c0[4], d[4];
-    long long dd = 0;
-    for (int c = 0; c < 4; ++c)
-    {
-        c0[c] = e0[c] * 2 + p0;
-        d[c] = e1[c] * 2 + p1 - c0[c];
-        dd += (long long)d[c] * d[c];
-    }
-    const int W4[16] = {0, 4, 9, 13, 17, 21, 26, 30, 34, 38, 43, 47, 51, 55, 60, 64};
-    int idx[16];
-    const double den = dd > 0 ? (double)dd : 1e-9;
-    for (int i = 0; i < 16; ++i)
-    {
-        long long dot = 0;
-        for (int c = 0; c < 4; ++c) dot += (long long)(px[i][c] - c0[c]) * d[c];
-        double t = (double)dot / den;
-        t = (t < 0.0 ? 0.0 : (t > 1.0 ? 1.0 : t)) * 64.0;
-        int bestK = 0;
-        double bestD = fabs(t - 0.0);
-        for (int k = 1; k < 16; ++k)
-        {
-            const double dk = fabs(t - (double)W4[k]);
-            if (dk < bestD) { bestD = dk; bestK = k; }
-        }
-        idx[i] = bestK;
-    }
-    if (idx[0] >= 8) // the anchor's MSB is implicit zero: swap the endpoints and mirror the indices
-    {
-        for (int i = 0; i < 16; ++i) idx[i] = 15 - idx[i];
-        for (int c = 0; c < 4; ++c) { const int t = e0[c]; e0[c] = e1[c]; e1[c] = t; }
-        const int t = p0; p0 = p1; p1 = t;
-    }
-    unsigned long long lo64 = 1ull << 6, hi64 = 0ull;
-    int bit = 7;
-    auto put = [&](unsigned long long v, int n) {
-        if (bit < 64)
-        {
-            lo64 |= v << bit;
-            if (bit + n > 64) hi64 |= v >> (64 - bit);
-        }
-        else
-            hi64 |= v << (bit - 64);
-        bit += n;
-    };
-    for (int c = 0; c < 4; ++c) { put((unsigned long long)e0[c], 7); put((unsigned long long)e1[c], 7); }
-    put((unsigned long long)p0, 1);
-    put((unsigned long long)p1, 1);
-    put((unsigned long long)idx[0], 3);
-    for (int i = 1; i < 16; ++i) put((unsigned long long)idx[i], 4);
-    blocks64[2 * (size_t)b + 0] = make_uint2((uint32_t)lo64, (uint32_t)(lo64 >> 32));
-    blocks64[2 * (size_t)b + 1] = make_uint2((uint32_t)hi64, (uint32_t)(hi64 >> 32));
+    uint64_t lo, hi;
+    bc7EncodeBlock(texels, lo, hi);
+    blocks64[2 * (size_t)b + 0] = make_uint2((uint32_t)lo, (uint32_t)(lo >> 32));
+    blocks64[2 * (size_t)b + 1] = make_uint2((uint32_t)hi, (uint32_t)(hi >> 32));
 }
 
 // out[i] = texel xy[i] as the texture units decode it (point view of the CUDA array; uniform handle)

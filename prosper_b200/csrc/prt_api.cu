@@ -694,7 +694,7 @@ extern "C" prt_status prt_encode_bc7(prt_ctx *c, const void *rgba8, uint32_t wid
     CK(src.ensure((size_t)width * height));
     CK(dst.ensure(nBlocks * 2));
     CK(cudaMemcpyAsync(src.p, rgba8, (size_t)width * height * 4, cudaMemcpyHostToDevice, c->stream));
-    k_bc7_encode_mode6<<<blocksFor(nBlocks, 64), 64, 0, c->stream>>>(src.p, width, height, dst.p);
+    k_bc7_encode<<<blocksFor(nBlocks, 64), 64, 0, c->stream>>>(src.p, width, height, dst.p);
     c->kernelLaunches++;
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(blocksOut, dst.p, nBlocks * 16, cudaMemcpyDeviceToHost, c->stream));
@@ -774,7 +774,7 @@ extern "C" prt_status prt_compress_texture(prt_ctx *c, const void *rgba8, uint32
         if (bc7)
         {
             const size_t nBlocks = (size_t)(w / 4) * (h / 4);
-            k_bc7_encode_mode6<<<blocksFor(nBlocks, 64), 64, 0, c->stream>>>(raw.p + rawOff[i], w, h, blocks.p + outOff[i] / 8);
+            k_bc7_encode<<<blocksFor(nBlocks, 64), 64, 0, c->stream>>>(raw.p + rawOff[i], w, h, blocks.p + outOff[i] / 8);
             c->kernelLaunches++;
         }
     }
@@ -880,7 +880,7 @@ extern "C" prt_status prt_compress_texture_static(prt_ctx *c, const void *rgba8,
         if (bc7)
         {
             const size_t nBlocks = (size_t)(w / 4) * (h / 4);
-            k_bc7_encode_mode6<<<blocksFor(nBlocks, 64), 64, 0, c->stream>>>(raw + rawOff[i], w, h, blocks + outOff[i] / 8);
+            k_bc7_encode<<<blocksFor(nBlocks, 64), 64, 0, c->stream>>>(raw + rawOff[i], w, h, blocks + outOff[i] / 8);
             c->kernelLaunches++;
         }
     }

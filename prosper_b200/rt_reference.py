@@ -264,7 +264,14 @@ class World:
                                        1 if shadow else 0, _p(hits)))
         return hits
 
-    def probe_texture(self, texture_sampler: int, uv: np.ndarray, exact: bool) -> np.ndarray:
+    def probe_texture(self, texture_sampler: int, uv: Optional[np.ndarray], exact: bool, texel_xy: Optional[np.ndarray] = None) -> np.ndarray:
+        """texture() at `uv` [n, 2] (hardware filter, or the software bilinear when `exact`), or -- with `texel_xy` int32
+        [n, 2] -- the raw texels at integer coordinates as the texture units decode them. -> float32 [n, 4]."""
+        if texel_xy is not None:
+            xy = np.ascontiguousarray(texel_xy, np.int32)
+            out = np.zeros((xy.shape[0], 4), np.float32)
+            _check(self.lib.prt_probe_texture(self.handle, texture_sampler, None, _p(xy), xy.shape[0], 1 if exact else 0, _p(out)))
+            return out
         uv = np.ascontiguousarray(uv, np.float32)
         out = np.zeros((uv.shape[0], 4), np.float32)
         _check(self.lib.prt_probe_texture(self.handle, texture_sampler, _p(uv), None, uv.shape[0], 1 if exact else 0, _p(out)))

@@ -46,6 +46,8 @@ def lib():
         l.hs_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_int]
         l.hs_render.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_int, C.c_void_p]
         l.hs_bc7_decode_block.restype = C.c_int
+        l.hs_bc7_encode.restype = None
+        l.hs_bc7_encode.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
         l.hs_build_check.restype = C.c_uint32
         l.hs_build_check.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
         l.hs_replace_blas.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
@@ -55,6 +57,16 @@ def lib():
 
 def _p(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
+
+
+def bc7_encode(rgba8: np.ndarray, want_modes: bool = False):
+    """The product's BC7 encoder core (core_bc7enc.h: modes 4 / 5 / 6) compiled for the host: uint8 [h, w, 4] -> uint8 blocks."""
+    img = np.ascontiguousarray(rgba8, np.uint8)
+    h, w, _ = img.shape
+    blocks = np.zeros((w // 4) * (h // 4) * 16, np.uint8)
+    modes = np.zeros((w // 4) * (h // 4), np.uint8)
+    lib().hs_bc7_encode(_p(img), w, h, _p(blocks), _p(modes))
+    return (blocks, modes) if want_modes else blocks
 
 
 class HostSim:

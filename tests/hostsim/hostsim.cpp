@@ -7,6 +7,7 @@
 // loads it and libprt_b200.so does not contain it. What it cannot cover (radix sort, scans, warp
 // compaction, texture units) is covered by the `-m gpu` tests.
 #include "../../prosper_b200/csrc/core_bc7.h"
+#include "../../prosper_b200/csrc/core_bc7enc.h"
 #include "../../prosper_b200/csrc/core_build.h"
 #include "../../prosper_b200/csrc/core_shade.h"
 #include "../../oracle/oracle.h" // orc_scene: the scene description struct shared with the oracle binding
@@ -511,6 +512,24 @@ int hs_bc7_decode_block(const uint8_t block[16], uint8_t out[64])
     memcpy(&lo, block, 8);
     memcpy(&hi, block + 8, 8);
     return bc7DecodeBlock(lo, hi, (uint32_t *)out) ? 0 : -1;
+}
+
+// The product's block encoder (core_bc7enc.h) on the CPU: rgba8 [height][width][4] -> width/4 * height/4 blocks of 16 bytes.
+// modes (optional): one byte per block, the mode written.
+void hs_bc7_encode(const uint8_t *rgba, uint32_t width, uint32_t height, uint8_t *blocks, uint8_t *modes)
+{
+    const uint32_t bx = width / 4, by = height / 4;
+    for (uint32_t b = 0; b < bx * by; ++b)
+    {
+        uint32_t texels[16];
+        for (uint32_t i = 0; i < 16; ++i)
+            memcpy(&texels[i], rgba + ((size_t)((b / bx) * 4 + i / 4) * width + (b % bx) * 4 + i % 4) * 4, 4);
+        uint64_t lo, hi;
+        const uint32_t mode = bc7EncodeBlock(texels, lo, hi);
+        memcpy(blocks + (size_t)b * 16, &lo, 8);
+        memcpy(blocks + (size_t)b * 16 + 8, &hi, 8);
+        if (modes) modes[b] = (uint8_t)mode;
+    }
 }
 
 // Builder check on bare boxes (n x {lo xyz, hi xyz}): builds the BLAS hierarchy with builder 0 = binned SAH, 1 = Karras,

@@ -1,6 +1,6 @@
 """Texture-cache build: the .dds container against the byte layout of writeDds / readDds (Dds.cpp),
 the level-chain rules of `compress` (Texture.cpp:213-296) and, on the GPU, prt_compress_texture against the numpy mip
-filter + the Python BC7 encoder, bit for bit."""
+filter + the host build of the BC7 encoder core (core_bc7enc.h; quality and decoders: tests/test_bc7.py), bit for bit."""
 import struct
 
 import numpy as np
@@ -136,8 +136,9 @@ def test_numpy_mip_filter_against_the_reference_stb(srgb):
 @pytest.mark.gpu
 @pytest.mark.parametrize("w,h,space", [(256, 256, tc.COLOR_SPACE_SRGB), (256, 128, tc.COLOR_SPACE_SRGB), (64, 64, tc.COLOR_SPACE_LINEAR),
                                        (100, 60, tc.COLOR_SPACE_SRGB), (4, 4, tc.COLOR_SPACE_SRGB)])
-def test_gpu_compress_matches_numpy_chain_and_python_encoder(tmp_path, w, h, space):
+def test_gpu_compress_matches_numpy_chain_and_host_build_of_the_encoder(tmp_path, w, h, space):
     from prosper_b200 import rt_reference as rt, scene_data as sd, scene_zoo
+    from tests import hostsim
     world = rt.World(scene_zoo.test_scene(fmt=sd.TEX_BC7), device=0, max_width=16, max_height=16, samples_per_launch=1)
     img = _image(w, h, seed=w + h)
     path = str(tmp_path / "cache.dds")
@@ -149,7 +150,7 @@ def test_gpu_compress_matches_numpy_chain_and_python_encoder(tmp_path, w, h, spa
         if i:
             level = tc.downsample_mitchell(level, space == tc.COLOR_SPACE_SRGB)
         if out.format == dds.FORMAT_BC7_UNORM:
-            want = bc7.encode_bc7_mode6(level)
+            want = hostsim.bc7_encode(level)
             assert np.array_equal(out.level(i), np.asarray(want, np.uint8).reshape(-1)), f"level {i}"
         else:
             assert np.array_equal(out.level(i), level.reshape(-1)), f"level {i}"
@@ -158,7 +159,7 @@ def test_gpu_compress_matches_numpy_chain_and_python_encoder(tmp_path, w, h, spa
     single = tc.compress(world, img, space, generate_mip_maps=False)
     assert single.mipLevelCount == 1 and single.format == tc.cache_format(w, h, 1)
     if single.format == dds.FORMAT_BC7_UNORM:
-        assert np.array_equal(single.level(0), bc7.encode_bc7_mode6(img).reshape(-1))
+        assert np.array_equal(single.level(0), hostsim.bc7_encode(img).reshape(-1))
     else:
         assert np.array_equal(single.level(0), img.reshape(-1))
     with pytest.raises(RuntimeError):
