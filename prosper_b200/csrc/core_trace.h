@@ -445,6 +445,13 @@ HD bool commitHit(const RayCtx &c, const Accel &as, const TraceIO &io, uint4 O, 
     return false;
 }
 
+#ifndef PRT_NODE_PER_ITEM
+#define PRT_NODE_PER_ITEM 1 // nodes one node item may descend through (see traceNodeItem)
+#endif
+#ifndef PRT_TRI_PER_ITEM
+#define PRT_TRI_PER_ITEM 2 // primitives one triangle item tests (1: round 1's one-per-item)
+#endif
+
 // KIND_NODE: take the nearest pending child of the node group, intersect its eight boxes.
 template <bool COUNT>
 HD int traceNodeItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceCounters *cnt)
@@ -457,25 +464,34 @@ HD int traceNodeItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceC
     const WideNode *nodes = levelNodes(c.row(ROW_P));
     const uint4 I = c.row(ROW_I);
     const uint32_t octinv = I.w & 7u;
-    const int bit = bfind(g.y);
-    const uint32_t imask = g.y;
-    g.y &= ~(1u << bit);
-    if (g.y & 0xFF000000u)
-    {
-        if (sp < (uint32_t)TRACE_STACK) top = make_uint2(g.x, g.y);
-        stackPush(c, sp, g.x, g.y, io);
-    }
-    const uint32_t slot = ((uint32_t)bit - 24u) ^ octinv;
-    const uint32_t rel = (uint32_t)popc(imask & 0xFFu & ((1u << slot) - 1u));
-    NodeWords n;
-    loadNodeWords(nodes + g.x + rel, n);
-    if (COUNT) cnt->nodes++;
     const uint4 O = c.row(ROW_O);
-    const uint32_t hits = intersectNode(n, V3{u2f(O.x), u2f(O.y), u2f(O.z)}, V3{u2f(I.x), u2f(I.y), u2f(I.z)}, octinv, u2f(m.y), u2f(O.w), as.planeBias);
-    g.x = n.w1.x;
-    g.y = (hits & 0xFF000000u) | (n.w0.w >> 24);
-    g.z = n.w1.y;
-    g.w = hits & 0x00FFFFFFu;
+    // Up to PRT_NODE_PER_ITEM nodes per item: a node whose test leaves node children only (no primitives, so no other kind
+    // and no pop comes first) is followed at once by its nearest child -- the rows are read and written once for both.
+#if defined(__CUDACC__)
+#pragma unroll
+#endif
+    for (int k = 0; k < PRT_NODE_PER_ITEM; ++k)
+    {
+        if (k > 0 && !(g.w == 0u && (g.y & 0xFF000000u))) break;
+        const int bit = bfind(g.y);
+        const uint32_t imask = g.y;
+        g.y &= ~(1u << bit);
+        if (g.y & 0xFF000000u)
+        {
+            if (sp < (uint32_t)TRACE_STACK) top = make_uint2(g.x, g.y);
+            stackPush(c, sp, g.x, g.y, io);
+        }
+        const uint32_t slot = ((uint32_t)bit - 24u) ^ octinv;
+        const uint32_t rel = (uint32_t)popc(imask & 0xFFu & ((1u << slot) - 1u));
+        NodeWords n;
+        loadNodeWords(nodes + g.x + rel, n);
+        if (COUNT) cnt->nodes++;
+        const uint32_t hits = intersectNode(n, V3{u2f(O.x), u2f(O.y), u2f(O.z)}, V3{u2f(I.x), u2f(I.y), u2f(I.z)}, octinv, u2f(m.y), u2f(O.w), as.planeBias);
+        g.x = n.w1.x;
+        g.y = (hits & 0xFF000000u) | (n.w0.w >> 24);
+        g.z = n.w1.y;
+        g.w = hits & 0x00FFFFFFu;
+    }
     return traceFinishItem(c, as, io, g, m, sp, blasP1, top);
 }
 
@@ -486,52 +502,62 @@ HD int traceTriItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceCo
     uint4 g = c.row(ROW_G);
     const uint4 m = c.row(ROW_M);
     const TriRec *tris = levelTris(c.row(ROW_P));
-    // this item ends in a pop exactly when it tests the group's last primitive with no node child pending
-    const bool willPop = (g.w & (g.w - 1u)) == 0 && (g.y & 0xFF000000u) == 0;
+    // One item tests up to PRT_TRI_PER_ITEM primitives of the group: the ray rows are read and written once per item, not
+    // once per triangle. It ends in a pop exactly when it tests the group's last primitives with no node child pending.
+    const bool willPop = popc(g.w) <= PRT_TRI_PER_ITEM && (g.y & 0xFF000000u) == 0;
     const uint2 top = willPop ? stackTop(c, m.x & 0xFFFFu) : make_uint2(0u, 0u);
-    const int pbit = bfind(g.w);
-    g.w &= ~(1u << pbit);
-    const uint32_t triIndex = g.z + (uint32_t)pbit;
-#if defined(__CUDA_ARCH__)
-    uint4 a, b;
-    ldg256(tris + triIndex, a, b);
-    const uint4 e = __ldg(reinterpret_cast<const uint4 *>(tris + triIndex) + 2);
-#else
-    uint4 a, b, e;
-    memcpy(&a, &tris[triIndex], 16); memcpy(&b, (const char *)&tris[triIndex] + 16, 16); memcpy(&e, (const char *)&tris[triIndex] + 32, 16);
+    uint4 O = c.row(ROW_O);
+    const uint4 D = c.row(ROW_D);
+#if defined(__CUDACC__)
+#pragma unroll
 #endif
-    if (COUNT) cnt->tris++;
-    const uint4 O = c.row(ROW_O), D = c.row(ROW_D);
-    const float curT = u2f(O.w);
-    float t, u, v;
-    // the open interval (tMin, tMax) and "closer than the committed hit" in one comparison against curT (the committed
-    // t is below tMax); an exact tie goes to the smallest (instance, geometry, primitive) -- betterHit's order
-    const bool inside = intersectTriangleExact(V3{u2f(O.x), u2f(O.y), u2f(O.z)}, V3{u2f(D.x), u2f(D.y), u2f(D.z)}, u2f(m.y), 3.402823466e38f,
-                                               V3{u2f(a.x), u2f(a.y), u2f(a.z)}, V3{u2f(b.x), u2f(b.y), u2f(b.z)}, V3{u2f(e.x), u2f(e.y), u2f(e.z)},
-                                               t, u, v);
-    bool candidate = inside & (t < curT);
-    const uint32_t geom = b.w & 0x7FFFFFFFu;
-    if (inside && t == curT && !SHADOW)
+    for (int k = 0; k < PRT_TRI_PER_ITEM; ++k)
     {
-        const uint32_t flags = c.row(ROW_I).w;
-        if (flags & TRACE_HAS_HIT)
+        if (k > 0 && g.w == 0u) break;
+        const int pbit = bfind(g.w);
+        g.w &= ~(1u << pbit);
+        const uint32_t triIndex = g.z + (uint32_t)pbit;
+#if defined(__CUDA_ARCH__)
+        uint4 a, b;
+        ldg256(tris + triIndex, a, b);
+        const uint4 e = __ldg(reinterpret_cast<const uint4 *>(tris + triIndex) + 2);
+#else
+        uint4 a, b, e;
+        memcpy(&a, &tris[triIndex], 16); memcpy(&b, (const char *)&tris[triIndex] + 16, 16); memcpy(&e, (const char *)&tris[triIndex] + 32, 16);
+#endif
+        if (COUNT) cnt->tris++;
+        const float curT = u2f(O.w);
+        float t, u, v;
+        // the open interval (tMin, tMax) and "closer than the committed hit" in one comparison against curT (the committed
+        // t is below tMax); an exact tie goes to the smallest (instance, geometry, primitive) -- betterHit's order
+        const bool inside = intersectTriangleExact(V3{u2f(O.x), u2f(O.y), u2f(O.z)}, V3{u2f(D.x), u2f(D.y), u2f(D.z)}, u2f(m.y), 3.402823466e38f,
+                                                   V3{u2f(a.x), u2f(a.y), u2f(a.z)}, V3{u2f(b.x), u2f(b.y), u2f(b.z)}, V3{u2f(e.x), u2f(e.y), u2f(e.z)},
+                                                   t, u, v);
+        bool candidate = inside & (t < curT);
+        const uint32_t geom = b.w & 0x7FFFFFFFu;
+        if (inside && t == curT && !SHADOW)
         {
-            const uint2 key = io.tie[m.z];
-            const uint32_t bestPrim = io.hits[m.z].y;
-            const uint32_t inst = as.instances[m.w].index;
-            candidate = inst != key.x ? inst < key.x : (geom != key.y ? geom < key.y : a.w < bestPrim);
+            const uint32_t flags = c.row(ROW_I).w;
+            if (flags & TRACE_HAS_HIT)
+            {
+                const uint2 key = io.tie[m.z];
+                const uint32_t bestPrim = io.hits[m.z].y;
+                const uint32_t inst = as.instances[m.w].index;
+                candidate = inst != key.x ? inst < key.x : (geom != key.y ? geom < key.y : a.w < bestPrim);
+            }
         }
-    }
-    if (candidate)
-    {
-        if (!(b.w >> 31))
+        if (candidate)
         {
-            // non-opaque geometry: park the candidate, its any-hit test is the ray's next item
-            *c.pend = make_uint4(f2u(t), f2u(u), f2u(v), triIndex);
-            g.z |= TRACE_PENDING;
+            if (!(b.w >> 31))
+            {
+                // non-opaque geometry: park the candidate, its any-hit test is the ray's next item
+                *c.pend = make_uint4(f2u(t), f2u(u), f2u(v), triIndex);
+                g.z |= TRACE_PENDING;
+                break;
+            }
+            if (commitHit<SHADOW>(c, as, io, O, m.z, m.w, geom, a.w, t, u, v)) return KIND_IDLE;
+            O.w = f2u(t); // the next primitive of this item is tested against the new hit
         }
-        else if (commitHit<SHADOW>(c, as, io, O, m.z, m.w, geom, a.w, t, u, v))
-            return KIND_IDLE;
     }
     return traceFinishItem(c, as, io, g, m, m.x & 0xFFFFu, m.x >> 16, top);
 }
