@@ -264,7 +264,7 @@ HD uint32_t bc7EncodeBlock(const uint32_t texels[16], uint64_t &lo, uint64_t &hi
         const uint32_t cEp = mode == 4u ? 5u : 7u, aEp = mode == 4u ? 6u : 8u;
         const uint32_t cIdx = mode == 4u ? (idxMode ? 3u : 2u) : 2u, aIdx = mode == 4u ? (idxMode ? 2u : 3u) : 2u;
         Bc7Candidate k{};
-        uint32_t cErr, aErr, unused[2], ae[4][2];
+        uint32_t cErr, aErr, unused[2], ae[4][2] = {};
         bc7FitVector(px, 0, 3, cEp, cIdx, 1, k.e, unused, k.ci, cErr);
         bc7FitVector(px, 3, 1, aEp, aIdx, 1, ae, unused, k.ai, aErr);
         k.e[3][0] = ae[0][0]; k.e[3][1] = ae[0][1];

@@ -43,7 +43,12 @@ struct Accel
     uint32_t instanceCount;    // 1: rays start inside the only instance (its BLAS root culls what the TLAS root would)
     uint32_t planeBias;        // 0x47000000 (the float 32768): handed in as data so that the node test's PRMTs keep it in a
                                // register and take their byte selectors as immediates (intersectNode)
+    uint64_t arena;            // 128-byte aligned address at or below every node / triangle array: a ray names the arrays of
+                               // its level by their distance from it in 128-byte units (ROW_M), 32 bits each = 512 GB of reach
 };
+HD uint32_t arenaUnits(const Accel &as, const void *p) { return (uint32_t)(((uint64_t)(uintptr_t)p - as.arena) >> 7); }
+HD const WideNode *arenaNodes(const Accel &as, uint32_t units) { return reinterpret_cast<const WideNode *>((uintptr_t)(as.arena + ((uint64_t)units << 7))); }
+HD const TriRec *arenaTris(const Accel &as, uint32_t units) { return reinterpret_cast<const TriRec *>((uintptr_t)(as.arena + ((uint64_t)units << 7))); }
 constexpr uint32_t PLANE_BIAS = 0x47000000u;
 
 struct NodeRay
@@ -303,16 +308,25 @@ HD uint32_t intersectNode(const NodeWords &n, V3 o, V3 idir, uint32_t octinv, fl
 //
 // The committed hit itself is not traversal state: a commit writes the 16-byte record straight to the caller's hit
 // queue (plus the two tie-break keys beside it), the rows keep only its t (`curT`) and a flag.
-enum : int { ROW_O = 0, ROW_D = 1, ROW_I = 2, ROW_G = 3, ROW_M = 4, ROW_P = 5, POOL_ROWS = 6 };
+enum : int { ROW_O = 0, ROW_D = 1, ROW_I = 2, ROW_G = 3, ROW_M = 4, POOL_ROWS = 5 };
 //  ROW_O  origin.xyz (current space: world in the TLAS, object in a BLAS), curT = committed hit ? its t : tMax
-//  ROW_D  direction.xyz (current space), unused
-//  ROW_I  reciprocal direction.xyz (zero components nudged), octinv | TRACE_HAS_HIT
-//  ROW_G  node group (base index, hit bits | imask), primitive group (base index | TRACE_PENDING, hit bits)
-//  ROW_M  sp | (stack depth at BLAS entry + 1) << 16 (0 while in the TLAS), tMin, queue slot, instance position
-//  ROW_P  node array, triangle array of the current level (two pointers)
+//  ROW_D  direction.xyz (current space), tMin
+//  ROW_I  reciprocal direction.xyz (zero components nudged), octinv | TRACE_HAS_HIT | a lower bound of tMin in the top 16 bits
+//         (the node test takes its tMin from here: the same row it reads anyway, and a lower bound only ever visits more)
+//  ROW_G  node group (base index, hit bits << 24 | state | imask), primitive group (base index | TRACE_PENDING, hit bits);
+//         state = sp << 8 | (stack depth at BLAS entry + 1) << 16 (0 while in the TLAS): the one row every item writes
+//  ROW_M  node array, triangle array of the current level (arenaUnits), queue slot, instance position: written on entering
+//         and leaving an instance only
+// A node item reads G M I O and writes G; a triangle item reads G M O D and writes G (and O I on a commit). Round 1's layout
+// had a sixth row for two 64-bit level pointers and kept sp in ROW_M: five reads and two writes per item, and 4 KB more
+// shared memory per block (= less L1) -- the L1 data pipe is what bounds this kernel.
 enum : int { KIND_NODE = 0, KIND_TRI = 1, KIND_ANYHIT = 2, KIND_INSTANCE = 3, KIND_COUNT = 4, KIND_IDLE = 7 };
 constexpr uint32_t TRACE_PENDING = 0x80000000u; // ROW_G.z: a candidate waits for its any-hit test (parked in RayCtx::pend)
 constexpr uint32_t TRACE_HAS_HIT = 0x100u;      // ROW_I.w
+constexpr uint32_t TRACE_STATE = 0x00FFFF00u;   // ROW_G.y: sp << 8 | blasP1 << 16
+HD uint32_t stateSp(uint32_t gy) { return (gy >> 8) & 0xFFu; }
+HD uint32_t stateBlas(uint32_t gy) { return (gy >> 16) & 0xFFu; }
+static_assert(TRACE_STACK + 1 < 256, "sp and blasP1 are bytes of ROW_G.y");
 // The stack is per-thread local memory (L1). Measured alternative: the first 8 entries in shared memory next to the rows
 // and the level pointers fetched through the instance record -- 942 instead of 990 Mrays/s, because the larger carve-out
 // leaves 28 KB of L1 for nodes and triangles (hit rate 16 % instead of 31-45 %) and the two-tier entry access costs 10 %
@@ -351,23 +365,18 @@ HD void stackPush(const RayCtx &c, uint32_t &sp, uint32_t a, uint32_t b, const T
     }
 }
 
-HD void storeRaySpace(const RayCtx &c, V3 o, V3 d, float curT, uint32_t flags)
+// `flags` = the TRACE_HAS_HIT bit to keep. The bound of tMin kept in ROW_I.w is tMin with its low 16 bits cleared (towards
+// minus infinity), so that the node test never starts later than the exact interval.
+HD void storeRaySpace(const RayCtx &c, V3 o, V3 d, float curT, uint32_t flags, float tMin)
 {
     NodeRay r;
     setupNodeRay(r, o, d);
+    uint32_t lower = f2u(tMin) & 0xFFFF0000u;
+    if ((f2u(tMin) >> 31) && (f2u(tMin) & 0xFFFFu)) lower += 0x10000u; // negative: one step further from zero
     c.row(ROW_O) = make_uint4(f2u(o.x), f2u(o.y), f2u(o.z), f2u(curT));
-    c.row(ROW_D) = make_uint4(f2u(d.x), f2u(d.y), f2u(d.z), 0u);
-    c.row(ROW_I) = make_uint4(f2u(r.ix), f2u(r.iy), f2u(r.iz), r.octinv | flags);
+    c.row(ROW_D) = make_uint4(f2u(d.x), f2u(d.y), f2u(d.z), f2u(tMin));
+    c.row(ROW_I) = make_uint4(f2u(r.ix), f2u(r.iy), f2u(r.iz), r.octinv | flags | lower);
 }
-
-// Node and triangle arrays of the level the ray is in.
-HD void storePointers(const RayCtx &c, const WideNode *nodes, const TriRec *tris)
-{
-    const uint64_t a = (uint64_t)(uintptr_t)nodes, b = (uint64_t)(uintptr_t)tris;
-    c.row(ROW_P) = make_uint4((uint32_t)a, (uint32_t)(a >> 32), (uint32_t)b, (uint32_t)(b >> 32));
-}
-HD const WideNode *levelNodes(const uint4 &P) { return reinterpret_cast<const WideNode *>((uintptr_t)(((uint64_t)P.y << 32) | P.x)); }
-HD const TriRec *levelTris(const uint4 &P) { return reinterpret_cast<const TriRec *>((uintptr_t)(((uint64_t)P.w << 32) | P.z)); }
 // The stack's top entry, loaded at the START of an item so that a pop at its end does not wait for local memory (the
 // pop runs at ~6 of 32 lanes and its load was 19 % of the kernel's stall samples).
 HD uint2 stackTop(const RayCtx &c, uint32_t sp) { return c.entry(sp ? sp - 1u : 0u); }
@@ -383,27 +392,26 @@ HD int traceBegin(const RayCtx &c, const Accel &as, const TraceIO &io, uint32_t 
     if (as.tlasNodes == nullptr) return KIND_IDLE;
     const float4 wo = io.rayO[qslot], wd = io.rayD[qslot];
     const V3 o = {wo.x, wo.y, wo.z}, d = {wd.x, wd.y, wd.z};
-    c.row(ROW_G) = make_uint4(0u, 0x80000000u, 0u, 0u);
     if (as.instanceCount == 1u)
     {
         // single-instance scene (a baked glTF such as Sponza): skip the one-node TLAS
         const InstRec &inst = as.instances[0];
         if (cnt) cnt->instances++;
         if ((inst.mask & 0xFFu) == 0) return KIND_IDLE;
-        storeRaySpace(c, xformPoint(inst.w2o, o), xformVector(inst.w2o, d), wd.w, 0u);
-        storePointers(c, inst.nodes, inst.tris);
-        c.row(ROW_M) = make_uint4(0u | (1u << 16), f2u(wo.w), qslot, 0u);
+        storeRaySpace(c, xformPoint(inst.w2o, o), xformVector(inst.w2o, d), wd.w, 0u, wo.w);
+        c.row(ROW_G) = make_uint4(0u, 0x80000000u | (1u << 16), 0u, 0u);
+        c.row(ROW_M) = make_uint4(arenaUnits(as, inst.nodes), arenaUnits(as, inst.tris), qslot, 0u);
         return KIND_NODE;
     }
-    storeRaySpace(c, o, d, wd.w, 0u);
-    storePointers(c, as.tlasNodes, nullptr);
-    c.row(ROW_M) = make_uint4(0u, f2u(wo.w), qslot, 0u);
+    storeRaySpace(c, o, d, wd.w, 0u, wo.w);
+    c.row(ROW_G) = make_uint4(0u, 0x80000000u, 0u, 0u);
+    c.row(ROW_M) = make_uint4(arenaUnits(as, as.tlasNodes), 0u, qslot, 0u);
     return KIND_NODE;
 }
 
 // End of every item: when both groups are exhausted pop the next one (leaving the BLAS when its entries are used up);
 // an empty stack finishes the ray. Stores the group row and the state row, returns the next item kind.
-HD int traceFinishItem(const RayCtx &c, const Accel &as, const TraceIO &io, uint4 g, uint4 m, uint32_t sp, uint32_t blasP1, uint2 top)
+HD int traceFinishItem(const RayCtx &c, const Accel &as, const TraceIO &io, uint4 g, uint32_t sp, uint32_t blasP1, uint2 top)
 {
     if (g.w == 0 && (g.y & 0xFF000000u) == 0 && !(g.z & TRACE_PENDING))
     {
@@ -412,18 +420,18 @@ HD int traceFinishItem(const RayCtx &c, const Accel &as, const TraceIO &io, uint
         {
             // BLAS exhausted: back to world space
             blasP1 = 0;
+            const uint4 m = c.row(ROW_M);
             const float4 wo = io.rayO[m.z], wd = io.rayD[m.z];
-            storeRaySpace(c, V3{wo.x, wo.y, wo.z}, V3{wd.x, wd.y, wd.z}, u2f(c.row(ROW_O).w), c.row(ROW_I).w & TRACE_HAS_HIT);
-            storePointers(c, as.tlasNodes, nullptr);
+            storeRaySpace(c, V3{wo.x, wo.y, wo.z}, V3{wd.x, wd.y, wd.z}, u2f(c.row(ROW_O).w), c.row(ROW_I).w & TRACE_HAS_HIT, wo.w);
+            c.row(ROW_M) = make_uint4(arenaUnits(as, as.tlasNodes), 0u, m.z, m.w);
         }
         sp--;
         const uint2 e = top;
         if (e.y & 0xFF000000u) { g.x = e.x; g.y = e.y; g.z = 0; g.w = 0; }
         else { g.x = 0; g.y = 0; g.z = e.x; g.w = e.y; } // a postponed primitive group (pushed when an instance was entered)
     }
+    g.y = (g.y & ~TRACE_STATE) | (sp << 8) | (blasP1 << 16);
     c.row(ROW_G) = g;
-    m.x = sp | (blasP1 << 16);
-    c.row(ROW_M) = m;
     return kindOf(g, blasP1);
 }
 
@@ -457,17 +465,17 @@ template <bool COUNT>
 HD int traceNodeItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceCounters *cnt)
 {
     uint4 g = c.row(ROW_G);
-    const uint4 m = c.row(ROW_M);
-    uint32_t sp = m.x & 0xFFFFu;
-    const uint32_t blasP1 = m.x >> 16;
+    uint32_t sp = stateSp(g.y);
+    const uint32_t blasP1 = stateBlas(g.y);
+    g.y &= ~TRACE_STATE;
     uint2 top = stackTop(c, sp);
-    const WideNode *nodes = levelNodes(c.row(ROW_P));
+    const WideNode *nodes = arenaNodes(as, c.row(ROW_M).x);
     const uint4 I = c.row(ROW_I);
     const uint32_t octinv = I.w & 7u;
     const uint4 O = c.row(ROW_O);
     // Up to PRT_NODE_PER_ITEM nodes per item: a node whose test leaves node children only (no primitives, so no other kind
     // and no pop comes first) is followed at once by its nearest child -- the rows are read and written once for both.
-#if defined(__CUDACC__)
+#if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
     for (int k = 0; k < PRT_NODE_PER_ITEM; ++k)
@@ -486,13 +494,13 @@ HD int traceNodeItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceC
         NodeWords n;
         loadNodeWords(nodes + g.x + rel, n);
         if (COUNT) cnt->nodes++;
-        const uint32_t hits = intersectNode(n, V3{u2f(O.x), u2f(O.y), u2f(O.z)}, V3{u2f(I.x), u2f(I.y), u2f(I.z)}, octinv, u2f(m.y), u2f(O.w), as.planeBias);
+        const uint32_t hits = intersectNode(n, V3{u2f(O.x), u2f(O.y), u2f(O.z)}, V3{u2f(I.x), u2f(I.y), u2f(I.z)}, octinv, u2f(I.w & 0xFFFF0000u), u2f(O.w), as.planeBias);
         g.x = n.w1.x;
         g.y = (hits & 0xFF000000u) | (n.w0.w >> 24);
         g.z = n.w1.y;
         g.w = hits & 0x00FFFFFFu;
     }
-    return traceFinishItem(c, as, io, g, m, sp, blasP1, top);
+    return traceFinishItem(c, as, io, g, sp, blasP1, top);
 }
 
 // KIND_TRI: one pending primitive of the primitive group inside a BLAS = one exact ray/triangle test.
@@ -500,15 +508,17 @@ template <bool SHADOW, bool COUNT>
 HD int traceTriItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceCounters *cnt)
 {
     uint4 g = c.row(ROW_G);
+    const uint32_t sp = stateSp(g.y), blasP1 = stateBlas(g.y);
+    g.y &= ~TRACE_STATE;
     const uint4 m = c.row(ROW_M);
-    const TriRec *tris = levelTris(c.row(ROW_P));
+    const TriRec *tris = arenaTris(as, m.y);
     // One item tests up to PRT_TRI_PER_ITEM primitives of the group: the ray rows are read and written once per item, not
     // once per triangle. It ends in a pop exactly when it tests the group's last primitives with no node child pending.
     const bool willPop = popc(g.w) <= PRT_TRI_PER_ITEM && (g.y & 0xFF000000u) == 0;
-    const uint2 top = willPop ? stackTop(c, m.x & 0xFFFFu) : make_uint2(0u, 0u);
+    const uint2 top = willPop ? stackTop(c, sp) : make_uint2(0u, 0u);
     uint4 O = c.row(ROW_O);
     const uint4 D = c.row(ROW_D);
-#if defined(__CUDACC__)
+#if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
     for (int k = 0; k < PRT_TRI_PER_ITEM; ++k)
@@ -530,7 +540,7 @@ HD int traceTriItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceCo
         float t, u, v;
         // the open interval (tMin, tMax) and "closer than the committed hit" in one comparison against curT (the committed
         // t is below tMax); an exact tie goes to the smallest (instance, geometry, primitive) -- betterHit's order
-        const bool inside = intersectTriangleExact(V3{u2f(O.x), u2f(O.y), u2f(O.z)}, V3{u2f(D.x), u2f(D.y), u2f(D.z)}, u2f(m.y), 3.402823466e38f,
+        const bool inside = intersectTriangleExact(V3{u2f(O.x), u2f(O.y), u2f(O.z)}, V3{u2f(D.x), u2f(D.y), u2f(D.z)}, u2f(D.w), 3.402823466e38f,
                                                    V3{u2f(a.x), u2f(a.y), u2f(a.z)}, V3{u2f(b.x), u2f(b.y), u2f(b.z)}, V3{u2f(e.x), u2f(e.y), u2f(e.z)},
                                                    t, u, v);
         bool candidate = inside & (t < curT);
@@ -559,7 +569,7 @@ HD int traceTriItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceCo
             O.w = f2u(t); // the next primitive of this item is tested against the new hit
         }
     }
-    return traceFinishItem(c, as, io, g, m, m.x & 0xFFFFu, m.x >> 16, top);
+    return traceFinishItem(c, as, io, g, sp, blasP1, top);
 }
 
 // KIND_ANYHIT: scene.rahit for the candidate parked by the triangle item (its own kind, so that the rays of a warp
@@ -568,6 +578,8 @@ template <bool SHADOW, bool COUNT>
 HD int traceAnyHitItem(const RayCtx &c, const Accel &as, const SceneView &sv, const TraceIO &io, TraceCounters *cnt)
 {
     uint4 g = c.row(ROW_G);
+    const uint32_t sp = stateSp(g.y), blasP1 = stateBlas(g.y);
+    g.y &= ~TRACE_STATE;
     const uint4 m = c.row(ROW_M);
     g.z &= ~TRACE_PENDING;
     const uint4 pd = *c.pend;
@@ -590,7 +602,7 @@ HD int traceAnyHitItem(const RayCtx &c, const Accel &as, const SceneView &sv, co
     }
     if (!fast) accept = anyHitAccept(sv, drawInstanceIndex, prim, u, v, seed);
     if (accept && commitHit<SHADOW>(c, as, io, c.row(ROW_O), m.z, m.w, geom, prim, t, u, v)) return KIND_IDLE;
-    return traceFinishItem(c, as, io, g, m, m.x & 0xFFFFu, m.x >> 16, stackTop(c, m.x & 0xFFFFu));
+    return traceFinishItem(c, as, io, g, sp, blasP1, stackTop(c, sp));
 }
 
 // KIND_INSTANCE: one pending primitive of a TLAS leaf = enter that instance (the TLAS groups go on the stack).
@@ -598,22 +610,22 @@ template <bool COUNT>
 HD int traceInstanceItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceCounters *cnt)
 {
     uint4 g = c.row(ROW_G);
-    uint4 m = c.row(ROW_M);
-    uint32_t sp = m.x & 0xFFFFu;
+    uint32_t sp = stateSp(g.y);
+    g.y &= ~TRACE_STATE;
+    const uint4 m = c.row(ROW_M);
     const int pbit = bfind(g.w);
     g.w &= ~(1u << pbit);
     const uint32_t instPos = g.z + (uint32_t)pbit;
     const InstRec &inst = as.instances[instPos];
     if (COUNT) cnt->instances++;
-    if ((inst.mask & 0xFFu) == 0) return traceFinishItem(c, as, io, g, m, sp, 0u, stackTop(c, sp));
+    if ((inst.mask & 0xFFu) == 0) return traceFinishItem(c, as, io, g, sp, 0u, stackTop(c, sp));
     if (g.y & 0xFF000000u) stackPush(c, sp, g.x, g.y, io);
     if (g.w != 0) stackPush(c, sp, g.z, g.w, io);
     const float4 wo = io.rayO[m.z], wd = io.rayD[m.z];
     storeRaySpace(c, xformPoint(inst.w2o, V3{wo.x, wo.y, wo.z}), xformVector(inst.w2o, V3{wd.x, wd.y, wd.z}), u2f(c.row(ROW_O).w),
-                  c.row(ROW_I).w & TRACE_HAS_HIT);
-    storePointers(c, inst.nodes, inst.tris);
-    c.row(ROW_G) = make_uint4(0u, 0x80000000u, 0u, 0u);
-    c.row(ROW_M) = make_uint4(sp | ((sp + 1u) << 16), m.y, m.z, instPos);
+                  c.row(ROW_I).w & TRACE_HAS_HIT, wo.w);
+    c.row(ROW_G) = make_uint4(0u, 0x80000000u | (sp << 8) | ((sp + 1u) << 16), 0u, 0u);
+    c.row(ROW_M) = make_uint4(arenaUnits(as, inst.nodes), arenaUnits(as, inst.tris), m.z, instPos);
     return KIND_NODE;
 }
 

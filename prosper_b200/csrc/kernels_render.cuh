@@ -119,6 +119,13 @@ __global__ void __launch_bounds__(RENDER_THREADS)
 // of the persistent trace kernels 32 rays that start close together and walk the tree in the same child order, which is
 // what the per-step vote and L1 want. Results do not depend on the order (every ray writes its own slot), so hit IDs and
 // radiance are unchanged bit for bit. Three small launches per queue: bin (key + histogram), scan, scatter.
+// a kind runs in a round when at least PRT_BAR_*_Q quarters as many lanes want it as want the most wanted kind
+#ifndef PRT_BAR_NODE_Q
+#define PRT_BAR_NODE_Q 2
+#endif
+#ifndef PRT_BAR_TRI_Q
+#define PRT_BAR_TRI_Q 2
+#endif
 #ifndef PRT_RAY_SORT_CELL_BITS
 #define PRT_RAY_SORT_CELL_BITS 5
 #endif
@@ -291,7 +298,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
         // which it then gets in the same round). The any-hit test is long and rare: it waits for a quarter of the warp.
         const uint32_t n0 = census & 63u, n1 = (census >> 6) & 63u, n2 = (census >> 12) & 63u, n3 = (census >> 18) & 63u;
         const uint32_t most = max(max(n0, n1), max(n2, n3));
-        const uint32_t bar = (most + 1u) >> 1;
+        const uint32_t barNode = (most * PRT_BAR_NODE_Q + 3u) >> 2, barTri = (most * PRT_BAR_TRI_Q + 3u) >> 2, bar = (most + 1u) >> 1;
         auto runKind = [&](const int run) {
             int r = -1;
 #pragma unroll
@@ -313,9 +320,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
         else if (n3 == most) runKind(KIND_INSTANCE);
         else runKind(KIND_NODE);
 #else
-        if (n0 >= bar) runKind(KIND_NODE);
+        if (n0 >= barNode) runKind(KIND_NODE);
         if (n3 >= bar) runKind(KIND_INSTANCE);
-        if (n1 >= bar) runKind(KIND_TRI);
+        if (n1 >= barTri) runKind(KIND_TRI);
         if (n2 == most || n2 >= 8u) runKind(KIND_ANYHIT);
 #endif
     }

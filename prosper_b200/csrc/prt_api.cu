@@ -304,8 +304,10 @@ struct prt_ctx
         a.instances = tlasInst.p;
         a.instanceCount = tlasInstances;
         a.planeBias = PLANE_BIAS;
+        a.arena = accelArena;
         return a;
     }
+    uint64_t accelArena = 0; // see Accel::arena; refreshed by prt_build_tlas (every BLAS an instance may name exists by then)
 };
 
 extern "C" const char *prt_last_error(void) { return g_lastError.c_str(); }
@@ -1266,6 +1268,17 @@ extern "C" prt_status prt_build_tlas(prt_ctx *c, const prt_tlas_instance *instan
         if (ref == 0) { direct = false; continue; }
         REQUIRE(ref - 1 < c->blas.size() && c->blas[ref - 1].built, "instance references a BLAS that was not built");
         if (c->blas[ref - 1].triCount == 0) direct = false;
+    }
+    {
+        // the arena of the level references a ray carries (Accel::arena): the lowest address of any node / triangle array
+        uint64_t lo = ~0ull, hi = 0;
+        auto span = [&](const void *p, size_t bytes) { if (p) { lo = std::min<uint64_t>(lo, (uint64_t)(uintptr_t)p); hi = std::max<uint64_t>(hi, (uint64_t)(uintptr_t)p + bytes); } };
+        CK(c->tlasNodes.ensure(std::max<uint32_t>(count, 1u)));
+        span(c->tlasNodes.p, c->tlasNodes.cap * sizeof(WideNode));
+        for (const BlasRes &b : c->blas) { span(b.nodes, (size_t)b.nodeCap * sizeof(WideNode)); span(b.tris, (size_t)b.triCap * sizeof(TriRec)); }
+        lo &= ~127ull;
+        REQUIRE(hi - lo < (1ull << 39), "acceleration structures spread over more than 512 GB of address space");
+        c->accelArena = lo;
     }
     std::vector<TlasInput> &in = c->hTlasInput;
     in.clear();

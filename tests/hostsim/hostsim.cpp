@@ -14,16 +14,65 @@
 
 #include <algorithm>
 #include <atomic>
+#include <mutex>
 #include <thread>
 #include <vector>
+
+#include <sys/mman.h>
 
 using namespace prt;
 
 namespace {
 
+// Node and triangle arrays come from ONE address range, because a ray names the arrays of its level by their distance from
+// Accel::arena in 128-byte units (32 bits = 512 GB; the GPU's allocations lie that close together, a process heap does
+// not). A 64 GB reservation without commit, bump-allocated; a freed array gives its pages back, its addresses are not reused.
+struct ArenaRange
+{
+    char *base = nullptr;
+    size_t used = 0;
+    std::mutex lock;
+    static constexpr size_t BYTES = 64ull << 30;
+    static ArenaRange &get()
+    {
+        static ArenaRange a;
+        return a;
+    }
+    void *take(size_t bytes)
+    {
+        std::lock_guard<std::mutex> g(lock);
+        if (!base)
+        {
+            void *p = mmap(nullptr, BYTES, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_NORESERVE, -1, 0);
+            if (p == MAP_FAILED) throw std::bad_alloc();
+            base = (char *)p;
+        }
+        const size_t at = (used + 4095) & ~(size_t)4095;
+        if (at + bytes > BYTES) throw std::bad_alloc();
+        used = at + bytes;
+        return base + at;
+    }
+};
+template <class T> struct ArenaAlloc
+{
+    using value_type = T;
+    ArenaAlloc() = default;
+    template <class U> ArenaAlloc(const ArenaAlloc<U> &) {}
+    T *allocate(size_t n) { return (T *)ArenaRange::get().take(n * sizeof(T)); }
+    void deallocate(T *p, size_t n)
+    {
+        const uintptr_t lo = ((uintptr_t)p + 4095) & ~(uintptr_t)4095, hi = ((uintptr_t)p + n * sizeof(T)) & ~(uintptr_t)4095;
+        if (hi > lo) madvise((void *)lo, hi - lo, MADV_DONTNEED);
+    }
+    template <class U> bool operator==(const ArenaAlloc<U> &) const { return true; }
+    template <class U> bool operator!=(const ArenaAlloc<U> &) const { return false; }
+};
+using NodeVec = std::vector<WideNode, ArenaAlloc<WideNode>>;
+using TriVec = std::vector<TriRec, ArenaAlloc<TriRec>>;
+
 struct HostBvh
 {
-    std::vector<WideNode> nodes;
+    NodeVec nodes;
     std::vector<uint32_t> primOut;
     uint32_t levels = 0;
 };
@@ -143,8 +192,8 @@ HostBvh buildHierarchyHost(std::vector<Box> &boxes, V3 lo, V3 hi, bool tlas, boo
 
 struct HostBlas
 {
-    std::vector<WideNode> nodes;
-    std::vector<TriRec> tris;
+    NodeVec nodes;
+    TriVec tris;
     std::vector<AlphaUv> uvs; // any-hit records, parallel to tris
 };
 
@@ -157,7 +206,7 @@ struct hs_ctx
     std::vector<std::vector<uint8_t>> alphaPlanes; // per texture (k_alpha_plane)
     std::vector<AlphaMat> alphaMats;               // per draw instance (k_alpha_mats)
     std::vector<HostBlas> blas;
-    std::vector<WideNode> tlasNodes;
+    NodeVec tlasNodes;
     std::vector<InstRec> tlasInst;
     SceneView sv{};
     Accel as{};
@@ -250,6 +299,7 @@ static void buildTlasHost(hs_ctx *c)
             c->as.instances = c->tlasInst.data();
             c->as.instanceCount = (uint32_t)c->tlasInst.size();
             c->as.planeBias = PLANE_BIAS;
+            c->as.arena = (uint64_t)(uintptr_t)ArenaRange::get().base;
         }
     }
 }
