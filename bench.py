@@ -48,7 +48,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
     ap.add_argument("--spp", type=int, default=64, help="frames per step (configs[1]: 64)")
-    ap.add_argument("--samples-per-launch", type=int, default=8)
+    ap.add_argument("--samples-per-launch", type=int, default=32,
+                    help="frames in flight per launch of the wavefront kernels (8 / 16 / 32 / 64: 1072 / 1088 / 1096 / 1098 Mrays/s; 208 B of queues per path)")
     ap.add_argument("--tex-size", type=int, default=1024)
     ap.add_argument("--detail", type=float, default=1.0)
     ap.add_argument("--lights", type=int, default=0, help="configs[2]: 1024 point/spot lights")
@@ -81,7 +82,7 @@ def workload_config(args, scene, n_gpus):
         "samples_per_launch": args.samples_per_launch, "blas_builder": args.builder,
         "partition": "by sample (frame indices), scene replicated" if n_gpus > 1 else "single GPU",
         "l2": "inputs larger than L2: path/ray/hit queues of one launch = "
-              f"{args.samples_per_launch * WIDTH * HEIGHT * 232 / 1e6:.0f} MB streamed per bounce (L2 126 MB)",
+              f"{args.samples_per_launch * WIDTH * HEIGHT * 208 / 1e6:.0f} MB streamed per bounce (L2 126 MB)",
     }
 
 
@@ -451,7 +452,7 @@ def run_helmet(args):
                                f"material, {sum(t is not None for t in scene.textures)} of 15 textures present at "
                                f"{max(t.width for t in scene.textures if t is not None)}^2 BC7), sky + default directional light, {w}x{h}, {spp} spp, "
                                f"{BOUNCES} bounces", "config_index": 0,
-                   "l2": "one launch holds all 16 spp: 4.2 M paths x 232 B = 973 MB of queues (L2 126 MB)"},
+                   "l2": "one launch holds all 16 spp: 4.2 M paths x 208 B = 872 MB of queues (L2 126 MB)"},
         "spp_per_s": spp / (sum(dev_ms) / args.steps * 1e-3),
         "e2e": {"value": rays * args.steps / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": w * h * 8,
                 "ms_per_step": e2e_s / args.steps * 1e3, "path": "World.updateBuffers + World.buildTlas + RtReference.record + fp16 read-back"},

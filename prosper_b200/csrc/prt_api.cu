@@ -326,6 +326,7 @@ static void launchTrace(prt_ctx *c, bool count, uint32_t grid, const Accel &as, 
     switch (c->poolRays)
     {
     case 1: launchTraceR<1, SHADOW>(c, count, grid, as, sv, q, b, perm); break;
+    case 3: launchTraceR<3, SHADOW>(c, count, grid, as, sv, q, b, perm); break;
     default: launchTraceR<2, SHADOW>(c, count, grid, as, sv, q, b, perm); break;
     }
 }
@@ -449,9 +450,9 @@ static prt_status createContext(const prt_config *cfg, prt_ctx **out)
         // persistent trace kernels: one resident wave of blocks (SM count x blocks per SM)
         int sms = 0;
         CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->cfg.device));
-        if (const char *e = std::getenv("PRT_POOL_RAYS")) c->poolRays = (uint32_t)std::min(2, std::max(1, std::atoi(e))); // experiment switch
+        if (const char *e = std::getenv("PRT_POOL_RAYS")) c->poolRays = (uint32_t)std::min(3, std::max(1, std::atoi(e))); // experiment switch
         c->refillAt = 8u * c->poolRays;
-        CK(c->poolRays == 1 ? configureTrace<1>(c, sms) : configureTrace<2>(c, sms));
+        CK(c->poolRays == 1 ? configureTrace<1>(c, sms) : c->poolRays == 3 ? configureTrace<3>(c, sms) : configureTrace<2>(c, sms));
         if (const char *e = std::getenv("PRT_POOL_REFILL")) c->refillAt = (uint32_t)std::max(1, std::atoi(e)); // experiment switch
         if (const char *e = std::getenv("PRT_RAY_SORT")) c->raySort = (uint32_t)std::atoi(e); // experiment switch
         int coop = 0, perSmCollapse = 0;
