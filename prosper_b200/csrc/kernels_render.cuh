@@ -360,7 +360,8 @@ __device__ __forceinline__ V4 warpTextureTap(const SceneView &sv, uint32_t textu
 
 // One loop iteration of main.rgen:241-283 minus the traces.
 #ifndef PRT_SHADE_MIN_BLOCKS
-#define PRT_SHADE_MIN_BLOCKS 8 // 64 registers (48 B of spills): 88 instead of 98 ms per step, the kernel waits on gathers
+#define PRT_SHADE_MIN_BLOCKS 8 // 64 registers (48 B of spills): 88 ms per step against 98 (6 blocks) and 96 (10 blocks); the kernel waits on
+                               // its gather chain -- prefetching the path state to L2 at the top changed nothing (88.7 vs 88.4)
 #endif
 __global__ void __launch_bounds__(RENDER_THREADS, PRT_SHADE_MIN_BLOCKS)
     k_shade(SceneView sv, prt_reference_pc pc, PathBuffers pb, int q, uint32_t bounce, GlobalCounters *gc, int countShaded)

@@ -1000,6 +1000,9 @@ static prt_status refreshAlphaMats(prt_ctx *c)
 // Shared back half of the BLAS and TLAS builds: boxes + bounds are in bBoxes/bBounds; produces the
 // wide nodes in bNodes and the node-order primitive permutation in bPrimOut.
 // bScalars layout: [0] nodeCount, [1] primCount, [8 .. 8 + MAX_LEVELS] per-level queue counts.
+// Collapse level budget. It cannot run out: a binary tree from the SAH builder is at most SAH_MAX_LEVELS = 96 deep, one from the
+// Karras builder at most 63 key bits + 32 position bits, and the wide tree is never deeper than the binary one. (PLOC gives no
+// such bound; prt_build_blas checks every build's primitive count after the collapse.)
 static constexpr uint32_t kMaxLevels = 128;
 #ifndef PRT_PLOC_RADIUS
 #define PRT_PLOC_RADIUS 16
