@@ -413,6 +413,38 @@ def test_animated_district_tlas_rebuild_per_frame(small_district):
     world.close()
 
 
+def test_rebuilds_reuse_buffers_and_replay_graphs(small_district):
+    """Round-2 builder paths: a BLAS rebuild reuses the model's buffers, a TLAS rebuild with the instance count of the previous
+    frame replays a captured CUDA graph, the caller's records go up unchanged when every instance is active and are compacted
+    on the host otherwise; a change of count or path re-captures. Hit records must not depend on any of it."""
+    import copy
+    scene = copy.deepcopy(small_district)
+    w, h = 160, 90
+    pc = sd.reference_pc(frame_index=1)
+    world = _world(scene, w, h)
+    first = world.trace_primary(pc, w, h)
+    world.buildAccelerationStructures(rebuild_blas=True)  # every BLAS again, into the same buffers, then the TLAS
+    assert np.array_equal(world.trace_primary(pc, w, h), first)
+    for _ in range(3):  # eager, capture, replay
+        world.buildTlas(scene.tlas_instances)
+        assert np.array_equal(world.trace_primary(pc, w, h), first)
+    thinned = scene.tlas_instances.copy()
+    thinned["blasReference"][::3] = 0  # inactive instances: the host compacts, the count changes, the graph is re-captured
+    fresh_scene = copy.deepcopy(scene)
+    fresh_scene.tlas_instances = thinned
+    fresh = _world(fresh_scene, w, h)
+    want = fresh.trace_primary(pc, w, h)
+    fresh.close()
+    for _ in range(3):
+        world.buildTlas(thinned)
+        assert np.array_equal(world.trace_primary(pc, w, h), want)
+    assert (want["drawInstanceIndex"] != first["drawInstanceIndex"]).any()
+    world.buildTlas(scene.tlas_instances)
+    assert np.array_equal(world.trace_primary(pc, w, h), first)
+    assert world.counters()["stackOverflows"] == 0
+    world.close()
+
+
 def test_degenerate_inputs_on_gpu(small_stress):
     """Edge cases through the C ABI: single-triangle model, 40 coincident triangles (Morton ties -> lowest primitive
     wins), inactive instances (blasReference 0, World.cpp:898-905), zero visibility mask, and an empty TLAS."""
