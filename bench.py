@@ -382,7 +382,8 @@ def run_district(args):
         "e2e": {"value": rays / wall / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": w * h * 8,
                 "ms_per_step": wall / args.steps * 1e3,
                 "path": "host animation (numpy) + World.updateBuffers + World.buildTlas + RtReference.record + fp16 read-back"},
-        "tlas": {"ms_per_rebuild": float(np.median(tlas_ms)), "instances": int(len(scene.tlas_instances))},
+        "tlas": {"ms_per_rebuild": float(np.median(tlas_ms)), "instances": int(len(scene.tlas_instances)),
+                 "graph_replays": int(tl["tlasGraphReplays"]), "graph_captures": int(tl["tlasGraphCaptures"])},
         "blas": {"build_wall_ms": blas_wall_ms, "nodes": stats["blasNodesTotal"], "triangles": stats["blasTrianglesTotal"]},
         "roofline": roofline, "gpu_launches": int(c["kernelLaunches"]), "clocks": clk,
     })
@@ -777,6 +778,7 @@ def run_ours(args):
             sw.synchronize()
         sc, stt = sw.counters(), sw.timings()
         tlas.update({"ms_per_rebuild": float(np.median(ms[2:])), "wall_ms_per_rebuild_from_host_records": float(np.median(wall[2:])),
+                     "graph_replays": int(stt["tlasGraphReplays"]), "graph_captures": int(stt["tlasGraphCaptures"]),
                      "instances": int(len(st_scene.tlas_instances)), "launches": int(stt["lastTlasLaunches"]),
                      "scene": f"{st_scene.name}: {st_scene.instanced_triangle_count} instanced triangles, "
                               f"{st_scene.triangle_count} unique", "bytes_per_instance_uploaded": 64,

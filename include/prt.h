@@ -242,6 +242,8 @@ typedef struct prt_timings {
     float lastTraceShadowMs;
     uint32_t lastTraceShadowLaunches;
     uint32_t ringWraps;       /* laps of the pinned upload ring so far (gfx::RingBuffer wraps to 0, RingBuffer.cpp:56-133) */
+    uint32_t tlasGraphReplays; /* prt_build_tlas calls so far that replayed the captured CUDA graph */
+    uint32_t tlasGraphCaptures; /* ... that captured it (first repeat of an instance count, or a scratch buffer moved) */
 } prt_timings;
 prt_status prt_get_timings(prt_ctx *ctx, prt_timings *out);
 

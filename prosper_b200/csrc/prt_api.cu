@@ -245,7 +245,7 @@ struct prt_ctx
     bool tlasGraphs = true, tlasGraphDirect = false, tlasEagerDirect = false;
     bool blasTableDirty = true; // dBlasTable lags behind `blas`
     cudaGraphExec_t tlasGraphExec = nullptr;
-    uint32_t tlasGraphN = 0, tlasGraphLaunches = 0, tlasEagerN = 0;
+    uint32_t tlasGraphN = 0, tlasGraphLaunches = 0, tlasEagerN = 0, tlasGraphReplays = 0, tlasGraphCaptures = 0;
     unsigned long long tlasGraphGeneration = 0, tlasEagerGeneration = 0;
     uint32_t sahBlocks = 0;     // grid of k_sah_all_levels (co-resident by construction)
     uint32_t coopBlocks = 0;    // co-resident blocks of k_collapse_all_levels_grid (0: cooperative launch unsupported)
@@ -1331,6 +1331,7 @@ extern "C" prt_status prt_build_tlas(prt_ctx *c, const prt_tlas_instance *instan
         {
             CK(cudaGraphLaunch(c->tlasGraphExec, st));
             launches = c->tlasGraphLaunches;
+            c->tlasGraphReplays++;
         }
         else if (c->tlasGraphs && c->tlasEagerN == n && c->tlasEagerDirect == direct && c->tlasEagerGeneration == g_allocGeneration)
         {
@@ -1359,6 +1360,7 @@ extern "C" prt_status prt_build_tlas(prt_ctx *c, const prt_tlas_instance *instan
                 c->tlasGraphDirect = direct;
                 c->tlasGraphGeneration = g_allocGeneration;
                 c->tlasGraphLaunches = launches;
+                c->tlasGraphCaptures++;
                 CK(cudaGraphLaunch(c->tlasGraphExec, st));
             }
         }
@@ -1959,6 +1961,8 @@ extern "C" prt_status prt_get_timings(prt_ctx *c, prt_timings *out)
     out->lastRecordLaunches = c->lastRecordLaunches;
     out->lastTlasLaunches = c->lastTlasLaunches;
     out->ringWraps = c->ring.wraps;
+    out->tlasGraphReplays = c->tlasGraphReplays;
+    out->tlasGraphCaptures = c->tlasGraphCaptures;
     return PRT_OK;
 }
 

@@ -51,7 +51,7 @@ class PrtTimings(C.Structure):
                 ("lastTraceClosestMs", C.c_float), ("lastTraceClosestLaunches", C.c_uint32),
                 ("lastRecordLaunches", C.c_uint32), ("lastTlasLaunches", C.c_uint32), ("lastShadeMs", C.c_float),
                 ("lastShadeLaunches", C.c_uint32), ("lastTraceShadowMs", C.c_float), ("lastTraceShadowLaunches", C.c_uint32),
-                ("ringWraps", C.c_uint32)]
+                ("ringWraps", C.c_uint32), ("tlasGraphReplays", C.c_uint32), ("tlasGraphCaptures", C.c_uint32)]
 
 
 class PrtBvhStats(C.Structure):

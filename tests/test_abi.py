@@ -35,7 +35,7 @@ def test_struct_sizes_match_reference_layouts():
     assert sd.CAMERA_UNIFORMS.itemsize == 532 and sd.DRAW_INSTANCE.itemsize == 12
     assert sd.MODEL_INSTANCE_TRANSFORMS.itemsize == 96 and sd.REFERENCE_PC.itemsize == 32
     assert sd.TLAS_INSTANCE.itemsize == 64 and sd.HIT.itemsize == 16
-    assert C.sizeof(rt.PrtConfig) == 24 and C.sizeof(rt.PrtCounters) == 120 and C.sizeof(rt.PrtTimings) == 48
+    assert C.sizeof(rt.PrtConfig) == 24 and C.sizeof(rt.PrtCounters) == 120 and C.sizeof(rt.PrtTimings) == 56
 
 
 def test_header_compiles_as_c_and_cpp(tmp_path):
