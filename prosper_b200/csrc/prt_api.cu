@@ -5,6 +5,7 @@
 // fallback: every entry point fails with PRT_ERR_NO_DEVICE / PRT_ERR_CUDA when the GPU is missing.
 #include "../../include/prt.h"
 
+#include <cuda.h> // types of the virtual-memory-management calls only; the entry points come from cudaGetDriverEntryPoint
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -135,6 +136,93 @@ struct TexRes
     uint32_t width = 0, height = 0, format = 0, mipLevels = 0;
 };
 
+// Every node / triangle array the trace kernels walk is allocated inside ONE reserved address range, so that a ray can name
+// the arrays of its level by 32-bit distances from Accel::arena (core_trace.h). Plain cudaMalloc does not give that: under
+// torch + NCCL two allocations of one process were seen more than 512 GB apart. The range is a 256 GB reservation
+// (cuMemAddressReserve: address space only), physical memory is created and mapped block by block (cuMemCreate / cuMemMap);
+// a freed block returns its memory, its addresses are not handed out again.
+struct AccelHeap
+{
+    static constexpr size_t RESERVE = 256ull << 30;
+    CUdeviceptr base = 0;
+    size_t used = 0, gran = 0;
+    int device = 0;
+    struct Block { CUdeviceptr p; size_t bytes; CUmemGenericAllocationHandle h; };
+    std::vector<Block> blocks;
+    CUresult (*memAddressReserve)(CUdeviceptr *, size_t, size_t, CUdeviceptr, unsigned long long) = nullptr;
+    CUresult (*memAddressFree)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*memCreate)(CUmemGenericAllocationHandle *, size_t, const CUmemAllocationProp *, unsigned long long) = nullptr;
+    CUresult (*memRelease)(CUmemGenericAllocationHandle) = nullptr;
+    CUresult (*memMap)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
+    CUresult (*memUnmap)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*memSetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc *, size_t) = nullptr;
+    CUresult (*memGetAllocationGranularity)(size_t *, const CUmemAllocationProp *, CUmemAllocationGranularity_flags) = nullptr;
+
+    CUmemAllocationProp prop() const
+    {
+        CUmemAllocationProp p{};
+        p.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+        p.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        p.location.id = device;
+        return p;
+    }
+    prt_status init(int dev)
+    {
+        device = dev;
+        struct { const char *name; void **fn; } wanted[] = {
+            {"cuMemAddressReserve", (void **)&memAddressReserve}, {"cuMemAddressFree", (void **)&memAddressFree},
+            {"cuMemCreate", (void **)&memCreate}, {"cuMemRelease", (void **)&memRelease}, {"cuMemMap", (void **)&memMap},
+            {"cuMemUnmap", (void **)&memUnmap}, {"cuMemSetAccess", (void **)&memSetAccess},
+            {"cuMemGetAllocationGranularity", (void **)&memGetAllocationGranularity}};
+        for (auto &w : wanted)
+        {
+            cudaDriverEntryPointQueryResult found;
+            CK(cudaGetDriverEntryPoint(w.name, w.fn, cudaEnableDefault, &found));
+            if (found != cudaDriverEntryPointSuccess || !*w.fn) return fail(PRT_ERR_CUDA, std::string("driver entry point missing: ") + w.name);
+        }
+        const CUmemAllocationProp p = prop();
+        if (memGetAllocationGranularity(&gran, &p, CU_MEM_ALLOC_GRANULARITY_MINIMUM) != CUDA_SUCCESS || gran == 0)
+            return fail(PRT_ERR_CUDA, "cuMemGetAllocationGranularity failed");
+        if (memAddressReserve(&base, RESERVE, gran, 0, 0) != CUDA_SUCCESS) return fail(PRT_ERR_CUDA, "cuMemAddressReserve(256 GB) failed");
+        return PRT_OK;
+    }
+    prt_status alloc(void **out, size_t bytes)
+    {
+        const size_t size = (std::max<size_t>(bytes, 1) + gran - 1) / gran * gran;
+        if (used + size > RESERVE) return fail(PRT_ERR_CUDA, "acceleration-structure address range (256 GB) exhausted");
+        Block b{base + used, size, 0};
+        const CUmemAllocationProp p = prop();
+        if (memCreate(&b.h, size, &p, 0) != CUDA_SUCCESS) return fail(PRT_ERR_CUDA, "cuMemCreate failed (out of device memory?)");
+        if (memMap(b.p, size, 0, b.h, 0) != CUDA_SUCCESS) { memRelease(b.h); return fail(PRT_ERR_CUDA, "cuMemMap failed"); }
+        CUmemAccessDesc access{};
+        access.location = p.location;
+        access.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        if (memSetAccess(b.p, size, &access, 1) != CUDA_SUCCESS) { memUnmap(b.p, size); memRelease(b.h); return fail(PRT_ERR_CUDA, "cuMemSetAccess failed"); }
+        used += size;
+        blocks.push_back(b);
+        *out = (void *)(uintptr_t)b.p;
+        return PRT_OK;
+    }
+    void release(void *ptr) // the stream must be idle
+    {
+        for (size_t i = 0; i < blocks.size(); ++i)
+            if (blocks[i].p == (CUdeviceptr)(uintptr_t)ptr)
+            {
+                memUnmap(blocks[i].p, blocks[i].bytes);
+                memRelease(blocks[i].h);
+                blocks.erase(blocks.begin() + (long)i);
+                return;
+            }
+    }
+    void destroy()
+    {
+        for (const Block &b : blocks) { memUnmap(b.p, b.bytes); memRelease(b.h); }
+        blocks.clear();
+        if (base) memAddressFree(base, RESERVE);
+        base = 0;
+    }
+};
+
 struct BlasRes
 {
     WideNode *nodes = nullptr;
@@ -181,7 +269,9 @@ struct prt_ctx
     bool haveCamera = false, haveLights = false;
 
     // TLAS
-    DBuf<WideNode> tlasNodes;
+    AccelHeap heap;
+    WideNode *tlasNodesP = nullptr; // in `heap`, like every BLAS's nodes and triangles
+    uint32_t tlasNodesCap = 0;
     DBuf<InstRec> tlasInst;
     uint32_t tlasInstances = 0;
     std::vector<TlasInput> hTlasInput;
@@ -300,7 +390,7 @@ struct prt_ctx
     Accel accel() const
     {
         Accel a{};
-        a.tlasNodes = tlasInstances ? tlasNodes.p : nullptr;
+        a.tlasNodes = tlasInstances ? tlasNodesP : nullptr;
         a.instances = tlasInst.p;
         a.instanceCount = tlasInstances;
         a.planeBias = PLANE_BIAS;
@@ -420,6 +510,7 @@ static prt_status createContext(const prt_config *cfg, prt_ctx **out)
     if (c->cfg.samplesPerLaunch == 0) c->cfg.samplesPerLaunch = 1;
     *out = c;
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CKS(c->heap.init(cfg->device));
     {
         size_t ringBytes = 32u << 20;
         if (const char *e = std::getenv("PRT_RING_BYTES")) ringBytes = std::max<size_t>(4096, (size_t)std::atoll(e)); // test switch: forces wraps
@@ -491,10 +582,11 @@ extern "C" void prt_destroy(prt_ctx *c)
     }
     for (BlasRes &b : c->blas)
     {
-        if (b.nodes) cudaFree(b.nodes);
-        if (b.tris) cudaFree(b.tris);
+        if (b.nodes) c->heap.release(b.nodes);
+        if (b.tris) c->heap.release(b.tris);
         if (b.uvs) cudaFree(b.uvs);
     }
+    c->heap.destroy(); // the TLAS nodes with it
     PathBuffers &pb = c->pb;
     void *ptrs[] = {pb.rng,      pb.throughput, pb.color,   pb.rayO[0], pb.rayO[1], pb.rayD[0],  pb.rayD[1], pb.rayId[0],
                     pb.rayId[1], pb.hits,       pb.shadowO, pb.shadowD, pb.shadowId, pb.shadowC, pb.counts,  c->dCounters, pb.tie};
@@ -502,7 +594,7 @@ extern "C" void prt_destroy(prt_ctx *c)
         if (p) cudaFree(p);
     c->geomTable.release(); c->dMeta.release(); c->dMat.release(); c->dSlots.release(); c->dSky.release();
     c->dDraw.release(); c->dXf.release(); c->dDir.release(); c->dPoints.release(); c->dSpots.release(); c->dCam.release();
-    c->tlasNodes.release(); c->tlasInst.release();
+    c->tlasInst.release();
     c->bTris.release(); c->bUvs.release(); c->dAlphaMats.release(); c->bInst.release(); c->bTlasIn.release(); c->bTlasRaw.release(); c->dBlasTable.release(); c->bBoxes.release(); c->bNodeBox.release();
     for (int i = 0; i < 2; ++i) { c->bKeys[i].release(); c->bOrder[i].release(); c->bQueue[i].release(); }
     for (int i = 0; i < 2; ++i) { c->bPlocRef[i].release(); c->bPlocBox[i].release(); }
@@ -1207,20 +1299,20 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
     b.triCount = n;
     if (b.nodeCap < b.nodeCount) // first build of the model, or it grew: the stream is idle after the read-back above
     {
-        if (b.nodes) CK(cudaFree(b.nodes));
+        if (b.nodes) c->heap.release(b.nodes);
         b.nodes = nullptr;
         b.nodeCap = 0;
         const uint32_t cap = b.nodeCount + b.nodeCount / 8u;
-        CK(cudaMalloc((void **)&b.nodes, (size_t)cap * sizeof(WideNode)));
+        CKS(c->heap.alloc((void **)&b.nodes, (size_t)cap * sizeof(WideNode)));
         b.nodeCap = cap;
     }
     if (b.triCap < n)
     {
-        if (b.tris) CK(cudaFree(b.tris));
+        if (b.tris) c->heap.release(b.tris);
         if (b.uvs) CK(cudaFree(b.uvs));
         b.tris = nullptr; b.uvs = nullptr;
         b.triCap = 0;
-        CK(cudaMalloc((void **)&b.tris, (size_t)n * sizeof(TriRec)));
+        CKS(c->heap.alloc((void **)&b.tris, (size_t)n * sizeof(TriRec)));
         CK(cudaMalloc((void **)&b.uvs, (size_t)n * sizeof(AlphaUv)));
         b.triCap = n;
     }
@@ -1243,13 +1335,12 @@ static prt_status enqueueTlasBuild(prt_ctx *c, uint32_t n, bool direct, uint32_t
     cudaStream_t st = c->stream;
     CK(c->bInst.ensure(n));
     CK(c->bBoxes.ensure(n));
-    CK(c->tlasNodes.ensure(n));
     CK(c->tlasInst.ensure(n));
     k_init_bounds<<<1, 32, 0, st>>>(c->bBounds.p, c->bScalars.p, 8);
     if (direct) k_tlas_instances_direct<<<blocksFor(n, 128), 128, 0, st>>>(c->bTlasRaw.p, c->dBlasTable.p, n, c->bInst.p, c->bBoxes.p, c->bBounds.p);
     else k_tlas_instances<<<blocksFor(n, 128), 128, 0, st>>>(c->bTlasIn.p, n, c->bInst.p, c->bBoxes.p, c->bBounds.p);
     *launches += 2;
-    CKS(buildHierarchy(c, n, true, c->tlasNodes.p, launches)); // wide nodes <= n: the collapse writes them in place
+    CKS(buildHierarchy(c, n, true, c->tlasNodesP, launches)); // wide nodes <= n: the collapse writes them in place
     k_emit_instances<<<blocksFor(n, 128), 128, 0, st>>>(c->bPrimOut.p, n, c->bInst.p, c->tlasInst.p);
     *launches += 1;
     CK(cudaGetLastError());
@@ -1277,8 +1368,18 @@ extern "C" prt_status prt_build_tlas(prt_ctx *c, const prt_tlas_instance *instan
         // the arena of the level references a ray carries (Accel::arena): the lowest address of any node / triangle array
         uint64_t lo = ~0ull, hi = 0;
         auto span = [&](const void *p, size_t bytes) { if (p) { lo = std::min<uint64_t>(lo, (uint64_t)(uintptr_t)p); hi = std::max<uint64_t>(hi, (uint64_t)(uintptr_t)p + bytes); } };
-        CK(c->tlasNodes.ensure(std::max<uint32_t>(count, 1u)));
-        span(c->tlasNodes.p, c->tlasNodes.cap * sizeof(WideNode));
+        if (c->tlasNodesCap < std::max<uint32_t>(count, 1u)) // grows rarely: the instance count of a scene is stable
+        {
+            CK(cudaStreamSynchronize(st));
+            if (c->tlasNodesP) c->heap.release(c->tlasNodesP);
+            c->tlasNodesP = nullptr;
+            c->tlasNodesCap = 0;
+            const uint32_t cap = std::max<uint32_t>(count, 1u) + count / 8u;
+            CKS(c->heap.alloc((void **)&c->tlasNodesP, (size_t)cap * sizeof(WideNode)));
+            c->tlasNodesCap = cap;
+            g_allocGeneration++; // a captured TLAS graph holds the old address
+        }
+        span(c->tlasNodesP, (size_t)c->tlasNodesCap * sizeof(WideNode));
         for (const BlasRes &b : c->blas) { span(b.nodes, (size_t)b.nodeCap * sizeof(WideNode)); span(b.tris, (size_t)b.triCap * sizeof(TriRec)); }
         lo &= ~127ull;
         REQUIRE(hi - lo < (1ull << 39), "acceleration structures spread over more than 512 GB of address space");
@@ -2057,7 +2158,7 @@ extern "C" prt_status prt_debug_read_tlas(prt_ctx *c, void *nodesOut, uint64_t n
     if (nodesOut && n)
     {
         REQUIRE(nodesBytes >= (uint64_t)n * WIDE_NODE_BYTES, "node buffer too small (instanceCount nodes)");
-        CK(cudaMemcpy2DAsync(nodesOut, WIDE_NODE_BYTES, c->tlasNodes.p, sizeof(WideNode), WIDE_NODE_BYTES, n, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaMemcpy2DAsync(nodesOut, WIDE_NODE_BYTES, c->tlasNodesP, sizeof(WideNode), WIDE_NODE_BYTES, n, cudaMemcpyDeviceToHost, c->stream));
     }
     if (instOut && n)
     {
