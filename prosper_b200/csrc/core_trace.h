@@ -209,13 +209,46 @@ struct NodeWords
 };
 static_assert(sizeof(NodeWords) == WIDE_NODE_BYTES, "NodeWords mirrors the payload of WideNode");
 
+// L1 policy of the node and triangle gathers (experiment switches): 0 = default, 1 = L1::no_allocate, 2 = L1::evict_first,
+// 3 = L1::evict_last. The idea: upper-level nodes are reused by every ray of an SM, a triangle record almost never.
+#ifndef PRT_NODE_L1
+#define PRT_NODE_L1 0
+#endif
+#ifndef PRT_TRI_L1
+#define PRT_TRI_L1 0
+#endif
 #if defined(__CUDA_ARCH__)
+#define PRT_LDG_HINT_0 ""
+#define PRT_LDG_HINT_1 ".L1::no_allocate"
+#define PRT_LDG_HINT_2 ".L1::evict_first"
+#define PRT_LDG_HINT_3 ".L1::evict_last"
+#define PRT_LDG_HINT_(h) PRT_LDG_HINT_##h
+#define PRT_LDG_HINT(h) PRT_LDG_HINT_(h)
 // One 256-bit read-only load (LDG.E.256, sm_100): `p` must be 32-byte aligned.
+template <int HINT>
 __device__ __forceinline__ void ldg256(const void *p, uint4 &a, uint4 &b)
 {
-    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
-        : "l"(p));
+#define PRT_LDG256(h)                                                                                                       \
+    asm("ld.global.nc" h ".v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"                                                        \
+        : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)                            \
+        : "l"(p))
+    if (HINT == 1) PRT_LDG256(PRT_LDG_HINT_1);
+    else if (HINT == 2) PRT_LDG256(PRT_LDG_HINT_2);
+    else if (HINT == 3) PRT_LDG256(PRT_LDG_HINT_3);
+    else PRT_LDG256(PRT_LDG_HINT_0);
+#undef PRT_LDG256
+}
+template <int HINT>
+__device__ __forceinline__ uint4 ldg128(const void *p)
+{
+    uint4 a;
+#define PRT_LDG128(h) asm("ld.global.nc" h ".v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w) : "l"(p))
+    if (HINT == 1) PRT_LDG128(PRT_LDG_HINT_1);
+    else if (HINT == 2) PRT_LDG128(PRT_LDG_HINT_2);
+    else if (HINT == 3) PRT_LDG128(PRT_LDG_HINT_3);
+    else PRT_LDG128(PRT_LDG_HINT_0);
+#undef PRT_LDG128
+    return a;
 }
 #endif
 
@@ -223,9 +256,9 @@ HD void loadNodeWords(const WideNode *p, NodeWords &n)
 {
 #if defined(__CUDA_ARCH__)
     const char *s = reinterpret_cast<const char *>(p);
-    ldg256(s, n.w0, n.w1);
-    ldg256(s + 32, n.w2, n.w3);
-    n.w4 = __ldg(reinterpret_cast<const uint4 *>(s + 64));
+    ldg256<PRT_NODE_L1>(s, n.w0, n.w1);
+    ldg256<PRT_NODE_L1>(s + 32, n.w2, n.w3);
+    n.w4 = ldg128<PRT_NODE_L1>(s + 64);
 #else
     memcpy(&n, p, sizeof(NodeWords));
 #endif
@@ -529,8 +562,8 @@ HD int traceTriItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceCo
         const uint32_t triIndex = g.z + (uint32_t)pbit;
 #if defined(__CUDA_ARCH__)
         uint4 a, b;
-        ldg256(tris + triIndex, a, b);
-        const uint4 e = __ldg(reinterpret_cast<const uint4 *>(tris + triIndex) + 2);
+        ldg256<PRT_TRI_L1>(tris + triIndex, a, b);
+        const uint4 e = ldg128<PRT_TRI_L1>(reinterpret_cast<const uint4 *>(tris + triIndex) + 2);
 #else
         uint4 a, b, e;
         memcpy(&a, &tris[triIndex], 16); memcpy(&b, (const char *)&tris[triIndex] + 16, 16); memcpy(&e, (const char *)&tris[triIndex] + 32, 16);

@@ -126,6 +126,9 @@ __global__ void __launch_bounds__(RENDER_THREADS)
 #ifndef PRT_BAR_TRI_Q
 #define PRT_BAR_TRI_Q 2
 #endif
+#ifndef PRT_BAR_ANYHIT
+#define PRT_BAR_ANYHIT 8 // lanes (of 32) holding a parked any-hit candidate that make the any-hit test run although another kind is wanted more
+#endif
 #ifndef PRT_RAY_SORT_CELL_BITS
 #define PRT_RAY_SORT_CELL_BITS 5
 #endif
@@ -323,7 +326,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, PRT_TRACE_MIN_BLOCKS)
         if (n0 >= barNode) runKind(KIND_NODE);
         if (n3 >= bar) runKind(KIND_INSTANCE);
         if (n1 >= barTri) runKind(KIND_TRI);
-        if (n2 == most || n2 >= 8u) runKind(KIND_ANYHIT);
+        if (n2 == most || n2 >= (uint32_t)PRT_BAR_ANYHIT) runKind(KIND_ANYHIT);
 #endif
     }
     if (COUNT) flushTraceCounters(gc, tc, SHADOW);
