@@ -192,7 +192,8 @@ prt_status prt_probe_texture(prt_ctx *ctx, uint32_t textureSampler, const float 
 
 /* Test hooks: read the built structures back (80-byte wide nodes, 48-byte triangle records, 96-byte
  * instance records; layouts in prosper_b200/csrc/core_bvh.h) so the tests can validate the GPU
- * builder's output structurally on the host. Pass NULL buffers to query the counts. */
+ * builder's output structurally on the host. Pass NULL buffers to query the counts. triCount counts triangle
+ * RECORDS: a non-opaque triangle appears once per builder reference, with identical contents. */
 prt_status prt_debug_read_blas(prt_ctx *ctx, uint32_t modelIndex, void *nodesOut, uint64_t nodesBytes,
                                void *trisOut, uint64_t trisBytes, uint32_t *nodeCount, uint32_t *triCount);
 prt_status prt_debug_read_tlas(prt_ctx *ctx, void *nodesOut, uint64_t nodesBytes, void *instOut,
@@ -254,6 +255,7 @@ typedef struct prt_bvh_stats {
     uint64_t blasTrianglesTotal;
     uint32_t blasCount;
     uint32_t tlasInstances;
+    uint64_t blasReferencesTotal; /* triangle records in the BLASes: a non-opaque triangle is referenced from several leaves */
 } prt_bvh_stats;
 prt_status prt_get_bvh_stats(prt_ctx *ctx, prt_bvh_stats *out);
 

@@ -16,8 +16,14 @@
 #define PRT_TRACE_PREFETCH 0 // measured twice (r01: -3 %, r02 pooled kernel: -14 %): prefetch.global.L1 of the next item costs more L1 than it hides
 #endif
 
+// Reference splitting of non-opaque triangles in the BLAS builder (core_build.h): rounds of midpoint subdivision, 0 = off.
+#ifndef PRT_BLAS_ALPHA_SPLIT
+#define PRT_BLAS_ALPHA_SPLIT 0
+#endif
+
 namespace prt {
 
+constexpr int PEND_ROWS = PRT_BLAS_ALPHA_SPLIT ? 2 : 1; // 128-bit words of RayCtx::pend per ray
 constexpr uint32_t MISS_INDEX = 0xFFFFFFFFu; // main.rgen:47
 constexpr int TRACE_STACK = 64;
 
@@ -369,7 +375,8 @@ struct RayCtx
     uint4 *rows;      // row i at rows[i * stride]
     uint32_t stride;
     uint2 *stack;     // TRACE_STACK entries
-    uint4 *pend;      // parked any-hit candidate: t, u, v bits and the triangle index
+    uint4 *pend;      // [0] parked any-hit candidate: t, u, v bits and the triangle index; [1] (PRT_BLAS_ALPHA_SPLIT builds only) the
+                      // triangle this ray's any-hit test rejected last: instance position, geometry, primitive, valid (traceTriItem)
     HD uint4 &row(int i) const { return rows[(uint32_t)i * stride]; }
     HD uint2 &entry(uint32_t i) const { return stack[i]; }
 };
@@ -423,6 +430,9 @@ HD int kindOf(const uint4 &g, uint32_t blasP1)
 HD int traceBegin(const RayCtx &c, const Accel &as, const TraceIO &io, uint32_t qslot, TraceCounters *cnt)
 {
     if (as.tlasNodes == nullptr) return KIND_IDLE;
+#if PRT_BLAS_ALPHA_SPLIT
+    c.pend[1] = make_uint4(0u, 0u, 0u, 0u); // the slot's previous ray may have left a rejected triangle behind
+#endif
     const float4 wo = io.rayO[qslot], wd = io.rayD[qslot];
     const V3 o = {wo.x, wo.y, wo.z}, d = {wd.x, wd.y, wd.z};
     if (as.instanceCount == 1u)
@@ -593,8 +603,15 @@ HD int traceTriItem(const RayCtx &c, const Accel &as, const TraceIO &io, TraceCo
         {
             if (!(b.w >> 31))
             {
+#if PRT_BLAS_ALPHA_SPLIT
+                // non-opaque geometry. The any-hit decision is a pure function of (ray, triangle) -- one random number per
+                // ray, scene.rahit:35 -- so the triangle this ray rejected last is skipped when it comes up again through
+                // another builder reference (core_build.h: with reference splitting a non-opaque triangle sits in several leaves).
+                const uint4 rej = c.pend[1];
+                if (rej.w != 0u && rej.x == m.w && rej.y == geom && rej.z == a.w) continue;
+#endif
                 // non-opaque geometry: park the candidate, its any-hit test is the ray's next item
-                *c.pend = make_uint4(f2u(t), f2u(u), f2u(v), triIndex);
+                c.pend[0] = make_uint4(f2u(t), f2u(u), f2u(v), triIndex);
                 g.z |= TRACE_PENDING;
                 break;
             }
@@ -615,7 +632,7 @@ HD int traceAnyHitItem(const RayCtx &c, const Accel &as, const SceneView &sv, co
     g.y &= ~TRACE_STATE;
     const uint4 m = c.row(ROW_M);
     g.z &= ~TRACE_PENDING;
-    const uint4 pd = *c.pend;
+    const uint4 pd = c.pend[0];
     const float t = u2f(pd.x), u = u2f(pd.y), v = u2f(pd.z);
     const uint32_t tri = pd.w;
     const InstRec &inst = as.instances[m.w];
@@ -634,6 +651,9 @@ HD int traceAnyHitItem(const RayCtx &c, const Accel &as, const SceneView &sv, co
         if (fast) accept = anyHitAcceptFast(am, loadAlphaUv(uvs + tri), u, v, seed);
     }
     if (!fast) accept = anyHitAccept(sv, drawInstanceIndex, prim, u, v, seed);
+#if PRT_BLAS_ALPHA_SPLIT
+    if (!accept) c.pend[1] = make_uint4(m.w, geom, prim, 1u);
+#endif
     if (accept && commitHit<SHADOW>(c, as, io, c.row(ROW_O), m.z, m.w, geom, prim, t, u, v)) return KIND_IDLE;
     return traceFinishItem(c, as, io, g, sp, blasP1, stackTop(c, sp));
 }
@@ -681,8 +701,8 @@ HDNI bool traceRay(const Accel &as, const SceneView &sv, V3 o, V3 d, float tMin,
 {
     uint4 rows[POOL_ROWS];
     uint2 stack[TRACE_STACK];
-    uint4 pend;
-    const RayCtx c = {rows, 1u, stack, &pend};
+    uint4 pend[PEND_ROWS];
+    const RayCtx c = {rows, 1u, stack, pend};
     const float4 wo = make_float4(o.x, o.y, o.z, tMin), wd = make_float4(d.x, d.y, d.z, tMax);
     const uint2 id = make_uint2(0u, seed);
     uint4 hit = make_uint4(MISS_INDEX, MISS_INDEX, 0u, 0u);

@@ -69,13 +69,21 @@ __global__ void k_blas_gather(SceneView sv, uint32_t meshIndex, uint32_t primCou
         return;
     }
     TriRec t;
-    V3 lo, hi;
-    gatherTriangle(sv, meshIndex, p, geometryIndex, opaque, t, lo, hi);
-    tris[outOffset + p] = t;
+    V3 lo, hi, corner[3];
+    gatherTriangle(sv, meshIndex, p, geometryIndex, opaque, t, lo, hi, corner);
     AlphaUv uv = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, {0u, 0u}};
     if (!opaque) gatherTriangleUvs(sv, meshIndex, p, uv);
-    uvs[outOffset + p] = uv;
-    boxes[outOffset + p] = makeBox(lo, hi);
+    // a non-opaque triangle enters the builder as several references with the same record (core_build.h)
+    const uint32_t refs = blasRefsPerTriangle(opaque);
+    for (uint32_t k = 0; k < refs; ++k)
+    {
+        const uint32_t slot = outOffset + p * refs + k;
+        V3 rl = lo, rh = hi;
+        if (refs > 1u) triangleRefBox(corner[0], corner[1], corner[2], k, rl, rh);
+        tris[slot] = t;
+        uvs[slot] = uv;
+        boxes[slot] = makeBox(rl, rh);
+    }
     atomicBounds(bounds, lo, hi, true);
 }
 

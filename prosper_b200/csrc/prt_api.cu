@@ -228,7 +228,8 @@ struct BlasRes
     WideNode *nodes = nullptr;
     TriRec *tris = nullptr;
     AlphaUv *uvs = nullptr; // any-hit records, parallel to tris
-    uint32_t nodeCount = 0, triCount = 0;
+    uint32_t nodeCount = 0, triCount = 0; // triCount = triangle RECORDS (builder references, core_build.h)
+    uint32_t primCount = 0;               // triangles of the model
     uint32_t nodeCap = 0, triCap = 0; // a rebuild reuses the buffers while they are large enough
     bool built = false;
 };
@@ -1248,18 +1249,22 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
     cudaStream_t st = c->stream;
     BlasRes &b = c->blas[modelIndex];
     b.built = false; // until this build has succeeded; the buffers of an earlier build are kept for reuse
-    uint64_t total = 0;
+    uint64_t total = 0, unique = 0;
     for (uint32_t g = c->modelOffsets[modelIndex]; g < c->modelOffsets[modelIndex + 1]; ++g)
     {
         const prt_sub_model &sm = c->subModels[g];
         REQUIRE(sm.meshIndex < c->hInfo.size(), "sub-model mesh index out of range");
-        total += c->hInfo[sm.meshIndex].indexCount / 3;
+        const prt_mesh_info &info = c->hInfo[sm.meshIndex];
+        REQUIRE(info.materialIndex < c->hMat.size(), "mesh material index out of range");
+        // builder references: a non-opaque triangle counts blasRefsPerTriangle times (core_build.h)
+        total += (uint64_t)(info.indexCount / 3) * blasRefsPerTriangle(c->hMat[info.materialIndex].alphaMode == PRT_ALPHA_OPAQUE ? 1u : 0u);
+        unique += info.indexCount / 3;
     }
     REQUIRE(total < (1ull << 31), "model too large");
     if (outReference) *outReference = (uint64_t)modelIndex + 1;
     if (total == 0)
     {
-        b.nodeCount = b.triCount = 0;
+        b.nodeCount = b.triCount = b.primCount = 0;
         b.built = true;
         return PRT_OK;
     }
@@ -1283,7 +1288,7 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
         k_blas_gather<<<blocksFor(prims, 128), 128, 0, st>>>(sv, sm.meshIndex, prims, g - c->modelOffsets[modelIndex], opaque, offset,
                                                              c->bTris.p, c->bUvs.p, c->bBoxes.p, c->bBounds.p);
         launches++;
-        offset += prims;
+        offset += prims * blasRefsPerTriangle(opaque);
     }
     CK(cudaGetLastError());
     CK(c->bNodes.ensure(n));
@@ -1297,6 +1302,7 @@ extern "C" prt_status prt_build_blas(prt_ctx *c, uint32_t modelIndex, uint64_t *
     REQUIRE(counts[1] == n, "collapse lost primitives");
     b.nodeCount = counts[0];
     b.triCount = n;
+    b.primCount = (uint32_t)unique;
     if (b.nodeCap < b.nodeCount) // first build of the model, or it grew: the stream is idle after the read-back above
     {
         if (b.nodes) c->heap.release(b.nodes);
@@ -2077,7 +2083,8 @@ extern "C" prt_status prt_get_bvh_stats(prt_ctx *c, prt_bvh_stats *out)
         if (!b.built) continue;
         out->blasCount++;
         out->blasNodesTotal += b.nodeCount;
-        out->blasTrianglesTotal += b.triCount;
+        out->blasTrianglesTotal += b.primCount;
+        out->blasReferencesTotal += b.triCount;
     }
     if (c->tlasInstances)
     {

@@ -56,7 +56,7 @@ class PrtTimings(C.Structure):
 
 class PrtBvhStats(C.Structure):
     _fields_ = [("tlasNodes", C.c_uint32), ("blasNodesTotal", C.c_uint32), ("blasTrianglesTotal", C.c_uint64),
-                ("blasCount", C.c_uint32), ("tlasInstances", C.c_uint32)]
+                ("blasCount", C.c_uint32), ("tlasInstances", C.c_uint32), ("blasReferencesTotal", C.c_uint64)]
 
 
 # every symbol include/prt.h declares (tests/test_abi.py checks the library exports exactly these)

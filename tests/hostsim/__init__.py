@@ -93,7 +93,7 @@ class HostSim:
     def stats(self):
         out = np.zeros(8, np.uint64)
         lib().hs_stats(self._ctx, _p(out))
-        keys = ("buildError", "blasNodes", "blasTris", "tlasNodes", "tlasInstances", "blasLevels", "tlasLevels")
+        keys = ("buildError", "blasNodes", "blasTris", "tlasNodes", "tlasInstances", "blasLevels", "tlasLevels", "blasRecords")
         return dict(zip(keys, (int(v) for v in out)))
 
     def trace_counters(self):

@@ -213,6 +213,7 @@ struct hs_ctx
     uint32_t blasLevels = 0, tlasLevels = 0;
     int buildError = 0;
     std::atomic<uint64_t> nodes{0}, tris{0}, instances{0}, anyHits{0}, overflow{0};
+    uint64_t uniqueTris = 0; // triangles gathered (a BLAS holds more records: non-opaque triangles are referenced several times)
 };
 
 static void flush(hs_ctx *c, const TraceCounters &tc)
@@ -391,10 +392,18 @@ hs_ctx *hs_create(const orc_scene *scene, int flags)
             for (uint32_t p = 0; p < info.indexCount / 3; ++p)
             {
                 TriRec t;
-                V3 l, h;
-                gatherTriangle(sv, subs[g].meshIndex, p, g - s.modelOffsets[m], opaque, t, l, h);
-                tris.push_back(t);
-                boxes.push_back(makeBox(l, h));
+                V3 l, h, corner[3];
+                gatherTriangle(sv, subs[g].meshIndex, p, g - s.modelOffsets[m], opaque, t, l, h, corner);
+                // k_blas_gather: a non-opaque triangle enters the builder as several references (core_build.h)
+                const uint32_t refs = blasRefsPerTriangle(opaque);
+                for (uint32_t k = 0; k < refs; ++k)
+                {
+                    V3 rl = l, rh = h;
+                    if (refs > 1u) triangleRefBox(corner[0], corner[1], corner[2], k, rl, rh);
+                    tris.push_back(t);
+                    boxes.push_back(makeBox(rl, rh));
+                }
+                c->uniqueTris++;
                 lo = vmin(lo, l);
                 hi = vmax(hi, h);
             }
@@ -425,13 +434,14 @@ void hs_replace_blas(hs_ctx *c, uint32_t model, const void *nodes, uint32_t node
     buildTlasHost(c);
 }
 
-// out[0..7]: buildError, blas wide nodes, blas tris, tlas wide nodes, tlas instances, blas levels, tlas levels, 0
+// out[0..7]: buildError, blas wide nodes, blas triangles, tlas wide nodes, tlas instances, blas levels, tlas levels,
+// blas triangle records (>= triangles: builder references of non-opaque triangles)
 void hs_stats(hs_ctx *c, uint64_t *out)
 {
     uint64_t bn = 0, bt = 0;
     for (const HostBlas &b : c->blas) { bn += b.nodes.size(); bt += b.tris.size(); }
-    out[0] = (uint64_t)c->buildError; out[1] = bn; out[2] = bt; out[3] = c->tlasNodes.size(); out[4] = c->tlasInst.size();
-    out[5] = c->blasLevels; out[6] = c->tlasLevels; out[7] = 0;
+    out[0] = (uint64_t)c->buildError; out[1] = bn; out[2] = c->uniqueTris; out[3] = c->tlasNodes.size(); out[4] = c->tlasInst.size();
+    out[5] = c->blasLevels; out[6] = c->tlasLevels; out[7] = bt;
 }
 
 // out[0..4]: nodes visited, triangles tested, instances entered, any-hit calls, stack overflows

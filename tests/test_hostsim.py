@@ -156,3 +156,43 @@ def test_builders_on_adversarial_boxes(builder):
         # PLOC (an experiment option, off by default) merges exact duplicates into a chain: correct but deep, and the
         # library refuses (REQUIRE) past its collapse level budget; the default builder and Karras stay shallow
         assert r["nodes"] >= 1 and r["depth"] <= (128 if builder == "ploc" else 40), (name, r)
+
+
+_SPLIT_SCRIPT = r"""
+import os, subprocess, sys, tempfile
+import numpy as np
+root = sys.argv[1]
+sys.path.insert(0, root)
+so = os.path.join(tempfile.mkdtemp(prefix="hostsim_split_"), "libhostsim_split.so")
+subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-fno-fast-math", "-pthread", "-DPRT_BLAS_ALPHA_SPLIT=" + sys.argv[2],
+                "-shared", "-o", so, os.path.join(root, "tests", "hostsim", "hostsim.cpp")], check=True)
+from tests import hostsim
+hostsim.build = lambda force=False: so
+import oracle
+from prosper_b200 import scene_data as sd, scene_zoo
+for scene, (w, h) in ((scene_zoo.test_scene(), (96, 64)), (scene_zoo.atrium(160, 90, tex_size=64, detail=0.08, bake=False, lights=32), (160, 90))):
+    orc, hs = oracle.Oracle(scene), hostsim.HostSim(scene)
+    st = hs.stats()
+    assert st["buildError"] == 0 and st["blasTris"] == scene.triangle_count and st["blasRecords"] > st["blasTris"], st
+    pc = sd.reference_pc(frame_index=5)
+    ho, _ = orc.trace_primary(pc, w, h)
+    assert np.array_equal(ho, hs.trace_primary(pc, w, h)), "references must not change a single hit record"
+    a, ca = orc.render(sd.reference_pc(max_bounces=4), w // 2, h // 2, 2)
+    b, cb = hs.render(sd.reference_pc(max_bounces=4), w // 2, h // 2, 2)
+    assert np.all(np.abs(ca.astype(np.int64) - cb.astype(np.int64)) <= np.maximum(1, ca // 1000)), (ca, cb)
+    assert hs.trace_counters()["overflow"] == 0
+print("SPLIT_OK")
+"""
+
+
+@pytest.mark.parametrize("rounds", [1, 2])
+def test_reference_splitting_switch_keeps_hit_records(rounds):
+    # PRT_BLAS_ALPHA_SPLIT (core_build.h, off by default): non-opaque triangles enter the builder as 4 / 16 references with
+    # the same record. A second simulator build with the switch on must reproduce the oracle's hit records bit for bit and
+    # its ray counts (any-hit decisions are per (ray, triangle), whichever reference finds the triangle).
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", _SPLIT_SCRIPT, root, str(rounds)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "SPLIT_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
