@@ -9,7 +9,7 @@ tests and any-hit calls -- plus the same counts when every closest ray is traced
 the GPU's per-step counters (bench.py `breakdown.counters_per_step`) to three digits, so builder and traversal-order ideas
 can be priced here without GPU time.
 
-usage: python tools/cpu_item_probe.py [-DPRT_SAH_GRANULE=2 ...]     (extra flags go to g++)
+usage: [PRT_PROBE_CSRC=/tmp/csrc_copy] python tools/cpu_item_probe.py [-DPRT_SAH_GRANULE=2 ...]     (extra flags go to g++)
 """
 import os
 import subprocess
@@ -22,7 +22,9 @@ sys.path.insert(0, ROOT)
 
 def patched_source():
     src = open(os.path.join(ROOT, "tests", "hostsim", "hostsim.cpp")).read()
-    src = src.replace('"../../prosper_b200/csrc/', '"%s/prosper_b200/csrc/' % ROOT).replace('"../../oracle/', '"%s/oracle/' % ROOT)
+    # PRT_PROBE_CSRC: an edited copy of prosper_b200/csrc to price (its core_scene.h includes ../../include/prt_types.h)
+    csrc = os.environ.get("PRT_PROBE_CSRC", os.path.join(ROOT, "prosper_b200", "csrc"))
+    src = src.replace('"../../prosper_b200/csrc/', '"%s/' % csrc).replace('"../../oracle/', '"%s/oracle/' % ROOT)
 
     def sub(old, new):
         nonlocal src
