@@ -196,3 +196,16 @@ def test_reference_splitting_switch_keeps_hit_records(rounds):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", _SPLIT_SCRIPT, root, str(rounds)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "SPLIT_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_cpu_item_probe_still_patches_the_simulator():
+    # tools/cpu_item_probe.py instruments a copy of hostsim.cpp by text substitution; every substitution asserts that its
+    # anchor exists, so an edit of the simulator that would silently disarm the probe fails here instead.
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("cpu_item_probe", os.path.join(root, "tools", "cpu_item_probe.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    src = mod.patched_source()
+    assert "ideal (tMax = the hit)" in src and "tcI" in src
