@@ -210,6 +210,25 @@ def test_random_rays_closest_and_shadow(test_scene, small_atrium_instanced):
         world.close()
 
 
+def test_box_tests_never_cull_flat_on_grid_triangles():
+    # the adversarial rays of tests/adversarial.py (round-1 advisor finding on intersectNode) through the GPU kernels, with
+    # each of the three builders: opaque geometry only, so every record must equal the oracle's, barycentrics included
+    from tests import adversarial
+    scene, centres = adversarial.flat_grid_scene()
+    orc = oracle.Oracle(scene)
+    o, d = adversarial.edge_rays(centres, 60000)
+    seeds = np.zeros(len(o), np.uint32)
+    ho = orc.trace_rays(o, d, seeds)[0]
+    occ_o = orc.trace_rays(o, d, seeds, shadow=True)[0]["drawInstanceIndex"] != sd.MISS
+    for extra in (0, rt.CFG_PLOC, rt.CFG_LBVH_BLAS):
+        world = _world(scene, 64, 48, flags=rt.CFG_COUNTERS | rt.CFG_EXACT_FILTER | extra)
+        hg = world.trace_rays(o, d, seeds)
+        assert _id_mismatch(ho, hg).sum() == 0 and np.array_equal(ho["bary"], hg["bary"])
+        assert np.array_equal(occ_o, world.trace_rays(o, d, seeds, shadow=True)["drawInstanceIndex"] != sd.MISS)
+        assert world.counters()["stackOverflows"] == 0
+        world.close()
+
+
 def _rel_rmse(a, b, floor=1e-2):
     la = a[..., :3] @ np.array([0.2126, 0.7152, 0.0722], np.float32)
     lb = b[..., :3] @ np.array([0.2126, 0.7152, 0.0722], np.float32)

@@ -209,3 +209,21 @@ def test_cpu_item_probe_still_patches_the_simulator():
     spec.loader.exec_module(mod)
     src = mod.patched_source()
     assert "ideal (tMax = the hit)" in src and "tcI" in src
+
+
+def test_box_tests_never_cull_flat_on_grid_triangles():
+    # Round-1 advisor finding (core_trace.h::intersectNode): zero-thickness boxes exactly on the quantisation grid of large
+    # nodes, rays that leave other surfaces of those nodes or graze the triangle's plane, aimed at edges and corners.
+    from tests import adversarial
+    scene, centres = adversarial.flat_grid_scene()
+    orc, hs = oracle.Oracle(scene), hostsim.HostSim(scene)
+    o, d = adversarial.edge_rays(centres, 60000)
+    seeds = np.zeros(len(o), np.uint32)
+    ho = orc.trace_rays(o, d, seeds)[0]
+    assert (ho["drawInstanceIndex"] != sd.MISS).mean() > 0.6
+    assert np.array_equal(ho, hs.trace_rays(o, d, seeds)), "a conservative box test never loses a hit the exact test accepts"
+    so = orc.trace_rays(o, d, seeds, shadow=True)[0]["drawInstanceIndex"] != sd.MISS
+    assert np.array_equal(so, hs.trace_rays(o, d, seeds, shadow=True)["drawInstanceIndex"] != sd.MISS)
+    for other in (dict(ploc=True), dict(lbvh_blas=True)):  # the other builders: other trees, same answers
+        assert np.array_equal(ho, hostsim.HostSim(scene, **other).trace_rays(o, d, seeds))
+    assert hs.trace_counters()["overflow"] == 0
